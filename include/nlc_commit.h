@@ -1,0 +1,201 @@
+/*
+ * nlc_commit.h -- C ABI of libnlc_commit.so: the B200-native commitment backend behind plonky2's
+ * PolynomialBatch / MerkleTree / fft helpers / FRI prover, as consumed by the unchanged starkyx and
+ * plonky2x provers of near/near-light-client.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns 0 on success and a
+ * non-zero code on failure (message via nlc_last_error).  There is NO CPU fallback: without a CUDA
+ * device nlc_init fails and nothing else can be called.  plonky2's own contract at this boundary is
+ * infallible-or-panic, so the Rust wrapper turns a non-zero code into panic!.
+ *
+ * "Replaces" cites the reference-side interface each entry point stands in for.  The plonky2 crate
+ * itself (0.1.4 @ d2598bd, /root/reference/Cargo.lock:4864-4866) is not vendored in the reference
+ * tree, so upstream paths are given by crate path and the in-tree CALL SITE by file:line.
+ *
+ * Conventions: field elements are uint64_t, canonical (< p = 2^64 - 2^32 + 1) on output; inputs may
+ * be any representative.  A "column" is one polynomial: n = 2^log_n contiguous uint64_t.
+ * Extension elements (D = 2) are two consecutive uint64_t [a0, a1].  A digest (HashOut) is 4 uint64_t.
+ * Pointers are HOST pointers unless the name ends in _dev (device pointers on the context's GPU).
+ * All entry points are thread-safe; calls on one context serialise on its stream.
+ */
+#ifndef NLC_COMMIT_H
+#define NLC_COMMIT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nlc_ctx nlc_ctx;     /* one per (process, GPU) */
+typedef struct nlc_batch nlc_batch; /* a committed PolynomialBatch living in HBM */
+typedef struct nlc_tree nlc_tree;   /* a stand-alone MerkleTree living in HBM */
+
+/* ---- lifecycle ---------------------------------------------------------------------------- */
+/* device < 0: use the current CUDA device. */
+int nlc_init(int device, nlc_ctx** out);
+void nlc_destroy(nlc_ctx* ctx);
+const char* nlc_last_error(nlc_ctx* ctx); /* ctx may be NULL: error of the last failed nlc_init */
+int nlc_device(nlc_ctx* ctx);
+/* Launch all work of this context on an existing CUDA stream (a cudaStream_t cast to void*); NULL
+ * restores the context's own stream.  Lets a harness time kernels with events on that stream. */
+int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream);
+int nlc_synchronize(nlc_ctx* ctx);
+/* Number of kernels this library has launched on ctx since creation (bench.py's gpu_launches). */
+uint64_t nlc_launch_count(nlc_ctx* ctx);
+
+/* ---- a1 / a2: PolynomialBatch::from_values / from_coeffs ----------------------------------- */
+/* Replaces plonky2::fri::oracle::PolynomialBatch::from_values(values, rate_bits, blinding=false,
+ * cap_height, timing, None); call sites vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:91-93 and
+ * plonky2/stark/config.rs:92-94.  cols[j] = the n evaluations of polynomial j over the subgroup. */
+int nlc_commit_from_values(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                           int cap_height, nlc_batch** out);
+/* Replaces PolynomialBatch::from_coeffs(polynomials, rate_bits, false, cap_height, timing, None);
+ * call site vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:171-178. */
+int nlc_commit_from_coeffs(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                           int cap_height, nlc_batch** out);
+/* Same, input already resident in HBM as one n_cols x n matrix (column j at values_dev + j*n). */
+int nlc_commit_from_values_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n, int rate_bits,
+                               int cap_height, nlc_batch** out);
+int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t n_cols, int log_n, int rate_bits,
+                               int cap_height, nlc_batch** out);
+/* "Next" row: commit straight from a row-major AirTrace (trace/mod.rs:19-24) instead of
+ * the serial column split of trace/mod.rs:270-285: rows x width host matrix, columns [col0, col0+n_cols). */
+int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols,
+                               int log_n, int rate_bits, int cap_height, nlc_batch** out);
+void nlc_batch_free(nlc_batch* b);
+
+/* Struct fields of PolynomialBatch / MerkleTree, materialised on demand. */
+int nlc_batch_info(const nlc_batch* b, size_t* n_cols, int* log_n, int* rate_bits, int* cap_height);
+/* merkle_tree.cap: 2^cap_height x 4 (prover.rs:95,180,210). */
+int nlc_batch_cap(nlc_batch* b, uint64_t* out);
+/* polynomials: column j written to out_cols[j] (n each), natural coefficient order (proof.rs:307-310). */
+int nlc_batch_coeffs(nlc_batch* b, uint64_t* const* out_cols);
+/* merkle_tree.leaves flattened: N x n_cols row-major, leaf k = LDE row bitrev_N(k). */
+int nlc_batch_leaves(nlc_batch* b, uint64_t* out);
+/* merkle_tree.digests: 2*(N - 2^cap_height) x 4 in plonky2's interleaved layout. */
+int nlc_batch_digests(nlc_batch* b, uint64_t* out);
+/* a6: get_lde_values(i, step) = leaves[bitrev_N(i*step)] for i in idx (prover.rs:289-294): m x n_cols. */
+int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step, uint64_t* out);
+/* merkle_tree.get(leaf_index) and merkle_tree.prove(leaf_index): row (n_cols) and siblings
+ * ((log N - cap_height) x 4, bottom-up). Either output may be NULL. */
+int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t* siblings_out);
+/* Device views (valid until nlc_batch_free): for callers that keep consuming on the GPU. */
+const uint64_t* nlc_batch_leaves_dev(const nlc_batch* b);
+const uint64_t* nlc_batch_coeffs_dev(const nlc_batch* b);
+const uint64_t* nlc_batch_cap_dev(const nlc_batch* b);
+/* StarkOpeningSet::new's eval_commitment (proof.rs:307-310): every polynomial of the batch evaluated
+ * at the extension point z -> n_cols x 2. */
+int nlc_batch_eval(nlc_batch* b, const uint64_t z[2], uint64_t* out);
+
+/* ---- a3: fft helpers (plonky2_field::fft, polynomial::{PolynomialValues,PolynomialCoeffs}) -- */
+/* In place on `n_cols` host columns stored back to back (data + j*n); natural order in and out.
+ * Replace fft_with_options / ifft_with_options / coset_fft / coset_ifft; in-tree call sites
+ * prover.rs:356 (coset_ifft(F::coset_shift())) and inside lde_onto_coset (prover.rs:280-284). */
+int nlc_fft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n);
+int nlc_ifft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n);
+int nlc_coset_fft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n, uint64_t shift);
+int nlc_coset_ifft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n, uint64_t shift);
+/* PolynomialValues::lde_onto_coset(rate_bits): in = n_cols x n values, out = n_cols x (n << rate_bits). */
+int nlc_lde_onto_coset(nlc_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n_cols, int log_n, int rate_bits);
+
+/* ---- a4: Poseidon (plonky2::hash::{poseidon,hashing}) -------------------------------------- */
+/* PoseidonPermutation::permute on `count` independent 12-lane states (in place). */
+int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count);
+/* PoseidonHash::hash_no_pad / hash_or_noop of `count` inputs of `len` elements each -> count x 4. */
+int nlc_hash_no_pad(nlc_ctx* ctx, const uint64_t* in, size_t count, size_t len, uint64_t* out);
+int nlc_hash_or_noop(nlc_ctx* ctx, const uint64_t* in, size_t count, size_t len, uint64_t* out);
+/* PoseidonHash::two_to_one on `count` pairs: left/right count x 4 -> out count x 4. */
+int nlc_two_to_one(nlc_ctx* ctx, const uint64_t* left, const uint64_t* right, size_t count, uint64_t* out);
+
+/* ---- a5: MerkleTree::new / prove (plonky2::hash::merkle_tree) ------------------------------ */
+/* leaves: n_leaves x leaf_len row-major (host). */
+int nlc_merkle_new(nlc_ctx* ctx, const uint64_t* leaves, size_t n_leaves, size_t leaf_len, int cap_height,
+                   nlc_tree** out);
+int nlc_tree_cap(nlc_tree* t, uint64_t* out);
+int nlc_tree_digests(nlc_tree* t, uint64_t* out);
+int nlc_tree_open(nlc_tree* t, size_t leaf_index, uint64_t* leaf_out, uint64_t* siblings_out);
+void nlc_tree_free(nlc_tree* t);
+
+/* ---- a9: Challenger (plonky2::iop::challenger) -------------------------------------------- */
+/* The transcript state crosses the boundary as plain data, exactly the fields of
+ * Challenger { sponge_state, input_buffer, output_buffer }.  The Rust Challenger keeps running on
+ * the host between calls; prove_openings advances it on the device (no host round trips inside). */
+typedef struct {
+    uint64_t sponge_state[12];
+    uint64_t input_buffer[8];
+    uint32_t input_len;
+    uint64_t output_buffer[8];
+    uint32_t output_len;
+} nlc_challenger;
+void nlc_challenger_init(nlc_challenger* c);
+/* Challenger::observe_elements / observe_cap / observe_extension_elements (prover.rs:67,94-100,181,193) */
+int nlc_challenger_observe(nlc_ctx* ctx, nlc_challenger* c, const uint64_t* elems, size_t n);
+/* Challenger::get_n_challenges (n = 2 gives get_extension_challenge) (prover.rs:99,183) */
+int nlc_challenger_get(nlc_ctx* ctx, nlc_challenger* c, size_t n, uint64_t* out);
+
+/* ---- a7 / a8 / a10: PolynomialBatch::prove_openings and the FRI prover --------------------- */
+/* FriParams { config: FriConfig { rate_bits, cap_height, proof_of_work_bits, num_query_rounds, .. },
+ * hiding = false, degree_bits, reduction_arity_bits } (plonky2::fri::{FriConfig,FriParams});
+ * knobs set at vendor/starkyx/starkyx/src/plonky2/stark/config.rs:64-70. */
+typedef struct {
+    int degree_bits;
+    int rate_bits;
+    int cap_height;
+    int proof_of_work_bits;
+    int num_query_rounds;
+    int n_reduction_rounds;
+    int reduction_arity_bits[16];
+} nlc_fri_params;
+/* FriConfig::fri_params(degree_bits, false) with FriReductionStrategy::ConstantArityBits(arity_bits,
+ * final_poly_bits) (config.rs:68 uses (4, 5); config.rs:75-77). */
+int nlc_fri_params_constant_arity(nlc_fri_params* p, int degree_bits, int rate_bits, int cap_height,
+                                  int proof_of_work_bits, int num_query_rounds, int arity_bits,
+                                  int final_poly_bits);
+
+/* FriInstanceInfo { oracles, batches: [FriBatchInfo { point, polynomials: [FriPolynomialInfo] }] }
+ * (built at vendor/starkyx/starkyx/src/plonky2/stark/mod.rs:56-96). */
+typedef struct {
+    int n_batches;
+    const uint64_t* points;        /* n_batches x 2 */
+    const uint32_t* batch_offsets; /* n_batches + 1, into the two arrays below */
+    const uint32_t* poly_oracle;   /* FriPolynomialInfo::oracle_index */
+    const uint32_t* poly_index;    /* FriPolynomialInfo::polynomial_index */
+} nlc_fri_instance;
+
+/* Size in uint64_t words of the flat FriProof written by nlc_prove_openings:
+ *   commit_phase_merkle_caps : n_rounds x 2^cap_height x 4
+ *   final_poly               : (2^degree_bits >> sum(arity_bits)) x 2
+ *   pow_witness              : 1
+ *   query_round_proofs       : num_query_rounds x { per oracle: leaf row (n_cols), siblings ((logN-cap) x 4);
+ *                                                   per round: evals (2 << arity), siblings ((logN_i - arity - cap) x 4) }
+ */
+size_t nlc_fri_proof_words(const nlc_fri_params* p, nlc_batch* const* oracles, int n_oracles);
+/* Replaces PolynomialBatch::prove_openings(&instance, &oracles, &mut challenger, &fri_params, timing);
+ * call site vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:200-206.  The proof-of-work witness is
+ * the SMALLEST valid nonce (upstream: rayon find_any, any valid nonce). */
+int nlc_prove_openings(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_batch* const* oracles, int n_oracles,
+                       nlc_challenger* challenger, const nlc_fri_params* p, uint64_t* proof_out);
+
+/* Finer-grained a8 steps for a Rust-driven commit phase (transcript stays in Rust between calls). */
+typedef struct nlc_fri_state nlc_fri_state;
+/* alpha-batched reduction + divide-by-linear + LDE + coset FFT over F_{p^2}: the state then holds
+ * lde_polynomial_coeffs / lde_polynomial_values of fri_proof(). */
+int nlc_fri_begin(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_batch* const* oracles, int n_oracles,
+                  const uint64_t alpha[2], const nlc_fri_params* p, nlc_fri_state** out);
+/* One fri_committed_trees iteration, first half: bit-reverse, chunk by arity, MerkleTree::new -> cap. */
+int nlc_fri_commit_round(nlc_fri_state* s, uint64_t* cap_out);
+/* Second half: fold coefficients by beta, shift ^= arity, coset FFT. */
+int nlc_fri_fold_round(nlc_fri_state* s, const uint64_t beta[2]);
+/* final_poly coefficients ((n >> sum arity) x 2). */
+int nlc_fri_final_poly(nlc_fri_state* s, uint64_t* out);
+/* fri_proof_of_work: grind on the challenger's duplex state; returns the smallest witness. */
+int nlc_fri_pow(nlc_ctx* ctx, const nlc_challenger* c, int proof_of_work_bits, uint64_t* witness_out);
+/* fri_prover_query_rounds for the given x_index values -> the query_round_proofs part of the flat proof. */
+int nlc_fri_queries(nlc_fri_state* s, const uint64_t* x_indices, size_t n_queries, uint64_t* out);
+void nlc_fri_state_free(nlc_fri_state* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NLC_COMMIT_H */

@@ -1,0 +1,150 @@
+// common.cuh -- context, error handling and launch bookkeeping shared by the nlc_commit translation units.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/nlc_commit.h"
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+
+struct NlcError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+#define NLC_CUDA(expr)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t _e = (expr);                                                                             \
+        if (_e != cudaSuccess)                                                                               \
+            throw NlcError(std::string(#expr) + " failed: " + cudaGetErrorString(_e) + " at " + __FILE__ +   \
+                           ":" + std::to_string(__LINE__));                                                  \
+    } while (0)
+
+#define NLC_CHECK(cond, msg)                                                              \
+    do {                                                                                  \
+        if (!(cond)) throw NlcError(std::string("nlc_commit: ") + (msg) + " [" #cond "]"); \
+    } while (0)
+
+// Table cache key: (kind, log size, digit bits, inverse?, shift/scale value)
+typedef std::tuple<int, int, int, int, u64, u64> TableKey;
+
+struct nlc_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::recursive_mutex mu;
+    std::string err;
+    std::atomic<u64> launches{0};
+    std::map<TableKey, u64*> tables; // device-resident twiddle / scale tables, built once
+    size_t table_bytes = 0;
+    // small pinned staging area + device scratch for transcript-sized transfers
+    u64* pinned = nullptr;
+    size_t pinned_words = 0;
+    int sm_count = 148;
+    bool ntt_attrs = false; // cudaFuncSetAttribute is per device: remembered per context
+
+    u64* dmalloc(size_t words) {
+        void* p = nullptr;
+        if (words == 0) words = 1;
+        NLC_CUDA(cudaMallocAsync(&p, words * sizeof(u64), stream));
+        return (u64*)p;
+    }
+    void dfree(void* p) {
+        if (p) cudaFreeAsync(p, stream);
+    }
+    u64* pin(size_t words) {
+        if (words > pinned_words) {
+            if (pinned) cudaFreeHost(pinned);
+            pinned = nullptr;
+            size_t w = words < (1u << 16) ? (1u << 16) : words;
+            NLC_CUDA(cudaMallocHost((void**)&pinned, w * sizeof(u64)));
+            pinned_words = w;
+        }
+        return pinned;
+    }
+};
+
+// RAII guard: selects the context's device and serialises calls on the context.
+struct CtxGuard {
+    nlc_ctx* c;
+    int prev = -1;
+    explicit CtxGuard(nlc_ctx* ctx) : c(ctx) {
+        c->mu.lock();
+        cudaGetDevice(&prev);
+        if (prev != c->device) cudaSetDevice(c->device);
+    }
+    ~CtxGuard() {
+        if (prev >= 0 && prev != c->device) cudaSetDevice(prev);
+        c->mu.unlock();
+    }
+};
+
+#define NLC_LAUNCH(ctx, kernel, grid, block, smem, ...)                         \
+    do {                                                                        \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);        \
+        (ctx)->launches.fetch_add(1, std::memory_order_relaxed);                \
+        NLC_CUDA(cudaGetLastError());                                           \
+    } while (0)
+
+// Every extern "C" entry point wraps its body with this: exceptions become error codes.
+template <class F>
+static inline int nlc_guarded(nlc_ctx* ctx, F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const std::exception& e) {
+        if (ctx) ctx->err = e.what();
+        cudaGetLastError(); // clear a non-sticky error so later calls can proceed
+        return 1;
+    }
+}
+
+static inline int ilog2(size_t n) {
+    int l = 0;
+    while (((size_t)1 << l) < n) l++;
+    return l;
+}
+
+// ---- ntt.cu ----
+// forward/inverse NTT of `n_cols` columns of 2^log_n elements (column j at src + j*src_stride).
+// ROWS: out is a row-major (rows x row_width) matrix; row = row_base + bitrev order position, column
+//       offset col0.  NATURAL: out is column-contiguous, natural order.
+struct NttJob {
+    const u64* src = nullptr;
+    size_t src_stride = 0;
+    size_t n_cols = 0;
+    int log_n = 0;
+    bool inverse = false;      // use inverse roots and scale by 1/n
+    u64 pre_shift = 1;         // multiply input j by pre_shift^j (coset_fft)
+    u64 post_shift = 1;        // NATURAL only: multiply output k by post_shift^k (coset_ifft)
+    bool rows = false;
+    u64* dst = nullptr;
+    size_t dst_stride = 0;     // NATURAL: column stride
+    size_t row_width = 0;      // ROWS: elements per row
+    size_t row_base = 0;       // ROWS: first row
+    size_t col0 = 0;           // ROWS: first column inside a row
+    u64* scratch = nullptr;    // n_cols * 2^log_n words, needed when log_n > one digit
+};
+void ntt_run(nlc_ctx* ctx, const NttJob& job);
+size_t ntt_scratch_words(size_t n_cols, int log_n);
+
+// ---- merkle.cu ----
+// Build MerkleTree::new over device-resident row-major leaves; digests in plonky2's interleaved layout.
+void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, int cap_height, u64* digests,
+                  u64* cap);
+// device copy of leaf + siblings for many leaf indices (indices in device memory)
+void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
+                      int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out, size_t out_stride,
+                      size_t out_offset);
+void poseidon_permute_many(nlc_ctx* ctx, u64* states_dev, size_t count);
+void hash_many(nlc_ctx* ctx, const u64* in_dev, size_t count, size_t len, bool or_noop, u64* out_dev);
+void two_to_one_many(nlc_ctx* ctx, const u64* l_dev, const u64* r_dev, size_t count, u64* out_dev);

@@ -1,0 +1,108 @@
+// gl.cuh -- Goldilocks field (p = 2^64 - 2^32 + 1) and its quadratic extension on the device.
+//
+// Replaces plonky2_field's GoldilocksField arithmetic (field/src/goldilocks_field.rs @ d2598bd, pinned
+// by /root/reference/Cargo.lock:4912-4924) for the sm_100a kernels.  Integer
+// pipe only: a 64x64->128 product is four IMAD.WIDE.U32, the reduction uses 2^64 == 2^32 - 1 and
+// 2^96 == -1 (mod p).  "nc" variants return any representative in [0, 2^64); everything written to
+// memory that the host can see is canonical (< p).
+#pragma once
+#include <cstdint>
+
+namespace gl {
+
+constexpr uint64_t P = 0xFFFFFFFF00000001ULL;
+constexpr uint64_t EPS = 0xFFFFFFFFULL;
+constexpr uint64_t GENERATOR = 7ULL;                        // MULTIPLICATIVE_GROUP_GENERATOR == coset_shift()
+constexpr uint64_t POW2_GENERATOR = 1753635133440165772ULL; // order 2^32
+
+__host__ __device__ __forceinline__ uint64_t canon(uint64_t x) { return x >= P ? x - P : x; }
+
+// canonical + canonical -> canonical
+__host__ __device__ __forceinline__ uint64_t add(uint64_t a, uint64_t b) {
+    uint64_t s = a + b;
+    return (s < a || s >= P) ? s + EPS : s; // s - p == s + eps (mod 2^64)
+}
+// any + canonical -> any (one operand canonical guarantees a single wrap)
+__host__ __device__ __forceinline__ uint64_t add_nc(uint64_t a, uint64_t b_canonical) {
+    uint64_t s = a + b_canonical;
+    return s < a ? s + EPS : s;
+}
+// canonical - canonical -> canonical
+__host__ __device__ __forceinline__ uint64_t sub(uint64_t a, uint64_t b) {
+    uint64_t d = a - b;
+    return a < b ? d - EPS : d; // d + p == d - eps (mod 2^64)
+}
+__host__ __device__ __forceinline__ uint64_t neg(uint64_t a) { return a ? P - a : 0; }
+
+// (lo + 2^64 hi) mod p, any representative.  hi = hi_hi 2^32 + hi_lo:  lo - hi_hi + hi_lo * eps.
+__host__ __device__ __forceinline__ uint64_t reduce128_nc(uint64_t lo, uint64_t hi) {
+    uint64_t hi_hi = hi >> 32, hi_lo = hi & EPS;
+    uint64_t t0 = lo - hi_hi;
+    if (lo < hi_hi) t0 -= EPS;
+    uint64_t t1 = (hi_lo << 32) - hi_lo; // hi_lo * eps
+    uint64_t r = t0 + t1;
+    if (r < t1) r += EPS;
+    return r;
+}
+
+__device__ __forceinline__ uint64_t mul_nc(uint64_t a, uint64_t b) {
+    return reduce128_nc(a * b, __umul64hi(a, b));
+}
+__device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return canon(mul_nc(a, b)); }
+__device__ __forceinline__ uint64_t sqr_nc(uint64_t a) { return mul_nc(a, a); }
+
+__device__ __forceinline__ uint64_t pow(uint64_t b, uint64_t e) {
+    uint64_t r = 1;
+    while (e) {
+        if (e & 1) r = mul(r, b);
+        b = mul(b, b);
+        e >>= 1;
+    }
+    return r;
+}
+__device__ __forceinline__ uint64_t inv(uint64_t a) { return pow(a, P - 2); }
+
+// ---- host-side scalar helpers (setup only: roots, shifts, table seeds; never on a data path) ----
+inline uint64_t h_mul(uint64_t a, uint64_t b) {
+    unsigned __int128 m = (unsigned __int128)a * b;
+    return canon(reduce128_nc((uint64_t)m, (uint64_t)(m >> 64)));
+}
+inline uint64_t h_pow(uint64_t b, uint64_t e) {
+    uint64_t r = 1;
+    while (e) {
+        if (e & 1) r = h_mul(r, b);
+        b = h_mul(b, b);
+        e >>= 1;
+    }
+    return r;
+}
+inline uint64_t h_inv(uint64_t a) { return h_pow(a, P - 2); }
+inline uint64_t h_root_of_unity(int n_log) { // primitive_root_of_unity(n_log)
+    uint64_t r = POW2_GENERATOR;
+    for (int i = n_log; i < 32; i++) r = h_mul(r, r);
+    return r;
+}
+
+// ---- quadratic extension F_p[X]/(X^2 - 7), element (a0, a1) ----
+struct Ext2 {
+    uint64_t a0, a1;
+};
+__device__ __forceinline__ Ext2 ext_add(Ext2 x, Ext2 y) { return {add(x.a0, y.a0), add(x.a1, y.a1)}; }
+__device__ __forceinline__ Ext2 ext_sub(Ext2 x, Ext2 y) { return {sub(x.a0, y.a0), sub(x.a1, y.a1)}; }
+__device__ __forceinline__ Ext2 ext_mul(Ext2 x, Ext2 y) {
+    uint64_t c0 = add(mul(x.a0, y.a0), mul(7, mul(x.a1, y.a1)));
+    uint64_t c1 = add(mul(x.a0, y.a1), mul(x.a1, y.a0));
+    return {c0, c1};
+}
+__device__ __forceinline__ Ext2 ext_scalar(Ext2 x, uint64_t s) { return {mul(x.a0, s), mul(x.a1, s)}; }
+__device__ __forceinline__ Ext2 ext_pow(Ext2 b, uint64_t e) {
+    Ext2 r = {1, 0};
+    while (e) {
+        if (e & 1) r = ext_mul(r, b);
+        b = ext_mul(b, b);
+        e >>= 1;
+    }
+    return r;
+}
+
+} // namespace gl

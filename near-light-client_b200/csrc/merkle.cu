@@ -1,0 +1,192 @@
+// merkle.cu -- Poseidon leaf hashing and level-by-level Merkle digests for sm_100a.
+//
+// Replaces plonky2::hash::merkle_tree::{MerkleTree::new, fill_digests_buf, fill_subtree,
+// MerkleTree::prove} and PoseidonHash::{hash_no_pad, hash_or_noop, two_to_one}
+// (plonky2 0.1.4 @ d2598bd), whose result is read in tree at
+// /root/reference/vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:95,180,210 (merkle_tree.cap).
+//
+// Digests are written straight into plonky2's interleaved `digests` layout, so the host struct can
+// be filled by one D2H copy and MerkleTree::prove's index arithmetic works unchanged:
+//   inside the chunk of cap subtree s, the sibling pair q of layer i (0 = leaf digests) sits at
+//   2*((q << (i+1)) + (1<<i) - 1) + {0,1};  the subtree root goes to cap[s].
+#include "common.cuh"
+#include "poseidon.cuh"
+
+namespace {
+
+constexpr int HASH_THREADS = 128;
+
+struct TreeGeom {
+    int sub_height;       // log2(leaves per cap subtree)
+    size_t sub_digests;   // digests per subtree = 2*(2^sub_height - 1)
+};
+
+// slot of node `j` (global index within its layer) of layer `i`; layer sub_height = cap.
+__device__ __forceinline__ u64* node_slot(u64* digests, u64* cap, TreeGeom g, int layer, size_t j) {
+    const int rem = g.sub_height - layer; // log2(nodes of this layer per subtree)
+    const size_t s = j >> rem;
+    if (rem == 0) return cap + s * 4;
+    const size_t jl = j & (((size_t)1 << rem) - 1);
+    const size_t q = jl >> 1;
+    const size_t idx = 2 * ((q << (layer + 1)) + ((size_t)1 << layer) - 1) + (jl & 1);
+    return digests + (s * g.sub_digests + idx) * 4;
+}
+
+// hash_or_noop of each leaf row (one thread per leaf), written to its layer-0 slot.
+__global__ void __launch_bounds__(HASH_THREADS)
+k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, TreeGeom g, u64* digests, u64* cap) {
+    const size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x;
+    if (row >= n_leaves) return;
+    const u64* in = leaves + row * leaf_len;
+    u64 s[poseidon::WIDTH];
+#pragma unroll
+    for (int i = 0; i < poseidon::WIDTH; i++) s[i] = 0;
+    if (leaf_len <= 4) { // hash_or_noop: short rows are copied, zero padded
+        for (size_t i = 0; i < leaf_len; i++) s[i] = gl::canon(in[i]);
+    } else {
+        size_t off = 0;
+        for (; off + poseidon::RATE <= leaf_len; off += poseidon::RATE) {
+#pragma unroll
+            for (int i = 0; i < poseidon::RATE; i++) s[i] = in[off + i]; // overwrite mode
+            poseidon::permute_nc(s);
+        }
+        if (off < leaf_len) {
+            const int rem = (int)(leaf_len - off);
+#pragma unroll
+            for (int i = 0; i < poseidon::RATE; i++)
+                if (i < rem) s[i] = in[off + i];
+            poseidon::permute_nc(s);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[i] = gl::canon(s[i]);
+    }
+    u64* out = node_slot(digests, cap, g, 0, row);
+    reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(s[0], s[1]);
+    reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(s[2], s[3]);
+}
+
+// layer (i) -> layer (i+1): one thread per parent.
+__global__ void __launch_bounds__(HASH_THREADS)
+k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) {
+    const size_t j = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x;
+    if (j >= n_parents) return;
+    const u64* kids = node_slot(digests, cap, g, layer, 2 * j); // the sibling pair is contiguous
+    u64 l[4], r[4], o[4];
+    const ulonglong2* k2 = reinterpret_cast<const ulonglong2*>(kids);
+    ulonglong2 a = k2[0], b = k2[1], c = k2[2], d = k2[3];
+    l[0] = a.x; l[1] = a.y; l[2] = b.x; l[3] = b.y;
+    r[0] = c.x; r[1] = c.y; r[2] = d.x; r[3] = d.y;
+    poseidon::two_to_one(l, r, o);
+    u64* out = node_slot(digests, cap, g, layer + 1, j);
+    reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(o[0], o[1]);
+    reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(o[2], o[3]);
+}
+
+// MerkleTree::get + MerkleTree::prove for many indices: out[i*stride + offset ..] = leaf row, siblings.
+__global__ void k_open_many(const u64* __restrict__ leaves, const u64* __restrict__ digests, size_t leaf_len,
+                            TreeGeom g, const u64* __restrict__ idx, int shift_right, u64 idx_mask, size_t n_idx,
+                            u64* out, size_t out_stride, size_t out_offset) {
+    const size_t qi = blockIdx.x;
+    if (qi >= n_idx) return;
+    const size_t leaf = (size_t)((idx[qi] & idx_mask) >> shift_right);
+    u64* o = out + qi * out_stride + out_offset;
+    const u64* row = leaves + leaf * leaf_len;
+    for (size_t i = threadIdx.x; i < leaf_len; i += blockDim.x) o[i] = gl::canon(row[i]);
+    o += leaf_len;
+    const size_t s = leaf >> g.sub_height;
+    size_t pair_index = leaf & (((size_t)1 << g.sub_height) - 1);
+    const u64* tree = digests + s * g.sub_digests * 4;
+    for (int i = threadIdx.x >> 2; i < g.sub_height; i += blockDim.x >> 2) {
+        size_t p = pair_index >> i; // index within layer i
+        size_t parity = p & 1;
+        size_t q = p >> 1;
+        size_t sib = 2 * ((q << (i + 1)) + ((size_t)1 << i) - 1) + (1 - parity);
+        o[(size_t)i * 4 + (threadIdx.x & 3)] = tree[sib * 4 + (threadIdx.x & 3)];
+    }
+}
+
+__global__ void k_permute_many(u64* states, size_t count) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    u64 s[poseidon::WIDTH];
+#pragma unroll
+    for (int k = 0; k < poseidon::WIDTH; k++) s[k] = states[i * poseidon::WIDTH + k];
+    poseidon::permute(s);
+#pragma unroll
+    for (int k = 0; k < poseidon::WIDTH; k++) states[i * poseidon::WIDTH + k] = s[k];
+}
+
+__global__ void k_two_to_one_many(const u64* l, const u64* r, size_t count, u64* out) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    u64 a[4], b[4], o[4];
+    for (int k = 0; k < 4; k++) { a[k] = l[i * 4 + k]; b[k] = r[i * 4 + k]; }
+    poseidon::two_to_one(a, b, o);
+    for (int k = 0; k < 4; k++) out[i * 4 + k] = o[k];
+}
+
+} // namespace
+
+void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, int cap_height, u64* digests,
+                  u64* cap) {
+    const int h = ilog2(n_leaves);
+    NLC_CHECK(((size_t)1 << h) == n_leaves, "MerkleTree::new: number of leaves must be a power of two");
+    NLC_CHECK(cap_height >= 0 && cap_height <= h,
+              "cap_height should be at most log2(leaves.len())"); // merkle_tree.rs assert in MerkleTree::new
+    TreeGeom g;
+    g.sub_height = h - cap_height;
+    g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
+    NLC_LAUNCH(ctx, k_leaf_hash, (unsigned)((n_leaves + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0, leaves,
+               n_leaves, leaf_len, g, digests, cap);
+    for (int layer = 0; layer < g.sub_height; layer++) {
+        size_t parents = n_leaves >> (layer + 1);
+        NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
+                   digests, cap, g, layer, parents);
+    }
+}
+
+void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
+                      int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out, size_t out_stride,
+                      size_t out_offset) {
+    if (n_idx == 0) return;
+    TreeGeom g;
+    g.sub_height = ilog2(n_leaves) - cap_height;
+    g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
+    // idx values are x_index of the ORIGINAL domain already reduced mod N by the caller; the leaf of
+    // this tree is x_index >> shift_right (fri_prover_query_round).
+    NLC_LAUNCH(ctx, k_open_many, (unsigned)n_idx, 128, 0, leaves, digests, leaf_len, g, idx_dev, shift_right,
+               ~(u64)0, n_idx, out, out_stride, out_offset);
+}
+
+void poseidon_permute_many(nlc_ctx* ctx, u64* states_dev, size_t count) {
+    if (!count) return;
+    NLC_LAUNCH(ctx, k_permute_many, (unsigned)((count + 127) / 128), 128, 0, states_dev, count);
+}
+
+void hash_many(nlc_ctx* ctx, const u64* in_dev, size_t count, size_t len, bool or_noop, u64* out_dev) {
+    if (!count) return;
+    // hash_no_pad == hash_or_noop for len > 4; for len <= 4 hash_no_pad still permutes.  Reuse the leaf
+    // kernel with a degenerate geometry (every "leaf" is its own cap entry: sub_height 0).
+    TreeGeom g;
+    g.sub_height = 0;
+    g.sub_digests = 0;
+    if (or_noop || len > 4) {
+        NLC_LAUNCH(ctx, k_leaf_hash, (unsigned)((count + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0, in_dev,
+                   count, len, g, (u64*)nullptr, out_dev);
+    } else {
+        // short hash_no_pad: pad into full states, permute, take 4 lanes
+        u64* st = ctx->dmalloc(count * 12);
+        NLC_CUDA(cudaMemsetAsync(st, 0, count * 12 * sizeof(u64), ctx->stream));
+        if (len) NLC_CUDA(cudaMemcpy2DAsync(st, 12 * sizeof(u64), in_dev, len * sizeof(u64), len * sizeof(u64), count,
+                                            cudaMemcpyDeviceToDevice, ctx->stream));
+        if (len) poseidon_permute_many(ctx, st, count);
+        NLC_CUDA(cudaMemcpy2DAsync(out_dev, 4 * sizeof(u64), st, 12 * sizeof(u64), 4 * sizeof(u64), count,
+                                   cudaMemcpyDeviceToDevice, ctx->stream));
+        ctx->dfree(st);
+    }
+}
+
+void two_to_one_many(nlc_ctx* ctx, const u64* l_dev, const u64* r_dev, size_t count, u64* out_dev) {
+    if (!count) return;
+    NLC_LAUNCH(ctx, k_two_to_one_many, (unsigned)((count + 127) / 128), 128, 0, l_dev, r_dev, count, out_dev);
+}
