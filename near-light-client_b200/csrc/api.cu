@@ -1,0 +1,682 @@
+// api.cu -- the extern "C" boundary of libnlc_commit.so (include/nlc_commit.h).
+//
+// Every entry point: lock the context, select its device, run on its stream, turn C++ exceptions into
+// a non-zero return code + nlc_last_error.  There is no CPU implementation behind any of them: if no
+// CUDA device is usable nlc_init fails and no other call can be made.
+#include <cstring>
+
+#include "batch.cuh"
+
+namespace {
+
+thread_local std::string g_init_error;
+
+void h2d(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    if (bytes) NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+}
+void d2h(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    if (bytes) NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+}
+void sync(nlc_ctx* ctx) { NLC_CUDA(cudaStreamSynchronize(ctx->stream)); }
+
+// RAII device buffer on the context's stream-ordered pool
+struct DevBuf {
+    nlc_ctx* ctx;
+    u64* p;
+    DevBuf(nlc_ctx* c, size_t words) : ctx(c), p(c->dmalloc(words)) {}
+    ~DevBuf() { ctx->dfree(p); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+void upload_cols(nlc_ctx* ctx, const u64* const* cols, size_t n_cols, size_t n, u64* dev) {
+    NLC_CHECK(cols != nullptr, "null column table");
+    for (size_t j = 0; j < n_cols; j++) {
+        NLC_CHECK(cols[j] != nullptr, "null column pointer");
+        h2d(ctx, dev + j * n, cols[j], n * sizeof(u64));
+    }
+}
+
+enum FftKind { FFT, IFFT, COSET_FFT, COSET_IFFT };
+
+int fft_host(nlc_ctx* ctx, u64* data, size_t n_cols, int log_n, FftKind kind, u64 shift) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(data != nullptr || n_cols == 0, "null data");
+        NLC_CHECK(log_n >= 0 && log_n <= 32, "log_n out of range (two-adicity is 32)");
+        if (n_cols == 0) return;
+        const size_t n = (size_t)1 << log_n;
+        DevBuf in(ctx, n_cols * n), out(ctx, n_cols * n), scratch(ctx, ntt_scratch_words(n_cols, log_n));
+        h2d(ctx, in.p, data, n_cols * n * sizeof(u64));
+        NttJob job;
+        job.src = in.p;
+        job.src_stride = n;
+        job.n_cols = n_cols;
+        job.log_n = log_n;
+        job.inverse = (kind == IFFT || kind == COSET_IFFT);
+        if (kind == COSET_FFT) job.pre_shift = gl::canon(shift);
+        if (kind == COSET_IFFT) {
+            NLC_CHECK(gl::canon(shift) != 0, "coset shift must be non-zero");
+            job.post_shift = gl::h_inv(gl::canon(shift));
+        }
+        job.rows = false;
+        job.dst = out.p;
+        job.dst_stride = n;
+        job.scratch = scratch.p;
+        ntt_run(ctx, job);
+        d2h(ctx, data, out.p, n_cols * n * sizeof(u64));
+        sync(ctx);
+    });
+}
+
+nlc_batch* commit_dev(nlc_ctx* ctx, const u64* src_dev, bool is_values, size_t W, int log_n, int rate_bits,
+                      int cap_height) {
+    nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height);
+    try {
+        const size_t n = (size_t)1 << log_n;
+        if (is_values)
+            batch_ifft_values(b, src_dev);
+        else
+            NLC_CUDA(cudaMemcpyAsync(b->coeffs, src_dev, W * n * sizeof(u64), cudaMemcpyDeviceToDevice, ctx->stream));
+        batch_lde_and_tree(b);
+    } catch (...) {
+        batch_release(b);
+        throw;
+    }
+    return b;
+}
+
+int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int rate_bits, int cap_height,
+                bool is_values, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out != nullptr, "null output handle");
+        *out = nullptr;
+        NLC_CHECK(W > 0 && log_n >= 0 && log_n <= 32, "bad shape");
+        const size_t n = (size_t)1 << log_n;
+        nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height);
+        try {
+            if (is_values) {
+                DevBuf vals(ctx, W * n);
+                upload_cols(ctx, cols, W, n, vals.p);
+                batch_ifft_values(b, vals.p);
+            } else {
+                upload_cols(ctx, cols, W, n, b->coeffs);
+            }
+            batch_lde_and_tree(b);
+            sync(ctx);
+        } catch (...) {
+            batch_release(b);
+            throw;
+        }
+        *out = b;
+    });
+}
+
+} // namespace
+
+extern "C" {
+
+int nlc_init(int device, nlc_ctx** out) {
+    if (!out) return 1;
+    *out = nullptr;
+    nlc_ctx* ctx = nullptr;
+    try {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0)
+            throw NlcError(std::string("nlc_init: no CUDA device (") + cudaGetErrorString(e) +
+                           "); this library has no CPU fallback");
+        if (device < 0) NLC_CUDA(cudaGetDevice(&device));
+        NLC_CHECK(device < count, "device index out of range");
+        int prev = 0;
+        cudaGetDevice(&prev);
+        NLC_CUDA(cudaSetDevice(device));
+        ctx = new nlc_ctx();
+        ctx->device = device;
+        cudaDeviceProp prop;
+        NLC_CUDA(cudaGetDeviceProperties(&prop, device));
+        NLC_CHECK(prop.major >= 10, "nlc_commit kernels are built for sm_100a (Blackwell) only");
+        ctx->sm_count = prop.multiProcessorCount;
+        NLC_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+        ctx->stream = ctx->own_stream;
+        cudaMemPool_t pool;
+        NLC_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        unsigned long long thresh = ~0ull; // keep freed blocks in the pool: commits reuse the same sizes
+        NLC_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        cudaSetDevice(prev);
+        *out = ctx;
+        return 0;
+    } catch (const std::exception& e) {
+        g_init_error = e.what();
+        cudaGetLastError();
+        delete ctx;
+        return 1;
+    }
+}
+
+void nlc_destroy(nlc_ctx* ctx) {
+    if (!ctx) return;
+    {
+        CtxGuard g(ctx);
+        cudaStreamSynchronize(ctx->stream);
+        for (auto& kv : ctx->tables) cudaFree(kv.second);
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    }
+    delete ctx;
+}
+
+const char* nlc_last_error(nlc_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+int nlc_device(nlc_ctx* ctx) { return ctx ? ctx->device : -1; }
+
+int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    });
+}
+int nlc_synchronize(nlc_ctx* ctx) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        sync(ctx);
+    });
+}
+uint64_t nlc_launch_count(nlc_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+// ---- a1 / a2 ----
+int nlc_commit_from_values(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                           int cap_height, nlc_batch** out) {
+    return commit_host(ctx, cols, n_cols, log_n, rate_bits, cap_height, true, out);
+}
+int nlc_commit_from_coeffs(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                           int cap_height, nlc_batch** out) {
+    return commit_host(ctx, cols, n_cols, log_n, rate_bits, cap_height, false, out);
+}
+int nlc_commit_from_values_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n, int rate_bits,
+                               int cap_height, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && values_dev, "null argument");
+        *out = commit_dev(ctx, values_dev, true, n_cols, log_n, rate_bits, cap_height);
+    });
+}
+int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t n_cols, int log_n, int rate_bits,
+                               int cap_height, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && coeffs_dev, "null argument");
+        *out = commit_dev(ctx, coeffs_dev, false, n_cols, log_n, rate_bits, cap_height);
+    });
+}
+int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols, int log_n,
+                               int rate_bits, int cap_height, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && rows, "null argument");
+        *out = nullptr;
+        NLC_CHECK(n_cols > 0 && col0 + n_cols <= width, "column range outside the trace");
+        NLC_CHECK(log_n >= 0 && log_n <= 32, "bad shape");
+        const size_t n = (size_t)1 << log_n;
+        DevBuf rows_dev(ctx, n * width), vals(ctx, n * n_cols);
+        h2d(ctx, rows_dev.p, rows, n * width * sizeof(u64));
+        transpose_trace_cols(ctx, rows_dev.p, width, col0, n_cols, n, vals.p);
+        *out = commit_dev(ctx, vals.p, true, n_cols, log_n, rate_bits, cap_height);
+        sync(ctx);
+    });
+}
+void nlc_batch_free(nlc_batch* b) {
+    if (!b) return;
+    CtxGuard g(b->ctx);
+    batch_release(b);
+}
+
+int nlc_batch_info(const nlc_batch* b, size_t* n_cols, int* log_n, int* rate_bits, int* cap_height) {
+    if (!b) return 1;
+    if (n_cols) *n_cols = b->W;
+    if (log_n) *log_n = b->log_n;
+    if (rate_bits) *rate_bits = b->rate_bits;
+    if (cap_height) *cap_height = b->cap_height;
+    return 0;
+}
+int nlc_batch_cap(nlc_batch* b, uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        CtxGuard g(b->ctx);
+        d2h(b->ctx, out, b->cap, ((size_t)4 << b->cap_height) * sizeof(u64));
+        sync(b->ctx);
+    });
+}
+int nlc_batch_coeffs(nlc_batch* b, uint64_t* const* out_cols) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        CtxGuard g(b->ctx);
+        const size_t n = (size_t)1 << b->log_n;
+        for (size_t j = 0; j < b->W; j++) d2h(b->ctx, out_cols[j], b->coeffs + j * n, n * sizeof(u64));
+        sync(b->ctx);
+    });
+}
+int nlc_batch_leaves(nlc_batch* b, uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        CtxGuard g(b->ctx);
+        d2h(b->ctx, out, b->leaves, (b->W << (b->log_n + b->rate_bits)) * sizeof(u64));
+        sync(b->ctx);
+    });
+}
+int nlc_batch_digests(nlc_batch* b, uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        CtxGuard g(b->ctx);
+        d2h(b->ctx, out, b->digests, b->n_digest_words * sizeof(u64));
+        sync(b->ctx);
+    });
+}
+int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step, uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        nlc_ctx* ctx = b->ctx;
+        CtxGuard g(ctx);
+        if (!m) return;
+        DevBuf idx_dev(ctx, m), rows(ctx, m * b->W);
+        h2d(ctx, idx_dev.p, idx, m * sizeof(u64));
+        batch_gather_lde_rows(b, idx_dev.p, m, step, rows.p);
+        d2h(ctx, out, rows.p, m * b->W * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t* siblings_out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        nlc_ctx* ctx = b->ctx;
+        CtxGuard g(ctx);
+        const int log_N = b->log_n + b->rate_bits;
+        NLC_CHECK(leaf_index < ((size_t)1 << log_N), "leaf index out of range");
+        const size_t sib = (size_t)4 * (log_N - b->cap_height);
+        DevBuf idx_dev(ctx, 1), buf(ctx, b->W + sib);
+        u64 idx = leaf_index;
+        h2d(ctx, idx_dev.p, &idx, sizeof(u64));
+        merkle_open_many(ctx, b->leaves, b->digests, (size_t)1 << log_N, b->W, b->cap_height, idx_dev.p, 0, 1, buf.p,
+                         b->W + sib, 0);
+        if (row_out) d2h(ctx, row_out, buf.p, b->W * sizeof(u64));
+        if (siblings_out) d2h(ctx, siblings_out, buf.p + b->W, sib * sizeof(u64));
+        sync(ctx);
+    });
+}
+const uint64_t* nlc_batch_leaves_dev(const nlc_batch* b) { return b ? b->leaves : nullptr; }
+const uint64_t* nlc_batch_coeffs_dev(const nlc_batch* b) { return b ? b->coeffs : nullptr; }
+const uint64_t* nlc_batch_cap_dev(const nlc_batch* b) { return b ? b->cap : nullptr; }
+int nlc_batch_eval(nlc_batch* b, const uint64_t z[2], uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        nlc_ctx* ctx = b->ctx;
+        CtxGuard g(ctx);
+        DevBuf res(ctx, 2 * b->W);
+        batch_eval_ext(b, z, res.p);
+        d2h(ctx, out, res.p, 2 * b->W * sizeof(u64));
+        sync(ctx);
+    });
+}
+
+// ---- a3 ----
+int nlc_fft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n) { return fft_host(ctx, data, n_cols, log_n, FFT, 1); }
+int nlc_ifft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n) {
+    return fft_host(ctx, data, n_cols, log_n, IFFT, 1);
+}
+int nlc_coset_fft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n, uint64_t shift) {
+    return fft_host(ctx, data, n_cols, log_n, COSET_FFT, shift);
+}
+int nlc_coset_ifft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n, uint64_t shift) {
+    return fft_host(ctx, data, n_cols, log_n, COSET_IFFT, shift);
+}
+int nlc_lde_onto_coset(nlc_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n_cols, int log_n, int rate_bits) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(in && out, "null argument");
+        NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "log_n + rate_bits out of range");
+        if (!n_cols) return;
+        const size_t n = (size_t)1 << log_n, N = n << rate_bits;
+        const int log_N = log_n + rate_bits;
+        DevBuf vals(ctx, n_cols * n), padded(ctx, n_cols * N), res(ctx, n_cols * N);
+        DevBuf scratch(ctx, std::max(ntt_scratch_words(n_cols, log_n), ntt_scratch_words(n_cols, log_N)));
+        h2d(ctx, vals.p, in, n_cols * n * sizeof(u64));
+        NLC_CUDA(cudaMemsetAsync(padded.p, 0, n_cols * N * sizeof(u64), ctx->stream));
+        NttJob inv;
+        inv.src = vals.p;
+        inv.src_stride = n;
+        inv.n_cols = n_cols;
+        inv.log_n = log_n;
+        inv.inverse = true;
+        inv.dst = padded.p;
+        inv.dst_stride = N; // coefficients land in the first n slots of each zero-padded column
+        inv.scratch = scratch.p;
+        ntt_run(ctx, inv);
+        NttJob fwd;
+        fwd.src = padded.p;
+        fwd.src_stride = N;
+        fwd.n_cols = n_cols;
+        fwd.log_n = log_N;
+        fwd.pre_shift = gl::GENERATOR;
+        fwd.dst = res.p;
+        fwd.dst_stride = N;
+        fwd.scratch = scratch.p;
+        ntt_run(ctx, fwd);
+        d2h(ctx, out, res.p, n_cols * N * sizeof(u64));
+        sync(ctx);
+    });
+}
+
+// ---- a4 ----
+int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        if (!count) return;
+        DevBuf st(ctx, count * 12);
+        h2d(ctx, st.p, states, count * 12 * sizeof(u64));
+        poseidon_permute_many(ctx, st.p, count);
+        d2h(ctx, states, st.p, count * 12 * sizeof(u64));
+        sync(ctx);
+    });
+}
+static int hash_host(nlc_ctx* ctx, const uint64_t* in, size_t count, size_t len, bool or_noop, uint64_t* out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        if (!count) return;
+        DevBuf din(ctx, count * len), dout(ctx, count * 4);
+        h2d(ctx, din.p, in, count * len * sizeof(u64));
+        hash_many(ctx, din.p, count, len, or_noop, dout.p);
+        d2h(ctx, out, dout.p, count * 4 * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_hash_no_pad(nlc_ctx* ctx, const uint64_t* in, size_t count, size_t len, uint64_t* out) {
+    return hash_host(ctx, in, count, len, false, out);
+}
+int nlc_hash_or_noop(nlc_ctx* ctx, const uint64_t* in, size_t count, size_t len, uint64_t* out) {
+    return hash_host(ctx, in, count, len, true, out);
+}
+int nlc_two_to_one(nlc_ctx* ctx, const uint64_t* left, const uint64_t* right, size_t count, uint64_t* out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        if (!count) return;
+        DevBuf l(ctx, count * 4), r(ctx, count * 4), o(ctx, count * 4);
+        h2d(ctx, l.p, left, count * 4 * sizeof(u64));
+        h2d(ctx, r.p, right, count * 4 * sizeof(u64));
+        two_to_one_many(ctx, l.p, r.p, count, o.p);
+        d2h(ctx, out, o.p, count * 4 * sizeof(u64));
+        sync(ctx);
+    });
+}
+
+// ---- a5 ----
+int nlc_merkle_new(nlc_ctx* ctx, const uint64_t* leaves, size_t n_leaves, size_t leaf_len, int cap_height,
+                   nlc_tree** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && leaves, "null argument");
+        *out = nullptr;
+        const int h = ilog2(n_leaves);
+        NLC_CHECK(n_leaves > 0 && ((size_t)1 << h) == n_leaves, "MerkleTree::new: number of leaves must be a power of two");
+        NLC_CHECK(cap_height >= 0 && cap_height <= h, "cap_height should be at most log2(leaves.len())");
+        nlc_tree* t = new nlc_tree();
+        t->ctx = ctx;
+        t->n_leaves = n_leaves;
+        t->leaf_len = leaf_len;
+        t->cap_height = cap_height;
+        try {
+            t->leaves = ctx->dmalloc(n_leaves * leaf_len);
+            t->digests = ctx->dmalloc(8 * (n_leaves - ((size_t)1 << cap_height)));
+            t->cap = ctx->dmalloc((size_t)4 << cap_height);
+            h2d(ctx, t->leaves, leaves, n_leaves * leaf_len * sizeof(u64));
+            merkle_build(ctx, t->leaves, n_leaves, leaf_len, cap_height, t->digests, t->cap);
+            sync(ctx);
+        } catch (...) {
+            ctx->dfree(t->leaves);
+            ctx->dfree(t->digests);
+            ctx->dfree(t->cap);
+            delete t;
+            throw;
+        }
+        *out = t;
+    });
+}
+int nlc_tree_cap(nlc_tree* t, uint64_t* out) {
+    if (!t) return 1;
+    return nlc_guarded(t->ctx, [&] {
+        CtxGuard g(t->ctx);
+        d2h(t->ctx, out, t->cap, ((size_t)4 << t->cap_height) * sizeof(u64));
+        sync(t->ctx);
+    });
+}
+int nlc_tree_digests(nlc_tree* t, uint64_t* out) {
+    if (!t) return 1;
+    return nlc_guarded(t->ctx, [&] {
+        CtxGuard g(t->ctx);
+        d2h(t->ctx, out, t->digests, 8 * (t->n_leaves - ((size_t)1 << t->cap_height)) * sizeof(u64));
+        sync(t->ctx);
+    });
+}
+int nlc_tree_open(nlc_tree* t, size_t leaf_index, uint64_t* leaf_out, uint64_t* siblings_out) {
+    if (!t) return 1;
+    return nlc_guarded(t->ctx, [&] {
+        nlc_ctx* ctx = t->ctx;
+        CtxGuard g(ctx);
+        NLC_CHECK(leaf_index < t->n_leaves, "leaf index out of range");
+        const size_t sib = (size_t)4 * (ilog2(t->n_leaves) - t->cap_height);
+        DevBuf idx_dev(ctx, 1), buf(ctx, t->leaf_len + sib);
+        u64 idx = leaf_index;
+        h2d(ctx, idx_dev.p, &idx, sizeof(u64));
+        merkle_open_many(ctx, t->leaves, t->digests, t->n_leaves, t->leaf_len, t->cap_height, idx_dev.p, 0, 1, buf.p,
+                         t->leaf_len + sib, 0);
+        if (leaf_out) d2h(ctx, leaf_out, buf.p, t->leaf_len * sizeof(u64));
+        if (siblings_out) d2h(ctx, siblings_out, buf.p + t->leaf_len, sib * sizeof(u64));
+        sync(ctx);
+    });
+}
+void nlc_tree_free(nlc_tree* t) {
+    if (!t) return;
+    CtxGuard g(t->ctx);
+    if (t->owns_leaves) t->ctx->dfree(t->leaves);
+    t->ctx->dfree(t->digests);
+    t->ctx->dfree(t->cap);
+    delete t;
+}
+
+// ---- a9 ----
+void nlc_challenger_init(nlc_challenger* c) {
+    if (c) memset(c, 0, sizeof *c);
+}
+int nlc_challenger_observe(nlc_ctx* ctx, nlc_challenger* c, const uint64_t* elems, size_t n) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(c && (elems || !n), "null argument");
+        NLC_CHECK(c->input_len < 8 && c->output_len <= 8, "corrupt challenger buffers");
+        if (!n) return;
+        const size_t cw = (sizeof(nlc_challenger) + 7) / 8;
+        DevBuf cd(ctx, cw), ed(ctx, n);
+        h2d(ctx, cd.p, c, sizeof *c);
+        h2d(ctx, ed.p, elems, n * sizeof(u64));
+        challenger_observe_dev(ctx, (nlc_challenger*)cd.p, ed.p, n);
+        d2h(ctx, c, cd.p, sizeof *c);
+        sync(ctx);
+    });
+}
+int nlc_challenger_get(nlc_ctx* ctx, nlc_challenger* c, size_t n, uint64_t* out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(c && (out || !n), "null argument");
+        NLC_CHECK(c->input_len < 8 && c->output_len <= 8, "corrupt challenger buffers");
+        if (!n) return;
+        const size_t cw = (sizeof(nlc_challenger) + 7) / 8;
+        DevBuf cd(ctx, cw), od(ctx, n);
+        h2d(ctx, cd.p, c, sizeof *c);
+        challenger_get_dev(ctx, (nlc_challenger*)cd.p, n, od.p);
+        d2h(ctx, c, cd.p, sizeof *c);
+        d2h(ctx, out, od.p, n * sizeof(u64));
+        sync(ctx);
+    });
+}
+
+// ---- a7 / a8 / a10 ----
+int nlc_fri_params_constant_arity(nlc_fri_params* p, int degree_bits, int rate_bits, int cap_height,
+                                  int proof_of_work_bits, int num_query_rounds, int arity_bits, int final_poly_bits) {
+    if (!p || arity_bits < 1 || arity_bits > 8 || degree_bits < 0 || rate_bits < 0) return 1;
+    memset(p, 0, sizeof *p);
+    p->degree_bits = degree_bits;
+    p->rate_bits = rate_bits;
+    p->cap_height = cap_height;
+    p->proof_of_work_bits = proof_of_work_bits;
+    p->num_query_rounds = num_query_rounds;
+    // FriReductionStrategy::ConstantArityBits: keep reducing while the result stays above the final
+    // polynomial size and the round's tree still has at least 2^cap_height leaves
+    int d = degree_bits;
+    while (d > final_poly_bits && d + rate_bits - arity_bits >= cap_height && p->n_reduction_rounds < 16) {
+        p->reduction_arity_bits[p->n_reduction_rounds++] = arity_bits;
+        d -= arity_bits;
+    }
+    return 0;
+}
+
+size_t nlc_fri_proof_words(const nlc_fri_params* p, nlc_batch* const* oracles, int n_oracles) {
+    if (!p || (!oracles && n_oracles)) return 0;
+    return fri_proof_words_impl(p, oracles, n_oracles, nullptr, nullptr, nullptr, nullptr);
+}
+
+int nlc_prove_openings(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_batch* const* oracles, int n_oracles,
+                       nlc_challenger* challenger, const nlc_fri_params* p, uint64_t* proof_out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(inst && oracles && challenger && p && proof_out, "null argument");
+        NLC_CHECK(challenger->input_len < 8 && challenger->output_len <= 8, "corrupt challenger buffers");
+        nlc_fri_state* s = fri_state_new(ctx, inst, oracles, n_oracles, p);
+        try {
+            const size_t cw = (sizeof(nlc_challenger) + 7) / 8;
+            DevBuf cd(ctx, cw);
+            h2d(ctx, cd.p, challenger, sizeof *challenger);
+            fri_prove_openings(s, inst, (nlc_challenger*)cd.p);
+            FriView v = fri_view(s);
+            u64 resp = 0;
+            d2h(ctx, proof_out, v.proof, v.proof_words * sizeof(u64));
+            d2h(ctx, challenger, cd.p, sizeof *challenger);
+            d2h(ctx, &resp, v.resp, sizeof(u64));
+            sync(ctx);
+            const int pb = p->proof_of_work_bits;
+            NLC_CHECK(pb == 0 || (resp >> (64 - pb)) == 0, "proof-of-work response check failed");
+        } catch (...) {
+            fri_state_release(s);
+            throw;
+        }
+        fri_state_release(s);
+    });
+}
+
+int nlc_fri_begin(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_batch* const* oracles, int n_oracles,
+                  const uint64_t alpha[2], const nlc_fri_params* p, nlc_fri_state** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(inst && oracles && alpha && p && out, "null argument");
+        *out = nullptr;
+        nlc_fri_state* s = fri_state_new(ctx, inst, oracles, n_oracles, p);
+        try {
+            u64 a[2] = {gl::canon(alpha[0]), gl::canon(alpha[1])};
+            h2d(ctx, fri_view(s).alpha, a, sizeof a);
+            fri_begin(s, inst);
+            sync(ctx);
+        } catch (...) {
+            fri_state_release(s);
+            throw;
+        }
+        *out = s;
+    });
+}
+int nlc_fri_commit_round(nlc_fri_state* s, uint64_t* cap_out) {
+    if (!s) return 1;
+    nlc_ctx* ctx = fri_view(s).ctx;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        fri_commit_round(s);
+        FriView v = fri_view(s);
+        const size_t cap_words = (size_t)4 << v.cap_height;
+        if (cap_out) d2h(ctx, cap_out, v.proof + (size_t)(v.round - 1) * cap_words, cap_words * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_fri_fold_round(nlc_fri_state* s, const uint64_t beta[2]) {
+    if (!s) return 1;
+    nlc_ctx* ctx = fri_view(s).ctx;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(beta != nullptr, "null argument");
+        u64 b[2] = {gl::canon(beta[0]), gl::canon(beta[1])};
+        h2d(ctx, fri_view(s).beta, b, sizeof b);
+        fri_fold_round(s);
+        sync(ctx);
+    });
+}
+int nlc_fri_final_poly(nlc_fri_state* s, uint64_t* out) {
+    if (!s) return 1;
+    nlc_ctx* ctx = fri_view(s).ctx;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        fri_final_poly_to_proof(s);
+        FriView v = fri_view(s);
+        d2h(ctx, out, v.proof + v.final_off, 2 * fri_final_poly_len(s) * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_fri_pow(nlc_ctx* ctx, const nlc_challenger* c, int proof_of_work_bits, uint64_t* witness_out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(c && witness_out, "null argument");
+        NLC_CHECK(c->input_len < 8, "corrupt challenger buffers");
+        NLC_CHECK(proof_of_work_bits >= 0 && proof_of_work_bits < 64, "proof_of_work_bits out of range");
+        const size_t cw = (sizeof(nlc_challenger) + 7) / 8;
+        DevBuf cd(ctx, cw), w(ctx, 1);
+        h2d(ctx, cd.p, c, sizeof *c);
+        fri_pow_dev(ctx, (const nlc_challenger*)cd.p, proof_of_work_bits, w.p);
+        d2h(ctx, witness_out, w.p, sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_fri_queries(nlc_fri_state* s, const uint64_t* x_indices, size_t n_queries, uint64_t* out) {
+    if (!s) return 1;
+    nlc_ctx* ctx = fri_view(s).ctx;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        FriView v = fri_view(s);
+        NLC_CHECK(x_indices && out, "null argument");
+        NLC_CHECK(n_queries <= (size_t)v.num_queries, "more queries than num_query_rounds");
+        if (!n_queries) return;
+        std::vector<u64> idx(n_queries);
+        for (size_t i = 0; i < n_queries; i++) idx[i] = x_indices[i] & (v.N - 1);
+        h2d(ctx, v.xidx, idx.data(), n_queries * sizeof(u64));
+        fri_queries(s, n_queries);
+        d2h(ctx, out, v.proof + v.query_off, n_queries * v.query_words * sizeof(u64));
+        sync(ctx);
+    });
+}
+void nlc_fri_state_free(nlc_fri_state* s) {
+    if (!s) return;
+    CtxGuard g(fri_view(s).ctx);
+    fri_state_release(s);
+}
+
+} // extern "C"

@@ -1,0 +1,61 @@
+// batch.cuh -- device-resident images of plonky2's PolynomialBatch and MerkleTree (internal header).
+#pragma once
+#include "common.cuh"
+#include "gl.cuh"
+
+struct nlc_batch {
+    nlc_ctx* ctx = nullptr;
+    size_t W = 0;
+    int log_n = 0, rate_bits = 0, cap_height = 0;
+    u64* coeffs = nullptr;  // W x n, column-major
+    u64* leaves = nullptr;  // N x W, row-major, index-bit-reversed rows
+    u64* digests = nullptr; // plonky2 interleaved layout
+    u64* cap = nullptr;     // 2^cap x 4
+    size_t n_digest_words = 0;
+};
+
+struct nlc_tree {
+    nlc_ctx* ctx = nullptr;
+    size_t n_leaves = 0, leaf_len = 0;
+    int cap_height = 0;
+    u64* leaves = nullptr;
+    u64* digests = nullptr;
+    u64* cap = nullptr;
+    bool owns_leaves = true;
+};
+
+// ---- commit.cu ----
+nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height);
+void batch_release(nlc_batch* b);
+void batch_ifft_values(nlc_batch* b, const u64* values_dev);
+void batch_lde_and_tree(nlc_batch* b);
+void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
+                          u64* out_dev);
+void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev);
+void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
+
+// ---- fri.cu ----
+void challenger_observe_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, const u64* elems_dev, size_t n);
+void challenger_get_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, size_t n, u64* out_dev);
+void fri_pow_dev(nlc_ctx* ctx, const nlc_challenger* ch_dev, int pow_bits, u64* witness_dev);
+struct nlc_fri_state;
+size_t fri_proof_words_impl(const nlc_fri_params* p, nlc_batch* const* oracles, int n_oracles, size_t* final_off,
+                            size_t* pow_off, size_t* query_off, size_t* query_words);
+nlc_fri_state* fri_state_new(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_batch* const* oracles, int n_oracles,
+                             const nlc_fri_params* p);
+void fri_state_release(nlc_fri_state* s);
+void fri_begin(nlc_fri_state* s, const nlc_fri_instance* inst);
+void fri_commit_round(nlc_fri_state* s);
+void fri_fold_round(nlc_fri_state* s);
+void fri_final_poly_to_proof(nlc_fri_state* s);
+size_t fri_final_poly_len(const nlc_fri_state* s);
+void fri_queries(nlc_fri_state* s, size_t nq);
+void fri_prove_openings(nlc_fri_state* s, const nlc_fri_instance* inst, nlc_challenger* ch_dev);
+// plain view of the opaque FRI state for the C ABI layer
+struct FriView {
+    nlc_ctx* ctx;
+    u64 *alpha, *beta, *pow, *resp, *xidx, *proof;
+    size_t proof_words, final_off, pow_off, query_off, query_words, N;
+    int round, cap_height, num_queries;
+};
+FriView fri_view(nlc_fri_state* s);

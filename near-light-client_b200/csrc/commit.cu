@@ -1,0 +1,171 @@
+// commit.cu -- PolynomialBatch::from_values / from_coeffs on the device, and the accessors that
+// materialise the fields of plonky2's PolynomialBatch / MerkleTree structs on demand.
+//
+// Replaces plonky2::fri::oracle::PolynomialBatch::{from_values, from_coeffs, lde_values,
+// get_lde_values} (plonky2 0.1.4 @ d2598bd), called in tree at
+// /root/reference/vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:91-93,171-178,289-294 and
+// plonky2/stark/config.rs:92-94.
+//
+// Data layout in HBM (one nlc_batch):
+//   coeffs  : W x n   column-major (polynomial j contiguous), natural coefficient order
+//   leaves  : N x W   row-major, leaf k = LDE row bitrev_N(k)      (N = n << rate_bits)
+//   digests : 2*(N - 2^cap) x 4 in plonky2's interleaved layout;  cap : 2^cap x 4
+// The LDE is computed coset by coset: LDE point i = m*2^r + k lies on the coset 7*w_N^k*<w_n>, and
+// after the index bit reversal coset k is the contiguous leaf range [bitrev_r(k)*n, +n).  So each
+// coset is one size-n NTT of coeff_j*(7 w_N^k)^j written straight into its row range: no zero
+// padding, no size-N transform, no transpose or bit-reversal pass.
+#include "batch.cuh"
+
+namespace {
+
+__global__ void k_transpose_cols(const u64* __restrict__ rows, size_t width, size_t col0, size_t n_cols, size_t n,
+                                 u64* __restrict__ out) {
+    __shared__ u64 tile[32][33];
+    const size_t r0 = (size_t)blockIdx.x * 32, c0 = (size_t)blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t r = r0 + i, c = c0 + threadIdx.x;
+        if (r < n && c < n_cols) tile[i][threadIdx.x] = rows[r * width + col0 + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t c = c0 + i, r = r0 + threadIdx.x;
+        if (r < n && c < n_cols) out[c * n + r] = tile[threadIdx.x][i];
+    }
+}
+
+// out[i*W + j] = leaves[bitrev_N(idx[i]*step)*W + j]
+__global__ void k_gather_lde_rows(const u64* __restrict__ leaves, size_t W, int log_N, const u64* __restrict__ idx,
+                                  size_t step, u64* __restrict__ out) {
+    const size_t i = blockIdx.x;
+    const u64 pt = (idx[i] * step) & (((u64)1 << log_N) - 1);
+    const u64 row = log_N ? (__brevll(pt) >> (64 - log_N)) : 0;
+    for (size_t j = threadIdx.x; j < W; j += blockDim.x) out[i * W + j] = leaves[row * W + j];
+}
+
+// One block per polynomial: sum_j c_j z^j over F_{p^2}.
+__global__ void __launch_bounds__(256) k_eval_ext(const u64* __restrict__ coeffs, size_t n, gl::Ext2 z, u64* out) {
+    __shared__ gl::Ext2 part[256];
+    const u64* c = coeffs + blockIdx.x * n;
+    const size_t per = (n + 255) / 256;
+    const size_t lo = threadIdx.x * per, hi = lo + per < n ? lo + per : n;
+    gl::Ext2 acc = {0, 0};
+    for (size_t j = hi; j-- > lo;) {
+        acc = gl::ext_mul(acc, z);
+        acc.a0 = gl::add(acc.a0, gl::canon(c[j]));
+    }
+    if (lo < n) acc = gl::ext_mul(acc, gl::ext_pow(z, lo));
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) part[threadIdx.x] = gl::ext_add(part[threadIdx.x], part[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out[2 * blockIdx.x] = part[0].a0;
+        out[2 * blockIdx.x + 1] = part[0].a1;
+    }
+}
+
+} // namespace
+
+nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height) {
+    NLC_CHECK(W > 0, "PolynomialBatch: at least one polynomial required");
+    NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
+    NLC_CHECK(cap_height >= 0 && cap_height <= log_n + rate_bits, "cap_height should be at most log2(leaves.len())");
+    nlc_batch* b = new nlc_batch();
+    b->ctx = ctx;
+    b->W = W;
+    b->log_n = log_n;
+    b->rate_bits = rate_bits;
+    b->cap_height = cap_height;
+    const size_t n = (size_t)1 << log_n, N = n << rate_bits;
+    try {
+        b->coeffs = ctx->dmalloc(W * n);
+        b->leaves = ctx->dmalloc(W * N);
+        b->n_digest_words = 8 * (N - ((size_t)1 << cap_height));
+        b->digests = ctx->dmalloc(b->n_digest_words);
+        b->cap = ctx->dmalloc((size_t)4 << cap_height);
+    } catch (...) {
+        batch_release(b);
+        throw;
+    }
+    return b;
+}
+
+void batch_release(nlc_batch* b) {
+    if (!b) return;
+    nlc_ctx* ctx = b->ctx;
+    ctx->dfree(b->coeffs);
+    ctx->dfree(b->leaves);
+    ctx->dfree(b->digests);
+    ctx->dfree(b->cap);
+    delete b;
+}
+
+// "FFT + blinding" + "transpose LDEs" + reverse_index_bits + "build Merkle tree" of from_coeffs.
+void batch_lde_and_tree(nlc_batch* b) {
+    nlc_ctx* ctx = b->ctx;
+    const int log_n = b->log_n, r = b->rate_bits;
+    const size_t n = (size_t)1 << log_n, N = n << r;
+    u64* scratch = nullptr;
+    const size_t sw = ntt_scratch_words(b->W, log_n);
+    if (sw) scratch = ctx->dmalloc(sw);
+    const u64 w_N = gl::h_root_of_unity(log_n + r);
+    for (size_t k = 0; k < ((size_t)1 << r); k++) {
+        NttJob job;
+        job.src = b->coeffs;
+        job.src_stride = n;
+        job.n_cols = b->W;
+        job.log_n = log_n;
+        job.pre_shift = gl::h_mul(gl::GENERATOR, gl::h_pow(w_N, k));
+        job.rows = true;
+        job.dst = b->leaves;
+        job.row_width = b->W;
+        size_t kr = 0; // bitrev_r(k)
+        for (int t = 0; t < r; t++) kr |= ((k >> t) & 1) << (r - 1 - t);
+        job.row_base = kr * n;
+        job.col0 = 0;
+        job.scratch = scratch;
+        ntt_run(ctx, job);
+    }
+    ctx->dfree(scratch);
+    merkle_build(ctx, b->leaves, N, b->W, b->cap_height, b->digests, b->cap);
+}
+
+// "IFFT" of from_values: values (W x n column-major, device) -> b->coeffs.
+void batch_ifft_values(nlc_batch* b, const u64* values_dev) {
+    nlc_ctx* ctx = b->ctx;
+    const size_t n = (size_t)1 << b->log_n;
+    u64* scratch = nullptr;
+    const size_t sw = ntt_scratch_words(b->W, b->log_n);
+    if (sw) scratch = ctx->dmalloc(sw);
+    NttJob job;
+    job.src = values_dev;
+    job.src_stride = n;
+    job.n_cols = b->W;
+    job.log_n = b->log_n;
+    job.inverse = true;
+    job.rows = false;
+    job.dst = b->coeffs;
+    job.dst_stride = n;
+    job.scratch = scratch;
+    ntt_run(ctx, job);
+    ctx->dfree(scratch);
+}
+
+void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
+                          u64* out_dev) {
+    dim3 grid((unsigned)((n + 31) / 32), (unsigned)((n_cols + 31) / 32));
+    NLC_LAUNCH(ctx, k_transpose_cols, grid, dim3(32, 8), 0, rows_dev, width, col0, n_cols, n, out_dev);
+}
+
+void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev) {
+    if (!m) return;
+    NLC_LAUNCH(b->ctx, k_gather_lde_rows, (unsigned)m, 128, 0, b->leaves, b->W, b->log_n + b->rate_bits, idx_dev, step,
+               out_dev);
+}
+
+void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev) {
+    gl::Ext2 ze = {gl::canon(z[0]), gl::canon(z[1])};
+    NLC_LAUNCH(b->ctx, k_eval_ext, (unsigned)b->W, 256, 0, b->coeffs, (size_t)1 << b->log_n, ze, out_dev);
+}
