@@ -1,0 +1,744 @@
+"""Host-side mirror of the plonky2 API surface that the starkyx / plonky2x provers consume on the
+commitment hot path, on top of the C ABI (include/nlc_commit.h).  Same names, argument order and
+panics-as-exceptions behaviour as the Rust items they stand for, so the parity tests read like the
+call sites in /root/reference/vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:50-225:
+
+    PolynomialBatch::from_values / from_coeffs / get_lde_values / prove_openings   (fri/oracle.rs)
+    MerkleTree::new / get / prove, MerkleCap                                       (hash/merkle_tree.rs)
+    PolynomialValues / PolynomialCoeffs fft helpers                                (field/polynomial)
+    PoseidonHash, PoseidonPermutation                                              (hash/poseidon.rs)
+    Challenger                                                                     (iop/challenger.rs)
+    FriConfig / FriParams / FriReductionStrategy / FriInstanceInfo                 (fri/mod.rs, structure.rs)
+
+All arithmetic runs in the CUDA library; numpy only carries buffers.  Field elements are uint64.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field as _field
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import NlcError, u64p, vp
+
+P = 0xFFFFFFFF00000001
+COSET_SHIFT = 7  # F::coset_shift() == MULTIPLICATIVE_GROUP_GENERATOR
+
+
+def _a(x, shape=None) -> np.ndarray:
+    a = np.ascontiguousarray(np.asarray(x, dtype=np.uint64))
+    return a if shape is None else a.reshape(shape)
+
+
+def _p(a: np.ndarray):
+    assert a.dtype == np.uint64 and a.flags.c_contiguous
+    return a.ctypes.data_as(u64p)
+
+
+def _log2_strict(n: int) -> int:
+    if n <= 0 or n & (n - 1):
+        raise NlcError(f"Not a power of two: {n}")  # plonky2_util::log2_strict panics
+    return n.bit_length() - 1
+
+
+class Context:
+    """One nlc_ctx: a (process, GPU) pair with its stream and table cache."""
+
+    def __init__(self, device: int = -1):
+        self._h = vp()
+        L = _ffi.lib()
+        if L.nlc_init(device, C.byref(self._h)) != 0:
+            raise NlcError((L.nlc_last_error(None) or b"nlc_init failed").decode())
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise NlcError((_ffi.lib().nlc_last_error(self._h) or b"unknown error").decode())
+
+    @property
+    def device(self) -> int:
+        return _ffi.lib().nlc_device(self._h)
+
+    def set_stream(self, cuda_stream: int | None):
+        self._check(_ffi.lib().nlc_set_stream(self._h, vp(cuda_stream or 0)))
+
+    def synchronize(self):
+        self._check(_ffi.lib().nlc_synchronize(self._h))
+
+    def launch_count(self) -> int:
+        return int(_ffi.lib().nlc_launch_count(self._h))
+
+    def close(self):
+        if self._h:
+            _ffi.lib().nlc_destroy(self._h)
+            self._h = vp()
+
+
+_default_ctx: Context | None = None
+
+
+def default_context() -> Context:
+    global _default_ctx
+    if _default_ctx is None:
+        _default_ctx = Context(-1)
+    return _default_ctx
+
+
+def set_default_context(ctx: Context | None):
+    global _default_ctx
+    _default_ctx = ctx
+
+
+# ---------------------------------------------------------------------------------------------
+# field/polynomial: PolynomialValues / PolynomialCoeffs and the fft helpers (a3)
+# ---------------------------------------------------------------------------------------------
+def _fft_call(fn_name, data, *extra, ctx=None):
+    ctx = ctx or default_context()
+    a = _a(data).copy()
+    one = a.ndim == 1
+    m = a.reshape(1, -1) if one else a
+    log_n = _log2_strict(m.shape[1])
+    ctx._check(getattr(_ffi.lib(), fn_name)(ctx._h, _p(m), m.shape[0], log_n, *extra))
+    return a
+
+
+def fft(coeffs, ctx=None):
+    return _fft_call("nlc_fft", coeffs, ctx=ctx)
+
+
+def ifft(values, ctx=None):
+    return _fft_call("nlc_ifft", values, ctx=ctx)
+
+
+def coset_fft(coeffs, shift=COSET_SHIFT, ctx=None):
+    return _fft_call("nlc_coset_fft", coeffs, C.c_uint64(int(shift)), ctx=ctx)
+
+
+def coset_ifft(values, shift=COSET_SHIFT, ctx=None):
+    return _fft_call("nlc_coset_ifft", values, C.c_uint64(int(shift)), ctx=ctx)
+
+
+def lde_onto_coset(values, rate_bits: int, ctx=None):
+    ctx = ctx or default_context()
+    v = _a(values)
+    one = v.ndim == 1
+    m = v.reshape(1, -1) if one else v
+    log_n = _log2_strict(m.shape[1])
+    out = np.zeros((m.shape[0], m.shape[1] << rate_bits), np.uint64)
+    ctx._check(_ffi.lib().nlc_lde_onto_coset(ctx._h, _p(m), _p(out), m.shape[0], log_n, rate_bits))
+    return out[0] if one else out
+
+
+class PolynomialValues:
+    """plonky2_field::polynomial::PolynomialValues (evaluations over the subgroup of order len)."""
+
+    def __init__(self, values):
+        self.values = _a(values).reshape(-1)
+        _log2_strict(self.values.size)
+
+    @classmethod
+    def selector(cls, n: int, index: int):
+        v = np.zeros(n, np.uint64)
+        v[index] = 1
+        return cls(v)
+
+    def __len__(self):
+        return self.values.size
+
+    def ifft(self):
+        return PolynomialCoeffs(ifft(self.values))
+
+    def coset_ifft(self, shift=COSET_SHIFT):
+        return PolynomialCoeffs(coset_ifft(self.values, shift))
+
+    def lde_onto_coset(self, rate_bits: int):
+        return PolynomialValues(lde_onto_coset(self.values, rate_bits))
+
+
+class PolynomialCoeffs:
+    """plonky2_field::polynomial::PolynomialCoeffs (natural coefficient order)."""
+
+    def __init__(self, coeffs):
+        self.coeffs = _a(coeffs).reshape(-1)
+
+    def __len__(self):
+        return self.coeffs.size
+
+    def lde(self, rate_bits: int):
+        out = np.zeros(self.coeffs.size << rate_bits, np.uint64)
+        out[: self.coeffs.size] = self.coeffs
+        return PolynomialCoeffs(out)
+
+    def fft(self):
+        return PolynomialValues(fft(self.coeffs))
+
+    def coset_fft(self, shift=COSET_SHIFT):
+        return PolynomialValues(coset_fft(self.coeffs, shift))
+
+
+# ---------------------------------------------------------------------------------------------
+# hash/poseidon.rs, hashing.rs (a4)
+# ---------------------------------------------------------------------------------------------
+class PoseidonPermutation:
+    WIDTH, RATE = 12, 8
+
+    @staticmethod
+    def permute(states, ctx=None):
+        """PoseidonPermutation::permute on one (12,) or many (k, 12) states."""
+        ctx = ctx or default_context()
+        s = _a(states).copy()
+        m = s.reshape(-1, 12)
+        ctx._check(_ffi.lib().nlc_poseidon_permute(ctx._h, _p(m), m.shape[0]))
+        return s
+
+
+class PoseidonHash:
+    @staticmethod
+    def _many(fn, inputs, ctx):
+        ctx = ctx or default_context()
+        x = _a(inputs)
+        one = x.ndim == 1
+        m = x.reshape(1, -1) if one else x
+        out = np.zeros((m.shape[0], 4), np.uint64)
+        ctx._check(getattr(_ffi.lib(), fn)(ctx._h, _p(m), m.shape[0], m.shape[1], _p(out)))
+        return out[0] if one else out
+
+    @staticmethod
+    def hash_no_pad(inputs, ctx=None):
+        return PoseidonHash._many("nlc_hash_no_pad", inputs, ctx)
+
+    @staticmethod
+    def hash_or_noop(inputs, ctx=None):
+        return PoseidonHash._many("nlc_hash_or_noop", inputs, ctx)
+
+    @staticmethod
+    def two_to_one(left, right, ctx=None):
+        ctx = ctx or default_context()
+        l, r = _a(left), _a(right)
+        one = l.ndim == 1
+        lm, rm = l.reshape(-1, 4), r.reshape(-1, 4)
+        out = np.zeros_like(lm)
+        ctx._check(_ffi.lib().nlc_two_to_one(ctx._h, _p(lm), _p(rm), lm.shape[0], _p(out)))
+        return out[0] if one else out
+
+
+# ---------------------------------------------------------------------------------------------
+# hash/merkle_tree.rs (a5)
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class MerkleProof:
+    siblings: np.ndarray  # (log2 N - cap_height, 4), bottom-up
+
+
+class MerkleTree:
+    """plonky2::hash::merkle_tree::MerkleTree living in HBM; fields are fetched on first use."""
+
+    def __init__(self, ctx: Context, handle, n_leaves: int, leaf_len: int, cap_height: int, leaves=None):
+        self._ctx, self._h = ctx, handle
+        self.n_leaves, self.leaf_len, self.cap_height = n_leaves, leaf_len, cap_height
+        self._leaves, self._cap, self._digests = leaves, None, None
+
+    @classmethod
+    def new(cls, leaves, cap_height: int, ctx=None):
+        ctx = ctx or default_context()
+        lv = _a(leaves)
+        if lv.ndim != 2:
+            raise NlcError("MerkleTree::new: leaves must be a (n_leaves, leaf_len) matrix")
+        h = vp()
+        ctx._check(_ffi.lib().nlc_merkle_new(ctx._h, _p(lv), lv.shape[0], lv.shape[1], cap_height, C.byref(h)))
+        return cls(ctx, h, lv.shape[0], lv.shape[1], cap_height, lv)
+
+    @property
+    def leaves(self):
+        return self._leaves
+
+    @property
+    def cap(self) -> np.ndarray:
+        if self._cap is None:
+            out = np.zeros((1 << self.cap_height, 4), np.uint64)
+            self._ctx._check(_ffi.lib().nlc_tree_cap(self._h, _p(out)))
+            self._cap = out
+        return self._cap
+
+    @property
+    def digests(self) -> np.ndarray:
+        if self._digests is None:
+            out = np.zeros((2 * (self.n_leaves - (1 << self.cap_height)), 4), np.uint64)
+            self._ctx._check(_ffi.lib().nlc_tree_digests(self._h, _p(out)))
+            self._digests = out
+        return self._digests
+
+    def get(self, i: int) -> np.ndarray:
+        out = np.zeros(self.leaf_len, np.uint64)
+        self._ctx._check(_ffi.lib().nlc_tree_open(self._h, i, _p(out), None))
+        return out
+
+    def prove(self, leaf_index: int) -> MerkleProof:
+        sib = np.zeros((_log2_strict(self.n_leaves) - self.cap_height, 4), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_tree_open(self._h, leaf_index, None, _p(sib)))
+        return MerkleProof(sib)
+
+    def __del__(self):
+        try:
+            if self._h:
+                _ffi.lib().nlc_tree_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class _BatchTree:
+    """The `merkle_tree` field of a PolynomialBatch (same accessors as MerkleTree, lazily materialised)."""
+
+    def __init__(self, batch: "PolynomialBatch"):
+        self._b = batch
+        self._cap = self._leaves = self._digests = None
+
+    @property
+    def cap(self) -> np.ndarray:
+        if self._cap is None:
+            out = np.zeros((1 << self._b.cap_height, 4), np.uint64)
+            self._b._ctx._check(_ffi.lib().nlc_batch_cap(self._b._h, _p(out)))
+            self._cap = out
+        return self._cap
+
+    @property
+    def leaves(self) -> np.ndarray:
+        if self._leaves is None:
+            out = np.zeros((self._b.lde_size, self._b.n_polys), np.uint64)
+            self._b._ctx._check(_ffi.lib().nlc_batch_leaves(self._b._h, _p(out)))
+            self._leaves = out
+        return self._leaves
+
+    @property
+    def digests(self) -> np.ndarray:
+        if self._digests is None:
+            out = np.zeros((2 * (self._b.lde_size - (1 << self._b.cap_height)), 4), np.uint64)
+            self._b._ctx._check(_ffi.lib().nlc_batch_digests(self._b._h, _p(out)))
+            self._digests = out
+        return self._digests
+
+    def get(self, i: int) -> np.ndarray:
+        out = np.zeros(self._b.n_polys, np.uint64)
+        self._b._ctx._check(_ffi.lib().nlc_batch_open(self._b._h, i, _p(out), None))
+        return out
+
+    def prove(self, leaf_index: int) -> MerkleProof:
+        sib = np.zeros((self._b.degree_log + self._b.rate_bits - self._b.cap_height, 4), np.uint64)
+        self._b._ctx._check(_ffi.lib().nlc_batch_open(self._b._h, leaf_index, None, _p(sib)))
+        return MerkleProof(sib)
+
+
+# ---------------------------------------------------------------------------------------------
+# iop/challenger.rs (a9)
+# ---------------------------------------------------------------------------------------------
+class Challenger:
+    """plonky2::iop::challenger::Challenger<F, PoseidonHash>; the struct's fields cross the C ABI as data."""
+
+    def __init__(self, ctx=None):
+        self._ctx = ctx or default_context()
+        self.c = _ffi.CChallenger()
+        _ffi.lib().nlc_challenger_init(C.byref(self.c))
+
+    def clone(self) -> "Challenger":
+        o = Challenger(self._ctx)
+        C.memmove(C.byref(o.c), C.byref(self.c), C.sizeof(_ffi.CChallenger))
+        return o
+
+    def observe_element(self, e):
+        self.observe_elements([e])
+
+    def observe_elements(self, elems):
+        x = _a(elems).reshape(-1)
+        if x.size:
+            self._ctx._check(_ffi.lib().nlc_challenger_observe(self._ctx._h, C.byref(self.c), _p(x), x.size))
+
+    def observe_extension_element(self, e):
+        self.observe_elements(e)
+
+    def observe_extension_elements(self, es):
+        self.observe_elements(es)
+
+    def observe_hash(self, h):
+        self.observe_elements(h)
+
+    def observe_cap(self, cap):
+        self.observe_elements(cap)
+
+    def get_n_challenges(self, n: int):
+        out = np.zeros(n, np.uint64)
+        if n:
+            self._ctx._check(_ffi.lib().nlc_challenger_get(self._ctx._h, C.byref(self.c), n, _p(out)))
+        return [int(v) for v in out]
+
+    def get_challenge(self) -> int:
+        return self.get_n_challenges(1)[0]
+
+    def get_extension_challenge(self):
+        return tuple(self.get_n_challenges(2))
+
+    def state(self):
+        c = self.c
+        return (list(c.sponge_state), list(c.input_buffer)[: c.input_len], list(c.output_buffer)[: c.output_len])
+
+
+# ---------------------------------------------------------------------------------------------
+# fri/mod.rs, fri/reduction_strategies.rs, fri/structure.rs (a10)
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class FriReductionStrategy:
+    kind: str
+    arity_bits: int = 4
+    final_poly_bits: int = 5
+
+    @classmethod
+    def ConstantArityBits(cls, arity_bits: int, final_poly_bits: int):
+        return cls("ConstantArityBits", arity_bits, final_poly_bits)
+
+
+@dataclass
+class FriParams:
+    config: "FriConfig"
+    hiding: bool
+    degree_bits: int
+    reduction_arity_bits: list
+
+    def lde_bits(self):
+        return self.degree_bits + self.config.rate_bits
+
+    def lde_size(self):
+        return 1 << self.lde_bits()
+
+    def final_poly_len(self):
+        return 1 << (self.degree_bits - sum(self.reduction_arity_bits))
+
+    def to_c(self) -> _ffi.CFriParams:
+        p = _ffi.CFriParams()
+        p.degree_bits, p.rate_bits, p.cap_height = self.degree_bits, self.config.rate_bits, self.config.cap_height
+        p.proof_of_work_bits, p.num_query_rounds = self.config.proof_of_work_bits, self.config.num_query_rounds
+        p.n_reduction_rounds = len(self.reduction_arity_bits)
+        for i, a in enumerate(self.reduction_arity_bits):
+            p.reduction_arity_bits[i] = a
+        return p
+
+
+@dataclass
+class FriConfig:
+    rate_bits: int
+    cap_height: int
+    proof_of_work_bits: int
+    reduction_strategy: FriReductionStrategy
+    num_query_rounds: int
+
+    @classmethod
+    def standard_fast_config(cls):
+        """starkyx StarkyConfig::standard_fast_config (plonky2/stark/config.rs:58-73)."""
+        return cls(1, 4, 16, FriReductionStrategy.ConstantArityBits(4, 5), 84)
+
+    @classmethod
+    def standard_recursion_config(cls):
+        """plonky2 CircuitConfig::standard_recursion_config().fri_config."""
+        return cls(3, 4, 16, FriReductionStrategy.ConstantArityBits(4, 5), 28)
+
+    def fri_params(self, degree_bits: int, hiding: bool = False) -> FriParams:
+        if hiding:
+            raise NlcError("hiding / blinding is not used on this path (all in-tree call sites pass false)")
+        if self.reduction_strategy.kind != "ConstantArityBits":
+            raise NlcError("only FriReductionStrategy::ConstantArityBits is used in tree (config.rs:68)")
+        p = _ffi.CFriParams()
+        rc = _ffi.lib().nlc_fri_params_constant_arity(C.byref(p), degree_bits, self.rate_bits, self.cap_height,
+                                                      self.proof_of_work_bits, self.num_query_rounds,
+                                                      self.reduction_strategy.arity_bits,
+                                                      self.reduction_strategy.final_poly_bits)
+        if rc:
+            raise NlcError("bad FriConfig")
+        return FriParams(self, hiding, degree_bits, [p.reduction_arity_bits[i] for i in range(p.n_reduction_rounds)])
+
+
+@dataclass
+class FriPolynomialInfo:
+    oracle_index: int
+    polynomial_index: int
+
+    @staticmethod
+    def from_range(oracle_index: int, polynomial_indices):
+        return [FriPolynomialInfo(oracle_index, i) for i in polynomial_indices]
+
+
+@dataclass
+class FriBatchInfo:
+    point: tuple  # extension element (a0, a1)
+    polynomials: list
+
+
+@dataclass
+class FriInstanceInfo:
+    oracles: list  # FriOracleInfo is only (num_polys, blinding); kept for shape parity
+    batches: list
+    _keep: list = _field(default_factory=list)
+
+    def to_c(self) -> _ffi.CFriInstance:
+        pts = _a([c for b in self.batches for c in b.point])
+        offs = np.zeros(len(self.batches) + 1, np.uint32)
+        po, pi = [], []
+        for k, b in enumerate(self.batches):
+            for info in b.polynomials:
+                po.append(info.oracle_index)
+                pi.append(info.polynomial_index)
+            offs[k + 1] = len(po)
+        po, pi = np.asarray(po, np.uint32), np.asarray(pi, np.uint32)
+        self._keep = [pts, offs, po, pi]
+        u32 = _ffi.u32p
+        return _ffi.CFriInstance(len(self.batches), _p(pts) if pts.size else None, offs.ctypes.data_as(u32),
+                                 po.ctypes.data_as(u32), pi.ctypes.data_as(u32))
+
+
+@dataclass
+class FriProof:
+    """fri::proof::FriProof, parsed from the flat layout documented in include/nlc_commit.h."""
+    commit_phase_merkle_caps: list
+    final_poly: np.ndarray       # (len, 2)
+    pow_witness: int
+    query_round_proofs: list     # per query: {"initial": [(leaf, siblings)], "steps": [(evals, siblings)]}
+    flat: np.ndarray
+
+    @classmethod
+    def parse(cls, flat: np.ndarray, params: FriParams, oracle_widths):
+        cfg = params.config
+        cap_words = 4 << cfg.cap_height
+        w = 0
+        caps = []
+        for _ in params.reduction_arity_bits:
+            caps.append(flat[w:w + cap_words].reshape(-1, 4))
+            w += cap_words
+        fl = params.final_poly_len()
+        final_poly = flat[w:w + 2 * fl].reshape(-1, 2)
+        w += 2 * fl
+        pow_witness = int(flat[w])
+        w += 1
+        log_N = params.lde_bits()
+        queries = []
+        for _ in range(cfg.num_query_rounds):
+            init, steps = [], []
+            for W in oracle_widths:
+                leaf = flat[w:w + W]
+                w += W
+                ns = 4 * (log_N - cfg.cap_height)
+                init.append((leaf, flat[w:w + ns].reshape(-1, 4)))
+                w += ns
+            lg = log_N
+            for ab in params.reduction_arity_bits:
+                ev = flat[w:w + (2 << ab)].reshape(-1, 2)
+                w += 2 << ab
+                ns = 4 * (lg - ab - cfg.cap_height)
+                steps.append((ev, flat[w:w + ns].reshape(-1, 4)))
+                w += ns
+                lg -= ab
+            queries.append({"initial": init, "steps": steps})
+        assert w == flat.size
+        return cls(caps, final_poly, pow_witness, queries, flat)
+
+
+# ---------------------------------------------------------------------------------------------
+# fri/oracle.rs: PolynomialBatch (a1, a2, a6, a7)
+# ---------------------------------------------------------------------------------------------
+def _col_table(cols):
+    """W host pointers, exactly a Vec<PolynomialValues<F>> / Vec<PolynomialCoeffs<F>>."""
+    arrs = []
+    for c in cols:
+        v = c.values if isinstance(c, PolynomialValues) else c.coeffs if isinstance(c, PolynomialCoeffs) else c
+        arrs.append(_a(v).reshape(-1))
+    if not arrs:
+        raise NlcError("PolynomialBatch: at least one polynomial required")
+    n = arrs[0].size
+    if any(a.size != n for a in arrs):
+        raise NlcError("All polynomials in a batch must have the same length")  # plonky2 assert
+    table = (u64p * len(arrs))(*[_p(a) for a in arrs])
+    return table, arrs, n
+
+
+class PolynomialBatch:
+    """plonky2::fri::oracle::PolynomialBatch resident in HBM.  Struct fields (`polynomials`,
+    `merkle_tree.{cap,leaves,digests}`) are materialised on first access."""
+
+    def __init__(self, ctx: Context, handle, n_polys: int, degree_log: int, rate_bits: int, cap_height: int):
+        self._ctx, self._h = ctx, handle
+        self.n_polys, self.degree_log, self.rate_bits, self.cap_height = n_polys, degree_log, rate_bits, cap_height
+        self.blinding = False
+        self.merkle_tree = _BatchTree(self)
+        self._polys = None
+
+    # -- constructors ---------------------------------------------------------------------------
+    @classmethod
+    def _commit(cls, fn, cols, rate_bits, blinding, cap_height, ctx):
+        if blinding:
+            raise NlcError("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)")
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(cols)
+        log_n = _log2_strict(n)
+        h = vp()
+        ctx._check(getattr(_ffi.lib(), fn)(ctx._h, table, len(arrs), log_n, rate_bits, cap_height, C.byref(h)))
+        return cls(ctx, h, len(arrs), log_n, rate_bits, cap_height)
+
+    @classmethod
+    def from_values(cls, values, rate_bits: int, blinding: bool, cap_height: int, timing=None, fft_root_table=None,
+                    ctx=None):
+        """PolynomialBatch::from_values(values, rate_bits, blinding, cap_height, timing, fft_root_table)."""
+        return cls._commit("nlc_commit_from_values", values, rate_bits, blinding, cap_height, ctx)
+
+    @classmethod
+    def from_coeffs(cls, polynomials, rate_bits: int, blinding: bool, cap_height: int, timing=None,
+                    fft_root_table=None, ctx=None):
+        """PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)."""
+        return cls._commit("nlc_commit_from_coeffs", polynomials, rate_bits, blinding, cap_height, ctx)
+
+    @classmethod
+    def from_device(cls, dev_ptr: int, n_polys: int, degree_log: int, rate_bits: int, cap_height: int,
+                    is_values: bool = True, ctx=None):
+        """Input already in HBM as an n_polys x n column-major matrix (asynchronous: no host sync)."""
+        ctx = ctx or default_context()
+        h = vp()
+        fn = _ffi.lib().nlc_commit_from_values_dev if is_values else _ffi.lib().nlc_commit_from_coeffs_dev
+        ctx._check(fn(ctx._h, vp(dev_ptr), n_polys, degree_log, rate_bits, cap_height, C.byref(h)))
+        return cls(ctx, h, n_polys, degree_log, rate_bits, cap_height)
+
+    @classmethod
+    def from_trace_rows(cls, rows, col0: int, n_cols: int, rate_bits: int, cap_height: int, ctx=None):
+        """Commit columns [col0, col0+n_cols) of a row-major AirTrace (starkyx trace/mod.rs:19-24)."""
+        ctx = ctx or default_context()
+        r = _a(rows)
+        log_n = _log2_strict(r.shape[0])
+        h = vp()
+        ctx._check(_ffi.lib().nlc_commit_from_trace_rows(ctx._h, _p(r), r.shape[1], col0, n_cols, log_n, rate_bits,
+                                                         cap_height, C.byref(h)))
+        return cls(ctx, h, n_cols, log_n, rate_bits, cap_height)
+
+    # -- fields ---------------------------------------------------------------------------------
+    @property
+    def lde_size(self) -> int:
+        return 1 << (self.degree_log + self.rate_bits)
+
+    @property
+    def polynomials(self):
+        if self._polys is None:
+            n = 1 << self.degree_log
+            out = np.zeros((self.n_polys, n), np.uint64)
+            table = (u64p * self.n_polys)(*[_p(out[j]) for j in range(self.n_polys)])
+            self._ctx._check(_ffi.lib().nlc_batch_coeffs(self._h, table))
+            self._coeff_matrix = out
+            self._polys = [PolynomialCoeffs(out[j]) for j in range(self.n_polys)]
+        return self._polys
+
+    @property
+    def coeff_matrix(self) -> np.ndarray:
+        self.polynomials
+        return self._coeff_matrix
+
+    def get_lde_values(self, index: int, step: int = 1) -> np.ndarray:
+        """leaves[reverse_bits(index * step, lde_bits)] (fri/oracle.rs get_lde_values)."""
+        return self.get_lde_rows([index], step)[0]
+
+    def get_lde_rows(self, indices, step: int = 1) -> np.ndarray:
+        idx = _a(indices).reshape(-1)
+        out = np.zeros((idx.size, self.n_polys), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_batch_lde_rows(self._h, _p(idx), idx.size, step, _p(out)))
+        return out
+
+    def get_lde_values_packed(self, index_start: int, step: int, width: int = 1) -> np.ndarray:
+        """P::WIDTH consecutive rows, transposed to n_polys x width like PackedField::from_slice per poly."""
+        return self.get_lde_rows(np.arange(index_start, index_start + width), step).T.copy()
+
+    def eval_at(self, z) -> np.ndarray:
+        """Every polynomial at the extension point z -> (n_polys, 2) (StarkOpeningSet::new, proof.rs:307-310)."""
+        out = np.zeros((self.n_polys, 2), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_batch_eval(self._h, _p(_a(z)), _p(out)))
+        return out
+
+    def device_pointers(self):
+        L = _ffi.lib()
+        return {"leaves": L.nlc_batch_leaves_dev(self._h), "coeffs": L.nlc_batch_coeffs_dev(self._h),
+                "cap": L.nlc_batch_cap_dev(self._h)}
+
+    # -- openings -------------------------------------------------------------------------------
+    @staticmethod
+    def prove_openings(instance: FriInstanceInfo, oracles, challenger: Challenger, fri_params: FriParams,
+                       timing=None) -> FriProof:
+        """PolynomialBatch::prove_openings(instance, oracles, challenger, fri_params, timing)."""
+        if not oracles:
+            raise NlcError("prove_openings: no oracles")
+        ctx = oracles[0]._ctx
+        handles = (vp * len(oracles))(*[o._h for o in oracles])
+        p = fri_params.to_c()
+        ci = instance.to_c()
+        words = _ffi.lib().nlc_fri_proof_words(C.byref(p), handles, len(oracles))
+        out = np.zeros(words, np.uint64)
+        ctx._check(_ffi.lib().nlc_prove_openings(ctx._h, C.byref(ci), handles, len(oracles), C.byref(challenger.c),
+                                                 C.byref(p), _p(out)))
+        return FriProof.parse(out, fri_params, [o.n_polys for o in oracles])
+
+    def free(self):
+        if self._h:
+            _ffi.lib().nlc_batch_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class FriCommitPhase:
+    """Rust-driven commit phase (transcript stays with the caller): nlc_fri_begin / commit_round /
+    fold_round / final_poly / queries -- the steps of fri_proof() in fri/prover.rs."""
+
+    def __init__(self, instance: FriInstanceInfo, oracles, alpha, fri_params: FriParams):
+        self._ctx = oracles[0]._ctx
+        self._oracles = oracles
+        self.params = fri_params
+        handles = (vp * len(oracles))(*[o._h for o in oracles])
+        p = fri_params.to_c()
+        ci = instance.to_c()
+        self._h = vp()
+        self._ctx._check(_ffi.lib().nlc_fri_begin(self._ctx._h, C.byref(ci), handles, len(oracles), _p(_a(alpha)),
+                                                  C.byref(p), C.byref(self._h)))
+        p2 = fri_params.to_c()
+        total = _ffi.lib().nlc_fri_proof_words(C.byref(p2), handles, len(oracles))
+        nq = fri_params.config.num_query_rounds
+        fixed = len(fri_params.reduction_arity_bits) * (4 << fri_params.config.cap_height) + 2 * fri_params.final_poly_len() + 1
+        self.query_words = (total - fixed) // nq if nq else 0
+
+    def commit_round(self) -> np.ndarray:
+        cap = np.zeros((1 << self.params.config.cap_height, 4), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_fri_commit_round(self._h, _p(cap)))
+        return cap
+
+    def fold_round(self, beta):
+        self._ctx._check(_ffi.lib().nlc_fri_fold_round(self._h, _p(_a(beta))))
+
+    def final_poly(self) -> np.ndarray:
+        out = np.zeros((self.params.final_poly_len(), 2), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_fri_final_poly(self._h, _p(out)))
+        return out
+
+    def queries(self, x_indices) -> np.ndarray:
+        x = _a(x_indices).reshape(-1)
+        out = np.zeros((x.size, self.query_words), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_fri_queries(self._h, _p(x), x.size, _p(out)))
+        return out
+
+    def __del__(self):
+        try:
+            if self._h:
+                _ffi.lib().nlc_fri_state_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def fri_proof_of_work(challenger: Challenger, proof_of_work_bits: int) -> int:
+    """fri_proof_of_work's search only (smallest valid witness); the caller observes it afterwards."""
+    out = np.zeros(1, np.uint64)
+    ctx = challenger._ctx
+    ctx._check(_ffi.lib().nlc_fri_pow(ctx._h, C.byref(challenger.c), proof_of_work_bits, _p(out)))
+    return int(out[0])

@@ -1,0 +1,124 @@
+"""a1/a2/a6: PolynomialBatch::from_values / from_coeffs / get_lde_values vs the oracle (bit-exact).
+
+Reads like the call sites in vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:91-93,171-178,289-294.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+P = 0xFFFFFFFF00000001
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+SHAPES = [  # (W, log_n, rate_bits, cap_height)
+    (1, 0, 0, 0), (1, 0, 1, 0), (2, 1, 1, 1), (2, 5, 1, 4), (3, 4, 3, 4), (4, 6, 1, 2), (5, 6, 2, 0),
+    (7, 9, 1, 4), (8, 10, 1, 4), (9, 10, 3, 4), (17, 11, 1, 4), (33, 12, 3, 4), (135, 12, 3, 4),
+    (20, 13, 3, 4), (16, 14, 3, 4), (64, 14, 1, 4), (5, 16, 1, 4), (3, 17, 1, 4), (2, 21, 1, 4),
+    (2, 8, 2, 10),  # cap_height == log2(N): digests empty, cap = leaf hashes
+]
+
+
+def check_batch(batch, ref, full=True):
+    assert np.array_equal(batch.merkle_tree.cap, ref.cap)
+    assert np.array_equal(batch.coeff_matrix, ref.coeffs)
+    if full:
+        assert np.array_equal(batch.merkle_tree.leaves, ref.leaves)
+        assert np.array_equal(batch.merkle_tree.digests, ref.digests)
+
+
+@pytest.mark.parametrize("W,log_n,rate_bits,cap_height", SHAPES)
+def test_from_values(P2, O, rng, W, log_n, rate_bits, cap_height):
+    values = O.random_field(rng, (W, 1 << log_n))
+    trace_cols = [P2.PolynomialValues(v) for v in values]
+    commitment = P2.PolynomialBatch.from_values(trace_cols, rate_bits, False, cap_height, None, None)
+    ref = O.commit_from_values(values, rate_bits, cap_height)
+    check_batch(commitment, ref)
+    assert commitment.degree_log == log_n and len(commitment.polynomials) == W
+
+
+@pytest.mark.parametrize("W,log_n,rate_bits,cap_height", SHAPES[::3])
+def test_from_coeffs(P2, O, rng, W, log_n, rate_bits, cap_height):
+    coeffs = O.random_field(rng, (W, 1 << log_n))
+    commitment = P2.PolynomialBatch.from_coeffs([P2.PolynomialCoeffs(c) for c in coeffs], rate_bits, False, cap_height)
+    check_batch(commitment, O.commit_from_coeffs(coeffs, rate_bits, cap_height))
+
+
+@pytest.mark.parametrize("kind", ["zero", "structured", "max", "noncanonical"])
+def test_structured_inputs(P2, O, kind):
+    W, log_n, r, cap = 9, 8, 1, 4
+    n = 1 << log_n
+    if kind == "zero":
+        v = np.zeros((W, n), np.uint64)
+    elif kind == "structured":  # value = row*W + col
+        v = (np.arange(n, dtype=np.uint64)[None, :] * np.uint64(W) + np.arange(W, dtype=np.uint64)[:, None])
+    elif kind == "max":
+        v = np.full((W, n), P - 1, np.uint64)
+    else:
+        v = np.full((W, n), 0xFFFFFFFFFFFFFFFF, np.uint64)
+    canon = np.where(v >= np.uint64(P), v - np.uint64(P), v)
+    check_batch(P2.PolynomialBatch.from_values(list(v), r, False, cap), O.commit_from_values(canon, r, cap))
+
+
+def test_get_lde_values_and_open(P2, O, rng):
+    W, log_n, r, cap = 13, 9, 2, 3
+    values = O.random_field(rng, (W, 1 << log_n))
+    b = P2.PolynomialBatch.from_values(list(values), r, False, cap)
+    ref = O.commit_from_values(values, r, cap)
+    N, log_N = 1 << (log_n + r), log_n + r
+    br = lambda x: int(format(x, f"0{log_N}b")[::-1], 2)
+    for i, step in [(0, 1), (5, 1), (7, 2), (100, 4), (N - 1, 1)]:
+        assert np.array_equal(b.get_lde_values(i, step), ref.leaves[br((i * step) % N)])
+    packed = b.get_lde_values_packed(8, 2, 4)  # prover.rs:292
+    assert packed.shape == (W, 4)
+    for k in range(4):
+        assert np.array_equal(packed[:, k], ref.leaves[br((8 + k) * 2)])
+    # LDE row i at step 2^r is the original trace row i... on the coset 7<w>: check through the oracle instead
+    for idx in [0, 1, N // 2, N - 1]:
+        assert np.array_equal(b.merkle_tree.get(idx), ref.leaves[idx])
+        sib = b.merkle_tree.prove(idx).siblings
+        assert np.array_equal(sib, O.merkle_prove(ref.digests, N, cap, idx))
+        assert O.merkle_verify(ref.leaves[idx], idx, ref.cap, sib)
+
+
+def test_eval_at(P2, O, rng):
+    values = O.random_field(rng, (6, 1 << 10))
+    b = P2.PolynomialBatch.from_values(list(values), 1, False, 4)
+    z = O.random_field(rng, (2,))
+    got = b.eval_at(z)
+    ref = O.commit_from_values(values, 1, 4)
+    for j in range(6):
+        assert tuple(int(x) for x in got[j]) == O.eval_poly_ext(ref.coeffs[j], z)
+
+
+def test_from_trace_rows(P2, O, rng):
+    n, width = 1 << 9, 23
+    trace = O.random_field(rng, (n, width))  # row-major AirTrace (trace/mod.rs:19-24)
+    b = P2.PolynomialBatch.from_trace_rows(trace, 3, 17, 1, 4)
+    ref = O.commit_from_values(np.ascontiguousarray(trace[:, 3:20].T), 1, 4)
+    check_batch(b, ref)
+
+
+def test_errors(P2, pkg, O, rng):
+    v = O.random_field(rng, (2, 16))
+    with pytest.raises(pkg.NlcError):
+        P2.PolynomialBatch.from_values(list(v), 1, True, 0)        # blinding unsupported on this path
+    with pytest.raises(pkg.NlcError, match="cap_height"):
+        P2.PolynomialBatch.from_values(list(v), 1, False, 6)       # cap_height > log2(N)
+    with pytest.raises(pkg.NlcError, match="power of two"):
+        P2.PolynomialBatch.from_values([v[0][:12]], 1, False, 0)
+    with pytest.raises(pkg.NlcError, match="same length"):
+        P2.PolynomialBatch.from_values([v[0], v[1][:8]], 1, False, 0)
+    with pytest.raises(pkg.NlcError):
+        P2.PolynomialBatch.from_values([], 1, False, 0)
+
+
+def test_golden_fixtures(P2):
+    """Frozen oracle outputs (tests/golden/gen_golden.py) -- guards against oracle and kernel drifting together."""
+    g = np.load(os.path.join(GOLDEN, "commit_small.npz"))
+    for key in sorted({k.split(":")[0] for k in g.files}):
+        W, log_n, r, cap = (int(x) for x in key.split("_"))
+        b = P2.PolynomialBatch.from_values(list(g[key + ":values"]), r, False, cap)
+        assert np.array_equal(b.merkle_tree.cap, g[key + ":cap"])
+        assert np.array_equal(b.get_lde_rows([0, 1, 5], 1), g[key + ":lde_rows"])
+        assert np.array_equal(b.coeff_matrix[:, :4], g[key + ":coeffs_head"])
