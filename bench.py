@@ -1,0 +1,327 @@
+#!/usr/bin/env python3
+"""bench.py -- LDE + Merkle commit throughput (BASELINE.json metric) on N B200s.
+
+A "step" is one PolynomialBatch::from_values commit (iFFT -> coset LDE -> Poseidon leaf hashing -> Merkle
+digests down to the cap) of one synthetic trace matrix.  Default workload = BASELINE.json configs[1]:
+2^16 rows x 135 columns, rate_bits 3, cap_height 4.
+
+  value    : input trace elements / s, whole job, inputs resident in HBM (nlc_commit_from_values_dev)
+  e2e      : same metric through the host-buffer C-ABI call a plonky2 caller makes
+             (nlc_commit_from_values with W host column pointers + nlc_batch_cap): H2D and D2H inside
+  roofline : the dominant kernel (Poseidon leaf hashing), algorithmic bytes / CUDA-event time vs measured HBM
+  cpu_baseline / --impl reference : the CPU oracle (plonky2's algorithm restated in C + OpenMP, all host cores)
+
+Multi-GPU: independent commit instances per rank (Verify map/reduce proofs, independent STARK commits):
+no data-path collective, weak scaling; time = max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as graft  # noqa: E402
+
+P = 0xFFFFFFFF00000001
+WORKLOADS = {
+    # name: (log_n, W, rate_bits, cap_height)
+    "commit_2^16x135_r3_cap4": (16, 135, 3, 4),   # BASELINE.json configs[1] (plonk wires commit)
+    "commit_2^16x20_r3_cap4": (16, 20, 3, 4),
+    "commit_2^20x400_r1_cap4": (20, 400, 1, 4),   # configs[3] (starkyx trace commitment)
+    "commit_2^14x64_r3_cap4": (14, 64, 3, 4),
+}
+DEFAULT_WORKLOAD = "commit_2^16x135_r3_cap4"
+
+
+def synth_values(W: int, n: int, seed: int) -> np.ndarray:
+    """i.i.d. uniform in [0, p): PCG64(seed), reject >= p."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    a = rng.integers(0, 1 << 64, size=(W, n), dtype=np.uint64)
+    bad = a >= np.uint64(P)
+    while bad.any():
+        a[bad] = rng.integers(0, 1 << 64, size=int(bad.sum()), dtype=np.uint64)
+        bad = a >= np.uint64(P)
+    return a
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(log_n, W, r, cap):
+    n, N = 1 << log_n, 1 << (log_n + r)
+    return {
+        "commit": 8 * W * n + 8 * W * n + 8 * W * N + 64 * (N - (1 << cap)),  # SURVEY.md 8(d) B_commit
+        "ntt": 8 * W * n + 8 * W * N,                                          # B_ntt (LDE only)
+        "ifft": 16 * W * n,
+        "leaf_hash": 8 * W * N + 32 * N,                                       # read every LDE row once, write N digests
+        "levels": 96 * (N - (1 << cap)),
+    }
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU algorithm for the path (oracle port; plonky2 itself cannot be built here)."""
+    if rank != 0:
+        return
+    O = graft.load_oracle()
+    log_n, W, r, cap = WORKLOADS[args.workload]
+    full_log_n = log_n
+    log_n = min(log_n, args.ref_sample_log_rows)  # bounded sample: same columns / rate / cap, fewer rows
+    n = 1 << log_n
+    values = synth_values(W, n, 0xC0FFEE + 1)
+    cores = O.get_threads()
+    for _ in range(max(1, min(args.warmup, 1))):
+        O.commit_from_values(values, r, cap)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.commit_from_values(values, r, cap)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = W * n / dt
+    line = {"impl": "reference", "metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": val,
+            "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+            "data": "synthetic", "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r,
+                                            "cap_height": cap},
+            "cpu_baseline": {"value": val, "unit": "elements/s", "cores": cores, "kind": "port",
+                             "sample": f"{args.steps} commits of 2^{log_n} of the workload's 2^{full_log_n} rows x {W} cols, "
+                                       f"rate_bits {r} (same per-row work; OpenMP over columns/rows/subtrees)"},
+            "e2e": {"value": val, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, local_rank, world):
+    import ctypes as C
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = graft.load_package()
+    P2, ffi = pkg.plonky2, pkg._ffi
+    L = ffi.lib()
+    ctx = P2.Context(local_rank)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)  # torch.cuda.Event only sees this stream: launch the library on it
+
+    log_n, W, r, cap = WORKLOADS[args.workload]
+    n, N = 1 << log_n, 1 << (log_n + r)
+    elems = W * n
+    host = torch.empty((W, n), dtype=torch.int64).pin_memory()
+    host.numpy().view(np.uint64)[:] = synth_values(W, n, 0xC0FFEE + 1 + rank)
+    dev = host.cuda(non_blocking=True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    cap_host = np.zeros((1 << cap, 4), np.uint64)
+    col_table = (ffi.u64p * W)(*[C.cast(host[j].data_ptr(), ffi.u64p) for j in range(W)])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    state = {"batch": None}
+
+    def free_prev():
+        if state["batch"] is not None:
+            L.nlc_batch_free(state["batch"])
+            state["batch"] = None
+
+    def step_resident():
+        free_prev()
+        h = ffi.vp()
+        ctx._check(L.nlc_commit_from_values_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, C.byref(h)))
+        state["batch"] = h
+
+    def step_e2e():
+        free_prev()
+        h = ffi.vp()
+        ctx._check(L.nlc_commit_from_values(ctx._h, col_table, W, log_n, r, cap, C.byref(h)))
+        state["batch"] = h
+        ctx._check(L.nlc_batch_cap(h, cap_host.ctypes.data_as(ffi.u64p)))
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step_resident()
+    torch.cuda.synchronize()
+
+    # ---- timed region: exactly K steps, device time from CUDA events on the launching stream ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = ctx.launch_count()
+    barrier()
+    torch.cuda.synchronize()
+    for a, b in evs:
+        flush.zero_()  # L2 flush between timed iterations (outside the event pair)
+        a.record(stream)
+        step_resident()
+        b.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    launches = ctx.launch_count() - launches0
+    clocks = sampler.stop()
+    ms_total = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+    value = world * elems / (ms_per_step * 1e-3)
+
+    # ---- per-phase device time (plonky2 TimingTree scopes) for the roofline of the dominant kernel ----
+    ctx.timing_enable(True)
+    ctx.timing_read()
+    for _ in range(3):
+        flush.zero_()
+        step_resident()
+    phases = ctx.timing_read()
+    ctx.timing_enable(False)
+    k = max(phases["commits"], 1)
+    ab = algorithmic_bytes(log_n, W, r, cap)
+    peak, peak_src = measured_peaks()
+    leaf_ms = phases["leaf hashing"] / k
+    ntt_ms = (phases["IFFT"] + phases["FFT + blinding"]) / k
+    achieved = ab["leaf_hash"] / (leaf_ms * 1e-3) / 1e9 if leaf_ms > 0 else 0.0
+    perms = N * ((W + 7) // 8 if W > 4 else 0)
+    roofline = {"bound": "hbm", "kernel": "k_leaf_hash (Poseidon sponge over LDE rows; INT-pipe limited)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "ms_per_launch": leaf_ms,
+                "poseidon_perms_per_s": perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None}
+    roofline_ntt = {"bound": "hbm", "kernel": "k_ntt_* (iFFT + 2^r coset NTTs into leaf rows)",
+                    "achieved": ab["ntt"] / (ntt_ms * 1e-3) / 1e9 if ntt_ms > 0 else 0.0, "peak": peak, "unit": "GB/s",
+                    "ms": ntt_ms}
+    roofline_ntt["frac"] = roofline_ntt["achieved"] / peak
+    commit_gbs = ab["commit"] / (ms_per_step * 1e-3) / 1e9
+
+    # ---- e2e through the host-buffer C-ABI call (pinned host columns in, cap out) ----
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_val = world * elems / (float(te.item()) / args.steps)
+    free_prev()
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        O = graft.load_oracle()
+        vals = host.numpy().view(np.uint64)
+        O.commit_from_values(vals[:8], r, cap)  # warm tables
+        t0 = time.perf_counter()
+        ref = O.commit_from_values(vals, r, cap)
+        dt = time.perf_counter() - t0
+        ok = bool(np.array_equal(ref.cap, cap_host))
+        cpu_baseline = {"value": elems / dt, "unit": "elements/s", "cores": O.get_threads(), "kind": "port",
+                        "sample": f"1 full commit of {args.workload} ({dt:.2f} s); cap equals the GPU's: {ok}"}
+
+    if rank == 0:
+        line = {"metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": value,
+                "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u64", "data": "synthetic",
+                "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r, "cap_height": cap,
+                           "parallelism": f"instances x{world}", "l2": "flushed between timed iterations (256 MiB write)"},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": e2e_val, "unit": "elements/s", "h2d_bytes_per_step": 8 * elems,
+                        "d2h_bytes_per_step": 32 << cap, "ms_per_step": float(te.item()) / args.steps * 1e3},
+                "roofline": roofline, "roofline_ntt": roofline_ntt,
+                "commit_algorithmic_gbs": commit_gbs, "commit_frac_of_hbm": commit_gbs / peak,
+                "phases_ms": {kk: (v / k if kk != "commits" else v) for kk, v in phases.items()},
+                "cpu_baseline": cpu_baseline}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-sample-log-rows", type=int, default=13,
+                    help="reference arm: rows of the bounded sample (log2); throughput is per input element")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -44,6 +44,20 @@ int nlc_synchronize(nlc_ctx* ctx);
 /* Number of kernels this library has launched on ctx since creation (bench.py's gpu_launches). */
 uint64_t nlc_launch_count(nlc_ctx* ctx);
 
+/* plonky2's `timing: &mut TimingTree` argument (prover.rs:91-93): per-phase device time of the commits
+ * issued since the last read, from CUDA events on the launching stream.  Phases follow upstream's scope
+ * names: "IFFT", "FFT + blinding" (+ "transpose LDEs", fused), "build Merkle tree" split into leaf hashing
+ * and the digest levels. */
+typedef struct {
+    double ifft_ms;
+    double lde_ms;
+    double leaf_hash_ms;
+    double merkle_levels_ms;
+    uint64_t commits;
+} nlc_timing;
+int nlc_timing_enable(nlc_ctx* ctx, int on);
+int nlc_timing_read(nlc_ctx* ctx, nlc_timing* out); /* synchronises the stream, then resets */
+
 /* ---- a1 / a2: PolynomialBatch::from_values / from_coeffs ----------------------------------- */
 /* Replaces plonky2::fri::oracle::PolynomialBatch::from_values(values, rate_bits, blinding=false,
  * cap_height, timing, None); call sites vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:91-93 and

@@ -24,6 +24,11 @@ class CChallenger(C.Structure):
                 ("output_buffer", C.c_uint64 * 8), ("output_len", C.c_uint32)]
 
 
+class CTiming(C.Structure):
+    _fields_ = [("ifft_ms", C.c_double), ("lde_ms", C.c_double), ("leaf_hash_ms", C.c_double),
+                ("merkle_levels_ms", C.c_double), ("commits", C.c_uint64)]
+
+
 class CFriParams(C.Structure):
     _fields_ = [("degree_bits", C.c_int), ("rate_bits", C.c_int), ("cap_height", C.c_int),
                 ("proof_of_work_bits", C.c_int), ("num_query_rounds", C.c_int), ("n_reduction_rounds", C.c_int),
@@ -44,6 +49,8 @@ SIGNATURES = {
     "nlc_set_stream": (C.c_int, [vp, vp]),
     "nlc_synchronize": (C.c_int, [vp]),
     "nlc_launch_count": (C.c_uint64, [vp]),
+    "nlc_timing_enable": (C.c_int, [vp, C.c_int]),
+    "nlc_timing_read": (C.c_int, [vp, C.POINTER(CTiming)]),
     "nlc_commit_from_values": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_coeffs": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_values_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),

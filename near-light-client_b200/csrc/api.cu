@@ -189,6 +189,34 @@ int nlc_synchronize(nlc_ctx* ctx) {
 }
 uint64_t nlc_launch_count(nlc_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
 
+int nlc_timing_enable(nlc_ctx* ctx, int on) {
+    if (!ctx) return 1;
+    CtxGuard g(ctx);
+    ctx->timing = on != 0;
+    return 0;
+}
+int nlc_timing_read(nlc_ctx* ctx, nlc_timing* out) {
+    if (!ctx || !out) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        sync(ctx);
+        memset(out, 0, sizeof *out);
+        for (auto& ev : ctx->timing_events) {
+            float ms = 0;
+            NLC_CUDA(cudaEventElapsedTime(&ms, ev.second.first, ev.second.second));
+            switch (ev.first) {
+                case 0: out->ifft_ms += ms; break;
+                case 1: out->lde_ms += ms; out->commits++; break;
+                case 2: out->leaf_hash_ms += ms; break;
+                default: out->merkle_levels_ms += ms; break;
+            }
+            cudaEventDestroy(ev.second.first);
+            cudaEventDestroy(ev.second.second);
+        }
+        ctx->timing_events.clear();
+    });
+}
+
 // ---- a1 / a2 ----
 int nlc_commit_from_values(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
                            int cap_height, nlc_batch** out) {

@@ -111,6 +111,7 @@ void batch_lde_and_tree(nlc_batch* b) {
     const size_t sw = ntt_scratch_words(b->W, log_n);
     if (sw) scratch = ctx->dmalloc(sw);
     const u64 w_N = gl::h_root_of_unity(log_n + r);
+    ctx->phase_begin(1);
     for (size_t k = 0; k < ((size_t)1 << r); k++) {
         NttJob job;
         job.src = b->coeffs;
@@ -128,6 +129,7 @@ void batch_lde_and_tree(nlc_batch* b) {
         job.scratch = scratch;
         ntt_run(ctx, job);
     }
+    ctx->phase_end();
     ctx->dfree(scratch);
     merkle_build(ctx, b->leaves, N, b->W, b->cap_height, b->digests, b->cap);
 }
@@ -149,7 +151,9 @@ void batch_ifft_values(nlc_batch* b, const u64* values_dev) {
     job.dst = b->coeffs;
     job.dst_stride = n;
     job.scratch = scratch;
+    ctx->phase_begin(0);
     ntt_run(ctx, job);
+    ctx->phase_end();
     ctx->dfree(scratch);
 }
 

@@ -51,6 +51,22 @@ struct nlc_ctx {
     size_t pinned_words = 0;
     int sm_count = 148;
     bool ntt_attrs = false; // cudaFuncSetAttribute is per device: remembered per context
+    // TimingTree-style phase timing (plonky2's "IFFT" / "FFT + blinding" / "build Merkle tree" scopes),
+    // measured with CUDA events on the launching stream when enabled
+    bool timing = false;
+    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> timing_events;
+    void phase_begin(int phase) {
+        if (!timing) return;
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, stream);
+        timing_events.push_back({phase, {a, b}});
+    }
+    void phase_end() {
+        if (!timing || timing_events.empty()) return;
+        cudaEventRecord(timing_events.back().second.second, stream);
+    }
 
     u64* dmalloc(size_t words) {
         void* p = nullptr;

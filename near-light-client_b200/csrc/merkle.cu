@@ -136,13 +136,17 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
     TreeGeom g;
     g.sub_height = h - cap_height;
     g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
+    ctx->phase_begin(2);
     NLC_LAUNCH(ctx, k_leaf_hash, (unsigned)((n_leaves + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0, leaves,
                n_leaves, leaf_len, g, digests, cap);
+    ctx->phase_end();
+    ctx->phase_begin(3);
     for (int layer = 0; layer < g.sub_height; layer++) {
         size_t parents = n_leaves >> (layer + 1);
         NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
                    digests, cap, g, layer, parents);
     }
+    ctx->phase_end();
 }
 
 void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,

@@ -68,6 +68,15 @@ class Context:
     def launch_count(self) -> int:
         return int(_ffi.lib().nlc_launch_count(self._h))
 
+    def timing_enable(self, on: bool = True):
+        self._check(_ffi.lib().nlc_timing_enable(self._h, int(on)))
+
+    def timing_read(self) -> dict:
+        t = _ffi.CTiming()
+        self._check(_ffi.lib().nlc_timing_read(self._h, C.byref(t)))
+        return {"IFFT": t.ifft_ms, "FFT + blinding": t.lde_ms, "leaf hashing": t.leaf_hash_ms,
+                "digest levels": t.merkle_levels_ms, "commits": int(t.commits)}
+
     def close(self):
         if self._h:
             _ffi.lib().nlc_destroy(self._h)

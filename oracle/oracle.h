@@ -25,7 +25,8 @@ extern "C" {
 void orc_poseidon_init(void);
 const uint64_t* orc_poseidon_round_constants(void); /* 360 */
 int orc_poseidon_selftest(void);
-void orc_poseidon_permute(uint64_t* state12);
+void orc_poseidon_permute(uint64_t* state12);       /* fast partial rounds (what plonky2 runs) */
+void orc_poseidon_permute_naive(uint64_t* state12); /* the definition: dense MDS every round */
 void orc_hash_no_pad(const uint64_t* in, size_t len, uint64_t* out4);
 void orc_two_to_one(const uint64_t* l4, const uint64_t* r4, uint64_t* out4);
 void orc_hash_or_noop(const uint64_t* in, size_t len, uint64_t* out4);

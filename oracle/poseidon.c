@@ -20,6 +20,7 @@
  * (tools/gen_poseidon_constants.py); tests compare the two.
  */
 #include "oracle.h"
+#include "poseidon_fast.h"
 #include <string.h>
 
 #define W 12
@@ -100,16 +101,27 @@ static inline gl_t sbox7(gl_t x) {
     return gl_mul(x3, x4);
 }
 static inline void mds_layer(gl_t* s) {
-    gl_t out[W];
-    for (int r = 0; r < W; r++) {
-        __uint128_t acc = 0; /* 12 * 2^64 * 41 + 8 * 2^64 < 2^74 */
-        for (int i = 0; i < W; i++) acc += (__uint128_t)s[(i + r) % W] * MDS_CIRC[i];
-        acc += (__uint128_t)s[r] * MDS_DIAG[r];
-        out[r] = gl_reduce128(acc);
+    /* the circulant entries are tiny, so (like upstream's mds_row_shf on 32-bit halves) the two 12-term dot
+     * products fit in plain u64: 12 * 2^32 * 41 < 2^42.  Doubled arrays avoid the index modulo; the loops
+     * vectorise. */
+    uint64_t lo[2 * W], hi[2 * W];
+    for (int i = 0; i < W; i++) {
+        lo[i] = lo[i + W] = s[i] & 0xFFFFFFFFULL;
+        hi[i] = hi[i + W] = s[i] >> 32;
     }
-    memcpy(s, out, sizeof out);
+    for (int r = 0; r < W; r++) {
+        uint64_t al = 0, ah = 0;
+        for (int i = 0; i < W; i++) {
+            al += lo[i + r] * MDS_CIRC[i];
+            ah += hi[i + r] * MDS_CIRC[i];
+        }
+        al += lo[r] * MDS_DIAG[r];
+        ah += hi[r] * MDS_DIAG[r];
+        s[r] = gl_reduce128((__uint128_t)al + ((__uint128_t)ah << 32));
+    }
 }
-void orc_poseidon_permute(uint64_t* s) {
+/* naive form: every round = constant layer, S-box layer, dense MDS (the definition; used as a cross-check) */
+void orc_poseidon_permute_naive(uint64_t* s) {
     if (!rc_ready) orc_poseidon_init();
     for (int i = 0; i < W; i++) s[i] = gl_canon(s[i]);
     int round = 0;
@@ -122,6 +134,51 @@ void orc_poseidon_permute(uint64_t* s) {
         s[0] = sbox7(s[0]);
         mds_layer(s);
     }
+    for (int r = 0; r < HALF_FULL; r++, round++) {
+        for (int i = 0; i < W; i++) s[i] = sbox7(gl_add(s[i], RC[round * W + i]));
+        mds_layer(s);
+    }
+}
+
+/* sum of up to 12 products of canonical elements: < 12 * 2^128, kept as (lo128, carry count) */
+static inline gl_t dot_reduce(const gl_t* a, const uint64_t* b, int n, __uint128_t init) {
+    __uint128_t acc = init;
+    uint64_t over = 0;
+    for (int i = 0; i < n; i++) {
+        __uint128_t t = (__uint128_t)a[i] * b[i];
+        acc += t;
+        over += acc < t;
+    }
+    /* 2^128 == -2^32 (mod p) since 2^96 == -1 */
+    gl_t r = gl_reduce128(acc);
+    return gl_sub(r, gl_reduce128((__uint128_t)over << 32));
+}
+
+/* poseidon.rs Poseidon::poseidon with the fast partial rounds (partial_first_constant_layer,
+ * mds_partial_layer_init, 22 x {sbox_monomial(state[0]) + constant, mds_partial_layer_fast}) -- what the
+ * reference CPU prover actually runs; constants in poseidon_fast.h (tools/gen_poseidon_fast.py). */
+void orc_poseidon_permute(uint64_t* s) {
+    if (!rc_ready) orc_poseidon_init();
+    for (int i = 0; i < W; i++) s[i] = gl_canon(s[i]);
+    int round = 0;
+    for (int r = 0; r < HALF_FULL; r++, round++) {
+        for (int i = 0; i < W; i++) s[i] = sbox7(gl_add(s[i], RC[round * W + i]));
+        mds_layer(s);
+    }
+    for (int i = 0; i < W; i++) s[i] = gl_add(s[i], PF_FIRST[i]);
+    {
+        gl_t t[W];
+        t[0] = s[0];
+        for (int r = 1; r < W; r++) t[r] = dot_reduce(s + 1, PF_INIT[r - 1], W - 1, 0);
+        memcpy(s, t, sizeof t);
+    }
+    for (int r = 0; r < N_PARTIAL; r++) {
+        gl_t s0 = gl_add(sbox7(s[0]), PF_POST[r]);
+        gl_t d = dot_reduce(s + 1, PF_W_HAT[r], W - 1, (__uint128_t)s0 * (MDS_CIRC[0] + MDS_DIAG[0]));
+        for (int i = 1; i < W; i++) s[i] = gl_add(s[i], gl_mul(s0, PF_VS[r][i - 1]));
+        s[0] = d;
+    }
+    round += N_PARTIAL;
     for (int r = 0; r < HALF_FULL; r++, round++) {
         for (int i = 0; i < W; i++) s[i] = sbox7(gl_add(s[i], RC[round * W + i]));
         mds_layer(s);
@@ -188,5 +245,16 @@ int orc_poseidon_selftest(void) {
     for (int i = 0; i < 12; i++) s[i] = GL_P - 1;
     orc_poseidon_permute(s);
     if (memcmp(s, kat_neg1, sizeof s)) return 5;
+    /* the definition (naive rounds) and the fast partial rounds must agree, on the KATs and on a pseudo-random walk */
+    uint64_t a[12], b[12];
+    for (int i = 0; i < 12; i++) a[i] = b[i] = GL_P - 1 - (uint64_t)i * 0x9E3779B97F4A7C15ULL % GL_P;
+    for (int it = 0; it < 64; it++) {
+        orc_poseidon_permute(a);
+        orc_poseidon_permute_naive(b);
+        if (memcmp(a, b, sizeof a)) return 6;
+    }
+    memset(s, 0, sizeof s);
+    orc_poseidon_permute_naive(s);
+    if (memcmp(s, kat_zero, sizeof s)) return 7;
     return 0;
 }
