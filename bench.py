@@ -166,8 +166,12 @@ def run_ours(args, rank, local_rank, world):
     P2, ffi = pkg.plonky2, pkg._ffi
     L = ffi.lib()
     ctx = P2.Context(local_rank)
-    stream = torch.cuda.current_stream()
-    ctx.set_stream(stream.cuda_stream)  # torch.cuda.Event only sees this stream: launch the library on it
+    # torch's default stream is the NULL stream, which the C ABI reads as "use your own stream": make a real
+    # stream current so that the library's kernels and torch.cuda.Event live on the same one
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    ctx.set_stream(stream.cuda_stream)
 
     log_n, W, r, cap = WORKLOADS[args.workload]
     n, N = 1 << log_n, 1 << (log_n + r)
