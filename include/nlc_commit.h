@@ -85,7 +85,8 @@ int nlc_batch_info(const nlc_batch* b, size_t* n_cols, int* log_n, int* rate_bit
 int nlc_batch_cap(nlc_batch* b, uint64_t* out);
 /* polynomials: column j written to out_cols[j] (n each), natural coefficient order (proof.rs:307-310). */
 int nlc_batch_coeffs(nlc_batch* b, uint64_t* const* out_cols);
-/* merkle_tree.leaves flattened: N x n_cols row-major, leaf k = LDE row bitrev_N(k). */
+/* merkle_tree.leaves flattened: N x n_cols row-major, leaf k = LDE row bitrev_N(k).  The device keeps the LDE
+ * column-major (the order the NTT produces); this call transposes it slab by slab on its way to the host. */
 int nlc_batch_leaves(nlc_batch* b, uint64_t* out);
 /* merkle_tree.digests: 2*(N - 2^cap_height) x 4 in plonky2's interleaved layout. */
 int nlc_batch_digests(nlc_batch* b, uint64_t* out);
@@ -94,8 +95,9 @@ int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step,
 /* merkle_tree.get(leaf_index) and merkle_tree.prove(leaf_index): row (n_cols) and siblings
  * ((log N - cap_height) x 4, bottom-up). Either output may be NULL. */
 int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t* siblings_out);
-/* Device views (valid until nlc_batch_free): for callers that keep consuming on the GPU. */
-const uint64_t* nlc_batch_leaves_dev(const nlc_batch* b);
+/* Device views (valid until nlc_batch_free): for callers that keep consuming on the GPU.
+ * lde: n_cols x N column-major, lde[j*N + k] = column j of leaf k (leaf k = LDE row bitrev_N(k)). */
+const uint64_t* nlc_batch_lde_dev(const nlc_batch* b);
 const uint64_t* nlc_batch_coeffs_dev(const nlc_batch* b);
 const uint64_t* nlc_batch_cap_dev(const nlc_batch* b);
 /* StarkOpeningSet::new's eval_commitment (proof.rs:307-310): every polynomial of the batch evaluated

@@ -65,7 +65,7 @@ SIGNATURES = {
     "nlc_batch_digests": (C.c_int, [vp, u64p]),
     "nlc_batch_lde_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, u64p]),
     "nlc_batch_open": (C.c_int, [vp, C.c_size_t, u64p, u64p]),
-    "nlc_batch_leaves_dev": (vp, [vp]),
+    "nlc_batch_lde_dev": (vp, [vp]),
     "nlc_batch_coeffs_dev": (vp, [vp]),
     "nlc_batch_cap_dev": (vp, [vp]),
     "nlc_batch_eval": (C.c_int, [vp, u64p, u64p]),

@@ -296,8 +296,19 @@ int nlc_batch_leaves(nlc_batch* b, uint64_t* out) {
     if (!b) return 1;
     return nlc_guarded(b->ctx, [&] {
         CtxGuard g(b->ctx);
-        d2h(b->ctx, out, b->leaves, (b->W << (b->log_n + b->rate_bits)) * sizeof(u64));
-        sync(b->ctx);
+        // the device keeps the LDE column-major; plonky2's row-major leaves are made on demand, a slab at a time
+        nlc_ctx* ctx = b->ctx;
+        const size_t N = (size_t)1 << (b->log_n + b->rate_bits);
+        size_t slab = ((size_t)8 << 20) / b->W; // ~64 MiB of rows
+        if (slab < 32) slab = 32;
+        if (slab > N) slab = N;
+        DevBuf rows(ctx, slab * b->W);
+        for (size_t r0 = 0; r0 < N; r0 += slab) {
+            const size_t nr = N - r0 < slab ? N - r0 : slab;
+            batch_leaf_rows(b, r0, nr, rows.p);
+            d2h(ctx, out + r0 * b->W, rows.p, nr * b->W * sizeof(u64));
+            sync(ctx); // the slab buffer is reused
+        }
     });
 }
 int nlc_batch_digests(nlc_batch* b, uint64_t* out) {
@@ -332,14 +343,14 @@ int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t*
         DevBuf idx_dev(ctx, 1), buf(ctx, b->W + sib);
         u64 idx = leaf_index;
         h2d(ctx, idx_dev.p, &idx, sizeof(u64));
-        merkle_open_many(ctx, b->leaves, b->digests, (size_t)1 << log_N, b->W, b->cap_height, idx_dev.p, 0, 1, buf.p,
+        merkle_open_many(ctx, b->lde, b->digests, (size_t)1 << log_N, b->W, (size_t)1 << log_N, b->cap_height, idx_dev.p, 0, 1, buf.p,
                          b->W + sib, 0);
         if (row_out) d2h(ctx, row_out, buf.p, b->W * sizeof(u64));
         if (siblings_out) d2h(ctx, siblings_out, buf.p + b->W, sib * sizeof(u64));
         sync(ctx);
     });
 }
-const uint64_t* nlc_batch_leaves_dev(const nlc_batch* b) { return b ? b->leaves : nullptr; }
+const uint64_t* nlc_batch_lde_dev(const nlc_batch* b) { return b ? b->lde : nullptr; }
 const uint64_t* nlc_batch_coeffs_dev(const nlc_batch* b) { return b ? b->coeffs : nullptr; }
 const uint64_t* nlc_batch_cap_dev(const nlc_batch* b) { return b ? b->cap : nullptr; }
 int nlc_batch_eval(nlc_batch* b, const uint64_t z[2], uint64_t* out) {
@@ -469,7 +480,7 @@ int nlc_merkle_new(nlc_ctx* ctx, const uint64_t* leaves, size_t n_leaves, size_t
             t->digests = ctx->dmalloc(8 * (n_leaves - ((size_t)1 << cap_height)));
             t->cap = ctx->dmalloc((size_t)4 << cap_height);
             h2d(ctx, t->leaves, leaves, n_leaves * leaf_len * sizeof(u64));
-            merkle_build(ctx, t->leaves, n_leaves, leaf_len, cap_height, t->digests, t->cap);
+            merkle_build(ctx, t->leaves, n_leaves, leaf_len, 0, cap_height, t->digests, t->cap);
             sync(ctx);
         } catch (...) {
             ctx->dfree(t->leaves);
@@ -507,7 +518,7 @@ int nlc_tree_open(nlc_tree* t, size_t leaf_index, uint64_t* leaf_out, uint64_t* 
         DevBuf idx_dev(ctx, 1), buf(ctx, t->leaf_len + sib);
         u64 idx = leaf_index;
         h2d(ctx, idx_dev.p, &idx, sizeof(u64));
-        merkle_open_many(ctx, t->leaves, t->digests, t->n_leaves, t->leaf_len, t->cap_height, idx_dev.p, 0, 1, buf.p,
+        merkle_open_many(ctx, t->leaves, t->digests, t->n_leaves, t->leaf_len, 0, t->cap_height, idx_dev.p, 0, 1, buf.p,
                          t->leaf_len + sib, 0);
         if (leaf_out) d2h(ctx, leaf_out, buf.p, t->leaf_len * sizeof(u64));
         if (siblings_out) d2h(ctx, siblings_out, buf.p + t->leaf_len, sib * sizeof(u64));

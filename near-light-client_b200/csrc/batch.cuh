@@ -8,7 +8,7 @@ struct nlc_batch {
     size_t W = 0;
     int log_n = 0, rate_bits = 0, cap_height = 0;
     u64* coeffs = nullptr;  // W x n, column-major
-    u64* leaves = nullptr;  // N x W, row-major, index-bit-reversed rows
+    u64* lde = nullptr;     // W x N, column-major: lde[j*N + k] = column j of leaf k (leaf k = LDE point bitrev_N(k))
     u64* digests = nullptr; // plonky2 interleaved layout
     u64* cap = nullptr;     // 2^cap x 4
     size_t n_digest_words = 0;
@@ -33,6 +33,8 @@ void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_
                           u64* out_dev);
 void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev);
 void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
+// rows [row0, row0+n_rows) of the leaf matrix, row-major, into out_dev (n_rows x W): plonky2's merkle_tree.leaves
+void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);
 
 // ---- fri.cu ----
 void challenger_observe_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, const u64* elems_dev, size_t n);

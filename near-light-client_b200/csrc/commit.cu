@@ -8,11 +8,14 @@
 //
 // Data layout in HBM (one nlc_batch):
 //   coeffs  : W x n   column-major (polynomial j contiguous), natural coefficient order
-//   leaves  : N x W   row-major, leaf k = LDE row bitrev_N(k)      (N = n << rate_bits)
+//   lde     : W x N   column-major, lde[j*N + k] = column j of leaf k, leaf k = LDE row bitrev_N(k)  (N = n << rate_bits)
+//             -- the order a decimation-in-frequency NTT produces by itself, so the LDE is never transposed or
+//             bit-reversed in HBM; the leaf hash reads it with coalesced column loads, and plonky2's row-major
+//             `leaves` are produced only when the host asks for them (batch_leaf_rows)
 //   digests : 2*(N - 2^cap) x 4 in plonky2's interleaved layout;  cap : 2^cap x 4
 // The LDE is computed coset by coset: LDE point i = m*2^r + k lies on the coset 7*w_N^k*<w_n>, and
 // after the index bit reversal coset k is the contiguous leaf range [bitrev_r(k)*n, +n).  So each
-// coset is one size-n NTT of coeff_j*(7 w_N^k)^j written straight into its row range: no zero
+// coset is one size-n NTT of coeff_j*(7 w_N^k)^j written straight into that range of every column: no zero
 // padding, no size-N transform, no transpose or bit-reversal pass.
 #include "batch.cuh"
 
@@ -33,13 +36,29 @@ __global__ void k_transpose_cols(const u64* __restrict__ rows, size_t width, siz
     }
 }
 
-// out[i*W + j] = leaves[bitrev_N(idx[i]*step)*W + j]
-__global__ void k_gather_lde_rows(const u64* __restrict__ leaves, size_t W, int log_N, const u64* __restrict__ idx,
+// out[i*W + j] = lde[j*N + bitrev_N(idx[i]*step)]
+__global__ void k_gather_lde_rows(const u64* __restrict__ lde, size_t W, int log_N, const u64* __restrict__ idx,
                                   size_t step, u64* __restrict__ out) {
     const size_t i = blockIdx.x;
     const u64 pt = (idx[i] * step) & (((u64)1 << log_N) - 1);
     const u64 row = log_N ? (__brevll(pt) >> (64 - log_N)) : 0;
-    for (size_t j = threadIdx.x; j < W; j += blockDim.x) out[i * W + j] = leaves[row * W + j];
+    for (size_t j = threadIdx.x; j < W; j += blockDim.x) out[i * W + j] = lde[(j << log_N) + row];
+}
+
+// out[(r - row0)*W + j] = lde[j*N + r], 32x32 tiles through shared memory (both sides coalesced)
+__global__ void k_leaf_rows(const u64* __restrict__ lde, size_t W, size_t N, size_t row0, size_t n_rows,
+                            u64* __restrict__ out) {
+    __shared__ u64 tile[32][33];
+    const size_t r0 = (size_t)blockIdx.x * 32, c0 = (size_t)blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t c = c0 + i, r = r0 + threadIdx.x;
+        if (r < n_rows && c < W) tile[i][threadIdx.x] = lde[c * N + row0 + r];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t r = r0 + i, c = c0 + threadIdx.x;
+        if (r < n_rows && c < W) out[r * W + c] = tile[threadIdx.x][i];
+    }
 }
 
 // One block per polynomial: sum_j c_j z^j over F_{p^2}.
@@ -81,7 +100,7 @@ nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap
     const size_t n = (size_t)1 << log_n, N = n << rate_bits;
     try {
         b->coeffs = ctx->dmalloc(W * n);
-        b->leaves = ctx->dmalloc(W * N);
+        b->lde = ctx->dmalloc(W * N);
         b->n_digest_words = 8 * (N - ((size_t)1 << cap_height));
         b->digests = ctx->dmalloc(b->n_digest_words);
         b->cap = ctx->dmalloc((size_t)4 << cap_height);
@@ -96,7 +115,7 @@ void batch_release(nlc_batch* b) {
     if (!b) return;
     nlc_ctx* ctx = b->ctx;
     ctx->dfree(b->coeffs);
-    ctx->dfree(b->leaves);
+    ctx->dfree(b->lde);
     ctx->dfree(b->digests);
     ctx->dfree(b->cap);
     delete b;
@@ -119,9 +138,9 @@ void batch_lde_and_tree(nlc_batch* b) {
         job.n_cols = b->W;
         job.log_n = log_n;
         job.pre_shift = gl::h_mul(gl::GENERATOR, gl::h_pow(w_N, k));
-        job.rows = true;
-        job.dst = b->leaves;
-        job.row_width = b->W;
+        job.cols = true;
+        job.dst = b->lde;
+        job.dst_stride = N;
         size_t kr = 0; // bitrev_r(k)
         for (int t = 0; t < r; t++) kr |= ((k >> t) & 1) << (r - 1 - t);
         job.row_base = kr * n;
@@ -131,7 +150,7 @@ void batch_lde_and_tree(nlc_batch* b) {
     }
     ctx->phase_end();
     ctx->dfree(scratch);
-    merkle_build(ctx, b->leaves, N, b->W, b->cap_height, b->digests, b->cap);
+    merkle_build(ctx, b->lde, N, b->W, N, b->cap_height, b->digests, b->cap);
 }
 
 // "IFFT" of from_values: values (W x n column-major, device) -> b->coeffs.
@@ -165,11 +184,18 @@ void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_
 
 void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev) {
     if (!m) return;
-    NLC_LAUNCH(b->ctx, k_gather_lde_rows, (unsigned)m, 128, 0, b->leaves, b->W, b->log_n + b->rate_bits, idx_dev, step,
+    NLC_LAUNCH(b->ctx, k_gather_lde_rows, (unsigned)m, 128, 0, b->lde, b->W, b->log_n + b->rate_bits, idx_dev, step,
                out_dev);
 }
 
 void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev) {
     gl::Ext2 ze = {gl::canon(z[0]), gl::canon(z[1])};
     NLC_LAUNCH(b->ctx, k_eval_ext, (unsigned)b->W, 256, 0, b->coeffs, (size_t)1 << b->log_n, ze, out_dev);
+}
+
+void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev) {
+    if (!n_rows) return;
+    const size_t N = (size_t)1 << (b->log_n + b->rate_bits);
+    dim3 grid((unsigned)((n_rows + 31) / 32), (unsigned)((b->W + 31) / 32));
+    NLC_LAUNCH(b->ctx, k_leaf_rows, grid, dim3(32, 8), 0, b->lde, b->W, N, row0, n_rows, out_dev);
 }

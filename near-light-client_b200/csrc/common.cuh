@@ -133,7 +133,8 @@ static inline int ilog2(size_t n) {
 // ---- ntt.cu ----
 // forward/inverse NTT of `n_cols` columns of 2^log_n elements (column j at src + j*src_stride).
 // ROWS: out is a row-major (rows x row_width) matrix; row = row_base + bitrev order position, column
-//       offset col0.  NATURAL: out is column-contiguous, natural order.
+//       offset col0.  COLS: the same matrix stored column-major (column stride dst_stride).
+//       NATURAL: out is column-contiguous, natural order.
 struct NttJob {
     const u64* src = nullptr;
     size_t src_stride = 0;
@@ -143,24 +144,27 @@ struct NttJob {
     u64 pre_shift = 1;         // multiply input j by pre_shift^j (coset_fft)
     u64 post_shift = 1;        // NATURAL only: multiply output k by post_shift^k (coset_ifft)
     bool rows = false;
+    bool cols = false;         // COLS: column-major out, index-bit-reversed order, column stride dst_stride
     u64* dst = nullptr;
-    size_t dst_stride = 0;     // NATURAL: column stride
+    size_t dst_stride = 0;     // NATURAL / COLS: column stride
     size_t row_width = 0;      // ROWS: elements per row
-    size_t row_base = 0;       // ROWS: first row
-    size_t col0 = 0;           // ROWS: first column inside a row
+    size_t row_base = 0;       // ROWS / COLS: first row (bit-reversed position)
+    size_t col0 = 0;           // ROWS / COLS: first column
     u64* scratch = nullptr;    // n_cols * 2^log_n words, needed when log_n > one digit
 };
 void ntt_run(nlc_ctx* ctx, const NttJob& job);
 size_t ntt_scratch_words(size_t n_cols, int log_n);
 
 // ---- merkle.cu ----
-// Build MerkleTree::new over device-resident row-major leaves; digests in plonky2's interleaved layout.
-void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, int cap_height, u64* digests,
-                  u64* cap);
+// Build MerkleTree::new over device-resident leaves; digests in plonky2's interleaved layout.
+// elem_stride == 0: row-major leaves (leaf k at leaves + k*leaf_len); elem_stride > 0: column-major
+// (element j of leaf k at leaves[j*elem_stride + k]), the layout of a PolynomialBatch's LDE.
+void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
+                  u64* digests, u64* cap);
 // device copy of leaf + siblings for many leaf indices (indices in device memory)
 void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
-                      int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out, size_t out_stride,
-                      size_t out_offset);
+                      size_t elem_stride, int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out,
+                      size_t out_stride, size_t out_offset);
 void poseidon_permute_many(nlc_ctx* ctx, u64* states_dev, size_t count);
 void hash_many(nlc_ctx* ctx, const u64* in_dev, size_t count, size_t len, bool or_noop, u64* out_dev);
 void two_to_one_many(nlc_ctx* ctx, const u64* l_dev, const u64* r_dev, size_t count, u64* out_dev);

@@ -384,7 +384,7 @@ void fri_commit_round(nlc_fri_state* s) {
     t.cap = s->proof + (size_t)s->round * ((size_t)4 << t.cap_height);
     s->trees.push_back(t);
     fri_values_to_leaves(s, t.leaves);
-    merkle_build(ctx, t.leaves, t.n_leaves, t.leaf_len, t.cap_height, t.digests, t.cap);
+    merkle_build(ctx, t.leaves, t.n_leaves, t.leaf_len, 0, t.cap_height, t.digests, t.cap);
     s->round++;
 }
 
@@ -419,7 +419,7 @@ void fri_queries(nlc_fri_state* s, size_t nq) {
     u64* out = s->proof + s->query_off;
     size_t off = 0;
     for (nlc_batch* b : s->oracles) {
-        merkle_open_many(ctx, b->leaves, b->digests, s->N, b->W, b->cap_height, s->xidx_dev(), 0, nq, out,
+        merkle_open_many(ctx, b->lde, b->digests, s->N, b->W, s->N, b->cap_height, s->xidx_dev(), 0, nq, out,
                          s->query_words, off);
         off += b->W + (size_t)4 * (s->log_N - b->cap_height);
     }
@@ -428,7 +428,7 @@ void fri_queries(nlc_fri_state* s, size_t nq) {
         const int ab = s->p.reduction_arity_bits[r];
         sh += ab;
         const nlc_tree& t = s->trees[r];
-        merkle_open_many(ctx, t.leaves, t.digests, t.n_leaves, t.leaf_len, t.cap_height, s->xidx_dev(), sh, nq, out,
+        merkle_open_many(ctx, t.leaves, t.digests, t.n_leaves, t.leaf_len, 0, t.cap_height, s->xidx_dev(), sh, nq, out,
                          s->query_words, off);
         off += t.leaf_len + (size_t)4 * (lg - ab - t.cap_height);
         lg -= ab;

@@ -45,55 +45,21 @@ __host__ __device__ __forceinline__ uint64_t reduce128_nc(uint64_t lo, uint64_t 
     return r;
 }
 
-// 64x64 -> 128 bit product as four 32-bit limbs p0..p3 (little endian): one IMAD/IMAD.HI pair and
-// three IMAD.WIDE.U32 with the carries riding the wide accumulators.
-__device__ __forceinline__ void mul_wide(uint64_t a, uint64_t b, uint32_t& p0, uint32_t& p1, uint32_t& p2,
-                                         uint32_t& p3) {
-    const uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
-    asm("{\n\t"
-        "mul.lo.u32 %0,%4,%6;\n\t"
-        "mul.hi.u32 %1,%4,%6;\n\t"
-        "mad.lo.cc.u32 %1,%4,%7,%1;\n\t"
-        "madc.hi.u32 %2,%4,%7,0;\n\t"
-        "mad.lo.cc.u32 %1,%5,%6,%1;\n\t"
-        "madc.hi.cc.u32 %2,%5,%6,%2;\n\t"
-        "addc.u32 %3,0,0;\n\t"
-        "mad.lo.cc.u32 %2,%5,%7,%2;\n\t"
-        "madc.hi.u32 %3,%5,%7,%3;\n\t"
-        "}"
-        : "=&r"(p0), "=&r"(p1), "=&r"(p2), "=&r"(p3)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+// (lo + 2^64 hi) mod p, any representative, for the device: with hi = 2^32 p3 + p2,
+// V = lo + (p2 << 32) - p2 - p3 lies in (-2^33, 2^65); it is formed in 128-bit arithmetic (IADD3/IADD3.X
+// chains, no multiplier), and its signed top word tw in {-1,0,1} weighs 2^64 == eps: one more 64-bit add
+// that cannot wrap (after a carry the low 64 bits are < 2^64 - 2^33, after a borrow they are > 2^64 - 2^33).
+__device__ __forceinline__ uint64_t reduce128_dev_nc(uint64_t lo, uint64_t hi) {
+    const uint32_t p2 = (uint32_t)hi, p3 = (uint32_t)(hi >> 32);
+    const __int128 V = (__int128)lo + ((__int128)(uint64_t)p2 << 32) - (__int128)(uint64_t)p2 - (__int128)(uint64_t)p3;
+    const int tw = (int)(V >> 64);
+    const uint64_t adj = ((uint64_t)(uint32_t)(tw >> 31) << 32) | (uint32_t)(-tw); // tw * eps mod 2^64
+    return (uint64_t)V + adj;
 }
-
-// (p0 + 2^32 p1 + 2^64 p2 + 2^96 p3) mod p, any representative:  (p1:p0) + p2*eps - p3 is accumulated in
-// three words with a signed top word tw in {-1,0,1}; tw*2^64 == tw*eps is folded back with one 64-bit add
-// (it cannot wrap twice: see DESIGN.md "field arithmetic").
-__device__ __forceinline__ uint64_t reduce_limbs_nc(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3) {
-    uint32_t r0, r1;
-    asm("{\n\t"
-        ".reg .u32 t0,t1,tw,u0,u1,m,s;\n\t"
-        "mul.lo.u32 u0,%4,0xffffffff;\n\t"
-        "mul.hi.u32 u1,%4,0xffffffff;\n\t"
-        "add.cc.u32 t0,%2,u0;\n\t"
-        "addc.cc.u32 t1,%3,u1;\n\t"
-        "addc.u32 tw,0,0;\n\t"
-        "sub.cc.u32 t0,t0,%5;\n\t"
-        "subc.cc.u32 t1,t1,0;\n\t"
-        "subc.u32 tw,tw,0;\n\t"
-        "sub.u32 m,0,tw;\n\t"
-        "shr.s32 s,tw,31;\n\t"
-        "add.cc.u32 %0,t0,m;\n\t"
-        "addc.u32 %1,t1,s;\n\t"
-        "}"
-        : "=r"(r0), "=r"(r1)
-        : "r"(p0), "r"(p1), "r"(p2), "r"(p3));
-    return ((uint64_t)r1 << 32) | r0;
-}
-
+// four IMAD.WIDE.U32 (the multiplier issues one per 4 clocks per sub-partition: they bound the S-box)
 __device__ __forceinline__ uint64_t mul_nc(uint64_t a, uint64_t b) {
-    uint32_t p0, p1, p2, p3;
-    mul_wide(a, b, p0, p1, p2, p3);
-    return reduce_limbs_nc(p0, p1, p2, p3);
+    const unsigned __int128 p = (unsigned __int128)a * b;
+    return reduce128_dev_nc((uint64_t)p, (uint64_t)(p >> 64));
 }
 __device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return canon(mul_nc(a, b)); }
 __device__ __forceinline__ uint64_t sqr_nc(uint64_t a) { return mul_nc(a, a); }

@@ -11,6 +11,7 @@
 //   2*((q << (i+1)) + (1<<i) - 1) + {0,1};  the subtree root goes to cap[s].
 #include "common.cuh"
 #include "poseidon.cuh"
+#include "transcript.cuh"
 
 namespace {
 
@@ -32,37 +33,49 @@ __device__ __forceinline__ u64* node_slot(u64* digests, u64* cap, TreeGeom g, in
     return digests + (s * g.sub_digests + idx) * 4;
 }
 
-// hash_or_noop of each leaf row (one thread per leaf), written to its layer-0 slot.
+// hash_or_noop of each leaf (one thread per leaf), written to its layer-0 slot.  Element j of leaf k is
+// leaves[k * leaf_stride + j * elem_stride]:
+//   COLS  (leaf_stride 1, elem_stride N): the column-major LDE of a PolynomialBatch, exactly as the NTT left it --
+//         the 8 loads of a sponge block are 8 fully coalesced 256-byte warp requests, nothing is transposed;
+//   !COLS (leaf_stride leaf_len, elem_stride 1): row-major leaves (FRI round trees, nlc_merkle_new).
+// Leaves are dealt to warps round-robin (grid-stride) so that a grid of a few warps per SM sub-partition
+// keeps every multiplier busy without a ragged last wave.
+template <bool COLS>
 __global__ void __launch_bounds__(HASH_THREADS)
-k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, TreeGeom g, u64* digests, u64* cap) {
-    const size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x;
-    if (row >= n_leaves) return;
-    const u64* in = leaves + row * leaf_len;
-    u64 s[poseidon::WIDTH];
+k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, size_t leaf_stride, size_t elem_stride,
+            TreeGeom g, u64* digests, u64* cap) {
+    const size_t step = (size_t)gridDim.x * HASH_THREADS;
+    for (size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x; row < n_leaves; row += step) {
+        const u64* in = leaves + row * (COLS ? 1 : leaf_stride);
+        const size_t es = COLS ? elem_stride : 1;
+        u64 s[poseidon::WIDTH];
 #pragma unroll
-    for (int i = 0; i < poseidon::WIDTH; i++) s[i] = 0;
-    if (leaf_len <= 4) { // hash_or_noop: short rows are copied, zero padded
-        for (size_t i = 0; i < leaf_len; i++) s[i] = gl::canon(in[i]);
-    } else {
-        size_t off = 0;
-        for (; off + poseidon::RATE <= leaf_len; off += poseidon::RATE) {
+        for (int i = 0; i < poseidon::WIDTH; i++) s[i] = 0;
+        if (leaf_len <= 4) { // hash_or_noop: short rows are copied, zero padded
 #pragma unroll
-            for (int i = 0; i < poseidon::RATE; i++) s[i] = in[off + i]; // overwrite mode
-            poseidon::permute_nc(s);
+            for (int i = 0; i < 4; i++)
+                if ((size_t)i < leaf_len) s[i] = gl::canon(in[i * es]);
+        } else {
+            size_t off = 0;
+            for (; off + poseidon::RATE <= leaf_len; off += poseidon::RATE) {
+#pragma unroll
+                for (int i = 0; i < poseidon::RATE; i++) s[i] = in[(off + i) * es]; // overwrite mode
+                poseidon::permute_nc(s);
+            }
+            if (off < leaf_len) {
+                const int rem = (int)(leaf_len - off);
+#pragma unroll
+                for (int i = 0; i < poseidon::RATE; i++)
+                    if (i < rem) s[i] = in[(off + i) * es];
+                poseidon::permute_nc(s);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) s[i] = gl::canon(s[i]);
         }
-        if (off < leaf_len) {
-            const int rem = (int)(leaf_len - off);
-#pragma unroll
-            for (int i = 0; i < poseidon::RATE; i++)
-                if (i < rem) s[i] = in[off + i];
-            poseidon::permute_nc(s);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; i++) s[i] = gl::canon(s[i]);
+        u64* out = node_slot(digests, cap, g, 0, row);
+        reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(s[0], s[1]);
+        reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(s[2], s[3]);
     }
-    u64* out = node_slot(digests, cap, g, 0, row);
-    reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(s[0], s[1]);
-    reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(s[2], s[3]);
 }
 
 // layer (i) -> layer (i+1): one thread per parent.
@@ -82,16 +95,43 @@ k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) 
     reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(o[2], o[3]);
 }
 
+// The top of every cap subtree, layers [layer0, sub_height): one CTA per subtree, one permutation per
+// half-warp (transcript::warp_permute), __syncthreads between layers.  Up there a layer has fewer nodes
+// than the GPU has sub-partitions, so the latency of one permutation is all that matters: the 12-lane
+// form is ~8x shorter than the one-thread form, and the layers cost no launches.
+constexpr int TOP_THREADS = 512;
+__global__ void __launch_bounds__(TOP_THREADS) k_merkle_top(u64* digests, u64* cap, TreeGeom g, int layer0) {
+    const int lane = threadIdx.x & 31, l16 = lane & 15;
+    const size_t group = (threadIdx.x >> 4), n_groups = TOP_THREADS / 16;
+    const size_t sub = blockIdx.x;
+    for (int layer = layer0; layer < g.sub_height; layer++) {
+        const size_t per_sub = (size_t)1 << (g.sub_height - layer - 1); // parents of this layer in one subtree
+        const size_t passes = (per_sub + n_groups - 1) / n_groups;
+        for (size_t pass = 0; pass < passes; pass++) {
+            const size_t jl = pass * n_groups + group;
+            const bool active = jl < per_sub;
+            const size_t j = sub * per_sub + (active ? jl : 0);
+            const u64* kids = node_slot(digests, cap, g, layer, 2 * j);
+            u64 x = 0;
+            if (active && l16 < 8) x = kids[l16];
+            x = transcript::warp_permute(x, lane);
+            if (active && l16 < 4) node_slot(digests, cap, g, layer + 1, j)[l16] = x;
+        }
+        __syncthreads();
+    }
+}
+
 // MerkleTree::get + MerkleTree::prove for many indices: out[i*stride + offset ..] = leaf row, siblings.
 __global__ void k_open_many(const u64* __restrict__ leaves, const u64* __restrict__ digests, size_t leaf_len,
-                            TreeGeom g, const u64* __restrict__ idx, int shift_right, u64 idx_mask, size_t n_idx,
-                            u64* out, size_t out_stride, size_t out_offset) {
+                            size_t leaf_stride, size_t elem_stride, TreeGeom g, const u64* __restrict__ idx,
+                            int shift_right, u64 idx_mask, size_t n_idx, u64* out, size_t out_stride,
+                            size_t out_offset) {
     const size_t qi = blockIdx.x;
     if (qi >= n_idx) return;
     const size_t leaf = (size_t)((idx[qi] & idx_mask) >> shift_right);
     u64* o = out + qi * out_stride + out_offset;
-    const u64* row = leaves + leaf * leaf_len;
-    for (size_t i = threadIdx.x; i < leaf_len; i += blockDim.x) o[i] = gl::canon(row[i]);
+    const u64* row = leaves + leaf * leaf_stride;
+    for (size_t i = threadIdx.x; i < leaf_len; i += blockDim.x) o[i] = gl::canon(row[i * elem_stride]);
     o += leaf_len;
     const size_t s = leaf >> g.sub_height;
     size_t pair_index = leaf & (((size_t)1 << g.sub_height) - 1);
@@ -127,8 +167,25 @@ __global__ void k_two_to_one_many(const u64* l, const u64* r, size_t count, u64*
 
 } // namespace
 
-void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, int cap_height, u64* digests,
-                  u64* cap) {
+// Leaves are dealt grid-stride to c CTAs per SM, c in 4..8 (8 x 128 threads x 64 registers fill the register
+// file).  More resident warps hide latency a little better (measured: 4 -> 8 CTAs/SM is +5%), but the work
+// per thread is ceil(n / threads): pick the c with the best product of the two.
+static unsigned leaf_grid(nlc_ctx* ctx, size_t n_leaves) {
+    const size_t want = (n_leaves + HASH_THREADS - 1) / HASH_THREADS;
+    if (want <= (size_t)ctx->sm_count * 8) return (unsigned)want;
+    static const double occ[9] = {0, 0, 0, 0, 0.95, 0.97, 0.98, 0.99, 1.0};
+    int best = 8;
+    double best_eff = 0;
+    for (int c = 4; c <= 8; c++) {
+        const double threads = (double)ctx->sm_count * c * HASH_THREADS, per = (double)n_leaves / threads;
+        const double eff = per / (double)(size_t)(per + 0.999999) * occ[c];
+        if (eff > best_eff) best_eff = eff, best = c;
+    }
+    return (unsigned)((size_t)ctx->sm_count * best);
+}
+
+void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
+                  u64* digests, u64* cap) {
     const int h = ilog2(n_leaves);
     NLC_CHECK(((size_t)1 << h) == n_leaves, "MerkleTree::new: number of leaves must be a power of two");
     NLC_CHECK(cap_height >= 0 && cap_height <= h,
@@ -137,29 +194,38 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
     g.sub_height = h - cap_height;
     g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
     ctx->phase_begin(2);
-    NLC_LAUNCH(ctx, k_leaf_hash, (unsigned)((n_leaves + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0, leaves,
-               n_leaves, leaf_len, g, digests, cap);
+    if (elem_stride)
+        NLC_LAUNCH(ctx, k_leaf_hash<true>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
+                   (size_t)1, elem_stride, g, digests, cap);
+    else
+        NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
+                   leaf_len, (size_t)1, g, digests, cap);
     ctx->phase_end();
     ctx->phase_begin(3);
-    for (int layer = 0; layer < g.sub_height; layer++) {
+    int layer = 0;
+    // wide layers: one thread per parent; once a subtree has at most 256 parents left, its top runs in one CTA
+    for (; layer < g.sub_height && ((size_t)1 << (g.sub_height - layer - 1)) > 256; layer++) {
         size_t parents = n_leaves >> (layer + 1);
         NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
                    digests, cap, g, layer, parents);
     }
+    if (layer < g.sub_height)
+        NLC_LAUNCH(ctx, k_merkle_top, (unsigned)((size_t)1 << cap_height), TOP_THREADS, 0, digests, cap, g, layer);
     ctx->phase_end();
 }
 
 void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
-                      int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out, size_t out_stride,
-                      size_t out_offset) {
+                      size_t elem_stride, int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out,
+                      size_t out_stride, size_t out_offset) {
     if (n_idx == 0) return;
     TreeGeom g;
     g.sub_height = ilog2(n_leaves) - cap_height;
     g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
     // idx values are x_index of the ORIGINAL domain already reduced mod N by the caller; the leaf of
     // this tree is x_index >> shift_right (fri_prover_query_round).
-    NLC_LAUNCH(ctx, k_open_many, (unsigned)n_idx, 128, 0, leaves, digests, leaf_len, g, idx_dev, shift_right,
-               ~(u64)0, n_idx, out, out_stride, out_offset);
+    NLC_LAUNCH(ctx, k_open_many, (unsigned)n_idx, 128, 0, leaves, digests, leaf_len, elem_stride ? (size_t)1 : leaf_len,
+               elem_stride ? elem_stride : (size_t)1, g, idx_dev, shift_right, ~(u64)0, n_idx, out, out_stride,
+               out_offset);
 }
 
 void poseidon_permute_many(nlc_ctx* ctx, u64* states_dev, size_t count) {
@@ -175,8 +241,8 @@ void hash_many(nlc_ctx* ctx, const u64* in_dev, size_t count, size_t len, bool o
     g.sub_height = 0;
     g.sub_digests = 0;
     if (or_noop || len > 4) {
-        NLC_LAUNCH(ctx, k_leaf_hash, (unsigned)((count + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0, in_dev,
-                   count, len, g, (u64*)nullptr, out_dev);
+        NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, count), HASH_THREADS, 0, in_dev, count, len, len, (size_t)1, g,
+                   (u64*)nullptr, out_dev);
     } else {
         // short hash_no_pad: pad into full states, permute, take 4 lanes
         u64* st = ctx->dmalloc(count * 12);

@@ -82,7 +82,8 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
 }
 
 // Last digit on contiguous data.  smem: [G][2^S + 1].
-template <bool ROWS>
+enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2 };
+template <int MODE>
 __global__ void __launch_bounds__(NTT_THREADS)
 k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_G, size_t n_cols,
          const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale, const u64* __restrict__ roots,
@@ -96,7 +97,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
     for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 g = idx >> S, e = idx & (len - 1);
         u64 v = 0;
-        if (ROWS) {
+        if (MODE != OUT_NATURAL) {
             size_t col = (size_t)blockIdx.y * G + g;
             size_t i = ((size_t)blockIdx.x << S) + e;
             if (col < n_cols) {
@@ -125,11 +126,22 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
         }
         __syncthreads();
     }
+    if (MODE == OUT_COLS) { // column-major, index-bit-reversed: position q of this block is contiguous in its column
+        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+            u32 g = idx >> S, q = idx & (len - 1);
+            size_t col = (size_t)blockIdx.y * G + g;
+            if (col >= n_cols) continue;
+            u64 v = sm[g * pitch + q];
+            if (scale != 1) v = gl::mul(v, scale);
+            dst[(col0 + col) * dst_stride + row_base + ((size_t)blockIdx.x << S) + q] = v;
+        }
+        return;
+    }
     for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 g = idx & (G - 1), q = idx >> log_G;
         u64 v = sm[g * pitch + q];
         if (scale != 1) v = gl::mul(v, scale);
-        if (ROWS) {
+        if (MODE == OUT_ROWS) {
             size_t col = (size_t)blockIdx.y * G + g;
             if (col < n_cols) {
                 size_t row = row_base + ((size_t)blockIdx.x << S) + q;
@@ -194,8 +206,9 @@ void ensure_attrs(nlc_ctx* ctx) {
     if (ctx->ntt_attrs) return;
     const int big = 160 * 1024;
     NLC_CUDA(cudaFuncSetAttribute(k_ntt_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_NATURAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_COLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ctx->ntt_attrs = true;
 }
 
@@ -220,7 +233,7 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
     const u64* pre = nullptr;
     if (gl::canon(job.pre_shift) != 1) pre = pw_table(ctx, log_n, gl::canon(job.pre_shift), 1);
     const u64* post = nullptr;
-    if (!job.rows && gl::canon(job.post_shift) != 1) { // fold 1/n into the post table
+    if (!job.rows && !job.cols && gl::canon(job.post_shift) != 1) { // fold 1/n into the post table
         post = pw_table(ctx, log_n, gl::canon(job.post_shift), scale);
         scale = 1;
     }
@@ -246,21 +259,28 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
     const int S = digits[d - 1];
     const u64* roots = roots_table(ctx, S, inv);
     const u64* lo_pre = d == 1 ? pre : nullptr;
-    if (job.rows) {
+    if (job.rows || job.cols) {
         int log_G = S >= 9 ? 3 : 4;
+        if (job.cols) log_G = 0; // a column is contiguous: no need to gang columns for coalescing
         while (log_G > 0 && ((size_t)1 << (log_G - 1)) >= job.n_cols) log_G--;
         const size_t G = (size_t)1 << log_G;
         dim3 grid((unsigned)(n >> S), (unsigned)((job.n_cols + G - 1) / G));
         size_t smem = G * (((size_t)1 << S) + 1) * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_lo<true>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols, lo_pre,
-                   (const u64*)nullptr, scale, roots, job.dst, (size_t)0, job.row_width, job.row_base, job.col0);
+        if (job.cols)
+            NLC_LAUNCH(ctx, k_ntt_lo<OUT_COLS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols,
+                       lo_pre, (const u64*)nullptr, scale, roots, job.dst, job.dst_stride, (size_t)0, job.row_base,
+                       job.col0);
+        else
+            NLC_LAUNCH(ctx, k_ntt_lo<OUT_ROWS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols,
+                       lo_pre, (const u64*)nullptr, scale, roots, job.dst, (size_t)0, job.row_width, job.row_base,
+                       job.col0);
     } else {
         NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
         int log_G = S >= 10 ? 3 : 4;
         if (log_G > log_n - S) log_G = log_n - S;
         dim3 grid((unsigned)((n >> S) >> log_G), (unsigned)job.n_cols);
         size_t smem = ((size_t)1 << log_G) * (((size_t)1 << S) + 1) * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_lo<false>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols, lo_pre,
+        NLC_LAUNCH(ctx, k_ntt_lo<OUT_NATURAL>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols, lo_pre,
                    post, scale, roots, job.dst, job.dst_stride, (size_t)0, (size_t)0, (size_t)0);
     }
 }

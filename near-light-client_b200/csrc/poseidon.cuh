@@ -4,10 +4,15 @@
 // poseidon_goldilocks.rs, hashing.rs @ d2598bd), the hasher bound at
 // /root/reference/vendor/starkyx/starkyx/src/plonky2/stark/config.rs:24,104.
 //
-// Integer-pipe kernel body: the state lives in 24 registers, values stay non-canonical ("nc") between
-// layers and are canonicalised once at the end.  The MDS layer exploits the tiny circulant constants:
-// each lane is split into 32-bit halves and the two 12-term dot products are accumulated in plain u64
-// (12 * 2^32 * 41 < 2^42) with IMAD.WIDE.U32, then recombined with a single cheap reduction.
+// Instruction budget (measured on B200, tools/ubench/ubench_pipes.cu): IMAD.WIDE/IMAD.HI issue once per 4
+// clocks per SM sub-partition, 32-bit IMAD/LOP3/SHF/PRMT once per 2, IADD3 once per clock.  So the S-box
+// keeps its 64x64 products on IMAD.WIDE (nothing cheaper exists), but the MDS layer uses NO multiplier:
+// the circulant was chosen by plonky2 so that its two-level even/odd split (y^12-1 = (y^6-1)(y^6+1),
+// y^6-1 = (y^3-1)(y^3+1)) has only powers of two as constants.  Each lane is cut into three limbs of
+// 22/21/21 bits, the 12-point circular correlation runs on the limbs in plain 32-bit wrap-around
+// arithmetic (adds and small shifts; the true result 264 * 2^22 < 2^32 fits), and the three limb sums are
+// glued back with three IMAD.WIDE and one fold of the bits above 2^64.  The next round's constants ride
+// along in limb form.  Values stay non-canonical ("nc", any representative below 2^64) between layers.
 #pragma once
 #include "gl.cuh"
 #include "poseidon_constants.h"
@@ -18,92 +23,140 @@ constexpr int WIDTH = 12;
 constexpr int RATE = 8;
 constexpr int HALF_FULL = 4;
 constexpr int N_PARTIAL = 22;
+constexpr int N_ROUNDS = 2 * HALF_FULL + N_PARTIAL;
 
 static __constant__ uint64_t c_rc[NLC_POSEIDON_N_RC] = NLC_POSEIDON_RC_INIT;
+
+// Round constants in limb form: v[(r*3 + limb)*12 + lane]; one extra all-zero round closes the last layer.
+struct RcLimbs {
+    uint32_t v[(N_ROUNDS + 1) * 3 * WIDTH];
+};
+constexpr RcLimbs make_rc_limbs() {
+    RcLimbs t{};
+    constexpr uint64_t rc[NLC_POSEIDON_N_RC] = NLC_POSEIDON_RC_INIT;
+    for (int r = 0; r < N_ROUNDS; r++)
+        for (int i = 0; i < WIDTH; i++) {
+            const uint64_t c = rc[r * WIDTH + i];
+            t.v[(r * 3 + 0) * WIDTH + i] = (uint32_t)(c & 0x3FFFFFu);
+            t.v[(r * 3 + 1) * WIDTH + i] = (uint32_t)((c >> 22) & 0x1FFFFFu);
+            t.v[(r * 3 + 2) * WIDTH + i] = (uint32_t)(c >> 43);
+        }
+    return t;
+}
+static __constant__ RcLimbs c_rc_limbs = make_rc_limbs();
+// Always 0, but not a compile-time constant: "a + b + z" has three live inputs, so ptxas must emit IADD3
+// (ALU pipe, one per clock) and cannot pick IMAD.IADD (the multiplier pipe, which the S-boxes need).
+static __constant__ uint32_t c_zero;
 
 __device__ __forceinline__ uint64_t sbox7(uint64_t x) {
     uint64_t x2 = gl::sqr_nc(x), x4 = gl::sqr_nc(x2), x3 = gl::mul_nc(x, x2);
     return gl::mul_nc(x3, x4);
 }
 
-// out[r] = sum_i s[(i+r)%12] * CIRC[i] + s[r] * DIAG[r]  (+ rc[r] when ADD_RC: the NEXT round's constant
-// layer is folded into the accumulators, where a 64-bit add cannot overflow).
-template <bool ADD_RC>
-__device__ __forceinline__ void mds_layer(uint64_t (&s)[WIDTH], const uint64_t* __restrict__ rc) {
-    constexpr uint32_t CIRC[WIDTH] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
-    uint32_t lo[WIDTH], hi[WIDTH];
+// o[r] = sum_i x[(i+r)%12] * CIRC[i] + [r==0] 8 x[0] + rc[r]  (mod 2^32), CIRC = 17 15 41 16 2 28 13 13 39 18 34 20.
+// Written as the cyclic convolution with k[m] = CIRC[-m]; even/odd split twice, halvings folded into the
+// constants:  k+ + = [16,32,16] (cyclic 3),  k+ - = [-1,-8,2] (negacyclic 3),  k- = [2,-4,16,1,-1,-1] (negacyclic 6).
+__device__ __forceinline__ void circ12(const uint32_t (&x)[WIDTH], uint32_t (&o)[WIDTH], const uint32_t* __restrict__ rc, const uint32_t z) {
+    uint32_t p[6], m[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        p[j] = x[j] + x[j + 6] + z;
+        m[j] = x[j] - x[j + 6] + z;
+    }
+    uint32_t t[3], w[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        t[j] = p[j] + p[j + 3] + z;
+        w[j] = p[j] - p[j + 3] + z;
+    }
+    const uint32_t S = t[0] + t[1] + t[2];
+    const uint32_t ap[3] = {S + t[2] + z, S + t[0] + z, S + t[1] + z}; // x16
+    const uint32_t am[3] = {8u * w[2] - 2u * w[1] - w[0], 0u - 8u * w[0] - 2u * w[2] - w[1],
+                            2u * w[0] - 8u * w[1] - w[2]};
+    uint32_t A[6];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        A[j] = 16u * ap[j] + am[j];
+        A[j + 3] = 16u * ap[j] - am[j];
+    }
+    uint32_t B[6];
+    B[0] = 2u * m[0] + 4u * m[5] - 16u * m[4] - m[3] + m[2] + m[1];
+    B[1] = 2u * m[1] - 4u * m[0] - 16u * m[5] - m[4] + m[3] + m[2];
+    B[2] = 2u * m[2] - 4u * m[1] + 16u * m[0] - m[5] + m[4] + m[3];
+    B[3] = 2u * m[3] - 4u * m[2] + 16u * m[1] + m[0] + m[5] + m[4];
+    B[4] = 2u * m[4] - 4u * m[3] + 16u * m[2] + m[1] - m[0] + m[5];
+    B[5] = 2u * m[5] - 4u * m[4] + 16u * m[3] + m[2] - m[1] - m[0];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        o[j] = A[j] + B[j] + rc[j];
+        o[j + 6] = A[j] - B[j] + rc[j + 6];
+    }
+    o[0] += 8u * x[0]; // MDS_MATRIX_DIAG = [8, 0, ...]
+}
+
+// s <- MDS s + rc, rc = 36 limb words of the NEXT round's constants.
+__device__ __forceinline__ void mds_layer(uint64_t (&s)[WIDTH], const uint32_t* __restrict__ rc, const uint32_t z) {
+    uint32_t L0[WIDTH], L1[WIDTH], L2[WIDTH], O0[WIDTH], O1[WIDTH], O2[WIDTH];
 #pragma unroll
     for (int i = 0; i < WIDTH; i++) {
-        lo[i] = (uint32_t)s[i];
-        hi[i] = (uint32_t)(s[i] >> 32);
+        L0[i] = (uint32_t)s[i] & 0x3FFFFFu;
+        L1[i] = (uint32_t)(s[i] >> 22) & 0x1FFFFFu;
+        L2[i] = (uint32_t)(s[i] >> 43);
     }
+    circ12(L0, O0, rc, z);
+    circ12(L1, O1, rc + WIDTH, z);
+    circ12(L2, O2, rc + 2 * WIDTH, z);
 #pragma unroll
-    for (int r = 0; r < WIDTH; r++) {
-        uint64_t alo = 0, ahi = 0;
-        if (ADD_RC) {
-            const uint64_t c = rc[r];
-            alo = (uint32_t)c;
-            ahi = c >> 32;
-        }
-#pragma unroll
-        for (int i = 0; i < WIDTH; i++) {
-            alo += (uint64_t)lo[(i + r) % WIDTH] * CIRC[i];
-            ahi += (uint64_t)hi[(i + r) % WIDTH] * CIRC[i];
-        }
-        if (r == 0) { // MDS_MATRIX_DIAG = [8, 0, ...]
-            alo += (uint64_t)lo[0] * 8u;
-            ahi += (uint64_t)hi[0] * 8u;
-        }
-        // value = alo + 2^32 ahi with alo, ahi < 2^43.  The top 11 bits of ahi weigh 2^64 == eps and go into alo
-        // (no overflow); the low word of ahi is added to the high word of that sum, and a carry out of it is
-        // one more 2^64 == eps, added to the (now small) wrapped value.
-        const uint32_t ahl = (uint32_t)ahi, ahh = (uint32_t)(ahi >> 32);
-        const uint64_t a2 = alo + (uint64_t)ahh * 0xffffffffu;
-        const uint32_t a2l = (uint32_t)a2, a2h = (uint32_t)(a2 >> 32);
+    for (int i = 0; i < WIDTH; i++) {
+        // V = O0 + 2^22 O1 + 2^43 O2 < 2^74 as three words (w2 < 2^10); w2 2^64 == w2 2^32 - w2 is folded into the
+        // low two words with a signed overflow word tw in {-1,0,1}, and tw 2^64 == tw eps closes it (no second wrap:
+        // after a carry the sum is < 2^42, after a borrow it is >= 2^64 - 2^10).
         uint32_t r0, r1;
         asm("{\n\t"
-            ".reg .u32 h,m;\n\t"
-            "add.cc.u32 h,%3,%4;\n\t"
-            "addc.u32 m,0,0;\n\t"
-            "sub.u32 m,0,m;\n\t" // m = carry ? 0xffffffff (= eps) : 0
-            "add.cc.u32 %0,%2,m;\n\t"
-            "addc.u32 %1,h,0;\n\t"
+            ".reg .u32 a,b,c,d,w0,w1,w2,m,tw,sg;\n\t"
+            "shl.b32 a,%3,22;\n\t"
+            "shr.u32 b,%3,10;\n\t"
+            "shl.b32 c,%4,11;\n\t"
+            "shr.u32 d,%4,21;\n\t"
+            "add.cc.u32 w0,%2,a;\n\t"
+            "addc.cc.u32 w1,b,c;\n\t"
+            "addc.u32 w2,d,0;\n\t"
+            "sub.cc.u32 w0,w0,w2;\n\t"
+            "subc.cc.u32 w1,w1,0;\n\t"
+            "subc.u32 tw,0,0;\n\t"
+            "add.cc.u32 w1,w1,w2;\n\t"
+            "addc.u32 tw,tw,0;\n\t"
+            "sub.u32 m,0,tw;\n\t"
+            "shr.s32 sg,tw,31;\n\t"
+            "add.cc.u32 %0,w0,m;\n\t"
+            "addc.u32 %1,w1,sg;\n\t"
             "}"
             : "=r"(r0), "=r"(r1)
-            : "r"(a2l), "r"(a2h), "r"(ahl));
-        s[r] = ((uint64_t)r1 << 32) | r0;
+            : "r"(O0[i]), "r"(O1[i]), "r"(O2[i]));
+        const uint64_t r = ((uint64_t)r1 << 32) | r0;
+        s[i] = r;
     }
 }
 
-// The permutation in plonky2's naive form (constant layer, S-box layer, MDS layer per round), with every
-// constant layer but the first folded into the preceding MDS layer.
+// plonky2's naive round structure (constant layer, S-box layer, MDS layer); every constant layer but the
+// first is folded into the preceding MDS layer.  One body per round kind keeps the loop inside the
+// instruction cache.
 __device__ __forceinline__ void permute_nc(uint64_t (&s)[WIDTH]) {
 #pragma unroll
     for (int i = 0; i < WIDTH; i++) s[i] = gl::add_nc(s[i], c_rc[i]);
-    const uint64_t* rc = c_rc + WIDTH;
+    const uint32_t* rc = c_rc_limbs.v;
+    const uint32_t z = c_zero;
 #pragma unroll 1
-    for (int r = 0; r < HALF_FULL; r++) {
+    for (int r = 0; r < N_ROUNDS; r++) {
+        if (r < HALF_FULL || r >= HALF_FULL + N_PARTIAL) {
 #pragma unroll
-        for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
-        mds_layer<true>(s, rc);
-        rc += WIDTH;
+            for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
+        } else {
+            s[0] = sbox7(s[0]);
+        }
+        rc += 3 * WIDTH;
+        mds_layer(s, rc, z);
     }
-#pragma unroll 1
-    for (int r = 0; r < N_PARTIAL; r++) {
-        s[0] = sbox7(s[0]);
-        mds_layer<true>(s, rc);
-        rc += WIDTH;
-    }
-#pragma unroll 1
-    for (int r = 0; r < HALF_FULL - 1; r++) {
-#pragma unroll
-        for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
-        mds_layer<true>(s, rc);
-        rc += WIDTH;
-    }
-#pragma unroll
-    for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
-    mds_layer<false>(s, nullptr);
 }
 
 // canonical output

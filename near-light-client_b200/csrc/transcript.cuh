@@ -12,27 +12,30 @@
 
 namespace transcript {
 
-// Lane i < 12 passes s_i and receives the permuted s_i (canonical).  All 32 lanes must call.
+// One permutation per half-warp: lanes base..base+11 (base = lane & 16) pass s_i and receive the permuted s_i
+// (canonical); lanes 12..15 of each half idle along.  All 32 lanes must call.  The latency of ONE permutation is
+// what this form is for (transcript, top of a Merkle tree): S-boxes run across lanes, the MDS layer is 12 shuffles.
 __device__ __forceinline__ u64 warp_permute(u64 x, int lane) {
     constexpr u32 CIRC[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
-    const int l12 = lane < 12 ? lane : 0;
+    const int base = lane & 16, l16 = lane & 15;
+    const int l12 = l16 < 12 ? l16 : 0;
 #pragma unroll 1
     for (int r = 0; r < 30; r++) {
         x = gl::add_nc(x, poseidon::c_rc[r * 12 + l12]);
         const bool full = r < 4 || r >= 26;
-        if (full || lane == 0) x = poseidon::sbox7(x);
+        if (full || l16 == 0) x = poseidon::sbox7(x);
         const u32 lo = (u32)x, hi = (u32)(x >> 32);
         u64 alo = 0, ahi = 0;
 #pragma unroll
         for (int i = 0; i < 12; i++) {
             int src = l12 + i;
-            src = src >= 12 ? src - 12 : src;
+            src = base + (src >= 12 ? src - 12 : src);
             u32 l = __shfl_sync(0xffffffffu, lo, src);
             u32 h = __shfl_sync(0xffffffffu, hi, src);
             alo += (u64)l * CIRC[i];
             ahi += (u64)h * CIRC[i];
         }
-        if (lane == 0) {
+        if (l16 == 0) {
             alo += (u64)lo * 8u;
             ahi += (u64)hi * 8u;
         }

@@ -665,7 +665,7 @@ class PolynomialBatch:
 
     def device_pointers(self):
         L = _ffi.lib()
-        return {"leaves": L.nlc_batch_leaves_dev(self._h), "coeffs": L.nlc_batch_coeffs_dev(self._h),
+        return {"lde": L.nlc_batch_lde_dev(self._h), "coeffs": L.nlc_batch_coeffs_dev(self._h),
                 "cap": L.nlc_batch_cap_dev(self._h)}
 
     # -- openings -------------------------------------------------------------------------------
