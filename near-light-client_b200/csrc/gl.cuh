@@ -45,6 +45,61 @@ __host__ __device__ __forceinline__ uint64_t reduce128_nc(uint64_t lo, uint64_t 
     return r;
 }
 
+// ---- device-only canonical arithmetic on IADD3 carry chains (full-rate; no compare/select, which issue at half rate) ----
+#ifdef __CUDACC__
+// canonical - canonical -> canonical: a - b, and a borrow is repaid with + p == - eps (m = 0xffffffff = eps)
+__device__ __forceinline__ uint64_t dsub(uint64_t a, uint64_t b) {
+    const uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
+    uint32_t r0, r1;
+    asm("{\n\t"
+        ".reg .u32 m;\n\t"
+        "sub.cc.u32 %0,%2,%4;\n\t"
+        "subc.cc.u32 %1,%3,%5;\n\t"
+        "subc.u32 m,0,0;\n\t"
+        "sub.cc.u32 %0,%0,m;\n\t"
+        "subc.u32 %1,%1,0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((uint64_t)r1 << 32) | r0;
+}
+// canonical + canonical -> canonical, as a - (p - b): p - b in (0, p] needs no correction of its own
+__device__ __forceinline__ uint64_t dadd(uint64_t a, uint64_t b) {
+    const uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
+    uint32_t r0, r1;
+    asm("{\n\t"
+        ".reg .u32 m,n0,n1;\n\t"
+        "sub.cc.u32 n0,1,%4;\n\t"
+        "subc.u32 n1,0xffffffff,%5;\n\t"
+        "sub.cc.u32 %0,%2,n0;\n\t"
+        "subc.cc.u32 %1,%3,n1;\n\t"
+        "subc.u32 m,0,0;\n\t"
+        "sub.cc.u32 %0,%0,m;\n\t"
+        "subc.u32 %1,%1,0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((uint64_t)r1 << 32) | r0;
+}
+// any representative -> canonical: x >= p exactly when x + eps carries out of 64 bits, and then x - p == x + eps
+__device__ __forceinline__ uint64_t dcanon(uint64_t x) {
+    const uint32_t x0 = (uint32_t)x, x1 = (uint32_t)(x >> 32);
+    uint32_t r0, r1;
+    asm("{\n\t"
+        ".reg .u32 t,c;\n\t"
+        "add.cc.u32 t,%2,0xffffffff;\n\t"
+        "addc.cc.u32 t,%3,0;\n\t"
+        "addc.u32 c,0,0;\n\t"
+        "sub.u32 c,0,c;\n\t"
+        "add.cc.u32 %0,%2,c;\n\t"
+        "addc.u32 %1,%3,0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x0), "r"(x1));
+    return ((uint64_t)r1 << 32) | r0;
+}
+#endif
+
 // (lo + 2^64 hi) mod p, any representative, for the device: with hi = 2^32 p3 + p2,
 // V = lo + (p2 << 32) - p2 - p3 lies in (-2^33, 2^65); it is formed in 128-bit arithmetic (IADD3/IADD3.X
 // chains, no multiplier), and its signed top word tw in {-1,0,1} weighs 2^64 == eps: one more 64-bit add
@@ -61,7 +116,7 @@ __device__ __forceinline__ uint64_t mul_nc(uint64_t a, uint64_t b) {
     const unsigned __int128 p = (unsigned __int128)a * b;
     return reduce128_dev_nc((uint64_t)p, (uint64_t)(p >> 64));
 }
-__device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return canon(mul_nc(a, b)); }
+__device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return dcanon(mul_nc(a, b)); }
 __device__ __forceinline__ uint64_t sqr_nc(uint64_t a) { return mul_nc(a, a); }
 
 __device__ __forceinline__ uint64_t pow(uint64_t b, uint64_t e) {

@@ -39,10 +39,97 @@ __global__ void k_tw_table(u64* out, int m, int S, u64 root) {
     out[i] = gl::pow(root, (u64)brev((u32)pos, S) * low);
 }
 
+// ---- the 2^S-point transform of a tile held in shared memory ---------------------------------------------
+// A decimation-in-frequency NTT in radix-2^R register steps (R <= 4).  With L = 2^(S-st) the length of the
+// current sub-problems and stride = L / 2^R, one task loads x[k*stride + b], k < 2^R, runs the 2^R-point DIF
+// in registers (twiddles w_{2^R}^e, e < 2^(R-1)), multiplies register k by the inter-step twiddle
+// w_L^(b * bitrev_R(k)) and stores it back to slot k: the sub-problem of frequency class m = bitrev_R(k) then
+// occupies the contiguous block k, which makes the final order the same index-bit-reversed order the radix-2
+// cascade gives -- at (S/R - 1) full multiplications per element between steps instead of S/2.
+// `roots` holds all 2^S powers of w_{2^S} (or its inverse).
+template <int R>
+__device__ __forceinline__ void dft_regs(u64 (&v)[1 << R], const u64* __restrict__ roots, int S) {
+#pragma unroll
+    for (int t = 0; t < R; t++) {
+        const int half = 1 << (R - 1 - t);
+#pragma unroll
+        for (int k = 0; k < (1 << R); k++) {
+            if (k & half) continue;
+            const u64 a = v[k], c = v[k + half];
+            v[k] = gl::dadd(a, c);
+            const u64 d = gl::dsub(a, c);
+            const int e = (k & (half - 1)) << t; // exponent of w_{2^R}
+            v[k + half] = e ? gl::mul(d, __ldg(roots + ((size_t)e << (S - R)))) : d;
+        }
+    }
+}
+
+__device__ __forceinline__ u32 pad16(u32 i) { return i + (i >> 4); } // LO layout: one pad word per 16
+
+// HI layout: element i of transform t at sm[i*T + t] (t fastest: what the strided gather delivers);
+// LO layout: element i of transform g at sm[g*pitch + pad16(i)].
+template <int R, bool HI>
+__device__ __forceinline__ void fft_step(u64* sm, int S, int st, int log_tr, u32 pitch, const u64* __restrict__ roots) {
+    const int L_log = S - st, s_log = L_log - R;
+    const u32 tasks = ((u32)1 << (S + log_tr)) >> R;
+    for (u32 tau = threadIdx.x; tau < tasks; tau += NTT_THREADS) {
+        u32 t, b, p;
+        if (HI) {
+            t = tau & (((u32)1 << log_tr) - 1);
+            const u32 rest = tau >> log_tr;
+            b = rest & (((u32)1 << s_log) - 1);
+            p = rest >> s_log;
+        } else {
+            b = tau & (((u32)1 << s_log) - 1);
+            const u32 rest = tau >> s_log;
+            p = rest & (((u32)1 << st) - 1);
+            t = rest >> st;
+        }
+        const u32 i0 = (p << L_log) + b;
+        u64 v[1 << R];
+#pragma unroll
+        for (int k = 0; k < (1 << R); k++) {
+            const u32 i = i0 + ((u32)k << s_log);
+            v[k] = sm[HI ? (i << log_tr) + t : t * pitch + pad16(i)];
+        }
+        dft_regs<R>(v, roots, S);
+        if (s_log > 0) {
+#pragma unroll
+            for (int k = 1; k < (1 << R); k++) {
+                const u32 m = __brev((u32)k) >> (32 - R);
+                v[k] = gl::mul(v[k], __ldg(roots + ((size_t)(b * m) << st)));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < (1 << R); k++) {
+            const u32 i = i0 + ((u32)k << s_log);
+            sm[HI ? (i << log_tr) + t : t * pitch + pad16(i)] = v[k];
+        }
+    }
+}
+
+// radix plan of a 2^S-point tile transform, packed 4 bits per step (host side: plan_steps)
+template <bool HI>
+__device__ __forceinline__ void fft_tile(u64* sm, int S, u32 plan, int log_tr, u32 pitch, const u64* __restrict__ roots) {
+    int st = 0;
+    while (plan) {
+        const int R = plan & 15;
+        plan >>= 4;
+        switch (R) {
+        case 4: fft_step<4, HI>(sm, S, st, log_tr, pitch, roots); break;
+        case 3: fft_step<3, HI>(sm, S, st, log_tr, pitch, roots); break;
+        case 2: fft_step<2, HI>(sm, S, st, log_tr, pitch, roots); break;
+        default: fft_step<1, HI>(sm, S, st, log_tr, pitch, roots); break;
+        }
+        st += R;
+        __syncthreads();
+    }
+}
+
 // One digit of a 2^m block, strided ("hi") pass.  smem: [2^S][T].
 __global__ void __launch_bounds__(NTT_THREADS)
 k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, size_t dst_stride, int m, int S,
-         int log_T, const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots) {
+         int log_T, u32 plan, const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots) {
     extern __shared__ u64 sm[];
     const int L = m - S;
     const int T = 1 << log_T;
@@ -62,18 +149,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
         sm[idx] = v;
     }
     __syncthreads();
-    for (int st = 0; st < S; st++) {
-        const u32 half = 1u << (S - 1 - st);
-        for (u32 b = threadIdx.x; b < (total >> 1); b += NTT_THREADS) {
-            u32 t = b & (T - 1), j = b >> log_T;
-            u32 jj = j & (half - 1);
-            u32 i0 = ((j - jj) << 1) + jj, i1 = i0 + half;
-            u64 a = sm[(i0 << log_T) + t], c = sm[(i1 << log_T) + t];
-            sm[(i0 << log_T) + t] = gl::add(a, c);
-            sm[(i1 << log_T) + t] = gl::mul(gl::sub(a, c), roots[jj << st]);
-        }
-        __syncthreads();
-    }
+    fft_tile<true>(sm, S, plan, log_T, 0, roots);
     for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 t = idx & (T - 1), pos = idx >> log_T;
         size_t off = ((size_t)pos << L) + low0 + t;
@@ -81,74 +157,67 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
     }
 }
 
-// Last digit on contiguous data.  smem: [G][2^S + 1].
+// Last digit on contiguous data.  A CTA takes Gb = 2^log_Gb blocks of 2^S elements in each of Gc = 2^log_Gc
+// columns (transform g = gb*Gc + gc).  smem: [Gb*Gc][pitch].
+//   COLS / ROWS : the Gb blocks are consecutive; NATURAL : Gc = 1 and the blocks are the bit-reversal-related
+//   ones whose outputs interleave into contiguous Gb-element segments.
 enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2 };
 template <int MODE>
 __global__ void __launch_bounds__(NTT_THREADS)
-k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_G, size_t n_cols,
-         const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale, const u64* __restrict__ roots,
-         u64* __restrict__ dst, size_t dst_stride, size_t row_width, size_t row_base, size_t col0) {
+k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_Gb, int log_Gc, u32 plan,
+         size_t n_cols, const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale,
+         const u64* __restrict__ roots, u64* __restrict__ dst, size_t dst_stride, size_t row_width, size_t row_base,
+         size_t col0) {
     extern __shared__ u64 sm[];
-    const int G = 1 << log_G;
-    const u32 len = 1u << S, pitch = len + 1;
-    const u32 total = (u32)G << S;
+    const int log_G = log_Gb + log_Gc;
+    const u32 len = 1u << S, pitch = pad16(len) + 1;
+    const u32 total = (u32)1 << (S + log_G);
     const int log_nb = log_n - S;
+    const u32 Gc_mask = (1u << log_Gc) - 1;
 
     for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
-        u32 g = idx >> S, e = idx & (len - 1);
+        const u32 g = idx >> S, e = idx & (len - 1);
+        const size_t col = ((size_t)blockIdx.y << log_Gc) + (g & Gc_mask);
+        size_t blk = ((size_t)blockIdx.x << log_Gb) + (g >> log_Gc);
+        if (MODE == OUT_NATURAL) blk = brev((u32)blk, log_nb);
+        const size_t i = (blk << S) + e;
         u64 v = 0;
-        if (MODE != OUT_NATURAL) {
-            size_t col = (size_t)blockIdx.y * G + g;
-            size_t i = ((size_t)blockIdx.x << S) + e;
-            if (col < n_cols) {
-                v = gl::canon(src[col * src_stride + i]);
-                if (pre) v = gl::mul(v, pre[i]);
-            }
-        } else {
-            size_t blk = brev((u32)(blockIdx.x * G + g), log_nb);
-            size_t i = (blk << S) + e;
-            v = gl::canon(src[blockIdx.y * src_stride + i]);
+        if (col < n_cols) {
+            v = gl::canon(src[col * src_stride + i]);
             if (pre) v = gl::mul(v, pre[i]);
         }
-        sm[g * pitch + e] = v;
+        sm[g * pitch + pad16(e)] = v;
     }
     __syncthreads();
-    for (int st = 0; st < S; st++) {
-        const u32 half = 1u << (S - 1 - st);
-        for (u32 b = threadIdx.x; b < (total >> 1); b += NTT_THREADS) {
-            u32 g = b >> (S - 1), j = b & ((len >> 1) - 1);
-            u32 jj = j & (half - 1);
-            u32 i0 = ((j - jj) << 1) + jj, i1 = i0 + half;
-            u64* row = sm + g * pitch;
-            u64 a = row[i0], c = row[i1];
-            row[i0] = gl::add(a, c);
-            row[i1] = gl::mul(gl::sub(a, c), roots[jj << st]);
-        }
-        __syncthreads();
-    }
-    if (MODE == OUT_COLS) { // column-major, index-bit-reversed: position q of this block is contiguous in its column
+    fft_tile<false>(sm, S, plan, log_G, pitch, roots);
+    if (MODE == OUT_COLS) { // column-major, index-bit-reversed: the tile is contiguous in its column
         for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
-            u32 g = idx >> S, q = idx & (len - 1);
-            size_t col = (size_t)blockIdx.y * G + g;
+            const u32 g = idx >> S, q = idx & (len - 1);
+            const size_t col = ((size_t)blockIdx.y << log_Gc) + (g & Gc_mask);
             if (col >= n_cols) continue;
-            u64 v = sm[g * pitch + q];
+            const size_t blk = ((size_t)blockIdx.x << log_Gb) + (g >> log_Gc);
+            u64 v = sm[g * pitch + pad16(q)];
             if (scale != 1) v = gl::mul(v, scale);
-            dst[(col0 + col) * dst_stride + row_base + ((size_t)blockIdx.x << S) + q] = v;
+            dst[(col0 + col) * dst_stride + row_base + (blk << S) + q] = v;
         }
-        return;
-    }
-    for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
-        u32 g = idx & (G - 1), q = idx >> log_G;
-        u64 v = sm[g * pitch + q];
-        if (scale != 1) v = gl::mul(v, scale);
-        if (MODE == OUT_ROWS) {
-            size_t col = (size_t)blockIdx.y * G + g;
-            if (col < n_cols) {
-                size_t row = row_base + ((size_t)blockIdx.x << S) + q;
-                dst[row * row_width + col0 + col] = v;
-            }
-        } else {
-            size_t k = ((size_t)brev(q, S) << log_nb) + (size_t)blockIdx.x * G + g;
+    } else if (MODE == OUT_ROWS) { // row-major: the Gc columns of a row are adjacent words
+        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+            const u32 gc = idx & Gc_mask, rest = idx >> log_Gc;
+            const u32 q = rest & (len - 1), gb = rest >> S;
+            const size_t col = ((size_t)blockIdx.y << log_Gc) + gc;
+            if (col >= n_cols) continue;
+            u64 v = sm[((gb << log_Gc) + gc) * pitch + pad16(q)];
+            if (scale != 1) v = gl::mul(v, scale);
+            const size_t row = row_base + ((((size_t)blockIdx.x << log_Gb) + gb) << S) + q;
+            dst[row * row_width + col0 + col] = v;
+        }
+    } else { // natural order: output k = bitrev_S(q) * 2^log_nb + block index, contiguous over the Gb blocks
+        const u32 G = 1u << log_G;
+        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+            const u32 g = idx & (G - 1), q = idx >> log_G;
+            u64 v = sm[g * pitch + pad16(q)];
+            if (scale != 1) v = gl::mul(v, scale);
+            const size_t k = ((size_t)brev(q, S) << log_nb) + ((size_t)blockIdx.x << log_G) + g;
             if (post) v = gl::mul(v, post[k]);
             dst[blockIdx.y * dst_stride + k] = v;
         }
@@ -167,7 +236,7 @@ u64* get_table(nlc_ctx* ctx, const TableKey& key, size_t words) {
 
 u64* roots_table(nlc_ctx* ctx, int S, bool inv) {
     TableKey key{KIND_ROOTS, S, 0, inv ? 1 : 0, 0, 0};
-    size_t words = S >= 1 ? ((size_t)1 << (S - 1)) : 1;
+    size_t words = (size_t)1 << S; // all powers: the inter-step twiddles of fft_step index the whole circle
     if (u64* p = get_table(ctx, key, words)) return p;
     u64* p = ctx->tables[key];
     u64 w = gl::h_root_of_unity(S);
@@ -200,6 +269,12 @@ std::vector<int> plan_digits(int log_n) {
     std::vector<int> v(d, log_n / d);
     for (int i = 0; i < log_n % d; i++) v[i]++;
     return v;
+}
+
+// register-radix steps of a 2^S-point tile transform, 4 bits each, first step in the low nibble
+u32 plan_steps(int S) {
+    static const u32 plans[11] = {0, 0x1, 0x2, 0x3, 0x4, 0x23, 0x33, 0x34, 0x44, 0x333, 0x334};
+    return plans[S];
 }
 
 void ensure_attrs(nlc_ctx* ctx) {
@@ -244,13 +319,14 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
     for (int lvl = 0; lvl + 1 < d; lvl++) {
         NLC_CHECK(job.scratch != nullptr, "ntt_run: scratch required for multi-digit transform");
         const int S = digits[lvl], L = m - S;
-        int log_T = S >= 9 ? 3 : 4;
+        int log_T = 12 - S; // 4096-element tiles: one radix-16 task per thread
+        if (log_T < 3) log_T = 3;
         if (log_T > L) log_T = L;
         const u64* tw = tw_table(ctx, m, S, inv);
         const u64* roots = roots_table(ctx, S, inv);
         dim3 grid((unsigned)((n >> m) << (L - log_T)), (unsigned)job.n_cols);
         size_t smem = ((size_t)1 << (S + log_T)) * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_hi, grid, NTT_THREADS, smem, cur, cur_stride, job.scratch, n, m, S, log_T,
+        NLC_LAUNCH(ctx, k_ntt_hi, grid, NTT_THREADS, smem, cur, cur_stride, job.scratch, n, m, S, log_T, plan_steps(S),
                    lvl == 0 ? pre : nullptr, tw, roots);
         cur = job.scratch;
         cur_stride = n;
@@ -259,28 +335,33 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
     const int S = digits[d - 1];
     const u64* roots = roots_table(ctx, S, inv);
     const u64* lo_pre = d == 1 ? pre : nullptr;
+    const int log_nb = log_n - S;
+    int log_G = 12 - S; // transforms per CTA
+    if (log_G < 2) log_G = 2;
+    const size_t pitch = ((size_t)1 << S) + ((size_t)1 << S >> 4) + 1;
     if (job.rows || job.cols) {
-        int log_G = S >= 9 ? 3 : 4;
-        if (job.cols) log_G = 0; // a column is contiguous: no need to gang columns for coalescing
-        while (log_G > 0 && ((size_t)1 << (log_G - 1)) >= job.n_cols) log_G--;
-        const size_t G = (size_t)1 << log_G;
-        dim3 grid((unsigned)(n >> S), (unsigned)((job.n_cols + G - 1) / G));
-        size_t smem = G * (((size_t)1 << S) + 1) * sizeof(u64);
+        int log_Gc = 0;
+        if (job.rows) // gang columns so a row segment is one store (FRI: the two planes of an extension element)
+            while (log_Gc < log_G && ((size_t)1 << log_Gc) < job.n_cols) log_Gc++;
+        int log_Gb = log_G - log_Gc;
+        if (log_Gb > log_nb) log_Gb = log_nb;
+        dim3 grid((unsigned)((n >> S) >> log_Gb), (unsigned)((job.n_cols + ((size_t)1 << log_Gc) - 1) >> log_Gc));
+        size_t smem = ((size_t)1 << (log_Gb + log_Gc)) * pitch * sizeof(u64);
         if (job.cols)
-            NLC_LAUNCH(ctx, k_ntt_lo<OUT_COLS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols,
-                       lo_pre, (const u64*)nullptr, scale, roots, job.dst, job.dst_stride, (size_t)0, job.row_base,
-                       job.col0);
+            NLC_LAUNCH(ctx, k_ntt_lo<OUT_COLS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
+                       plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, job.dst_stride,
+                       (size_t)0, job.row_base, job.col0);
         else
-            NLC_LAUNCH(ctx, k_ntt_lo<OUT_ROWS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols,
-                       lo_pre, (const u64*)nullptr, scale, roots, job.dst, (size_t)0, job.row_width, job.row_base,
-                       job.col0);
+            NLC_LAUNCH(ctx, k_ntt_lo<OUT_ROWS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
+                       plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, (size_t)0,
+                       job.row_width, job.row_base, job.col0);
     } else {
         NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
-        int log_G = S >= 10 ? 3 : 4;
-        if (log_G > log_n - S) log_G = log_n - S;
+        if (log_G > log_nb) log_G = log_nb;
         dim3 grid((unsigned)((n >> S) >> log_G), (unsigned)job.n_cols);
-        size_t smem = ((size_t)1 << log_G) * (((size_t)1 << S) + 1) * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_lo<OUT_NATURAL>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, job.n_cols, lo_pre,
-                   post, scale, roots, job.dst, job.dst_stride, (size_t)0, (size_t)0, (size_t)0);
+        size_t smem = ((size_t)1 << log_G) * pitch * sizeof(u64);
+        NLC_LAUNCH(ctx, k_ntt_lo<OUT_NATURAL>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, 0,
+                   plan_steps(S), job.n_cols, lo_pre, post, scale, roots, job.dst, job.dst_stride, (size_t)0,
+                   (size_t)0, (size_t)0);
     }
 }
