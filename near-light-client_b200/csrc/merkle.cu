@@ -99,7 +99,8 @@ k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) 
 // half-warp (transcript::warp_permute), __syncthreads between layers.  Up there a layer has fewer nodes
 // than the GPU has sub-partitions, so the latency of one permutation is all that matters: the 12-lane
 // form is ~8x shorter than the one-thread form, and the layers cost no launches.
-constexpr int TOP_THREADS = 512;
+constexpr int TOP_THREADS = 1024;
+constexpr size_t TOP_PARENTS = TOP_THREADS / 16; // parents per subtree the top kernel finishes in one pass per layer
 __global__ void __launch_bounds__(TOP_THREADS) k_merkle_top(u64* digests, u64* cap, TreeGeom g, int layer0) {
     const int lane = threadIdx.x & 31, l16 = lane & 15;
     const size_t group = (threadIdx.x >> 4), n_groups = TOP_THREADS / 16;
@@ -203,8 +204,8 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
     ctx->phase_end();
     ctx->phase_begin(3);
     int layer = 0;
-    // wide layers: one thread per parent; once a subtree has at most 256 parents left, its top runs in one CTA
-    for (; layer < g.sub_height && ((size_t)1 << (g.sub_height - layer - 1)) > 256; layer++) {
+    // wide layers: one thread per parent; once a subtree's layer fits one pass of half-warp permutations, one CTA finishes it
+    for (; layer < g.sub_height && ((size_t)1 << (g.sub_height - layer - 1)) > TOP_PARENTS; layer++) {
         size_t parents = n_leaves >> (layer + 1);
         NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
                    digests, cap, g, layer, parents);

@@ -17,6 +17,13 @@
 #include "gl.cuh"
 #include "poseidon_constants.h"
 
+// Pipe balance knob (tools/ubench/ubench_perm.cu): bit k set => the adds of network level k get a runtime-zero third
+// addend, which forces IADD3 (ALU pipe) where ptxas would otherwise pick IMAD.IADD (multiplier pipe).  With the
+// carry-chain recombination the multiplier pipe has slack and ptxas' own split wins: 0 measured best (1.17 vs 1.10 G/s).
+#ifndef NLC_ZMASK
+#define NLC_ZMASK 0
+#endif
+
 namespace poseidon {
 
 constexpr int WIDTH = 12;
@@ -60,17 +67,17 @@ __device__ __forceinline__ void circ12(const uint32_t (&x)[WIDTH], uint32_t (&o)
     uint32_t p[6], m[6];
 #pragma unroll
     for (int j = 0; j < 6; j++) {
-        p[j] = x[j] + x[j + 6] + z;
-        m[j] = x[j] - x[j + 6] + z;
+        p[j] = x[j] + x[j + 6] + (NLC_ZMASK & 1 ? z : 0u);
+        m[j] = x[j] - x[j + 6] + (NLC_ZMASK & 2 ? z : 0u);
     }
     uint32_t t[3], w[3];
 #pragma unroll
     for (int j = 0; j < 3; j++) {
-        t[j] = p[j] + p[j + 3] + z;
-        w[j] = p[j] - p[j + 3] + z;
+        t[j] = p[j] + p[j + 3] + (NLC_ZMASK & 4 ? z : 0u);
+        w[j] = p[j] - p[j + 3] + (NLC_ZMASK & 4 ? z : 0u);
     }
     const uint32_t S = t[0] + t[1] + t[2];
-    const uint32_t ap[3] = {S + t[2] + z, S + t[0] + z, S + t[1] + z}; // x16
+    const uint32_t ap[3] = {S + t[2] + (NLC_ZMASK & 8 ? z : 0u), S + t[0] + (NLC_ZMASK & 8 ? z : 0u), S + t[1] + (NLC_ZMASK & 8 ? z : 0u)}; // x16
     const uint32_t am[3] = {8u * w[2] - 2u * w[1] - w[0], 0u - 8u * w[0] - 2u * w[2] - w[1],
                             2u * w[0] - 8u * w[1] - w[2]};
     uint32_t A[6];
@@ -94,53 +101,59 @@ __device__ __forceinline__ void circ12(const uint32_t (&x)[WIDTH], uint32_t (&o)
     o[0] += 8u * x[0]; // MDS_MATRIX_DIAG = [8, 0, ...]
 }
 
-// s <- MDS s + rc, rc = 36 limb words of the NEXT round's constants.
+// V = O0 + 2^22 O1 + 2^43 O2 (O0, O1 < 2^32 unsigned, O2 < 2^31) mod p, any representative.  V < 2^75 is formed as
+// three words (w2 < 2^11); w2 2^64 == w2 2^32 - w2 is folded into the low two words with a signed overflow word
+// tw in {-1,0,1}, and tw 2^64 == tw eps closes it (no second wrap: after a carry the sum is < 2^43, after a borrow it
+// is >= 2^64 - 2^11).
+__device__ __forceinline__ uint64_t glue3(uint32_t O0, uint32_t O1, uint32_t O2) {
+    uint32_t r0, r1;
+    asm("{\n\t"
+        ".reg .u32 a,b,c,d,w0,w1,w2,m,tw,sg;\n\t"
+        "shl.b32 a,%3,22;\n\t"
+        "shr.u32 b,%3,10;\n\t"
+        "shl.b32 c,%4,11;\n\t"
+        "shr.u32 d,%4,21;\n\t"
+        "add.cc.u32 w0,%2,a;\n\t"
+        "addc.cc.u32 w1,b,c;\n\t"
+        "addc.u32 w2,d,0;\n\t"
+        "sub.cc.u32 w0,w0,w2;\n\t"
+        "subc.cc.u32 w1,w1,0;\n\t"
+        "subc.u32 tw,0,0;\n\t"
+        "add.cc.u32 w1,w1,w2;\n\t"
+        "addc.u32 tw,tw,0;\n\t"
+        "sub.u32 m,0,tw;\n\t"
+        "shr.s32 sg,tw,31;\n\t"
+        "add.cc.u32 %0,w0,m;\n\t"
+        "addc.u32 %1,w1,sg;\n\t"
+        "}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(O0), "r"(O1), "r"(O2));
+    return ((uint64_t)r1 << 32) | r0;
+}
+
+__device__ __forceinline__ void split3(uint64_t v, uint32_t& l0, uint32_t& l1, uint32_t& l2) {
+    l0 = (uint32_t)v & 0x3FFFFFu;
+    l1 = (uint32_t)(v >> 22) & 0x1FFFFFu;
+    l2 = (uint32_t)(v >> 43);
+}
+
+// s <- MDS s + rc, rc = 36 limb words of the NEXT round's constants (full rounds: 64-bit lanes in and out).
 __device__ __forceinline__ void mds_layer(uint64_t (&s)[WIDTH], const uint32_t* __restrict__ rc, const uint32_t z) {
     uint32_t L0[WIDTH], L1[WIDTH], L2[WIDTH], O0[WIDTH], O1[WIDTH], O2[WIDTH];
 #pragma unroll
-    for (int i = 0; i < WIDTH; i++) {
-        L0[i] = (uint32_t)s[i] & 0x3FFFFFu;
-        L1[i] = (uint32_t)(s[i] >> 22) & 0x1FFFFFu;
-        L2[i] = (uint32_t)(s[i] >> 43);
-    }
+    for (int i = 0; i < WIDTH; i++) split3(s[i], L0[i], L1[i], L2[i]);
     circ12(L0, O0, rc, z);
     circ12(L1, O1, rc + WIDTH, z);
     circ12(L2, O2, rc + 2 * WIDTH, z);
 #pragma unroll
-    for (int i = 0; i < WIDTH; i++) {
-        // V = O0 + 2^22 O1 + 2^43 O2 < 2^74 as three words (w2 < 2^10); w2 2^64 == w2 2^32 - w2 is folded into the
-        // low two words with a signed overflow word tw in {-1,0,1}, and tw 2^64 == tw eps closes it (no second wrap:
-        // after a carry the sum is < 2^42, after a borrow it is >= 2^64 - 2^10).
-        uint32_t r0, r1;
-        asm("{\n\t"
-            ".reg .u32 a,b,c,d,w0,w1,w2,m,tw,sg;\n\t"
-            "shl.b32 a,%3,22;\n\t"
-            "shr.u32 b,%3,10;\n\t"
-            "shl.b32 c,%4,11;\n\t"
-            "shr.u32 d,%4,21;\n\t"
-            "add.cc.u32 w0,%2,a;\n\t"
-            "addc.cc.u32 w1,b,c;\n\t"
-            "addc.u32 w2,d,0;\n\t"
-            "sub.cc.u32 w0,w0,w2;\n\t"
-            "subc.cc.u32 w1,w1,0;\n\t"
-            "subc.u32 tw,0,0;\n\t"
-            "add.cc.u32 w1,w1,w2;\n\t"
-            "addc.u32 tw,tw,0;\n\t"
-            "sub.u32 m,0,tw;\n\t"
-            "shr.s32 sg,tw,31;\n\t"
-            "add.cc.u32 %0,w0,m;\n\t"
-            "addc.u32 %1,w1,sg;\n\t"
-            "}"
-            : "=r"(r0), "=r"(r1)
-            : "r"(O0[i]), "r"(O1[i]), "r"(O2[i]));
-        const uint64_t r = ((uint64_t)r1 << 32) | r0;
-        s[i] = r;
-    }
+    for (int i = 0; i < WIDTH; i++) s[i] = glue3(O0[i], O1[i], O2[i]);
 }
 
 // plonky2's naive round structure (constant layer, S-box layer, MDS layer); every constant layer but the
 // first is folded into the preceding MDS layer.  One body per round kind keeps the loop inside the
-// instruction cache.
+// instruction cache.  (Tried and dropped: keeping lanes 1..11 in limb form across the partial rounds with a
+// signed carry normalisation instead of glue + split -- 12% fewer instructions, but 114 registers and more
+// half-rate shift/logic work: 1.04 vs 1.17 G permutations/s.)
 __device__ __forceinline__ void permute_nc(uint64_t (&s)[WIDTH]) {
 #pragma unroll
     for (int i = 0; i < WIDTH; i++) s[i] = gl::add_nc(s[i], c_rc[i]);
