@@ -77,6 +77,18 @@ int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t 
  * the serial column split of trace/mod.rs:270-285: rows x width host matrix, columns [col0, col0+n_cols). */
 int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols,
                                int log_n, int rate_bits, int cap_height, nlc_batch** out);
+/* SURVEY.md 8(e).2 -- one GPU's share of a commit, split by LDE coset.  n_shards (a power of two, at most
+ * 2^rate_bits and at most 2^cap_height) ranks each call this with their shard_idx: the batch then holds the
+ * leaves [shard_idx, shard_idx + 1) * N / n_shards (whole cosets = whole cap subtrees), their digests, and
+ * 2^cap_height / n_shards cap entries; concatenating the shards' caps / digests / leaves in shard order gives exactly
+ * the single-GPU MerkleCap / digests / leaves.  The only exchange is the all-gather of the cap entries (32 bytes
+ * each), done by the caller (NCCL all_gather in near-light-client_b200/plonky2.py). */
+int nlc_commit_from_values_shard(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                                 int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out);
+int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n,
+                                     int rate_bits, int cap_height, size_t shard_idx, size_t n_shards,
+                                     nlc_batch** out);
+int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards);
 void nlc_batch_free(nlc_batch* b);
 
 /* Struct fields of PolynomialBatch / MerkleTree, materialised on demand. */

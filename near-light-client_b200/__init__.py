@@ -7,3 +7,4 @@ with ``__graft_entry__.load_package()`` (alias ``nlc_b200``).
 from . import _ffi  # noqa: F401
 from ._ffi import NlcError  # noqa: F401
 from . import plonky2  # noqa: F401
+from . import sharding  # noqa: F401

@@ -54,6 +54,11 @@ SIGNATURES = {
     "nlc_commit_from_values": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_coeffs": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_values_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+    "nlc_commit_from_values_shard": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                               C.c_size_t, C.POINTER(vp)]),
+    "nlc_commit_from_values_shard_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                                   C.c_size_t, C.POINTER(vp)]),
+    "nlc_batch_shard": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "nlc_commit_from_coeffs_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_trace_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                              C.POINTER(vp)]),

@@ -71,8 +71,8 @@ int fft_host(nlc_ctx* ctx, u64* data, size_t n_cols, int log_n, FftKind kind, u6
 }
 
 nlc_batch* commit_dev(nlc_ctx* ctx, const u64* src_dev, bool is_values, size_t W, int log_n, int rate_bits,
-                      int cap_height) {
-    nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height);
+                      int cap_height, int shard_log = 0, size_t shard_idx = 0) {
+    nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height, shard_log, shard_idx);
     try {
         const size_t n = (size_t)1 << log_n;
         if (is_values)
@@ -88,7 +88,7 @@ nlc_batch* commit_dev(nlc_ctx* ctx, const u64* src_dev, bool is_values, size_t W
 }
 
 int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int rate_bits, int cap_height,
-                bool is_values, nlc_batch** out) {
+                bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0) {
     if (!ctx) return 1;
     return nlc_guarded(ctx, [&] {
         CtxGuard g(ctx);
@@ -96,7 +96,7 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
         *out = nullptr;
         NLC_CHECK(W > 0 && log_n >= 0 && log_n <= 32, "bad shape");
         const size_t n = (size_t)1 << log_n;
-        nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height);
+        nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height, shard_log, shard_idx);
         try {
             if (is_values) {
                 DevBuf vals(ctx, W * n);
@@ -244,6 +244,38 @@ int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t 
         *out = commit_dev(ctx, coeffs_dev, false, n_cols, log_n, rate_bits, cap_height);
     });
 }
+// ---- 8e.2: one coset shard of a commit ----
+static int shard_log_of(size_t n_shards) {
+    int l = 0;
+    while (((size_t)1 << l) < n_shards) l++;
+    return ((size_t)1 << l) == n_shards ? l : -1;
+}
+int nlc_commit_from_values_shard(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                                 int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out) {
+    if (!ctx) return 1;
+    const int sl = shard_log_of(n_shards);
+    if (sl < 0) return nlc_guarded(ctx, [&] { NLC_CHECK(false, "n_shards must be a power of two"); });
+    return commit_host(ctx, cols, n_cols, log_n, rate_bits, cap_height, true, out, sl, shard_idx);
+}
+int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n,
+                                     int rate_bits, int cap_height, size_t shard_idx, size_t n_shards,
+                                     nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && values_dev, "null argument");
+        const int sl = shard_log_of(n_shards);
+        NLC_CHECK(sl >= 0, "n_shards must be a power of two");
+        *out = commit_dev(ctx, values_dev, true, n_cols, log_n, rate_bits, cap_height, sl, shard_idx);
+    });
+}
+int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards) {
+    if (!b) return 1;
+    if (shard_idx) *shard_idx = b->shard_idx;
+    if (n_shards) *n_shards = (size_t)1 << b->shard_log;
+    return 0;
+}
+
 int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols, int log_n,
                                int rate_bits, int cap_height, nlc_batch** out) {
     if (!ctx) return 1;
@@ -279,7 +311,7 @@ int nlc_batch_cap(nlc_batch* b, uint64_t* out) {
     if (!b) return 1;
     return nlc_guarded(b->ctx, [&] {
         CtxGuard g(b->ctx);
-        d2h(b->ctx, out, b->cap, ((size_t)4 << b->cap_height) * sizeof(u64));
+        d2h(b->ctx, out, b->cap, ((size_t)4 << b->cap_local()) * sizeof(u64));
         sync(b->ctx);
     });
 }
@@ -298,7 +330,7 @@ int nlc_batch_leaves(nlc_batch* b, uint64_t* out) {
         CtxGuard g(b->ctx);
         // the device keeps the LDE column-major; plonky2's row-major leaves are made on demand, a slab at a time
         nlc_ctx* ctx = b->ctx;
-        const size_t N = (size_t)1 << (b->log_n + b->rate_bits);
+        const size_t N = b->n_local();
         size_t slab = ((size_t)8 << 20) / b->W; // ~64 MiB of rows
         if (slab < 32) slab = 32;
         if (slab > N) slab = N;
@@ -324,6 +356,7 @@ int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step,
     return nlc_guarded(b->ctx, [&] {
         nlc_ctx* ctx = b->ctx;
         CtxGuard g(ctx);
+        NLC_CHECK(b->shard_log == 0, "get_lde_values on a coset shard: rows of other shards live on other GPUs");
         if (!m) return;
         DevBuf idx_dev(ctx, m), rows(ctx, m * b->W);
         h2d(ctx, idx_dev.p, idx, m * sizeof(u64));
@@ -337,6 +370,7 @@ int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t*
     return nlc_guarded(b->ctx, [&] {
         nlc_ctx* ctx = b->ctx;
         CtxGuard g(ctx);
+        NLC_CHECK(b->shard_log == 0, "MerkleTree::prove on a coset shard is not supported");
         const int log_N = b->log_n + b->rate_bits;
         NLC_CHECK(leaf_index < ((size_t)1 << log_N), "leaf index out of range");
         const size_t sib = (size_t)4 * (log_N - b->cap_height);

@@ -12,6 +12,12 @@ struct nlc_batch {
     u64* digests = nullptr; // plonky2 interleaved layout
     u64* cap = nullptr;     // 2^cap x 4
     size_t n_digest_words = 0;
+    // Coset shard: this batch holds leaves [shard_idx, shard_idx+1) * (N >> shard_log) only,
+    // i.e. 2^(rate_bits - shard_log) whole cosets and 2^(cap_height - shard_log) whole cap subtrees.
+    int shard_log = 0;
+    size_t shard_idx = 0;
+    size_t n_local() const { return ((size_t)1 << (log_n + rate_bits)) >> shard_log; }
+    int cap_local() const { return cap_height - shard_log; }
 };
 
 struct nlc_tree {
@@ -25,7 +31,8 @@ struct nlc_tree {
 };
 
 // ---- commit.cu ----
-nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height);
+nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height, int shard_log = 0,
+                       size_t shard_idx = 0);
 void batch_release(nlc_batch* b);
 void batch_ifft_values(nlc_batch* b, const u64* values_dev);
 void batch_lde_and_tree(nlc_batch* b);

@@ -87,23 +87,29 @@ __global__ void __launch_bounds__(256) k_eval_ext(const u64* __restrict__ coeffs
 
 } // namespace
 
-nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height) {
+nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap_height, int shard_log,
+                       size_t shard_idx) {
     NLC_CHECK(W > 0, "PolynomialBatch: at least one polynomial required");
     NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
     NLC_CHECK(cap_height >= 0 && cap_height <= log_n + rate_bits, "cap_height should be at most log2(leaves.len())");
+    NLC_CHECK(shard_log >= 0 && shard_log <= rate_bits && shard_log <= cap_height,
+              "coset sharding needs n_shards <= 2^rate_bits and n_shards <= 2^cap_height");
+    NLC_CHECK(shard_idx < ((size_t)1 << shard_log), "shard index out of range");
     nlc_batch* b = new nlc_batch();
     b->ctx = ctx;
     b->W = W;
     b->log_n = log_n;
     b->rate_bits = rate_bits;
     b->cap_height = cap_height;
-    const size_t n = (size_t)1 << log_n, N = n << rate_bits;
+    b->shard_log = shard_log;
+    b->shard_idx = shard_idx;
+    const size_t n = (size_t)1 << log_n, N = b->n_local();
     try {
         b->coeffs = ctx->dmalloc(W * n);
         b->lde = ctx->dmalloc(W * N);
-        b->n_digest_words = 8 * (N - ((size_t)1 << cap_height));
+        b->n_digest_words = 8 * (N - ((size_t)1 << b->cap_local()));
         b->digests = ctx->dmalloc(b->n_digest_words);
-        b->cap = ctx->dmalloc((size_t)4 << cap_height);
+        b->cap = ctx->dmalloc((size_t)4 << b->cap_local());
     } catch (...) {
         batch_release(b);
         throw;
@@ -125,13 +131,17 @@ void batch_release(nlc_batch* b) {
 void batch_lde_and_tree(nlc_batch* b) {
     nlc_ctx* ctx = b->ctx;
     const int log_n = b->log_n, r = b->rate_bits;
-    const size_t n = (size_t)1 << log_n, N = n << r;
+    const size_t n = (size_t)1 << log_n, N = b->n_local();
     u64* scratch = nullptr;
     const size_t sw = ntt_scratch_words(b->W, log_n);
     if (sw) scratch = ctx->dmalloc(sw);
     const u64 w_N = gl::h_root_of_unity(log_n + r);
+    const size_t cosets_local = ((size_t)1 << r) >> b->shard_log, kr0 = b->shard_idx * cosets_local;
     ctx->phase_begin(1);
     for (size_t k = 0; k < ((size_t)1 << r); k++) {
+        size_t kr = 0; // bitrev_r(k): coset k is the leaf range [kr*n, (kr+1)*n)
+        for (int t = 0; t < r; t++) kr |= ((k >> t) & 1) << (r - 1 - t);
+        if (kr < kr0 || kr >= kr0 + cosets_local) continue; // another shard's coset
         NttJob job;
         job.src = b->coeffs;
         job.src_stride = n;
@@ -141,16 +151,14 @@ void batch_lde_and_tree(nlc_batch* b) {
         job.cols = true;
         job.dst = b->lde;
         job.dst_stride = N;
-        size_t kr = 0; // bitrev_r(k)
-        for (int t = 0; t < r; t++) kr |= ((k >> t) & 1) << (r - 1 - t);
-        job.row_base = kr * n;
+        job.row_base = (kr - kr0) * n;
         job.col0 = 0;
         job.scratch = scratch;
         ntt_run(ctx, job);
     }
     ctx->phase_end();
     ctx->dfree(scratch);
-    merkle_build(ctx, b->lde, N, b->W, N, b->cap_height, b->digests, b->cap);
+    merkle_build(ctx, b->lde, N, b->W, N, b->cap_local(), b->digests, b->cap);
 }
 
 // "IFFT" of from_values: values (W x n column-major, device) -> b->coeffs.
@@ -195,7 +203,7 @@ void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev) {
 
 void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev) {
     if (!n_rows) return;
-    const size_t N = (size_t)1 << (b->log_n + b->rate_bits);
+    const size_t N = b->n_local();
     dim3 grid((unsigned)((n_rows + 31) / 32), (unsigned)((b->W + 31) / 32));
     NLC_LAUNCH(b->ctx, k_leaf_rows, grid, dim3(32, 8), 0, b->lde, b->W, N, row0, n_rows, out_dev);
 }

@@ -301,20 +301,30 @@ class _BatchTree:
 
     def __init__(self, batch: "PolynomialBatch"):
         self._b = batch
-        self._cap = self._leaves = self._digests = None
+        self._cap = self._local_cap = self._leaves = self._digests = None
+
+    @property
+    def local_cap(self) -> np.ndarray:
+        """This shard's cap entries (the whole cap when the batch is not sharded)."""
+        if self._local_cap is None:
+            out = np.zeros(((1 << self._b.cap_height) // self._b.n_shards, 4), np.uint64)
+            self._b._ctx._check(_ffi.lib().nlc_batch_cap(self._b._h, _p(out)))
+            self._local_cap = out
+        return self._local_cap
 
     @property
     def cap(self) -> np.ndarray:
         if self._cap is None:
-            out = np.zeros((1 << self._b.cap_height, 4), np.uint64)
-            self._b._ctx._check(_ffi.lib().nlc_batch_cap(self._b._h, _p(out)))
-            self._cap = out
+            if self._b.n_shards > 1:
+                raise NlcError("sharded batch: the full MerkleCap exists only after sharding.gather_cap()")
+            self._cap = self.local_cap
         return self._cap
 
     @property
     def leaves(self) -> np.ndarray:
+        """Rows of this shard's leaf range (all N rows when not sharded)."""
         if self._leaves is None:
-            out = np.zeros((self._b.lde_size, self._b.n_polys), np.uint64)
+            out = np.zeros((self._b.lde_size // self._b.n_shards, self._b.n_polys), np.uint64)
             self._b._ctx._check(_ffi.lib().nlc_batch_leaves(self._b._h, _p(out)))
             self._leaves = out
         return self._leaves
@@ -322,7 +332,7 @@ class _BatchTree:
     @property
     def digests(self) -> np.ndarray:
         if self._digests is None:
-            out = np.zeros((2 * (self._b.lde_size - (1 << self._b.cap_height)), 4), np.uint64)
+            out = np.zeros((2 * (self._b.lde_size - (1 << self._b.cap_height)) // self._b.n_shards, 4), np.uint64)
             self._b._ctx._check(_ffi.lib().nlc_batch_digests(self._b._h, _p(out)))
             self._digests = out
         return self._digests
@@ -574,6 +584,7 @@ class PolynomialBatch:
         self._ctx, self._h = ctx, handle
         self.n_polys, self.degree_log, self.rate_bits, self.cap_height = n_polys, degree_log, rate_bits, cap_height
         self.blinding = False
+        self.shard_idx, self.n_shards = 0, 1
         self.merkle_tree = _BatchTree(self)
         self._polys = None
 
@@ -600,6 +611,33 @@ class PolynomialBatch:
                     fft_root_table=None, ctx=None):
         """PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)."""
         return cls._commit("nlc_commit_from_coeffs", polynomials, rate_bits, blinding, cap_height, ctx)
+
+    @classmethod
+    def from_values_sharded(cls, values, rate_bits: int, blinding: bool, cap_height: int, shard_idx=None,
+                            n_shards=None, group=None, ctx=None):
+        """this rank's coset shard of from_values, then the all-gather of the cap entries.
+
+        With torch.distributed initialised, shard_idx / n_shards default to the rank / world size of `group` and
+        the returned batch's merkle_tree.cap is the full MerkleCap; called with explicit shard_idx / n_shards and no
+        process group it returns the bare shard (merkle_tree.local_cap)."""
+        from . import sharding
+        if blinding:
+            raise NlcError("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)")
+        distributed = shard_idx is None
+        if distributed:
+            shard_idx, n_shards = sharding.rank_and_world(group)
+        sharding.check_plan(rate_bits, cap_height, n_shards)
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(values)
+        log_n = _log2_strict(n)
+        h = vp()
+        ctx._check(_ffi.lib().nlc_commit_from_values_shard(ctx._h, table, len(arrs), log_n, rate_bits, cap_height,
+                                                           shard_idx, n_shards, C.byref(h)))
+        b = cls(ctx, h, len(arrs), log_n, rate_bits, cap_height)
+        b.shard_idx, b.n_shards = shard_idx, n_shards
+        if distributed:
+            b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
+        return b
 
     @classmethod
     def from_device(cls, dev_ptr: int, n_polys: int, degree_log: int, rate_bits: int, cap_height: int,

@@ -1,0 +1,78 @@
+"""Host logic of the coset-sharded commit.
+
+A commit of N = n * 2^rate_bits leaves splits by LDE coset: after the index bit reversal coset k occupies the
+contiguous leaf range [bitrev_r(k) * n, +n), so rank g of G = 2^s ranks owns the leaves [g, g+1) * N / G, i.e.
+2^(rate_bits - s) whole cosets and 2^(cap_height - s) whole cap subtrees.  Each rank computes its shard with
+nlc_commit_from_values_shard (no communication), and the only exchange on the path is the all-gather of the
+cap entries, 32 bytes each: NCCL over NVLink on GPUs, gloo in the CPU tests of this logic.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+class ShardPlanError(ValueError):
+    pass
+
+
+def check_plan(rate_bits: int, cap_height: int, n_shards: int) -> int:
+    """Validate a shard count; returns log2(n_shards)."""
+    if n_shards < 1 or n_shards & (n_shards - 1):
+        raise ShardPlanError(f"n_shards = {n_shards} must be a power of two")
+    s = n_shards.bit_length() - 1
+    if s > rate_bits:
+        raise ShardPlanError(f"coset sharding needs n_shards <= 2^rate_bits = {1 << rate_bits} (got {n_shards}); "
+                             "shard independent commits across the remaining GPUs instead")
+    if s > cap_height:
+        raise ShardPlanError(f"coset sharding needs n_shards <= 2^cap_height = {1 << cap_height} (got {n_shards})")
+    return s
+
+
+def leaf_range(log_n: int, rate_bits: int, shard_idx: int, n_shards: int):
+    """[first, last) leaf (index-bit-reversed LDE row) owned by a shard."""
+    per = (1 << (log_n + rate_bits)) // n_shards
+    return shard_idx * per, (shard_idx + 1) * per
+
+
+def cosets_of(rate_bits: int, shard_idx: int, n_shards: int):
+    """The cosets k (LDE point i = m * 2^r + k) a shard evaluates: those with bitrev_r(k) in its range."""
+    per = (1 << rate_bits) // n_shards
+    out = []
+    for k in range(1 << rate_bits):
+        kr = int(format(k, f"0{rate_bits}b")[::-1], 2) if rate_bits else 0
+        if shard_idx * per <= kr < (shard_idx + 1) * per:
+            out.append(k)
+    return out
+
+
+def cap_slice(cap_height: int, shard_idx: int, n_shards: int) -> slice:
+    per = (1 << cap_height) // n_shards
+    return slice(shard_idx * per, (shard_idx + 1) * per)
+
+
+def rank_and_world(group=None):
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise ShardPlanError("from_values_sharded without shard_idx needs an initialised torch.distributed group")
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def gather_cap(local_cap: np.ndarray, cap_height: int, group=None, device=None) -> np.ndarray:
+    """all_gather of the shards' cap entries -> the full MerkleCap (2^cap_height x 4), identical on every rank."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    per = (1 << cap_height) // world
+    local = np.ascontiguousarray(local_cap, dtype=np.uint64).reshape(per, 4)
+    backend = dist.get_backend(group)
+    t = torch.from_numpy(local.view(np.int64).copy())
+    if backend == "nccl":
+        t = t.cuda(device if device is not None and device >= 0 else torch.cuda.current_device())
+    out = torch.empty((world * per, 4), dtype=torch.int64, device=t.device)
+    dist.all_gather_into_tensor(out, t, group=group)
+    return out.cpu().numpy().view(np.uint64).reshape(1 << cap_height, 4)
+
+
+def assemble(parts):
+    """Concatenate per-shard arrays (cap entries, digests or leaf rows) in shard order: the single-GPU array."""
+    return np.concatenate(list(parts), axis=0)
