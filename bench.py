@@ -177,7 +177,7 @@ def run_ours(args, rank, local_rank, world):
     n, N = 1 << log_n, 1 << (log_n + r)
     elems = W * n
     host = torch.empty((W, n), dtype=torch.int64).pin_memory()
-    host.numpy().view(np.uint64)[:] = synth_values(W, n, 0xC0FFEE + 1 + rank)
+    host.numpy().view(np.uint64)[:] = synth_values(W, n, 0xC0FFEE + 1 + (0 if args.shard_commit else rank))
     dev = host.cuda(non_blocking=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     cap_host = np.zeros((1 << cap, 4), np.uint64)
@@ -194,18 +194,40 @@ def run_ours(args, rank, local_rank, world):
             L.nlc_batch_free(state["batch"])
             state["batch"] = None
 
+    sharded = bool(args.shard_commit) and world > 1
+    if sharded:  # ONE commit split by coset over the ranks, cap entries all-gathered over NCCL
+        pkg.sharding.check_plan(r, cap, world)
+        cap_local = torch.empty(((1 << cap) // world, 4), dtype=torch.int64, device="cuda")
+        cap_full = torch.empty((1 << cap, 4), dtype=torch.int64, device="cuda")
+        cudart = C.CDLL("libcudart.so.12")
+
     def step_resident():
         free_prev()
         h = ffi.vp()
-        ctx._check(L.nlc_commit_from_values_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, C.byref(h)))
+        if sharded:
+            ctx._check(L.nlc_commit_from_values_shard_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, rank, world,
+                                                          C.byref(h)))
+            # cudaMemcpyAsync(dst, src, bytes, D2D = 3, stream): the shard's cap entries into the all-gather input
+            cudart.cudaMemcpyAsync(C.c_void_p(cap_local.data_ptr()), C.c_void_p(L.nlc_batch_cap_dev(h)),
+                                   C.c_size_t(cap_local.numel() * 8), 3, C.c_void_p(stream.cuda_stream))
+            dist.all_gather_into_tensor(cap_full, cap_local)
+        else:
+            ctx._check(L.nlc_commit_from_values_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, C.byref(h)))
         state["batch"] = h
 
     def step_e2e():
         free_prev()
         h = ffi.vp()
-        ctx._check(L.nlc_commit_from_values(ctx._h, col_table, W, log_n, r, cap, C.byref(h)))
-        state["batch"] = h
-        ctx._check(L.nlc_batch_cap(h, cap_host.ctypes.data_as(ffi.u64p)))
+        if sharded:
+            ctx._check(L.nlc_commit_from_values_shard(ctx._h, col_table, W, log_n, r, cap, rank, world, C.byref(h)))
+            state["batch"] = h
+            local = np.zeros(((1 << cap) // world, 4), np.uint64)
+            ctx._check(L.nlc_batch_cap(h, local.ctypes.data_as(ffi.u64p)))
+            cap_host[:] = pkg.sharding.gather_cap(local, cap, device=local_rank)
+        else:
+            ctx._check(L.nlc_commit_from_values(ctx._h, col_table, W, log_n, r, cap, C.byref(h)))
+            state["batch"] = h
+            ctx._check(L.nlc_batch_cap(h, cap_host.ctypes.data_as(ffi.u64p)))
 
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
@@ -233,7 +255,7 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t.item()) / args.steps
-    value = world * elems / (ms_per_step * 1e-3)
+    value = (1 if sharded else world) * elems / (ms_per_step * 1e-3)
 
     # ---- per-phase device time (plonky2 TimingTree scopes) for the roofline of the dominant kernel ----
     ctx.timing_enable(True)
@@ -273,7 +295,7 @@ def run_ours(args, rank, local_rank, world):
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_val = world * elems / (float(te.item()) / args.steps)
+    e2e_val = (1 if sharded else world) * elems / (float(te.item()) / args.steps)
     free_prev()
 
     cpu_baseline = None
@@ -291,10 +313,11 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0:
         line = {"metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": value,
                 "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r, "cap_height": cap,
-                           "parallelism": f"instances x{world}", "l2": "flushed between timed iterations (256 MiB write)"},
+                           "parallelism": (f"one commit, coset shards x{world} + NCCL all-gather of the cap" if sharded
+                                           else f"instances x{world}"), "l2": "flushed between timed iterations (256 MiB write)"},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_val, "unit": "elements/s", "h2d_bytes_per_step": 8 * elems,
                         "d2h_bytes_per_step": 32 << cap, "ms_per_step": float(te.item()) / args.steps * 1e3},
@@ -315,6 +338,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard-commit", action="store_true",
+                    help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
+                         "of one independent commit per rank")
     ap.add_argument("--ref-sample-log-rows", type=int, default=13,
                     help="reference arm: rows of the bounded sample (log2); throughput is per input element")
     args = ap.parse_args()
