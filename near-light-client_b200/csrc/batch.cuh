@@ -36,6 +36,9 @@ nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap
 void batch_release(nlc_batch* b);
 void batch_ifft_values(nlc_batch* b, const u64* values_dev);
 void batch_lde_and_tree(nlc_batch* b);
+void batch_ifft_cols(nlc_batch* b, const u64* values_dev, size_t c0, size_t nc);
+void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc);
+void batch_tree(nlc_batch* b);
 void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
                           u64* out_dev);
 void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev);

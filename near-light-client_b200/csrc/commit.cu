@@ -127,13 +127,15 @@ void batch_release(nlc_batch* b) {
     delete b;
 }
 
-// "FFT + blinding" + "transpose LDEs" + reverse_index_bits + "build Merkle tree" of from_coeffs.
-void batch_lde_and_tree(nlc_batch* b) {
+// "FFT + blinding" (+ "transpose LDEs" + reverse_index_bits, which never happen) of from_coeffs for the columns
+// [c0, c0 + nc): columns are independent until the leaf hash, so a host-fed commit can run this on one chunk while
+// the next chunk is still crossing PCIe.
+void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc) {
     nlc_ctx* ctx = b->ctx;
     const int log_n = b->log_n, r = b->rate_bits;
     const size_t n = (size_t)1 << log_n, N = b->n_local();
     u64* scratch = nullptr;
-    const size_t sw = ntt_scratch_words(b->W, log_n);
+    const size_t sw = ntt_scratch_words(nc, log_n);
     if (sw) scratch = ctx->dmalloc(sw);
     const u64 w_N = gl::h_root_of_unity(log_n + r);
     const size_t cosets_local = ((size_t)1 << r) >> b->shard_log, kr0 = b->shard_idx * cosets_local;
@@ -143,39 +145,49 @@ void batch_lde_and_tree(nlc_batch* b) {
         for (int t = 0; t < r; t++) kr |= ((k >> t) & 1) << (r - 1 - t);
         if (kr < kr0 || kr >= kr0 + cosets_local) continue; // another shard's coset
         NttJob job;
-        job.src = b->coeffs;
+        job.src = b->coeffs + c0 * n;
         job.src_stride = n;
-        job.n_cols = b->W;
+        job.n_cols = nc;
         job.log_n = log_n;
         job.pre_shift = gl::h_mul(gl::GENERATOR, gl::h_pow(w_N, k));
         job.cols = true;
         job.dst = b->lde;
         job.dst_stride = N;
         job.row_base = (kr - kr0) * n;
-        job.col0 = 0;
+        job.col0 = c0;
         job.scratch = scratch;
         ntt_run(ctx, job);
     }
     ctx->phase_end();
     ctx->dfree(scratch);
-    merkle_build(ctx, b->lde, N, b->W, N, b->cap_local(), b->digests, b->cap);
 }
 
-// "IFFT" of from_values: values (W x n column-major, device) -> b->coeffs.
-void batch_ifft_values(nlc_batch* b, const u64* values_dev) {
+// "build Merkle tree"
+void batch_tree(nlc_batch* b) {
+    const size_t N = b->n_local();
+    merkle_build(b->ctx, b->lde, N, b->W, N, b->cap_local(), b->digests, b->cap);
+}
+
+void batch_lde_and_tree(nlc_batch* b) {
+    batch_lde_cols(b, 0, b->W);
+    batch_tree(b);
+}
+
+// "IFFT" of from_values for the columns [c0, c0 + nc): values (column-major, device; column c0 first) -> b->coeffs.
+void batch_ifft_cols(nlc_batch* b, const u64* values_dev, size_t c0, size_t nc) {
     nlc_ctx* ctx = b->ctx;
     const size_t n = (size_t)1 << b->log_n;
     u64* scratch = nullptr;
-    const size_t sw = ntt_scratch_words(b->W, b->log_n);
+    const size_t sw = ntt_scratch_words(nc, b->log_n);
     if (sw) scratch = ctx->dmalloc(sw);
     NttJob job;
     job.src = values_dev;
     job.src_stride = n;
-    job.n_cols = b->W;
+    job.n_cols = nc;
     job.log_n = b->log_n;
     job.inverse = true;
     job.rows = false;
-    job.dst = b->coeffs;
+    job.dst = b->coeffs + c0 * n;
     job.dst_stride = n;
     job.scratch = scratch;
     ctx->phase_begin(0);
@@ -183,6 +195,7 @@ void batch_ifft_values(nlc_batch* b, const u64* values_dev) {
     ctx->phase_end();
     ctx->dfree(scratch);
 }
+void batch_ifft_values(nlc_batch* b, const u64* values_dev) { batch_ifft_cols(b, values_dev, 0, b->W); }
 
 void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
                           u64* out_dev) {

@@ -41,6 +41,18 @@ struct nlc_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    // host-fed commits upload column chunks on copy_stream while the compute stream transforms the previous chunk
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_ready = nullptr;
+    std::vector<cudaEvent_t> chunk_events;
+    cudaEvent_t chunk_event(size_t i) {
+        while (chunk_events.size() <= i) {
+            cudaEvent_t e;
+            NLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            chunk_events.push_back(e);
+        }
+        return chunk_events[i];
+    }
     std::recursive_mutex mu;
     std::string err;
     std::atomic<u64> launches{0};
