@@ -95,31 +95,23 @@ k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) 
     reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(o[2], o[3]);
 }
 
-// The top of every cap subtree, layers [layer0, sub_height): one CTA per subtree, one permutation per
-// half-warp (transcript::warp_permute), __syncthreads between layers.  Up there a layer has fewer nodes
-// than the GPU has sub-partitions, so the latency of one permutation is all that matters: the 12-lane
-// form is ~8x shorter than the one-thread form, and the layers cost no launches.
-constexpr int TOP_THREADS = 1024;
-constexpr size_t TOP_PARENTS = TOP_THREADS / 16; // parents per subtree the top kernel finishes in one pass per layer
-__global__ void __launch_bounds__(TOP_THREADS) k_merkle_top(u64* digests, u64* cap, TreeGeom g, int layer0) {
+// Narrow layers (fewer parents than the GPU has threads): one permutation per half-warp
+// (transcript::warp_permute: 12 lanes, S-boxes across lanes, MDS by shuffles), two per warp, spread over all SMs.
+// There the latency of ONE permutation is all that matters, and the 12-lane form is several times shorter than
+// the one-thread form (measured: 32 us per layer with one thread per parent, 36 us with all of a subtree's
+// half-warps crowded onto one SM).
+constexpr int COOP_THREADS = 128;
+constexpr size_t COOP_MAX_PARENTS = 8192;
+__global__ void __launch_bounds__(COOP_THREADS) k_merkle_level_coop(u64* digests, u64* cap, TreeGeom g, int layer,
+                                                                     size_t n_parents) {
     const int lane = threadIdx.x & 31, l16 = lane & 15;
-    const size_t group = (threadIdx.x >> 4), n_groups = TOP_THREADS / 16;
-    const size_t sub = blockIdx.x;
-    for (int layer = layer0; layer < g.sub_height; layer++) {
-        const size_t per_sub = (size_t)1 << (g.sub_height - layer - 1); // parents of this layer in one subtree
-        const size_t passes = (per_sub + n_groups - 1) / n_groups;
-        for (size_t pass = 0; pass < passes; pass++) {
-            const size_t jl = pass * n_groups + group;
-            const bool active = jl < per_sub;
-            const size_t j = sub * per_sub + (active ? jl : 0);
-            const u64* kids = node_slot(digests, cap, g, layer, 2 * j);
-            u64 x = 0;
-            if (active && l16 < 8) x = kids[l16];
-            x = transcript::warp_permute(x, lane);
-            if (active && l16 < 4) node_slot(digests, cap, g, layer + 1, j)[l16] = x;
-        }
-        __syncthreads();
-    }
+    const size_t j = (blockIdx.x * (size_t)COOP_THREADS + threadIdx.x) >> 4; // one parent per half-warp
+    const bool active = j < n_parents;
+    const u64* kids = node_slot(digests, cap, g, layer, 2 * (active ? j : 0));
+    u64 x = 0;
+    if (active && l16 < 8) x = kids[l16];
+    x = transcript::warp_permute(x, lane);
+    if (active && l16 < 4) node_slot(digests, cap, g, layer + 1, j)[l16] = x;
 }
 
 // MerkleTree::get + MerkleTree::prove for many indices: out[i*stride + offset ..] = leaf row, siblings.
@@ -203,15 +195,15 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
                    leaf_len, (size_t)1, g, digests, cap);
     ctx->phase_end();
     ctx->phase_begin(3);
-    int layer = 0;
-    // wide layers: one thread per parent; once a subtree's layer fits one pass of half-warp permutations, one CTA finishes it
-    for (; layer < g.sub_height && ((size_t)1 << (g.sub_height - layer - 1)) > TOP_PARENTS; layer++) {
-        size_t parents = n_leaves >> (layer + 1);
-        NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
-                   digests, cap, g, layer, parents);
+    for (int layer = 0; layer < g.sub_height; layer++) {
+        const size_t parents = n_leaves >> (layer + 1);
+        if (parents > COOP_MAX_PARENTS)
+            NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
+                       digests, cap, g, layer, parents);
+        else
+            NLC_LAUNCH(ctx, k_merkle_level_coop, (unsigned)((parents * 16 + COOP_THREADS - 1) / COOP_THREADS),
+                       COOP_THREADS, 0, digests, cap, g, layer, parents);
     }
-    if (layer < g.sub_height)
-        NLC_LAUNCH(ctx, k_merkle_top, (unsigned)((size_t)1 << cap_height), TOP_THREADS, 0, digests, cap, g, layer);
     ctx->phase_end();
 }
 

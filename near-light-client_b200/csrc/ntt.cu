@@ -22,6 +22,9 @@ namespace {
 
 enum { KIND_ROOTS = 1, KIND_TW = 2, KIND_PW = 3 };
 constexpr int NTT_THREADS = 256;
+#ifndef NTT_MINB
+#define NTT_MINB 4
+#endif
 
 __device__ __forceinline__ u32 brev(u32 x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
 
@@ -127,7 +130,7 @@ __device__ __forceinline__ void fft_tile(u64* sm, int S, u32 plan, int log_tr, u
 }
 
 // One digit of a 2^m block, strided ("hi") pass.  smem: [2^S][T].
-__global__ void __launch_bounds__(NTT_THREADS)
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, size_t dst_stride, int m, int S,
          int log_T, u32 plan, const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots) {
     extern __shared__ u64 sm[];
@@ -163,7 +166,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
 //   ones whose outputs interleave into contiguous Gb-element segments.
 enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2 };
 template <int MODE>
-__global__ void __launch_bounds__(NTT_THREADS)
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_Gb, int log_Gc, u32 plan,
          size_t n_cols, const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale,
          const u64* __restrict__ roots, u64* __restrict__ dst, size_t dst_stride, size_t row_width, size_t row_base,
