@@ -110,6 +110,16 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_traffic(workload: str, kernel: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full`
+    capture of this workload (profiles/traffic.json names the capture); None when no capture exists."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[workload][kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def algorithmic_bytes(log_n, W, r, cap):
     n, N = 1 << log_n, 1 << (log_n + r)
     return {
@@ -142,8 +152,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": val,
             "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
-            "data": "synthetic", "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r,
-                                            "cap_height": cap},
+            "data": "synthetic", "config": {"workload": args.workload, "rows": 1 << full_log_n, "cols": W, "rate_bits": r,
+                                            "cap_height": cap, "sample_rows": n},
             "cpu_baseline": {"value": val, "unit": "elements/s", "cores": cores, "kind": "port",
                              "sample": f"{args.steps} commits of 2^{log_n} of the workload's 2^{full_log_n} rows x {W} cols, "
                                        f"rate_bits {r} (same per-row work; OpenMP over columns/rows/subtrees)"},
@@ -273,7 +283,8 @@ def run_ours(args, rank, local_rank, world):
     achieved = ab["leaf_hash"] / (leaf_ms * 1e-3) / 1e9 if leaf_ms > 0 else 0.0
     perms = N * ((W + 7) // 8 if W > 4 else 0)
     roofline = {"bound": "hbm", "kernel": "k_leaf_hash (Poseidon sponge over LDE rows; INT-pipe limited)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(args.workload, "k_leaf_hash"), "algorithmic_bytes_per_launch": ab["leaf_hash"],
                 "peak_source": peak_src, "ms_per_launch": leaf_ms,
                 "poseidon_perms_per_s": perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None}
     roofline_ntt = {"bound": "hbm", "kernel": "k_ntt_* (iFFT + 2^r coset NTTs into leaf rows)",
