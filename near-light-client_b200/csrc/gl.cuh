@@ -117,6 +117,30 @@ __device__ __forceinline__ uint64_t mul_nc(uint64_t a, uint64_t b) {
     return reduce128_dev_nc((uint64_t)p, (uint64_t)(p >> 64));
 }
 __device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return dcanon(mul_nc(a, b)); }
+
+// x * 2^s (mod p) for a compile-time s in [0, 96), canonical in, canonical out, no multiplier: 2 generates the
+// 192-element subgroup of F_p^* (2^96 == -1), so every root of unity of order <= 64 is a power of two and the
+// twiddles inside a radix-2^R register step are shifts.  z = x << (s % 32) is three words; the word offset
+// s / 32 is folded with 2^64 == 2^32 - 1, 2^96 == -1, 2^128 == -2^32 into a signed 128-bit sum whose top word
+// tw in {-1,0,1} is closed exactly as in reduce128_dev_nc.
+__device__ __forceinline__ uint64_t mul_pow2(uint64_t x, const int s) {
+    if (s == 0) return x;
+    const int q = s >> 5, r = s & 31;
+    const uint32_t x0 = (uint32_t)x, x1 = (uint32_t)(x >> 32);
+    const uint64_t z0 = r ? (uint32_t)(x0 << r) : x0;
+    const uint64_t z1 = r ? __funnelshift_l(x0, x1, r) : x1;
+    const uint64_t z2 = r ? (x1 >> (32 - r)) : 0u;
+    __int128 V;
+    if (q == 0)
+        V = (__int128)(z0 | (z1 << 32)) + (__int128)(z2 << 32) - (__int128)z2;
+    else if (q == 1)
+        V = ((__int128)(z0 + z1) << 32) - (__int128)z1 - (__int128)z2;
+    else
+        V = (((__int128)z0 - (__int128)z2) << 32) - (__int128)z0 - (__int128)z1;
+    const int tw = (int)(V >> 64);
+    const uint64_t adj = ((uint64_t)(uint32_t)(tw >> 31) << 32) | (uint32_t)(-tw);
+    return dcanon((uint64_t)V + adj);
+}
 __device__ __forceinline__ uint64_t sqr_nc(uint64_t a) { return mul_nc(a, a); }
 
 __device__ __forceinline__ uint64_t pow(uint64_t b, uint64_t e) {
