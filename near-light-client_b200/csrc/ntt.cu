@@ -50,8 +50,11 @@ __global__ void k_tw_table(u64* out, int m, int S, u64 root) {
 // occupies the contiguous block k, which makes the final order the same index-bit-reversed order the radix-2
 // cascade gives -- at (S/R - 1) full multiplications per element between steps instead of S/2.
 // `roots` holds all 2^S powers of w_{2^S} (or its inverse).
-template <int R>
-__device__ __forceinline__ void dft_regs(u64 (&v)[1 << R], const u64* __restrict__ roots, int S) {
+// The twiddles INSIDE a register step are powers of w_{2^R} = w_16^(2^(4-R)), and plonky2's w_16 =
+// primitive_root_of_unity(4) is 2^156 (2 has order 192 in F_p^*): multiplication by w_{2^R}^e is a shift by
+// s = 156 e 2^(4-R) mod 192 bits (gl::mul_pow2), negated when s >= 96 (2^96 == -1) by swapping the subtraction.
+template <int R, bool INV>
+__device__ __forceinline__ void dft_regs(u64 (&v)[1 << R]) {
 #pragma unroll
     for (int t = 0; t < R; t++) {
         const int half = 1 << (R - 1 - t);
@@ -60,9 +63,9 @@ __device__ __forceinline__ void dft_regs(u64 (&v)[1 << R], const u64* __restrict
             if (k & half) continue;
             const u64 a = v[k], c = v[k + half];
             v[k] = gl::dadd(a, c);
-            const u64 d = gl::dsub(a, c);
-            const int e = (k & (half - 1)) << t; // exponent of w_{2^R}
-            v[k + half] = e ? gl::mul(d, __ldg(roots + ((size_t)e << (S - R)))) : d;
+            const int e = ((k & (half - 1)) << t) << (4 - R); // exponent of w_16
+            const int s = ((INV ? 192 - 156 : 156) * e) % 192;
+            v[k + half] = s >= 96 ? gl::mul_pow2(gl::dsub(c, a), s - 96) : gl::mul_pow2(gl::dsub(a, c), s);
         }
     }
 }
@@ -71,7 +74,7 @@ __device__ __forceinline__ u32 pad16(u32 i) { return i + (i >> 4); } // LO layou
 
 // HI layout: element i of transform t at sm[i*T + t] (t fastest: what the strided gather delivers);
 // LO layout: element i of transform g at sm[g*pitch + pad16(i)].
-template <int R, bool HI>
+template <int R, bool HI, bool INV>
 __device__ __forceinline__ void fft_step(u64* sm, int S, int st, int log_tr, u32 pitch, const u64* __restrict__ roots) {
     const int L_log = S - st, s_log = L_log - R;
     const u32 tasks = ((u32)1 << (S + log_tr)) >> R;
@@ -95,7 +98,7 @@ __device__ __forceinline__ void fft_step(u64* sm, int S, int st, int log_tr, u32
             const u32 i = i0 + ((u32)k << s_log);
             v[k] = sm[HI ? (i << log_tr) + t : t * pitch + pad16(i)];
         }
-        dft_regs<R>(v, roots, S);
+        dft_regs<R, INV>(v);
         if (s_log > 0) {
 #pragma unroll
             for (int k = 1; k < (1 << R); k++) {
@@ -112,17 +115,17 @@ __device__ __forceinline__ void fft_step(u64* sm, int S, int st, int log_tr, u32
 }
 
 // radix plan of a 2^S-point tile transform, packed 4 bits per step (host side: plan_steps)
-template <bool HI>
+template <bool HI, bool INV>
 __device__ __forceinline__ void fft_tile(u64* sm, int S, u32 plan, int log_tr, u32 pitch, const u64* __restrict__ roots) {
     int st = 0;
     while (plan) {
         const int R = plan & 15;
         plan >>= 4;
         switch (R) {
-        case 4: fft_step<4, HI>(sm, S, st, log_tr, pitch, roots); break;
-        case 3: fft_step<3, HI>(sm, S, st, log_tr, pitch, roots); break;
-        case 2: fft_step<2, HI>(sm, S, st, log_tr, pitch, roots); break;
-        default: fft_step<1, HI>(sm, S, st, log_tr, pitch, roots); break;
+        case 4: fft_step<4, HI, INV>(sm, S, st, log_tr, pitch, roots); break;
+        case 3: fft_step<3, HI, INV>(sm, S, st, log_tr, pitch, roots); break;
+        case 2: fft_step<2, HI, INV>(sm, S, st, log_tr, pitch, roots); break;
+        default: fft_step<1, HI, INV>(sm, S, st, log_tr, pitch, roots); break;
         }
         st += R;
         __syncthreads();
@@ -130,6 +133,7 @@ __device__ __forceinline__ void fft_tile(u64* sm, int S, u32 plan, int log_tr, u
 }
 
 // One digit of a 2^m block, strided ("hi") pass.  smem: [2^S][T].
+template <bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, size_t dst_stride, int m, int S,
          int log_T, u32 plan, const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots) {
@@ -152,7 +156,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
         sm[idx] = v;
     }
     __syncthreads();
-    fft_tile<true>(sm, S, plan, log_T, 0, roots);
+    fft_tile<true, INV>(sm, S, plan, log_T, 0, roots);
     for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 t = idx & (T - 1), pos = idx >> log_T;
         size_t off = ((size_t)pos << L) + low0 + t;
@@ -165,7 +169,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
 //   COLS / ROWS : the Gb blocks are consecutive; NATURAL : Gc = 1 and the blocks are the bit-reversal-related
 //   ones whose outputs interleave into contiguous Gb-element segments.
 enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2 };
-template <int MODE>
+template <int MODE, bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_Gb, int log_Gc, u32 plan,
          size_t n_cols, const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale,
@@ -192,7 +196,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
         sm[g * pitch + pad16(e)] = v;
     }
     __syncthreads();
-    fft_tile<false>(sm, S, plan, log_G, pitch, roots);
+    fft_tile<false, INV>(sm, S, plan, log_G, pitch, roots);
     if (MODE == OUT_COLS) { // column-major, index-bit-reversed: the tile is contiguous in its column
         for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
             const u32 g = idx >> S, q = idx & (len - 1);
@@ -283,10 +287,14 @@ u32 plan_steps(int S) {
 void ensure_attrs(nlc_ctx* ctx) {
     if (ctx->ntt_attrs) return;
     const int big = 160 * 1024;
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_NATURAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    NLC_CUDA(cudaFuncSetAttribute(k_ntt_lo<OUT_COLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute(k_ntt_hi<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute(k_ntt_hi<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_NATURAL, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_NATURAL, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_ROWS, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_ROWS, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_COLS, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_COLS, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ctx->ntt_attrs = true;
 }
 
@@ -329,7 +337,8 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
         const u64* roots = roots_table(ctx, S, inv);
         dim3 grid((unsigned)((n >> m) << (L - log_T)), (unsigned)job.n_cols);
         size_t smem = ((size_t)1 << (S + log_T)) * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_hi, grid, NTT_THREADS, smem, cur, cur_stride, job.scratch, n, m, S, log_T, plan_steps(S),
+        auto k_hi = inv ? k_ntt_hi<true> : k_ntt_hi<false>;
+        NLC_LAUNCH(ctx, k_hi, grid, NTT_THREADS, smem, cur, cur_stride, job.scratch, n, m, S, log_T, plan_steps(S),
                    lvl == 0 ? pre : nullptr, tw, roots);
         cur = job.scratch;
         cur_stride = n;
@@ -350,20 +359,24 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
         if (log_Gb > log_nb) log_Gb = log_nb;
         dim3 grid((unsigned)((n >> S) >> log_Gb), (unsigned)((job.n_cols + ((size_t)1 << log_Gc) - 1) >> log_Gc));
         size_t smem = ((size_t)1 << (log_Gb + log_Gc)) * pitch * sizeof(u64);
-        if (job.cols)
-            NLC_LAUNCH(ctx, k_ntt_lo<OUT_COLS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
+        if (job.cols) {
+            auto k_lo = inv ? k_ntt_lo<OUT_COLS, true> : k_ntt_lo<OUT_COLS, false>;
+            NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
                        plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, job.dst_stride,
                        (size_t)0, job.row_base, job.col0);
-        else
-            NLC_LAUNCH(ctx, k_ntt_lo<OUT_ROWS>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
+        } else {
+            auto k_lo = inv ? k_ntt_lo<OUT_ROWS, true> : k_ntt_lo<OUT_ROWS, false>;
+            NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
                        plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, (size_t)0,
                        job.row_width, job.row_base, job.col0);
+        }
     } else {
         NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
         if (log_G > log_nb) log_G = log_nb;
         dim3 grid((unsigned)((n >> S) >> log_G), (unsigned)job.n_cols);
         size_t smem = ((size_t)1 << log_G) * pitch * sizeof(u64);
-        NLC_LAUNCH(ctx, k_ntt_lo<OUT_NATURAL>, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, 0,
+        auto k_lo = inv ? k_ntt_lo<OUT_NATURAL, true> : k_ntt_lo<OUT_NATURAL, false>;
+        NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, 0,
                    plan_steps(S), job.n_cols, lo_pre, post, scale, roots, job.dst, job.dst_stride, (size_t)0,
                    (size_t)0, (size_t)0);
     }
