@@ -308,6 +308,26 @@ def run_ours(args, rank, local_rank, world):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_val = (1 if sharded else world) * elems / (float(te.item()) / args.steps)
     free_prev()
+    # the same call fed from PAGEABLE host vectors (what a Rust Vec<PolynomialValues> is): csrc/staging.h
+    e2e_pageable = None
+    if not sharded:
+        pageable = host.numpy().view(np.uint64).copy()
+        ptab = (ffi.u64p * W)(*[pageable[j].ctypes.data_as(ffi.u64p) for j in range(W)])
+
+        def step_pageable():
+            free_prev()
+            h = ffi.vp()
+            ctx._check(L.nlc_commit_from_values(ctx._h, ptab, W, log_n, r, cap, C.byref(h)))
+            state["batch"] = h
+            ctx._check(L.nlc_batch_cap(h, cap_host.ctypes.data_as(ffi.u64p)))
+        step_pageable()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_pageable()
+        torch.cuda.synchronize()
+        e2e_pageable = (time.perf_counter() - t0) / args.steps * 1e3
+        free_prev()
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -331,7 +351,8 @@ def run_ours(args, rank, local_rank, world):
                                            else f"instances x{world}"), "l2": "flushed between timed iterations (256 MiB write)"},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_val, "unit": "elements/s", "h2d_bytes_per_step": 8 * elems,
-                        "d2h_bytes_per_step": 32 << cap, "ms_per_step": float(te.item()) / args.steps * 1e3},
+                        "d2h_bytes_per_step": 32 << cap, "ms_per_step": float(te.item()) / args.steps * 1e3,
+                        "host_memory": "pinned", "pageable_host_ms_per_step": e2e_pageable},
                 "roofline": roofline, "roofline_ntt": roofline_ntt,
                 "commit_algorithmic_gbs": commit_gbs, "commit_frac_of_hbm": commit_gbs / peak,
                 "phases_ms": {kk: (v / k if kk != "commits" else v) for kk, v in phases.items()},

@@ -11,9 +11,18 @@ namespace {
 
 thread_local std::string g_init_error;
 
-void h2d(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) {
-    if (bytes) NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+// Large pageable sources go through the pinned-slot stager (staging.h); everything else is a plain async copy.
+void h2d_on(nlc_ctx* ctx, cudaStream_t stream, void* dst, const void* src, size_t bytes, bool flush = true) {
+    if (!bytes) return;
+    if (bytes >= ((size_t)256 << 10) && HostStager::pageable(src)) {
+        ctx->stager.upload(stream, dst, src, bytes);
+        if (flush) ctx->stager.flush(stream);
+    } else {
+        ctx->stager.flush(stream);
+        NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream));
+    }
 }
+void h2d(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) { h2d_on(ctx, ctx->stream, dst, src, bytes); }
 void d2h(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) {
     if (bytes) NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 }
@@ -33,8 +42,9 @@ void upload_cols(nlc_ctx* ctx, const u64* const* cols, size_t n_cols, size_t n, 
     NLC_CHECK(cols != nullptr, "null column table");
     for (size_t j = 0; j < n_cols; j++) {
         NLC_CHECK(cols[j] != nullptr, "null column pointer");
-        h2d(ctx, dev + j * n, cols[j], n * sizeof(u64));
+        h2d_on(ctx, ctx->stream, dev + j * n, cols[j], n * sizeof(u64), false); // adjacent columns share a slot
     }
+    ctx->stager.flush(ctx->stream);
 }
 
 enum FftKind { FFT, IFFT, COSET_FFT, COSET_IFFT };
@@ -111,9 +121,9 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                 const size_t nc = W - c0 < chunk ? W - c0 : chunk;
                 for (size_t j = c0; j < c0 + nc; j++) {
                     NLC_CHECK(cols[j] != nullptr, "null column pointer");
-                    NLC_CUDA(cudaMemcpyAsync(stage + j * n, cols[j], n * sizeof(u64), cudaMemcpyHostToDevice,
-                                             ctx->copy_stream));
+                    h2d_on(ctx, ctx->copy_stream, stage + j * n, cols[j], n * sizeof(u64), false);
                 }
+                ctx->stager.flush(ctx->copy_stream);
                 cudaEvent_t e = ctx->chunk_event(evs.size());
                 evs.push_back(e);
                 NLC_CUDA(cudaEventRecord(e, ctx->copy_stream));
@@ -182,6 +192,7 @@ void nlc_destroy(nlc_ctx* ctx) {
         cudaStreamSynchronize(ctx->stream);
         for (auto& kv : ctx->tables) cudaFree(kv.second);
         if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->stager.destroy();
         if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
         if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
         if (ctx->ev_ready) cudaEventDestroy(ctx->ev_ready);

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../include/nlc_commit.h"
+#include "staging.h"
 
 typedef uint64_t u64;
 typedef uint32_t u32;
@@ -59,6 +60,7 @@ struct nlc_ctx {
     std::map<TableKey, u64*> tables; // device-resident twiddle / scale tables, built once
     size_t table_bytes = 0;
     // small pinned staging area + device scratch for transcript-sized transfers
+    HostStager stager; // pageable host columns -> HBM through pinned slots (staging.h)
     u64* pinned = nullptr;
     size_t pinned_words = 0;
     int sm_count = 148;
