@@ -24,7 +24,11 @@ void h2d_on(nlc_ctx* ctx, cudaStream_t stream, void* dst, const void* src, size_
 }
 void h2d(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) { h2d_on(ctx, ctx->stream, dst, src, bytes); }
 void d2h(nlc_ctx* ctx, void* dst, const void* src, size_t bytes) {
-    if (bytes) NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (!bytes) return;
+    if (bytes >= ((size_t)1 << 20) && HostStager::pageable(dst))
+        ctx->stager.download(ctx->stream, src, {{dst, bytes}}); // synchronous; callers sync anyway
+    else
+        NLC_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 }
 void sync(nlc_ctx* ctx) { NLC_CUDA(cudaStreamSynchronize(ctx->stream)); }
 
@@ -352,7 +356,14 @@ int nlc_batch_coeffs(nlc_batch* b, uint64_t* const* out_cols) {
     return nlc_guarded(b->ctx, [&] {
         CtxGuard g(b->ctx);
         const size_t n = (size_t)1 << b->log_n;
-        for (size_t j = 0; j < b->W; j++) d2h(b->ctx, out_cols[j], b->coeffs + j * n, n * sizeof(u64));
+        NLC_CHECK(out_cols != nullptr, "null column table");
+        if (b->W * n * sizeof(u64) >= ((size_t)1 << 20) && HostStager::pageable(out_cols[0])) {
+            std::vector<HostStager::Seg> segs; // W separate Vecs on the host, one contiguous matrix on the device
+            for (size_t j = 0; j < b->W; j++) segs.push_back({out_cols[j], n * sizeof(u64)});
+            b->ctx->stager.download(b->ctx->stream, b->coeffs, segs);
+        } else {
+            for (size_t j = 0; j < b->W; j++) d2h(b->ctx, out_cols[j], b->coeffs + j * n, n * sizeof(u64));
+        }
         sync(b->ctx);
     });
 }

@@ -162,4 +162,57 @@ struct HostStager {
             bytes -= take;
         }
     }
+
+    // device -> pageable host: `segs` lists the host destinations of consecutive device bytes starting at `src`
+    // (one segment = one Vec of the caller).  DMA into slot k+1 overlaps the host threads scattering slot k.
+    // Synchronous: the data is in place on return.
+    struct Seg {
+        void* dst;
+        size_t len;
+    };
+    void download(cudaStream_t stream, const void* src, const std::vector<Seg>& segs) {
+        init();
+        flush(stream);
+        size_t total = 0;
+        for (const Seg& g : segs) total += g.len;
+        const char* s = (const char*)src;
+        size_t issued = 0, drained = 0, seg_i = 0, seg_off = 0;
+        int head = cur, tail = cur;
+        size_t len_of[N_SLOTS] = {};
+        while (drained < total) {
+            while (issued < total && issued - drained < (size_t)N_SLOTS * SLOT_BYTES && !(issued > drained && head == tail)) {
+                if (busy[head]) {
+                    cudaEventSynchronize(ev[head]);
+                    busy[head] = false;
+                }
+                const size_t take = total - issued < SLOT_BYTES ? total - issued : SLOT_BYTES;
+                if (cudaMemcpyAsync(slot[head], s + issued, take, cudaMemcpyDeviceToHost, stream) != cudaSuccess)
+                    throw std::runtime_error("HostStager: cudaMemcpyAsync (D2H) failed");
+                cudaEventRecord(ev[head], stream);
+                len_of[head] = take;
+                issued += take;
+                head = (head + 1) % N_SLOTS;
+            }
+            cudaEventSynchronize(ev[tail]);
+            pending.clear();
+            size_t left = len_of[tail], so = 0;
+            while (left) {
+                const Seg& g = segs[seg_i];
+                size_t take = g.len - seg_off < left ? g.len - seg_off : left;
+                for (size_t o = 0; o < take; o += GRANULE) {
+                    const size_t len = take - o < GRANULE ? take - o : GRANULE;
+                    pending.push_back({(char*)g.dst + seg_off + o, (const char*)slot[tail] + so + o, len});
+                }
+                so += take;
+                left -= take;
+                seg_off += take;
+                if (seg_off == g.len) seg_i++, seg_off = 0;
+            }
+            pool->parallel_for(pending.size(), [&](size_t i) { memcpy(pending[i].dst, pending[i].src, pending[i].len); });
+            pending.clear();
+            drained += len_of[tail];
+            tail = (tail + 1) % N_SLOTS;
+        }
+        cur = head;
+    }
 };
