@@ -120,6 +120,15 @@ def ncu_traffic(workload: str, kernel: str):
         return None
 
 
+def ncu_pipes(workload: str, kernel: str):
+    """Pipe utilisation of `kernel` from the same committed capture (explains an HBM fraction of ~1 %)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[workload][kernel]["pipes_pct_of_peak"]
+    except Exception:
+        return None
+
+
 def algorithmic_bytes(log_n, W, r, cap):
     n, N = 1 << log_n, 1 << (log_n + r)
     return {
@@ -285,6 +294,7 @@ def run_ours(args, rank, local_rank, world):
     roofline = {"bound": "hbm", "kernel": "k_leaf_hash (Poseidon sponge over LDE rows; INT-pipe limited)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(args.workload, "k_leaf_hash"), "algorithmic_bytes_per_launch": ab["leaf_hash"],
+                "ncu_pipes_pct_of_peak": ncu_pipes(args.workload, "k_leaf_hash"),
                 "peak_source": peak_src, "ms_per_launch": leaf_ms,
                 "poseidon_perms_per_s": perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None}
     roofline_ntt = {"bound": "hbm", "kernel": "k_ntt_* (iFFT + 2^r coset NTTs into leaf rows)",
