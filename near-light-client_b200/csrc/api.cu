@@ -112,17 +112,28 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
         const size_t n = (size_t)1 << log_n;
         nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height, shard_log, shard_idx);
         try {
-            // Columns are independent until the leaf hash: upload them in chunks on the copy stream and run
-            // IFFT + the coset NTTs of chunk c on the compute stream while chunk c+1 crosses PCIe.
-            const size_t chunk = W <= 8 ? W : (W + 4) / 5;
+            // Columns are independent until the leaf hash, and the leaf sponge absorbs them in order: upload them in
+            // chunks on the copy stream and run IFFT + coset NTTs + the sponge blocks of chunk c on the compute
+            // stream while chunk c+1 crosses PCIe (inner chunks are whole 8-column sponge blocks; the 12-word
+            // sponge states wait in HBM between chunks).  Only the first, short chunk's upload is exposed.
+            // Chunk sizes: 16 columns first, then doubling (each upload hides behind the previous chunk's compute
+            // as long as a column computes at least twice as long as it uploads: true from rate_bits 1 up), tripling
+            // at rate_bits >= 2 where compute is >= 8x the upload, also from pageable memory (fewer, fuller NTT grids).
+            const bool stream_hash = W >= 32;
+            const size_t chunk = W <= 8 ? W : (W + 4) / 5; // narrow batches: plain fifths, one leaf-hash launch
+            const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
+            DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
             u64* stage = is_values ? vals.p : b->coeffs;
             NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream)); // buffers allocated on the compute stream
             NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
             NLC_CHECK(cols != nullptr, "null column table");
             std::vector<cudaEvent_t> evs;
-            for (size_t c0 = 0; c0 < W; c0 += chunk) {
-                const size_t nc = W - c0 < chunk ? W - c0 : chunk;
+            for (size_t c0 = 0, nc = 0; c0 < W; c0 += nc) {
+                size_t want = chunk;
+                if (stream_hash) want = c0 == 0 ? 16 : (rate_bits >= 2 ? 3 * nc : 2 * nc);
+                nc = W - c0 < want ? W - c0 : want;
+                if (stream_hash && W - c0 - nc < 16) nc = W - c0; // no tiny last chunk
                 for (size_t j = c0; j < c0 + nc; j++) {
                     NLC_CHECK(cols[j] != nullptr, "null column pointer");
                     h2d_on(ctx, ctx->copy_stream, stage + j * n, cols[j], n * sizeof(u64), false);
@@ -134,6 +145,15 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                 NLC_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0));
                 if (is_values) batch_ifft_cols(b, vals.p + c0 * n, c0, nc);
                 batch_lde_cols(b, c0, nc);
+                if (stream_hash)
+                    merkle_leaf_absorb(ctx, b->lde, N, N, c0, nc, c0 == 0, c0 + nc == W, sponge.p, b->cap_local(),
+                                       b->digests, b->cap);
+            }
+            if (stream_hash) {
+                merkle_levels(ctx, N, b->cap_local(), b->digests, b->cap);
+                sync(ctx);
+                *out = b;
+                return;
             }
             batch_tree(b);
             sync(ctx);
@@ -244,6 +264,7 @@ int nlc_timing_read(nlc_ctx* ctx, nlc_timing* out) {
                 case 0: out->ifft_ms += ms; break;
                 case 1: out->lde_ms += ms; break;
                 case 2: out->leaf_hash_ms += ms; out->commits++; break; // one leaf-hash launch per commit
+                case 4: out->leaf_hash_ms += ms; break;                  // chunked leaf sponge (host-fed commits)
                 default: out->merkle_levels_ms += ms; break;
             }
             cudaEventDestroy(ev.second.first);

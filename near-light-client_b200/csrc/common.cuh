@@ -175,6 +175,9 @@ size_t ntt_scratch_words(size_t n_cols, int log_n);
 // (element j of leaf k at leaves[j*elem_stride + k]), the layout of a PolynomialBatch's LDE.
 void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
                   u64* digests, u64* cap);
+void merkle_levels(nlc_ctx* ctx, size_t n_leaves, int cap_height, u64* digests, u64* cap);
+void merkle_leaf_absorb(nlc_ctx* ctx, const u64* lde, size_t n_leaves, size_t elem_stride, size_t col0, size_t n_cols,
+                        bool first, bool last, u64* state, int cap_height, u64* digests, u64* cap);
 // device copy of leaf + siblings for many leaf indices (indices in device memory)
 void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
                       size_t elem_stride, int cap_height, const u64* idx_dev, int shift_right, size_t n_idx, u64* out,

@@ -78,6 +78,43 @@ k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, si
     }
 }
 
+// The same sponge, fed a column range at a time (host-fed commits: columns [col0, col0 + n_cols) have just been
+// extended while later columns are still crossing PCIe).  Every chunk but the last covers whole 8-element blocks;
+// between chunks the 12-word sponge state of each leaf waits in `state` (state[i * n_leaves + row]: coalesced).
+// Same permutations, same order, same result as k_leaf_hash<true> over all columns (leaf_len > 4 only).
+__global__ void __launch_bounds__(HASH_THREADS)
+k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, size_t col0, size_t n_cols, bool first,
+              bool last, u64* __restrict__ state, TreeGeom g, u64* digests, u64* cap) {
+    const size_t step = (size_t)gridDim.x * HASH_THREADS;
+    for (size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x; row < n_leaves; row += step) {
+        const u64* in = lde + col0 * elem_stride + row;
+        u64 s[poseidon::WIDTH];
+#pragma unroll
+        for (int i = 0; i < poseidon::WIDTH; i++) s[i] = first ? 0 : state[i * n_leaves + row];
+        size_t off = 0;
+        for (; off + poseidon::RATE <= n_cols; off += poseidon::RATE) {
+#pragma unroll
+            for (int i = 0; i < poseidon::RATE; i++) s[i] = in[(off + i) * elem_stride];
+            poseidon::permute_nc(s);
+        }
+        if (off < n_cols) { // ragged tail: only the last chunk has one
+            const int rem = (int)(n_cols - off);
+#pragma unroll
+            for (int i = 0; i < poseidon::RATE; i++)
+                if (i < rem) s[i] = in[(off + i) * elem_stride];
+            poseidon::permute_nc(s);
+        }
+        if (last) {
+            u64* out = node_slot(digests, cap, g, 0, row);
+            reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
+            reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
+        } else {
+#pragma unroll
+            for (int i = 0; i < poseidon::WIDTH; i++) state[i * n_leaves + row] = s[i];
+        }
+    }
+}
+
 // layer (i) -> layer (i+1): one thread per parent.
 __global__ void __launch_bounds__(HASH_THREADS)
 k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) {
@@ -177,8 +214,7 @@ static unsigned leaf_grid(nlc_ctx* ctx, size_t n_leaves) {
     return (unsigned)((size_t)ctx->sm_count * best);
 }
 
-void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
-                  u64* digests, u64* cap) {
+static TreeGeom tree_geom(size_t n_leaves, int cap_height) {
     const int h = ilog2(n_leaves);
     NLC_CHECK(((size_t)1 << h) == n_leaves, "MerkleTree::new: number of leaves must be a power of two");
     NLC_CHECK(cap_height >= 0 && cap_height <= h,
@@ -186,14 +222,12 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
     TreeGeom g;
     g.sub_height = h - cap_height;
     g.sub_digests = 2 * (((size_t)1 << g.sub_height) - 1);
-    ctx->phase_begin(2);
-    if (elem_stride)
-        NLC_LAUNCH(ctx, k_leaf_hash<true>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
-                   (size_t)1, elem_stride, g, digests, cap);
-    else
-        NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
-                   leaf_len, (size_t)1, g, digests, cap);
-    ctx->phase_end();
+    return g;
+}
+
+// digest layers above the leaf digests, down to the cap
+void merkle_levels(nlc_ctx* ctx, size_t n_leaves, int cap_height, u64* digests, u64* cap) {
+    const TreeGeom g = tree_geom(n_leaves, cap_height);
     ctx->phase_begin(3);
     for (int layer = 0; layer < g.sub_height; layer++) {
         const size_t parents = n_leaves >> (layer + 1);
@@ -204,6 +238,31 @@ void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_
             NLC_LAUNCH(ctx, k_merkle_level_coop, (unsigned)((parents * 16 + COOP_THREADS - 1) / COOP_THREADS),
                        COOP_THREADS, 0, digests, cap, g, layer, parents);
     }
+    ctx->phase_end();
+}
+
+void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
+                  u64* digests, u64* cap) {
+    const TreeGeom g = tree_geom(n_leaves, cap_height);
+    ctx->phase_begin(2);
+    if (elem_stride)
+        NLC_LAUNCH(ctx, k_leaf_hash<true>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
+                   (size_t)1, elem_stride, g, digests, cap);
+    else
+        NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
+                   leaf_len, (size_t)1, g, digests, cap);
+    ctx->phase_end();
+    merkle_levels(ctx, n_leaves, cap_height, digests, cap);
+}
+
+// One chunk of the leaf sponge over a column-major LDE (k_leaf_absorb); `state` = 12 * n_leaves words.
+void merkle_leaf_absorb(nlc_ctx* ctx, const u64* lde, size_t n_leaves, size_t elem_stride, size_t col0, size_t n_cols,
+                        bool first, bool last, u64* state, int cap_height, u64* digests, u64* cap) {
+    NLC_CHECK(last || n_cols % poseidon::RATE == 0, "leaf absorb: inner chunks must be whole sponge blocks");
+    const TreeGeom g = tree_geom(n_leaves, cap_height);
+    ctx->phase_begin(4);
+    NLC_LAUNCH(ctx, k_leaf_absorb, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, lde, n_leaves, elem_stride, col0, n_cols,
+               first, last, state, g, digests, cap);
     ctx->phase_end();
 }
 

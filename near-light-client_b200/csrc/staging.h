@@ -3,7 +3,7 @@
 // The plonky2 caller hands nlc_commit_from_values a Vec<PolynomialValues<F>>: W separate, PAGEABLE heap vectors
 // (vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:91-93).  cudaMemcpyAsync from pageable memory goes through
 // the driver's single-threaded bounce buffer (measured here: 8.4 GB/s, 15.9 ms for the 71 MB of config 2 against
-// 11.6 ms from pinned memory).  The stager copies the columns into a ring of pinned slots with a small pool of
+// 11.6 ms from pinned memory).  The stager copies the columns into a ring of 4 MiB pinned slots with a small pool of
 // host threads and issues one asynchronous H2D per slot, so the CPU fills slot k+1 while the DMA engine drains
 // slot k.  Pinned / registered sources skip it.
 #pragma once
@@ -75,9 +75,9 @@ struct CopyPool {
 };
 
 struct HostStager {
-    static constexpr size_t SLOT_BYTES = (size_t)8 << 20;
+    static constexpr size_t SLOT_BYTES = (size_t)4 << 20;
     static constexpr size_t GRANULE = (size_t)512 << 10;
-    static constexpr int N_SLOTS = 4;
+    static constexpr int N_SLOTS = 6;
     void* slot[N_SLOTS] = {};
     cudaEvent_t ev[N_SLOTS] = {};
     bool busy[N_SLOTS] = {};
