@@ -132,7 +132,10 @@ static inline int nlc_guarded(nlc_ctx* ctx, F&& f) {
         f();
         return 0;
     } catch (const std::exception& e) {
-        if (ctx) ctx->err = e.what();
+        if (ctx) {
+            ctx->err = e.what();
+            ctx->stager.abandon();
+        }
         cudaGetLastError(); // clear a non-sticky error so later calls can proceed
         return 1;
     }

@@ -123,6 +123,12 @@ struct HostStager {
             cudaEventDestroy(ev[i]);
         }
     }
+    // drop anything not yet flushed (error paths: the destination may be gone)
+    void abandon() {
+        pending.clear();
+        fill = 0;
+        dst_base = nullptr;
+    }
     // flush slot[cur]: memcpy the pending granules in parallel, one async H2D, move to the next slot
     void flush(cudaStream_t stream) {
         if (fill == 0) return;
