@@ -140,6 +140,86 @@ def algorithmic_bytes(log_n, W, r, cap):
     }
 
 
+def proof_shapes(kind):
+    """(log_n, rate_bits, cap, pow_bits, queries, oracles[(name, W, is_values, timed)], next_polys[(oracle, count)])."""
+    if kind == "plonk":
+        return 16, 3, 4, 16, 28, [("constants_sigmas", 84, True, False), ("wires", 135, True, True),
+                                  ("zs_partial_products", 20, True, True), ("quotient", 16, False, True)], [(2, 2)]
+    return 16, 1, 4, 16, 84, [("trace", 418, True, True), ("quotient", 4, False, True)], [(0, 418)]
+
+
+def replay(kind, mod, commit_v, commit_c, make_inst, make_params, challenger, prove, seed):
+    log_n, r, cap, pow_bits, queries, oracles, nxt = proof_shapes(kind)
+    n = 1 << log_n
+    mats = [synth_values(W, n, seed + i) for i, (_, W, _, _) in enumerate(oracles)]
+    batches, t_commit = [], 0.0
+    ch = challenger()
+    for (name, W, is_values, timed), m in zip(oracles, mats):
+        t0 = time.perf_counter()
+        b = (commit_v if is_values else commit_c)(m, r, cap)
+        c = np.array(b.merkle_tree.cap if hasattr(b, "merkle_tree") else b.cap)
+        if timed:
+            t_commit += time.perf_counter() - t0
+        ch.observe_cap(c)
+        batches.append(b)
+    zeta = (0x1234567, 0x89ABCDE)
+    g = pow(1753635133440165772, 1 << (32 - log_n), P)
+    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
+    all_polys = [(o, i) for o, (_, W, _, _) in enumerate(oracles) for i in range(W)]
+    next_polys = [(o, i) for o, cnt in nxt for i in range(cnt)]
+    inst = make_inst([(zeta, all_polys), (zeta_next, next_polys)])
+    params = make_params(log_n, r, cap, pow_bits, queries)
+    t0 = time.perf_counter()
+    proof = prove(inst, batches, ch, params)
+    t_open = time.perf_counter() - t0
+    return t_commit, t_open, proof
+
+
+def _gpu_replay_once(kind, P2):
+    return replay(
+        kind, P2,
+        lambda m, r, cap: P2.PolynomialBatch.from_values(list(m), r, False, cap),
+        lambda m, r, cap: P2.PolynomialBatch.from_coeffs(list(m), r, False, cap),
+        lambda bs: P2.FriInstanceInfo([], [P2.FriBatchInfo(pt, [P2.FriPolynomialInfo(o, i) for o, i in polys])
+                                           for pt, polys in bs]),
+        lambda log_n, r, cap, pw, q: P2.FriConfig(r, cap, pw, P2.FriReductionStrategy.ConstantArityBits(4, 5),
+                                                  q).fri_params(log_n),
+        P2.Challenger, P2.PolynomialBatch.prove_openings, 0xC0FFEE + 10)
+
+
+def replay_gpu(kind, steps, keep_proof=False):
+    """One proof's commit path (configs[0]/[2] replaced by their sequence of commit shapes) through
+    the host mirror: pageable host columns in, caps + FriProof out."""
+    P2 = graft.load_package().plonky2
+    _gpu_replay_once(kind, P2)
+    runs = [_gpu_replay_once(kind, P2) for _ in range(steps)]
+    tc, to = float(np.median([x[0] for x in runs])), float(np.median([x[1] for x in runs]))
+    line = {"replay": kind, "shape": proof_shapes(kind)[:5], "oracles": [o[:2] for o in proof_shapes(kind)[5]],
+            "gpu_commit_s": tc, "gpu_prove_openings_s": to, "gpu_total_s": tc + to,
+            "note": "host columns in, caps + FriProof out (H2D/D2H inside)"}
+    return (line, runs[-1][2]) if keep_proof else line
+
+
+def run_replay_workload(args):
+    """--workload replay_plonk / replay_stark: time per proof of the commit path, GPU vs the CPU oracle."""
+    kind = args.workload.split("_")[1]
+    line, gproof = replay_gpu(kind, args.steps, keep_proof=True)
+    O = graft.load_oracle()
+    c = replay(kind, O, O.commit_from_values, O.commit_from_coeffs, O.FriInstance,
+               lambda log_n, r, cap, pw, q: O.fri_params(log_n, r, cap, pw, q, 4, 5),
+               O.Challenger, O.prove_openings, 0xC0FFEE + 10)
+    same = bool(np.array_equal(np.asarray(gproof.flat), np.asarray(c[2])))
+    out = {"metric": "commit-path time per proof (commits + prove_openings), host to host", "value": line["gpu_total_s"],
+           "unit": "s", "n_gpus": 1, "steps": args.steps, "warmup": 1, "ms_per_step": line["gpu_total_s"] * 1e3,
+           "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+           "config": {"workload": args.workload, "shape": line["shape"], "oracles": line["oracles"]},
+           "gpu_commit_s": line["gpu_commit_s"], "gpu_prove_openings_s": line["gpu_prove_openings_s"],
+           "cpu_baseline": {"value": c[0] + c[1], "unit": "s", "cores": O.get_threads(), "kind": "port",
+                            "sample": f"the same proof once: commits {c[0]:.2f} s, prove_openings {c[1]:.2f} s",
+                            "proof_bit_exact": same}}
+    print(json.dumps(out), flush=True)
+
+
 def run_reference(args, rank, world):
     """The reference's CPU algorithm for the path (oracle port; plonky2 itself cannot be built here)."""
     if rank != 0:
@@ -378,7 +458,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
@@ -389,7 +469,10 @@ def main():
     rank = int(os.environ.get("RANK", 0))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
-    if args.impl == "reference":
+    if args.workload.startswith("replay_"):
+        if rank == 0:
+            run_replay_workload(args)
+    elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
         run_ours(args, rank, local_rank, world)

@@ -9,8 +9,9 @@
                       quotient 16 (from_coeffs), openings over the 4 oracles (constants/sigmas 84) at zeta, g*zeta
               stark : starky standard_fast_config proof, 2^16 x 418 trace (SHA-256 AIR width, sha256/air.rs:221),
                       quotient 2^16 x 4, openings at zeta and g*zeta (prover.rs:50-225)
-            each timed end to end through the host mirror (host columns in, FriProof out) and, with --cpu, on the
-            CPU oracle for the same sequence.
+            each timed end to end through the host mirror (host columns in, FriProof out).  The CPU-oracle leg and
+            the bit-exact proof comparison live in bench.py (--workload replay_plonk / replay_stark), the only
+            place besides tests/ that may run oracle/.
 bench.py stays the contract line; the output of this tool is committed under profiles/.
 """
 from __future__ import annotations
@@ -78,75 +79,11 @@ def run_sweep(args):
                 torch.cuda.empty_cache()
 
 
-def proof_shapes(kind):
-    """(log_n, rate_bits, cap, pow_bits, queries, oracles[(name, W, is_values, timed)], next_polys[(oracle, count)])."""
-    if kind == "plonk":
-        return 16, 3, 4, 16, 28, [("constants_sigmas", 84, True, False), ("wires", 135, True, True),
-                                  ("zs_partial_products", 20, True, True), ("quotient", 16, False, True)], [(2, 2)]
-    return 16, 1, 4, 16, 84, [("trace", 418, True, True), ("quotient", 4, False, True)], [(0, 418)]
-
-
-def replay(kind, mod, commit_v, commit_c, make_inst, make_params, challenger, prove, seed):
-    log_n, r, cap, pow_bits, queries, oracles, nxt = proof_shapes(kind)
-    n = 1 << log_n
-    mats = [synth_values(W, n, seed + i) for i, (_, W, _, _) in enumerate(oracles)]
-    batches, t_commit = [], 0.0
-    ch = challenger()
-    for (name, W, is_values, timed), m in zip(oracles, mats):
-        t0 = time.perf_counter()
-        b = (commit_v if is_values else commit_c)(m, r, cap)
-        c = np.array(b.merkle_tree.cap if hasattr(b, "merkle_tree") else b.cap)
-        if timed:
-            t_commit += time.perf_counter() - t0
-        ch.observe_cap(c)
-        batches.append(b)
-    zeta = (0x1234567, 0x89ABCDE)
-    g = pow(1753635133440165772, 1 << (32 - log_n), P)
-    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
-    all_polys = [(o, i) for o, (_, W, _, _) in enumerate(oracles) for i in range(W)]
-    next_polys = [(o, i) for o, cnt in nxt for i in range(cnt)]
-    inst = make_inst([(zeta, all_polys), (zeta_next, next_polys)])
-    params = make_params(log_n, r, cap, pow_bits, queries)
-    t0 = time.perf_counter()
-    proof = prove(inst, batches, ch, params)
-    t_open = time.perf_counter() - t0
-    return t_commit, t_open, proof
-
-
 def run_replay(args):
-    pkg = graft.load_package()
-    P2 = pkg.plonky2
-    out = {}
+    """GPU side of the proof-shape replay (bench.py --workload replay_* adds the CPU oracle leg and the bit-exact check)."""
+    import bench
     for kind in ("plonk", "stark"):
-        def gpu_once():
-            return replay(
-                kind, P2,
-                lambda m, r, cap: P2.PolynomialBatch.from_values(list(m), r, False, cap),
-                lambda m, r, cap: P2.PolynomialBatch.from_coeffs(list(m), r, False, cap),
-                lambda bs: P2.FriInstanceInfo([], [P2.FriBatchInfo(pt, [P2.FriPolynomialInfo(o, i) for o, i in polys])
-                                                   for pt, polys in bs]),
-                lambda log_n, r, cap, pw, q: P2.FriConfig(r, cap, pw, P2.FriReductionStrategy.ConstantArityBits(4, 5),
-                                                          q).fri_params(log_n),
-                P2.Challenger, P2.PolynomialBatch.prove_openings, 0xC0FFEE + 10)
-        gpu_once()
-        runs = [gpu_once() for _ in range(args.steps)]
-        tc, to = float(np.median([x[0] for x in runs])), float(np.median([x[1] for x in runs]))
-        line = {"replay": kind, "shape": proof_shapes(kind)[:5], "oracles": [o[:2] for o in proof_shapes(kind)[5]],
-                "gpu_commit_s": tc, "gpu_prove_openings_s": to, "gpu_total_s": tc + to,
-                "note": "host columns in, caps + FriProof out (H2D/D2H inside)"}
-        if args.cpu:
-            O = graft.load_oracle()
-            c = replay(kind, O, O.commit_from_values, O.commit_from_coeffs, O.FriInstance,
-                       lambda log_n, r, cap, pw, q: O.fri_params(log_n, r, cap, pw, q, 4, 5),
-                       O.Challenger, O.prove_openings, 0xC0FFEE + 10)
-            gp, cp = runs[-1][2], c[2]
-            same = bool(np.array_equal(np.asarray(gp.flat), np.asarray(cp)))
-            line.update({"cpu_commit_s": c[0], "cpu_prove_openings_s": c[1], "cpu_total_s": c[0] + c[1],
-                         "cpu_cores": O.get_threads(), "cpu_kind": "port (oracle, OpenMP)",
-                         "proof_bit_exact": same, "speedup": (c[0] + c[1]) / (tc + to)})
-        print(json.dumps(line), flush=True)
-        out[kind] = line
-    return out
+        print(json.dumps(bench.replay_gpu(kind, args.steps)), flush=True)
 
 
 def main():
@@ -156,7 +93,6 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--min-log", type=int, default=14)
     ap.add_argument("--max-log", type=int, default=22)
-    ap.add_argument("--cpu", action="store_true", help="replay: also time the CPU oracle on the same sequence")
     args = ap.parse_args()
     (run_sweep if args.mode == "sweep" else run_replay)(args)
 
