@@ -1,0 +1,227 @@
+// tests/cpp/test_plonky2_mirror.cpp -- drives include/nlc_plonky2.hpp the way starkyx's prover drives plonky2
+// (/root/reference/vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:50-225): trace commit -> observe cap ->
+// alphas -> quotient values -> coset_ifft -> chunks -> from_coeffs -> observe cap -> zeta -> openings ->
+// prove_openings, and checks every artefact bit for bit against the CPU oracle (oracle/oracle.h), whose restated
+// plonky2 verifier must also accept the device's proof.  Built and run by tests/test_gpu_cpp_mirror.py.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "nlc_plonky2.hpp"
+#include "oracle.h"
+
+using namespace plonky2;
+
+#define CHECK(cond)                                                      \
+    do {                                                                 \
+        if (!(cond)) {                                                   \
+            std::fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+            std::exit(1);                                                \
+        }                                                                \
+    } while (0)
+
+static uint64_t rng_state = 0x9E3779B97F4A7C15ULL;
+static F rand_field() { // splitmix64, rejected to [0, p)
+    for (;;) {
+        uint64_t z = (rng_state += 0x9E3779B97F4A7C15ULL);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+        z ^= z >> 31;
+        if (z < ORDER) return z;
+    }
+}
+static F mulmod(F a, F b) { return (F)((unsigned __int128)a * b % ORDER); }
+static F powmod(F b, uint64_t e) {
+    F r = 1;
+    for (; e; e >>= 1, b = mulmod(b, b))
+        if (e & 1) r = mulmod(r, b);
+    return r;
+}
+
+struct OracleBatch { // host arrays of the oracle's PolynomialBatch
+    size_t W;
+    int log_n, r, cap;
+    std::vector<uint64_t> coeffs, leaves, digests, capv;
+    orc_batch view() const { return {W, coeffs.data(), leaves.data(), digests.data(), capv.data()}; }
+};
+static OracleBatch oracle_commit(const std::vector<std::vector<F>>& cols, int r, int cap, bool is_values) {
+    OracleBatch b;
+    b.W = cols.size();
+    const size_t n = cols[0].size();
+    b.log_n = (int)log2_strict(n), b.r = r, b.cap = cap;
+    const size_t N = n << r;
+    std::vector<uint64_t> in;
+    for (const auto& c : cols) in.insert(in.end(), c.begin(), c.end());
+    b.coeffs.resize(b.W * n), b.leaves.resize(N * b.W), b.digests.resize(8 * (N - ((size_t)1 << cap))), b.capv.resize((size_t)4 << cap);
+    if (is_values)
+        orc_commit_from_values(in.data(), b.W, b.log_n, r, cap, b.coeffs.data(), b.leaves.data(), b.digests.data(), b.capv.data());
+    else {
+        b.coeffs = in;
+        orc_commit_from_coeffs(in.data(), b.W, b.log_n, r, cap, b.leaves.data(), b.digests.data(), b.capv.data());
+    }
+    return b;
+}
+
+int main() {
+    orc_poseidon_init();
+    CHECK(orc_poseidon_selftest() == 0);
+    const FriConfig fri_config = FriConfig::standard_fast_config(); // starkyx config.rs:58-73
+    const size_t degree_bits = 10, degree = (size_t)1 << degree_bits, W = 11, quotient_degree_factor = 2, num_challenges = 2;
+    const size_t rate_bits = fri_config.rate_bits, cap_height = fri_config.cap_height;
+
+    // ---- trace commitment (prover.rs:86-100) ----
+    std::vector<PolynomialValues> trace_cols;
+    std::vector<std::vector<F>> raw_cols;
+    for (size_t j = 0; j < W; j++) {
+        std::vector<F> v(degree);
+        for (F& x : v) x = rand_field();
+        raw_cols.push_back(v);
+        trace_cols.emplace_back(v);
+    }
+    PolynomialBatch trace_commitment = PolynomialBatch::from_values(trace_cols, rate_bits, false, cap_height);
+    OracleBatch otrace = oracle_commit(raw_cols, (int)rate_bits, (int)cap_height, true);
+    CHECK(trace_commitment.merkle_tree.cap.flatten() == otrace.capv);
+    CHECK(trace_commitment.degree_log == degree_bits);
+    for (size_t j = 0; j < W; j++)
+        CHECK(std::memcmp(trace_commitment.polynomials()[j].coeffs.data(), otrace.coeffs.data() + j * degree, degree * 8) == 0);
+
+    Challenger challenger;
+    orc_challenger och;
+    orc_challenger_init(&och);
+    challenger.observe_cap(trace_commitment.merkle_tree.cap);
+    orc_challenger_observe(&och, otrace.capv.data(), otrace.capv.size());
+    std::vector<F> alphas = challenger.get_n_challenges(num_challenges);
+    std::vector<F> oalphas(num_challenges);
+    orc_challenger_get_n(&och, num_challenges, oalphas.data());
+    CHECK(alphas == oalphas);
+
+    // ---- get_lde_values_packed in the quotient loop (prover.rs:289-294) ----
+    const size_t log_N = degree_bits + rate_bits;
+    auto bitrev = [&](size_t x) { size_t r = 0; for (size_t b = 0; b < log_N; b++) r |= ((x >> b) & 1) << (log_N - 1 - b); return r; };
+    auto packed = trace_commitment.get_lde_values_packed(8, 1, 4);
+    for (size_t i = 0; i < 4; i++)
+        for (size_t j = 0; j < W; j++) CHECK(packed[j][i] == otrace.leaves[bitrev(8 + i) * W + j]);
+    CHECK(trace_commitment.get_lde_values(5, 2) == std::vector<F>(otrace.leaves.begin() + bitrev(10) * W, otrace.leaves.begin() + (bitrev(10) + 1) * W));
+
+    // ---- quotient polys: values on the coset of size degree * 2^q -> coset_ifft -> chunks(degree) (prover.rs:147-178,352-358) ----
+    std::vector<PolynomialCoeffs> all_quotient_chunks;
+    std::vector<std::vector<F>> oquot_cols;
+    for (size_t a = 0; a < num_challenges; a++) {
+        std::vector<F> qv(degree * quotient_degree_factor);
+        for (F& x : qv) x = mulmod(rand_field(), alphas[a]);
+        PolynomialCoeffs quotient_poly = PolynomialValues(qv).coset_ifft(COSET_SHIFT);
+        orc_coset_ifft(qv.data(), (int)log2_strict(qv.size()), COSET_SHIFT);
+        CHECK(quotient_poly.coeffs == qv);
+        for (PolynomialCoeffs& chunk : quotient_poly.chunks(degree)) {
+            oquot_cols.push_back(chunk.coeffs);
+            all_quotient_chunks.push_back(std::move(chunk));
+        }
+    }
+    PolynomialBatch quotient_commitment = PolynomialBatch::from_coeffs(all_quotient_chunks, rate_bits, false, cap_height);
+    OracleBatch oquot = oracle_commit(oquot_cols, (int)rate_bits, (int)cap_height, false);
+    CHECK(quotient_commitment.merkle_tree.cap.flatten() == oquot.capv);
+    challenger.observe_cap(quotient_commitment.merkle_tree.cap);
+    orc_challenger_observe(&och, oquot.capv.data(), oquot.capv.size());
+
+    // ---- zeta, openings (prover.rs:183-193; proof.rs:300-328) ----
+    FE zeta = challenger.get_extension_challenge();
+    uint64_t ozeta[2];
+    orc_challenger_get_ext(&och, ozeta);
+    CHECK(zeta.first == ozeta[0] && zeta.second == ozeta[1]);
+    const F g = powmod(1753635133440165772ULL, (uint64_t)1 << (32 - degree_bits)); // F::primitive_root_of_unity(degree_bits)
+    FE zeta_next = {mulmod(zeta.first, g), mulmod(zeta.second, g)};
+    std::vector<FE> local_values = trace_commitment.eval_all(zeta), next_values = trace_commitment.eval_all(zeta_next),
+                    quotient_polys = quotient_commitment.eval_all(zeta);
+    std::vector<uint64_t> openings; // to_fri_openings order: [local ++ quotient] at zeta, [next] at g * zeta
+    auto push = [&](const std::vector<FE>& v) { for (const FE& e : v) openings.push_back(e.first), openings.push_back(e.second); };
+    push(local_values), push(quotient_polys), push(next_values);
+    for (size_t j = 0; j < W; j++) {
+        uint64_t z2[2] = {zeta.first, zeta.second}, o2[2];
+        orc_eval_poly_ext(otrace.coeffs.data() + j * degree, degree, z2, o2);
+        CHECK(local_values[j].first == o2[0] && local_values[j].second == o2[1]);
+    }
+    challenger.observe_extension_elements(local_values);
+    challenger.observe_extension_elements(quotient_polys);
+    challenger.observe_extension_elements(next_values);
+    orc_challenger_observe(&och, openings.data(), openings.size());
+    orc_challenger verifier_ch = och; // the verifier's transcript right after observe_openings
+
+    // ---- prove_openings (prover.rs:195-206; instance built as in plonky2/stark/mod.rs:56-96) ----
+    FriInstanceInfo instance;
+    instance.oracles = {{W, false}, {all_quotient_chunks.size(), false}};
+    FriBatchInfo zeta_batch{zeta, FriPolynomialInfo::from_range(0, 0, W)};
+    auto qinfo = FriPolynomialInfo::from_range(1, 0, all_quotient_chunks.size());
+    zeta_batch.polynomials.insert(zeta_batch.polynomials.end(), qinfo.begin(), qinfo.end());
+    instance.batches = {zeta_batch, FriBatchInfo{zeta_next, FriPolynomialInfo::from_range(0, 0, W)}};
+    FriParams fri_params = fri_config.fri_params(degree_bits, false);
+    FriProof opening_proof = PolynomialBatch::prove_openings(instance, {&trace_commitment, &quotient_commitment}, challenger, fri_params);
+
+    std::vector<uint64_t> pts = {zeta.first, zeta.second, zeta_next.first, zeta_next.second};
+    std::vector<uint32_t> offs{0}, po, pi;
+    for (const FriBatchInfo& b : instance.batches) {
+        for (const auto& i : b.polynomials) po.push_back((uint32_t)i.oracle_index), pi.push_back((uint32_t)i.polynomial_index);
+        offs.push_back((uint32_t)po.size());
+    }
+    orc_fri_instance oinst{2, pts.data(), offs.data(), po.data(), pi.data()};
+    orc_fri_params op;
+    orc_fri_params_constant_arity(&op, (int)degree_bits, (int)rate_bits, (int)cap_height, (int)fri_config.proof_of_work_bits,
+                                  (int)fri_config.num_query_rounds, 4, 5);
+    CHECK(op.n_rounds == fri_params.c.n_reduction_rounds);
+    orc_batch obs[2] = {otrace.view(), oquot.view()};
+    std::vector<uint64_t> oproof(orc_fri_proof_words(&op, obs, 2));
+    CHECK(oproof.size() == opening_proof.flat.size());
+    CHECK(orc_prove_openings(&oinst, obs, 2, &och, &op, oproof.data()) == 0);
+    CHECK(oproof == opening_proof.flat); // bit-exact FriProof
+    CHECK(opening_proof.query_round_proofs.size() == fri_config.num_query_rounds);
+    CHECK(opening_proof.final_poly.size() == fri_params.final_poly_len());
+    CHECK(std::memcmp(challenger.raw()->sponge_state, och.state, sizeof och.state) == 0); // transcripts stay in step
+
+    // the restated plonky2 verifier accepts the device's proof
+    const uint64_t* caps[2] = {otrace.capv.data(), oquot.capv.data()};
+    const size_t Ws[2] = {W, all_quotient_chunks.size()};
+    CHECK(orc_fri_verify(&oinst, openings.data(), caps, Ws, 2, &verifier_ch, &op, opening_proof.flat.data()) == 0);
+
+    // ---- Merkle openings of the committed batch; MerkleTree::new; hashing ----
+    auto opened = trace_commitment.open(77);
+    CHECK(orc_merkle_verify(opened.first.data(), W, 77, otrace.capv.data(), (int)cap_height,
+                            opened.second.siblings[0].elements, (int)opened.second.siblings.size()) == 0);
+    std::vector<std::vector<F>> leaves(64, std::vector<F>(9));
+    std::vector<uint64_t> flat_leaves;
+    for (auto& l : leaves)
+        for (F& x : l) x = rand_field(), flat_leaves.push_back(x);
+    MerkleTree tree(leaves, 2);
+    std::vector<uint64_t> od(8 * (64 - 4)), oc(16);
+    orc_merkle_new(flat_leaves.data(), 64, 9, 2, od.data(), oc.data());
+    CHECK(tree.cap.flatten() == oc);
+    CHECK(tree.get(13) == leaves[13]);
+    MerkleProof mp = tree.prove(13);
+    CHECK(orc_merkle_verify(leaves[13].data(), 9, 13, oc.data(), 2, mp.siblings[0].elements, (int)mp.siblings.size()) == 0);
+    uint64_t oh[4];
+    orc_hash_no_pad(leaves[0].data(), 9, oh);
+    CHECK(std::memcmp(PoseidonHash::hash_no_pad(leaves[0]).elements, oh, 32) == 0);
+    HashOut l = PoseidonHash::hash_or_noop({1, 2, 3}), rr = PoseidonHash::hash_no_pad({4, 5, 6, 7, 8});
+    orc_two_to_one(l.elements, rr.elements, oh);
+    CHECK(std::memcmp(PoseidonHash::two_to_one(l, rr).elements, oh, 32) == 0);
+
+    // ---- lde_onto_coset / selector (prover.rs:280-284) ----
+    PolynomialValues lagrange_first = PolynomialValues::selector(degree, 0).lde_onto_coset(1);
+    std::vector<uint64_t> sel(degree, 0), olde(degree * 2);
+    sel[0] = 1;
+    orc_lde_onto_coset(sel.data(), (int)degree_bits, 1, olde.data());
+    CHECK(lagrange_first.values == olde);
+
+    // ---- plonky2's contract at this boundary: inconsistent input panics ----
+    bool panicked = false;
+    try {
+        std::vector<PolynomialValues> ragged = {PolynomialValues(std::vector<F>(8, 1)), PolynomialValues(std::vector<F>(16, 1))};
+        PolynomialBatch::from_values(ragged, 1, false, 0);
+    } catch (const Panic&) { panicked = true; }
+    CHECK(panicked);
+    panicked = false;
+    try { PolynomialBatch::from_values({PolynomialValues(std::vector<F>(8, 1))}, 1, false, 9); } // cap_height > log2(leaves)
+    catch (const Panic&) { panicked = true; }
+    CHECK(panicked);
+
+    std::puts("plonky2 C++ mirror: all checks passed");
+    return 0;
+}
