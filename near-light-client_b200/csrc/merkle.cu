@@ -16,6 +16,9 @@
 namespace {
 
 constexpr int HASH_THREADS = 128;
+// the limb-resident partial rounds want ~96 registers: 5 CTAs of 128 threads per SM (measured best, tools/ubench/ubench_perm.cu;
+// throughput is flat from 4 to 8 CTAs/SM: the integer pipes, not latency, are the limit)
+constexpr int HASH_MINB = 5;
 
 struct TreeGeom {
     int sub_height;       // log2(leaves per cap subtree)
@@ -41,7 +44,7 @@ __device__ __forceinline__ u64* node_slot(u64* digests, u64* cap, TreeGeom g, in
 // Leaves are dealt to warps round-robin (grid-stride) so that a grid of a few warps per SM sub-partition
 // keeps every multiplier busy without a ragged last wave.
 template <bool COLS>
-__global__ void __launch_bounds__(HASH_THREADS)
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, size_t leaf_stride, size_t elem_stride,
             TreeGeom g, u64* digests, u64* cap) {
     const size_t step = (size_t)gridDim.x * HASH_THREADS;
@@ -56,17 +59,14 @@ k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, si
             for (int i = 0; i < 4; i++)
                 if ((size_t)i < leaf_len) s[i] = gl::canon(in[i * es]);
         } else {
-            size_t off = 0;
-            for (; off + poseidon::RATE <= leaf_len; off += poseidon::RATE) {
-#pragma unroll
-                for (int i = 0; i < poseidon::RATE; i++) s[i] = in[(off + i) * es]; // overwrite mode
-                poseidon::permute_nc(s);
-            }
-            if (off < leaf_len) {
-                const int rem = (int)(leaf_len - off);
+            // one call site for the permutation (its two round bodies are ~29 KB of code: a second inlined copy
+            // for the ragged last block would not fit the instruction cache beside the first)
+#pragma unroll 1
+            for (size_t off = 0; off < leaf_len; off += poseidon::RATE) {
+                const size_t rem = leaf_len - off;
 #pragma unroll
                 for (int i = 0; i < poseidon::RATE; i++)
-                    if (i < rem) s[i] = in[(off + i) * es];
+                    if ((size_t)i < rem) s[i] = in[(off + i) * es]; // overwrite mode
                 poseidon::permute_nc(s);
             }
 #pragma unroll
@@ -82,7 +82,7 @@ k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, si
 // extended while later columns are still crossing PCIe).  Every chunk but the last covers whole 8-element blocks;
 // between chunks the 12-word sponge state of each leaf waits in `state` (state[i * n_leaves + row]: coalesced).
 // Same permutations, same order, same result as k_leaf_hash<true> over all columns (leaf_len > 4 only).
-__global__ void __launch_bounds__(HASH_THREADS)
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, size_t col0, size_t n_cols, bool first,
               bool last, u64* __restrict__ state, TreeGeom g, u64* digests, u64* cap) {
     const size_t step = (size_t)gridDim.x * HASH_THREADS;
@@ -91,17 +91,12 @@ k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, 
         u64 s[poseidon::WIDTH];
 #pragma unroll
         for (int i = 0; i < poseidon::WIDTH; i++) s[i] = first ? 0 : state[i * n_leaves + row];
-        size_t off = 0;
-        for (; off + poseidon::RATE <= n_cols; off += poseidon::RATE) {
-#pragma unroll
-            for (int i = 0; i < poseidon::RATE; i++) s[i] = in[(off + i) * elem_stride];
-            poseidon::permute_nc(s);
-        }
-        if (off < n_cols) { // ragged tail: only the last chunk has one
-            const int rem = (int)(n_cols - off);
+#pragma unroll 1
+        for (size_t off = 0; off < n_cols; off += poseidon::RATE) { // a ragged block only ends the last chunk
+            const size_t rem = n_cols - off;
 #pragma unroll
             for (int i = 0; i < poseidon::RATE; i++)
-                if (i < rem) s[i] = in[(off + i) * elem_stride];
+                if ((size_t)i < rem) s[i] = in[(off + i) * elem_stride];
             poseidon::permute_nc(s);
         }
         if (last) {
@@ -116,7 +111,7 @@ k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, 
 }
 
 // layer (i) -> layer (i+1): one thread per parent.
-__global__ void __launch_bounds__(HASH_THREADS)
+__global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) {
     const size_t j = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x;
     if (j >= n_parents) return;
@@ -197,16 +192,15 @@ __global__ void k_two_to_one_many(const u64* l, const u64* r, size_t count, u64*
 
 } // namespace
 
-// Leaves are dealt grid-stride to c CTAs per SM, c in 4..8 (8 x 128 threads x 64 registers fill the register
-// file).  More resident warps hide latency a little better (measured: 4 -> 8 CTAs/SM is +5%), but the work
-// per thread is ceil(n / threads): pick the c with the best product of the two.
+// Leaves are dealt grid-stride to c CTAs per SM, c <= HASH_MINB.  The work per thread is ceil(n / threads): pick the c
+// with the least ragged last wave (throughput barely depends on c itself).
 static unsigned leaf_grid(nlc_ctx* ctx, size_t n_leaves) {
     const size_t want = (n_leaves + HASH_THREADS - 1) / HASH_THREADS;
-    if (want <= (size_t)ctx->sm_count * 8) return (unsigned)want;
-    static const double occ[9] = {0, 0, 0, 0, 0.95, 0.97, 0.98, 0.99, 1.0};
-    int best = 8;
+    if (want <= (size_t)ctx->sm_count * HASH_MINB) return (unsigned)want;
+    static const double occ[HASH_MINB + 1] = {0, 0, 0, 0.96, 0.985, 1.0};
+    int best = HASH_MINB;
     double best_eff = 0;
-    for (int c = 4; c <= 8; c++) {
+    for (int c = 3; c <= HASH_MINB; c++) {
         const double threads = (double)ctx->sm_count * c * HASH_THREADS, per = (double)n_leaves / threads;
         const double eff = per / (double)(size_t)(per + 0.999999) * occ[c];
         if (eff > best_eff) best_eff = eff, best = c;

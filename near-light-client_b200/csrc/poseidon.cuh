@@ -34,6 +34,13 @@ constexpr int N_ROUNDS = 2 * HALF_FULL + N_PARTIAL;
 
 static __constant__ uint64_t c_rc[NLC_POSEIDON_N_RC] = NLC_POSEIDON_RC_INIT;
 
+// Every limb-form constant carries a bias (BIAS0, BIAS1, BIAS2) with BIAS0 + 2^22 BIAS1 + 2^43 BIAS2 = 256 p: it
+// changes no value mod p, and it keeps every limb sum of a layer strictly positive even when a loosely normalised
+// input limb (partial rounds, below) has dipped under zero -- so carries are plain logical shifts and glue3's
+// unsigned preconditions (O0, O1 < 2^32, O2 < 2^31) hold with room to spare.
+constexpr uint32_t BIAS0 = (1u << 22) + 256u, BIAS1 = 7u * (1u << 18) - 1u, BIAS2 = (1u << 29) - 1u;
+static_assert(((unsigned __int128)BIAS0 + ((unsigned __int128)BIAS1 << 22) + ((unsigned __int128)BIAS2 << 43)) %
+                      0xFFFFFFFF00000001ULL == 0, "limb bias must be a multiple of p");
 // Round constants in limb form: v[(r*3 + limb)*12 + lane]; one extra all-zero round closes the last layer.
 struct RcLimbs {
     uint32_t v[(N_ROUNDS + 1) * 3 * WIDTH];
@@ -44,10 +51,15 @@ constexpr RcLimbs make_rc_limbs() {
     for (int r = 0; r < N_ROUNDS; r++)
         for (int i = 0; i < WIDTH; i++) {
             const uint64_t c = rc[r * WIDTH + i];
-            t.v[(r * 3 + 0) * WIDTH + i] = (uint32_t)(c & 0x3FFFFFu);
-            t.v[(r * 3 + 1) * WIDTH + i] = (uint32_t)((c >> 22) & 0x1FFFFFu);
-            t.v[(r * 3 + 2) * WIDTH + i] = (uint32_t)(c >> 43);
+            t.v[(r * 3 + 0) * WIDTH + i] = (uint32_t)(c & 0x3FFFFFu) + BIAS0;
+            t.v[(r * 3 + 1) * WIDTH + i] = (uint32_t)((c >> 22) & 0x1FFFFFu) + BIAS1;
+            t.v[(r * 3 + 2) * WIDTH + i] = (uint32_t)(c >> 43) + BIAS2;
         }
+    for (int i = 0; i < WIDTH; i++) { // the closing all-zero round carries the bias too
+        t.v[(N_ROUNDS * 3 + 0) * WIDTH + i] = BIAS0;
+        t.v[(N_ROUNDS * 3 + 1) * WIDTH + i] = BIAS1;
+        t.v[(N_ROUNDS * 3 + 2) * WIDTH + i] = BIAS2;
+    }
     return t;
 }
 static __constant__ RcLimbs c_rc_limbs = make_rc_limbs();
@@ -150,25 +162,56 @@ __device__ __forceinline__ void mds_layer(uint64_t (&s)[WIDTH], const uint32_t* 
 }
 
 // plonky2's naive round structure (constant layer, S-box layer, MDS layer); every constant layer but the
-// first is folded into the preceding MDS layer.  One body per round kind keeps the loop inside the
-// instruction cache.  (Tried and dropped: keeping lanes 1..11 in limb form across the partial rounds with a
-// signed carry normalisation instead of glue + split -- 12% fewer instructions, but 114 registers and more
-// half-rate shift/logic work: 1.04 vs 1.17 G permutations/s.)
+// first is folded into the preceding MDS layer.
+//
+// Full rounds take and return 64-bit lanes (every lane meets an S-box).  In the 22 partial rounds only lane 0
+// does: lanes 1..11 go from one MDS layer straight into the next, so they STAY in limb form.  After a layer
+// the limb sums O_k (< 2^31 in magnitude) are brought back under ~2^22.6 by one parallel carry step, no ripple:
+//   L0 = (O0 & m22) - c2,  L1 = (O1 & m21) + c0 + (c2 << 10),  L2 = (O2 & m21) + c1,   c_k = O_k >> {22,21,21}
+// (the carry out of the top limb weighs 2^64 == 2^32 - 1: +2^10 units of limb 1, -1 unit of limb 0; L0 may dip a
+// few hundred below zero, which the bias of the next layer's constants absorbs).  10 instructions per lane instead of glue (16) + split (5);
+// only lane 0 is glued for its S-box.  264 * 2^22.6 + 2^22 < 2^31, so the next layer cannot overflow.
+// One body per round kind, both visited from one outer loop, keeps the code inside the instruction cache.
 __device__ __forceinline__ void permute_nc(uint64_t (&s)[WIDTH]) {
 #pragma unroll
     for (int i = 0; i < WIDTH; i++) s[i] = gl::add_nc(s[i], c_rc[i]);
     const uint32_t* rc = c_rc_limbs.v;
     const uint32_t z = c_zero;
 #pragma unroll 1
-    for (int r = 0; r < N_ROUNDS; r++) {
-        if (r < HALF_FULL || r >= HALF_FULL + N_PARTIAL) {
+    for (int phase = 0; phase < 2; phase++) {
+#pragma unroll 1
+        for (int r = 0; r < HALF_FULL; r++) {
 #pragma unroll
             for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
-        } else {
-            s[0] = sbox7(s[0]);
+            rc += 3 * WIDTH;
+            mds_layer(s, rc, z);
         }
-        rc += 3 * WIDTH;
-        mds_layer(s, rc, z);
+        if (phase) break;
+        uint32_t L0[WIDTH], L1[WIDTH], L2[WIDTH];
+#pragma unroll
+        for (int i = 1; i < WIDTH; i++) split3(s[i], L0[i], L1[i], L2[i]);
+        uint64_t s0 = s[0];
+        uint32_t O0[WIDTH], O1[WIDTH], O2[WIDTH];
+#pragma unroll 1
+        for (int r = 0;; r++) {
+            s0 = sbox7(s0);
+            split3(s0, L0[0], L1[0], L2[0]);
+            rc += 3 * WIDTH;
+            circ12(L0, O0, rc, z);
+            circ12(L1, O1, rc + WIDTH, z);
+            circ12(L2, O2, rc + 2 * WIDTH, z);
+            if (r == N_PARTIAL - 1) break; // the last layer's sums go back to 64-bit lanes below
+            s0 = glue3(O0[0], O1[0], O2[0]);
+#pragma unroll
+            for (int i = 1; i < WIDTH; i++) {
+                const uint32_t c0 = O0[i] >> 22, c1 = O1[i] >> 21, c2 = O2[i] >> 21; // O_k > 0 thanks to the bias
+                L0[i] = (O0[i] & 0x3FFFFFu) - c2;
+                L1[i] = (O1[i] & 0x1FFFFFu) + c0 + (c2 << 10);
+                L2[i] = (O2[i] & 0x1FFFFFu) + c1;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < WIDTH; i++) s[i] = glue3(O0[i], O1[i], O2[i]);
     }
 }
 
