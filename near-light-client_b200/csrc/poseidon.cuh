@@ -113,30 +113,26 @@ __device__ __forceinline__ void circ12(const uint32_t (&x)[WIDTH], uint32_t (&o)
     o[0] += 8u * x[0]; // MDS_MATRIX_DIAG = [8, 0, ...]
 }
 
-// V = O0 + 2^22 O1 + 2^43 O2 (O0, O1 < 2^32 unsigned, O2 < 2^31) mod p, any representative.  V < 2^75 is formed as
-// three words (w2 < 2^11); w2 2^64 == w2 2^32 - w2 is folded into the low two words with a signed overflow word
-// tw in {-1,0,1}, and tw 2^64 == tw eps closes it (no second wrap: after a carry the sum is < 2^43, after a borrow it
-// is >= 2^64 - 2^11).
+// V = O0 + 2^22 O1 + 2^43 O2 (mod p), any representative.  With O2 = 2^21 h + l the top part h 2^64 == h 2^32 - h is
+// folded BEFORE the limbs are assembled: V == (O0 - h) + 2^22 O1 + 2^32 h + 2^43 l, where O0 - h >= 0 because every
+// limb sum carries BIAS0 > 2^22 > h, and the sum is below 2^64 + 2^53: at most one carry out of 64 bits, repaid with
+// + eps (2^64 == eps), which cannot wrap again.  12 instructions.
 __device__ __forceinline__ uint64_t glue3(uint32_t O0, uint32_t O1, uint32_t O2) {
     uint32_t r0, r1;
     asm("{\n\t"
-        ".reg .u32 a,b,c,d,w0,w1,w2,m,tw,sg;\n\t"
+        ".reg .u32 h,a,b,c,t,w0,w1,k,m;\n\t"
+        "shr.u32 h,%4,21;\n\t"
         "shl.b32 a,%3,22;\n\t"
         "shr.u32 b,%3,10;\n\t"
         "shl.b32 c,%4,11;\n\t"
-        "shr.u32 d,%4,21;\n\t"
-        "add.cc.u32 w0,%2,a;\n\t"
+        "sub.u32 t,%2,h;\n\t"
+        "add.u32 b,b,h;\n\t"
+        "add.cc.u32 w0,t,a;\n\t"
         "addc.cc.u32 w1,b,c;\n\t"
-        "addc.u32 w2,d,0;\n\t"
-        "sub.cc.u32 w0,w0,w2;\n\t"
-        "subc.cc.u32 w1,w1,0;\n\t"
-        "subc.u32 tw,0,0;\n\t"
-        "add.cc.u32 w1,w1,w2;\n\t"
-        "addc.u32 tw,tw,0;\n\t"
-        "sub.u32 m,0,tw;\n\t"
-        "shr.s32 sg,tw,31;\n\t"
+        "addc.u32 k,0,0;\n\t"
+        "sub.u32 m,0,k;\n\t"
         "add.cc.u32 %0,w0,m;\n\t"
-        "addc.u32 %1,w1,sg;\n\t"
+        "addc.u32 %1,w1,0;\n\t"
         "}"
         : "=r"(r0), "=r"(r1)
         : "r"(O0), "r"(O1), "r"(O2));
