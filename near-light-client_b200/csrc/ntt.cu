@@ -148,7 +148,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
     u64* d = dst + blockIdx.y * dst_stride + base;
     const u32 total = (u32)T << S;
 
-    for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+    _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 t = idx & (T - 1), ih = idx >> log_T;
         size_t off = ((size_t)ih << L) + low0 + t;
         u64 v = gl::canon(s[off]);
@@ -157,7 +157,7 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
     }
     __syncthreads();
     fft_tile<true, INV>(sm, S, plan, log_T, 0, roots);
-    for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+    _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         u32 t = idx & (T - 1), pos = idx >> log_T;
         size_t off = ((size_t)pos << L) + low0 + t;
         d[off] = gl::mul(sm[idx], tw[off]);
@@ -182,7 +182,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
     const int log_nb = log_n - S;
     const u32 Gc_mask = (1u << log_Gc) - 1;
 
-    for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+    _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
         const u32 g = idx >> S, e = idx & (len - 1);
         const size_t col = ((size_t)blockIdx.y << log_Gc) + (g & Gc_mask);
         size_t blk = ((size_t)blockIdx.x << log_Gb) + (g >> log_Gc);
@@ -198,7 +198,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
     __syncthreads();
     fft_tile<false, INV>(sm, S, plan, log_G, pitch, roots);
     if (MODE == OUT_COLS) { // column-major, index-bit-reversed: the tile is contiguous in its column
-        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+        _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
             const u32 g = idx >> S, q = idx & (len - 1);
             const size_t col = ((size_t)blockIdx.y << log_Gc) + (g & Gc_mask);
             if (col >= n_cols) continue;
@@ -208,7 +208,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
             dst[(col0 + col) * dst_stride + row_base + (blk << S) + q] = v;
         }
     } else if (MODE == OUT_ROWS) { // row-major: the Gc columns of a row are adjacent words
-        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+        _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
             const u32 gc = idx & Gc_mask, rest = idx >> log_Gc;
             const u32 q = rest & (len - 1), gb = rest >> S;
             const size_t col = ((size_t)blockIdx.y << log_Gc) + gc;
@@ -220,7 +220,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
         }
     } else { // natural order: output k = bitrev_S(q) * 2^log_nb + block index, contiguous over the Gb blocks
         const u32 G = 1u << log_G;
-        for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
+        _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
             const u32 g = idx & (G - 1), q = idx >> log_G;
             u64 v = sm[g * pitch + pad16(q)];
             if (scale != 1) v = gl::mul(v, scale);
