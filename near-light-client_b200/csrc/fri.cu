@@ -92,7 +92,8 @@ k_reduce_polys(const u64* const* __restrict__ polys, const u64* __restrict__ apo
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     u64 acc0 = 0, acc1 = 0;
-    for (u32 k = 0; k < K; k++) {
+#pragma unroll 8
+    for (u32 k = 0; k < K; k++) { // the loads do not depend on the accumulators: eight in flight per thread
         const u64 c = gl::canon(polys[k][i]);
         acc0 = gl::add(acc0, gl::mul(apow[2 * k], c));
         acc1 = gl::add(acc1, gl::mul(apow[2 * k + 1], c));
@@ -172,7 +173,7 @@ inline unsigned blocks_for(size_t n, unsigned t = 256) { return (unsigned)((n + 
 // E = exclusive suffix Horner scan of x (planes, length len) with ratio rho.
 void suffix_scan(nlc_ctx* ctx, const u64* x0, const u64* x1, size_t len, Ext2 rho, u64* e0, u64* e1) {
     const int L = 32;
-    if (len <= 2048) {
+    if (len <= 64 || len % L) { // one thread, one step per element: only for the top of the recursion
         NLC_LAUNCH(ctx, k_scan_serial, 1, 32, 0, x0, x1, len, rho, e0, e1);
         return;
     }

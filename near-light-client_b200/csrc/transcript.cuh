@@ -13,32 +13,47 @@
 namespace transcript {
 
 // One permutation per half-warp: lanes base..base+11 (base = lane & 16) pass s_i and receive the permuted s_i
-// (canonical); lanes 12..15 of each half idle along.  All 32 lanes must call.  The latency of ONE permutation is
-// what this form is for (transcript, top of a Merkle tree): S-boxes run across lanes, the MDS layer is 12 shuffles.
+// (canonical); lanes 12..15 of each half idle along.  All 32 lanes must call; at most 8 warps per block.  The
+// latency of ONE permutation is what this form is for (transcript, narrow Merkle layers): with a single warp on the
+// scheduler every dependent instruction costs its full latency, so the round is kept short -- S-boxes run across
+// lanes, the state is exchanged through shared memory (one 8-byte store, six 16-byte broadcast loads; double
+// buffered, one __syncwarp per round) and lane r forms its MDS row with 24 IMAD.WIDE on coefficients it rotated
+// into registers once, in four independent accumulation chains.
+// Lane-varying reads of a __constant__ array are serialised per distinct address (12 replays per round here, the
+// single biggest latency item of the first version): the round constants of this form live in global memory instead
+// (L1-resident after the first permutation) and the next round's is fetched a round ahead.
+static __device__ const uint64_t g_rc[NLC_POSEIDON_N_RC + 12] = NLC_POSEIDON_RC_INIT;
+static __constant__ uint32_t c_circ2[24] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20,
+                                            17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
 __device__ __forceinline__ u64 warp_permute(u64 x, int lane) {
-    constexpr u32 CIRC[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
-    const int base = lane & 16, l16 = lane & 15;
-    const int l12 = l16 < 12 ? l16 : 0;
+    __shared__ ulonglong2 xch[8][2][2][6]; // [warp][half-warp][buffer][6 pairs = 12 lanes]
+    const int l16 = lane & 15, l12 = l16 < 12 ? l16 : 0;
+    ulonglong2(*buf)[6] = xch[(threadIdx.x >> 5) & 7][lane >> 4];
+    // out[r] = sum_j x[j] * CIRC[(j - r) mod 12]  (+ 8 x[0] for r = 0: MDS_MATRIX_DIAG)
+    u32 coef[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) coef[j] = c_circ2[j + 12 - l12];
+    if (l12 == 0) coef[0] += 8;
+    u64 rc = __ldg(g_rc + l12);
 #pragma unroll 1
     for (int r = 0; r < 30; r++) {
-        x = gl::add_nc(x, poseidon::c_rc[r * 12 + l12]);
+        x = gl::add_nc(x, rc);
+        rc = __ldg(g_rc + (r + 1) * 12 + l12); // round 30 reads the zero padding
         const bool full = r < 4 || r >= 26;
         if (full || l16 == 0) x = poseidon::sbox7(x);
-        const u32 lo = (u32)x, hi = (u32)(x >> 32);
-        u64 alo = 0, ahi = 0;
+        u64* mine = reinterpret_cast<u64*>(buf[r & 1]);
+        if (l16 < 12) mine[l16] = x;
+        __syncwarp();
+        u64 a0 = 0, a1 = 0, b0 = 0, b1 = 0; // low-word and high-word sums, two chains each
 #pragma unroll
-        for (int i = 0; i < 12; i++) {
-            int src = l12 + i;
-            src = base + (src >= 12 ? src - 12 : src);
-            u32 l = __shfl_sync(0xffffffffu, lo, src);
-            u32 h = __shfl_sync(0xffffffffu, hi, src);
-            alo += (u64)l * CIRC[i];
-            ahi += (u64)h * CIRC[i];
+        for (int q = 0; q < 6; q++) {
+            const ulonglong2 v = buf[r & 1][q];
+            a0 += (u64)(u32)v.x * coef[2 * q];
+            b0 += (u64)(u32)(v.x >> 32) * coef[2 * q];
+            a1 += (u64)(u32)v.y * coef[2 * q + 1];
+            b1 += (u64)(u32)(v.y >> 32) * coef[2 * q + 1];
         }
-        if (l16 == 0) {
-            alo += (u64)lo * 8u;
-            ahi += (u64)hi * 8u;
-        }
+        const u64 alo = a0 + a1, ahi = b0 + b1; // < 2^41 each
         u64 l = alo + (ahi << 32);
         u64 h = (ahi >> 32) + (l < alo ? 1 : 0);
         u64 t1 = (h << 32) - h;
