@@ -86,20 +86,35 @@ __global__ void k_ext_pows(const u64* alpha, size_t count, u64* out) {
     out[2 * k + 1] = r.a1;
 }
 
-// reduce_polys_base: comp[i] = sum_k alpha^k * poly_k[i]
+// reduce_polys_base: comp[i] = sum_k alpha^k * poly_k[i].  A streaming pass over every committed coefficient
+// (221 MB for a 422-column STARK): the polynomials are cut into slices (blockIdx.y) so that enough warps are in
+// flight to cover HBM latency; slice sums are added by k_reduce_sum.
 __global__ void __launch_bounds__(256)
-k_reduce_polys(const u64* const* __restrict__ polys, const u64* __restrict__ apow, u32 K, size_t n, u64* c0, u64* c1) {
+k_reduce_polys(const u64* const* __restrict__ polys, const u64* __restrict__ apow, u32 K, u32 k_per, size_t n, u64* p0,
+               u64* p1) {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const u32 k0 = blockIdx.y * k_per, k1 = k0 + k_per < K ? k0 + k_per : K;
     u64 acc0 = 0, acc1 = 0;
-#pragma unroll 8
-    for (u32 k = 0; k < K; k++) { // the loads do not depend on the accumulators: eight in flight per thread
+#pragma unroll 4
+    for (u32 k = k0; k < k1; k++) { // the loads do not depend on the accumulators: several in flight per thread
         const u64 c = gl::canon(polys[k][i]);
         acc0 = gl::add(acc0, gl::mul(apow[2 * k], c));
         acc1 = gl::add(acc1, gl::mul(apow[2 * k + 1], c));
     }
-    c0[i] = acc0;
-    c1[i] = acc1;
+    p0[blockIdx.y * n + i] = acc0;
+    p1[blockIdx.y * n + i] = acc1;
+}
+__global__ void k_reduce_sum(const u64* p0, const u64* p1, u32 S, size_t n, u64* c0, u64* c1) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    u64 a0 = 0, a1 = 0;
+    for (u32 s = 0; s < S; s++) {
+        a0 = gl::add(a0, p0[s * n + i]);
+        a1 = gl::add(a1, p1[s * n + i]);
+    }
+    c0[i] = a0;
+    c1[i] = a1;
 }
 
 // Exclusive suffix Horner scan E[i] = sum_{j>i} x[j] rho^(j-i-1), three kernels + recursion.
@@ -196,7 +211,10 @@ void challenger_get_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, size_t n, u64* out
 }
 void fri_pow_dev(nlc_ctx* ctx, const nlc_challenger* ch_dev, int pow_bits, u64* witness_dev) {
     NLC_CUDA(cudaMemsetAsync(witness_dev, 0xFF, sizeof(u64), ctx->stream));
-    NLC_LAUNCH(ctx, k_pow, (unsigned)(ctx->sm_count * 4), 256, 0, ch_dev, pow_bits, (unsigned long long*)witness_dev);
+    // one wave of nonces ~ the expected search length 2^pow_bits: a bigger grid only hashes nonces nobody needs
+    size_t ctas = pow_bits >= 8 && pow_bits < 40 ? (((size_t)1 << pow_bits) + 255) / 256 : 1;
+    if (ctas > (size_t)ctx->sm_count * 3) ctas = (size_t)ctx->sm_count * 3;
+    NLC_LAUNCH(ctx, k_pow, (unsigned)ctas, 256, 0, ch_dev, pow_bits, (unsigned long long*)witness_dev);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -356,7 +374,16 @@ void fri_begin(nlc_fri_state* s, const nlc_fri_instance* inst) {
         // the pointer table is consumed by the kernel launched right after; a pageable source makes this copy
         // complete (staged) before the call returns, so the vector may go out of scope
         if (K) NLC_CUDA(cudaMemcpyAsync(ptrs_dev, ptrs.data(), K * sizeof(u64*), cudaMemcpyHostToDevice, ctx->stream));
-        NLC_LAUNCH(ctx, k_reduce_polys, blocks_for(n), 256, 0, ptrs_dev, apow, K, n, c0, c1);
+        const u32 S = K >= 64 ? std::min<u32>(16, K / 32) : 1, k_per = (K + S - 1) / S;
+        if (S == 1) {
+            NLC_LAUNCH(ctx, k_reduce_polys, dim3(blocks_for(n), 1), 256, 0, ptrs_dev, apow, K, K ? K : 1, n, c0, c1);
+        } else {
+            u64* part = ctx->dmalloc(2 * (size_t)S * n);
+            NLC_LAUNCH(ctx, k_reduce_polys, dim3(blocks_for(n), S), 256, 0, ptrs_dev, apow, K, k_per, n, part,
+                       part + (size_t)S * n);
+            NLC_LAUNCH(ctx, k_reduce_sum, blocks_for(n), 256, 0, part, part + (size_t)S * n, S, n, c0, c1);
+            ctx->dfree(part);
+        }
         const Ext2 z = {gl::canon(inst->points[2 * b]), gl::canon(inst->points[2 * b + 1])};
         suffix_scan(ctx, c0, c1, n, z, q0, q1);
         NLC_LAUNCH(ctx, k_shift_add, blocks_for(n), 256, 0, s->plane(0, 0), s->plane(0, 1), q0, q1, apow + 2 * (size_t)K, n);
