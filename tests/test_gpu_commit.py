@@ -16,6 +16,8 @@ SHAPES = [  # (W, log_n, rate_bits, cap_height)
     (7, 9, 1, 4), (8, 10, 1, 4), (9, 10, 3, 4), (17, 11, 1, 4), (33, 12, 3, 4), (135, 12, 3, 4),
     (20, 13, 3, 4), (16, 14, 3, 4), (64, 14, 1, 4), (5, 16, 1, 4), (3, 17, 1, 4), (2, 21, 1, 4),
     (2, 8, 2, 10),  # cap_height == log2(N): digests empty, cap = leaf hashes
+    # host-fed commits stream the leaf sponge in column chunks (16, then doubling / tripling): chunk boundaries
+    (32, 10, 1, 4), (47, 9, 3, 4), (48, 9, 1, 2), (49, 9, 1, 2), (63, 8, 2, 4), (100, 8, 2, 4), (113, 8, 1, 3),
 ]
 
 
