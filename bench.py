@@ -205,6 +205,7 @@ def run_replay_workload(args):
     kind = args.workload.split("_")[1]
     line, gproof = replay_gpu(kind, args.steps, keep_proof=True)
     O = graft.load_oracle()
+    O.set_threads(len(os.sched_getaffinity(0)))
     c = replay(kind, O, O.commit_from_values, O.commit_from_coeffs, O.FriInstance,
                lambda log_n, r, cap, pw, q: O.fri_params(log_n, r, cap, pw, q, 4, 5),
                O.Challenger, O.prove_openings, 0xC0FFEE + 10)
@@ -230,6 +231,8 @@ def run_reference(args, rank, world):
     log_n = min(log_n, args.ref_sample_log_rows)  # bounded sample: same columns / rate / cap, fewer rows
     n = 1 << log_n
     values = synth_values(W, n, 0xC0FFEE + 1)
+    # torchrun exports OMP_NUM_THREADS=1 to every rank: the reference arm runs on rank 0 alone and takes every core
+    O.set_threads(len(os.sched_getaffinity(0)))
     cores = O.get_threads()
     for _ in range(max(1, min(args.warmup, 1))):
         O.commit_from_values(values, r, cap)
@@ -422,6 +425,7 @@ def run_ours(args, rank, local_rank, world):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         O = graft.load_oracle()
+        O.set_threads(len(os.sched_getaffinity(0)))
         vals = host.numpy().view(np.uint64)
         O.commit_from_values(vals[:8], r, cap)  # warm tables
         t0 = time.perf_counter()
