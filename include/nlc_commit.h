@@ -127,6 +127,31 @@ int nlc_coset_ifft(nlc_ctx* ctx, uint64_t* data, size_t n_cols, int log_n, uint6
 /* PolynomialValues::lde_onto_coset(rate_bits): in = n_cols x n values, out = n_cols x (n << rate_bits). */
 int nlc_lde_onto_coset(nlc_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n_cols, int log_n, int rate_bits);
 
+/* ---- "next" row SURVEY.md 8f.1: quotient_polys without the AIR evaluation -------------------- */
+/* The tables vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:278-302 builds before its evaluation loop, over the
+ * quotient domain of size = n << quotient_degree_bits (any output may be NULL):
+ *   coset_x[i]        = g * w_size^i              (cyclic_subgroup_coset_known_order, prover.rs:298-302)
+ *   lagrange_first/last = PolynomialValues::selector(n, 0 / n-1).lde_onto_coset(quotient_degree_bits) (prover.rs:278-283)
+ *   zh_inv[k], k < 2^quotient_degree_bits: ZeroPolyOnCoset::new(log_n, quotient_degree_bits).eval_inverse(i) =
+ *                       zh_inv[i mod 2^quotient_degree_bits]   (prover.rs:285, 336-337) */
+int nlc_quotient_domain(nlc_ctx* ctx, int log_n, int quotient_degree_bits, uint64_t* coset_x, uint64_t* lagrange_first,
+                        uint64_t* lagrange_last, uint64_t* zh_inv);
+/* What prover.rs does with the constraint accumulators once the AIR has been evaluated (prover.rs:336-357 and
+ * 158-178): evals = size x n_challenges row-major (one row per point of the quotient domain, natural order: the
+ * `quotient_values` before `transpose`); if divide_by_zh the rows are first multiplied by 1/Z_H (pass the raw
+ * accumulators), else they are taken as already divided.  Each column is coset_ifft(F::coset_shift())'d, checked
+ * by trim_to_len(n * quotient_degree_factor) (error "Quotient has failed, the vanishing polynomial is not divisible
+ * by Z_H" like the reference's expect), split into quotient_degree_factor chunks of n coefficients (polynomial j,
+ * chunk c -> column j*factor + c) and committed as PolynomialBatch::from_coeffs(chunks, rate_bits, false,
+ * cap_height, ..).  Errors if quotient_degree_bits > rate_bits (the assert of prover.rs:270-273). */
+int nlc_quotient_commit(nlc_ctx* ctx, const uint64_t* evals, size_t n_challenges, int log_n, int quotient_degree_bits,
+                        size_t quotient_degree_factor, int divide_by_zh, int rate_bits, int cap_height,
+                        nlc_batch** out);
+/* Same with the accumulators already in HBM (an on-device AIR evaluator, SURVEY.md 8f.3, feeds this). */
+int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_challenges, int log_n,
+                            int quotient_degree_bits, size_t quotient_degree_factor, int divide_by_zh, int rate_bits,
+                            int cap_height, nlc_batch** out);
+
 /* ---- a4: Poseidon (plonky2::hash::{poseidon,hashing}) -------------------------------------- */
 /* PoseidonPermutation::permute on `count` independent 12-lane states (in place). */
 int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count);

@@ -337,6 +337,24 @@ struct FriProof {
 };
 
 // ---- fri/oracle.rs: PolynomialBatch --------------------------------------------------------------------------
+// The tables quotient_polys builds before its evaluation loop (prover.rs:278-302), computed on the device:
+// coset[i] = g w^i over the quotient domain, lagrange_first / lagrange_last = selector(n, 0 | n-1)
+// .lde_onto_coset(quotient_degree_bits), and ZeroPolyOnCoset::eval_inverse(i) = z_h_inverses[i % 2^bits].
+struct QuotientDomain {
+    std::vector<F> coset, z_h_inverses;
+    PolynomialValues lagrange_first, lagrange_last;
+    QuotientDomain(size_t degree_bits, size_t quotient_degree_bits)
+        : coset((size_t)1 << (degree_bits + quotient_degree_bits)),
+          z_h_inverses((size_t)1 << quotient_degree_bits),
+          lagrange_first(std::vector<F>((size_t)1 << (degree_bits + quotient_degree_bits))),
+          lagrange_last(std::vector<F>((size_t)1 << (degree_bits + quotient_degree_bits))) {
+        Context& c = Context::current();
+        c.check(nlc_quotient_domain(c.raw(), (int)degree_bits, (int)quotient_degree_bits, coset.data(),
+                                    lagrange_first.values.data(), lagrange_last.values.data(), z_h_inverses.data()));
+    }
+    F eval_inverse(size_t i) const { return z_h_inverses[i % z_h_inverses.size()]; }
+};
+
 class PolynomialBatch {
   public:
     struct Tree { // the fields of merkle_tree the prover reads (prover.rs:95,180,210); leaves / digests on demand
@@ -359,6 +377,32 @@ class PolynomialBatch {
         for (const auto& p : polynomials) cols.push_back(p.coeffs.data());
         return commit(cols, polynomials.empty() ? 0 : polynomials[0].len(), lens_equal(polynomials), rate_bits, blinding,
                       cap_height, false);
+    }
+    // SURVEY.md 8f.1 -- what prover.rs:336-357 and :158-178 do with the constraint evaluations: `quotient_values` is
+    // the row-per-point Vec<Vec<F>> (num_challenges values per row, size = n << log2_ceil(quotient_degree_factor)
+    // rows) flattened; per challenge coset_ifft(F::coset_shift()), trim_to_len(n * factor).expect("Quotient has
+    // failed ..."), chunks(n), from_coeffs(chunks, rate_bits, false, cap_height).  divide_by_zh: rows are the raw
+    // accumulators, multiplied by ZeroPolyOnCoset::eval_inverse first (prover.rs:336-340).
+    static PolynomialBatch from_quotient_values(const std::vector<F>& quotient_values, size_t num_challenges,
+                                                size_t degree_log, size_t quotient_degree_factor, size_t rate_bits,
+                                                size_t cap_height, bool divide_by_zh = false) {
+        size_t qdb = 0;
+        while (((size_t)1 << qdb) < quotient_degree_factor) qdb++; // log2_ceil
+        if (num_challenges == 0 || quotient_values.size() != (num_challenges << (degree_log + qdb)))
+            throw Panic("quotient_values must hold (n << log2_ceil(quotient_degree_factor)) rows of num_challenges");
+        Context& c = Context::current();
+        nlc_batch* h = nullptr;
+        c.check(nlc_quotient_commit(c.raw(), quotient_values.data(), num_challenges, (int)degree_log, (int)qdb,
+                                    quotient_degree_factor, divide_by_zh ? 1 : 0, (int)rate_bits, (int)cap_height, &h));
+        PolynomialBatch b;
+        b.h_.reset(h, nlc_batch_free);
+        b.n_polys_ = num_challenges * quotient_degree_factor;
+        b.degree_log = degree_log;
+        b.rate_bits = rate_bits;
+        b.cap_height_ = cap_height;
+        b.merkle_tree.cap.hashes.resize((size_t)1 << cap_height);
+        c.check(nlc_batch_cap(h, b.merkle_tree.cap.hashes[0].elements));
+        return b;
     }
     size_t num_polys() const { return n_polys_; }
     // `polynomials` field (proof.rs:307-310 evaluates them at zeta): fetched from HBM on first use

@@ -62,6 +62,11 @@ SIGNATURES = {
     "nlc_commit_from_coeffs_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_trace_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                              C.POINTER(vp)]),
+    "nlc_quotient_domain": (C.c_int, [vp, C.c_int, C.c_int, u64p, u64p, u64p, u64p]),
+    "nlc_quotient_commit": (C.c_int, [vp, u64p, C.c_size_t, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_int,
+                                      C.POINTER(vp)]),
+    "nlc_quotient_commit_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
+                                          C.c_int, C.POINTER(vp)]),
     "nlc_batch_free": (None, [vp]),
     "nlc_batch_info": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nlc_batch_cap": (C.c_int, [vp, u64p]),

@@ -512,6 +512,99 @@ int nlc_lde_onto_coset(nlc_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n
     });
 }
 
+// ---- quotient_polys without the AIR evaluation (prover.rs:253-358, 158-178) ----
+int nlc_quotient_domain(nlc_ctx* ctx, int log_n, int quotient_degree_bits, uint64_t* coset_x, uint64_t* lagrange_first,
+                        uint64_t* lagrange_last, uint64_t* zh_inv) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        const int qdb = quotient_degree_bits;
+        NLC_CHECK(log_n >= 0 && qdb >= 0 && log_n + qdb <= 32, "log_n + quotient_degree_bits out of range");
+        const size_t n = (size_t)1 << log_n, size = n << qdb;
+        const int log_size = log_n + qdb;
+        if (zh_inv) {
+            const std::vector<u64> inv = zero_poly_on_coset_inverses(log_n, qdb);
+            memcpy(zh_inv, inv.data(), inv.size() * sizeof(u64));
+        }
+        if (coset_x) {
+            DevBuf x(ctx, size);
+            coset_points(ctx, log_size, x.p);
+            d2h(ctx, coset_x, x.p, size * sizeof(u64));
+            sync(ctx);
+        }
+        if (lagrange_first || lagrange_last) {
+            // PolynomialValues::selector(degree, i).lde_onto_coset(quotient_degree_bits), i = 0 and degree - 1
+            DevBuf vals(ctx, 2 * n), padded(ctx, 2 * size), res(ctx, 2 * size);
+            DevBuf scratch(ctx, std::max(ntt_scratch_words(2, log_n), ntt_scratch_words(2, log_size)));
+            NLC_CUDA(cudaMemsetAsync(vals.p, 0, 2 * n * sizeof(u64), ctx->stream));
+            NLC_CUDA(cudaMemsetAsync(padded.p, 0, 2 * size * sizeof(u64), ctx->stream));
+            const u64 one = 1;
+            NLC_CUDA(cudaMemcpyAsync(vals.p, &one, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+            NLC_CUDA(cudaMemcpyAsync(vals.p + 2 * n - 1, &one, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+            NttJob inv;
+            inv.src = vals.p;
+            inv.src_stride = n;
+            inv.n_cols = 2;
+            inv.log_n = log_n;
+            inv.inverse = true;
+            inv.dst = padded.p;
+            inv.dst_stride = size;
+            inv.scratch = scratch.p;
+            ntt_run(ctx, inv);
+            NttJob fwd;
+            fwd.src = padded.p;
+            fwd.src_stride = size;
+            fwd.n_cols = 2;
+            fwd.log_n = log_size;
+            fwd.pre_shift = gl::GENERATOR;
+            fwd.dst = res.p;
+            fwd.dst_stride = size;
+            fwd.scratch = scratch.p;
+            ntt_run(ctx, fwd);
+            if (lagrange_first) d2h(ctx, lagrange_first, res.p, size * sizeof(u64));
+            if (lagrange_last) d2h(ctx, lagrange_last, res.p + size, size * sizeof(u64));
+            sync(ctx);
+        }
+    });
+}
+
+static void quotient_check(size_t n_ch, int log_n, int qdb, size_t qdf, int rate_bits) {
+    NLC_CHECK(n_ch > 0, "no challenges");
+    NLC_CHECK(log_n >= 0 && qdb >= 0 && log_n + qdb <= 32, "log_n + quotient_degree_bits out of range");
+    NLC_CHECK(qdb <= rate_bits, "Having constraints of degree higher than the rate is not supported yet.");
+    NLC_CHECK(qdf >= 1 && qdf <= ((size_t)1 << qdb), "quotient_degree_factor exceeds 2^quotient_degree_bits");
+}
+int nlc_quotient_commit(nlc_ctx* ctx, const uint64_t* evals, size_t n_challenges, int log_n, int quotient_degree_bits,
+                        size_t quotient_degree_factor, int divide_by_zh, int rate_bits, int cap_height,
+                        nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && evals, "null argument");
+        *out = nullptr;
+        quotient_check(n_challenges, log_n, quotient_degree_bits, quotient_degree_factor, rate_bits);
+        const size_t words = n_challenges << (log_n + quotient_degree_bits);
+        DevBuf ev(ctx, words);
+        h2d(ctx, ev.p, evals, words * sizeof(u64));
+        *out = quotient_commit_dev(ctx, ev.p, n_challenges, log_n, quotient_degree_bits, quotient_degree_factor,
+                                   divide_by_zh != 0, rate_bits, cap_height);
+        sync(ctx);
+    });
+}
+int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_challenges, int log_n,
+                            int quotient_degree_bits, size_t quotient_degree_factor, int divide_by_zh, int rate_bits,
+                            int cap_height, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && evals_dev, "null argument");
+        *out = nullptr;
+        quotient_check(n_challenges, log_n, quotient_degree_bits, quotient_degree_factor, rate_bits);
+        *out = quotient_commit_dev(ctx, evals_dev, n_challenges, log_n, quotient_degree_bits, quotient_degree_factor,
+                                   divide_by_zh != 0, rate_bits, cap_height);
+    });
+}
+
 // ---- a4 ----
 int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count) {
     if (!ctx) return 1;

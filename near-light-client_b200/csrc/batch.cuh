@@ -46,6 +46,12 @@ void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
 // rows [row0, row0+n_rows) of the leaf matrix, row-major, into out_dev (n_rows x W): plonky2's merkle_tree.leaves
 void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);
 
+// SURVEY.md 8f.1 (prover.rs:253-358 without the AIR evaluation)
+std::vector<u64> zero_poly_on_coset_inverses(int log_n, int qdb);
+void coset_points(nlc_ctx* ctx, int log_size, u64* out_dev);
+nlc_batch* quotient_commit_dev(nlc_ctx* ctx, const u64* evals_dev, size_t n_ch, int log_n, int qdb, size_t qdf,
+                               bool divide_by_zh, int rate_bits, int cap_height);
+
 // ---- fri.cu ----
 void challenger_observe_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, const u64* elems_dev, size_t n);
 void challenger_get_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, size_t n, u64* out_dev);

@@ -36,6 +36,37 @@ __global__ void k_transpose_cols(const u64* __restrict__ rows, size_t width, siz
     }
 }
 
+// quotient_values of prover.rs:312-352 turned into columns: evals is the size x n_ch row-major matrix the AIR
+// evaluation produced (one row per LDE point, natural order); column j, natural order, optionally multiplied by
+// 1/Z_H(x_i) = zh_inv[i mod 2^qdb] (ZeroPolyOnCoset::eval_inverse, prover.rs:336-340)
+__global__ void k_quotient_cols(const u64* __restrict__ evals, size_t n_ch, size_t size, const u64* __restrict__ zh_inv,
+                                u64 zh_mask, u64* __restrict__ out) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < size; i += stride) {
+        const u64 d = zh_inv ? zh_inv[i & zh_mask] : 1;
+        for (size_t j = 0; j < n_ch; j++) {
+            const u64 v = gl::dcanon(evals[i * n_ch + j]);
+            out[j * size + i] = zh_inv ? gl::mul(v, d) : v;
+        }
+    }
+}
+
+// trim_to_len (prover.rs:161-165): every coefficient of column j at index >= keep must be zero
+__global__ void k_trim_check(const u64* __restrict__ coeffs, size_t n_cols, size_t size, size_t keep, int* __restrict__ bad) {
+    const size_t tail = size - keep, total = n_cols * tail, stride = (size_t)gridDim.x * blockDim.x;
+    int any = 0;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride)
+        any |= gl::dcanon(coeffs[(t / tail) * size + keep + t % tail]) != 0;
+    if (__syncthreads_or(any) && threadIdx.x == 0) atomicOr(bad, 1);
+}
+
+// x_i = shift * w^i, i < size (cyclic_subgroup_coset_known_order, prover.rs:298-302)
+__global__ void k_coset_points(u64 shift, u64 w, size_t size, u64* __restrict__ out) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < size; i += stride)
+        out[i] = gl::mul(shift, gl::pow(w, i));
+}
+
 // out[i*W + j] = lde[j*N + bitrev_N(idx[i]*step)]
 __global__ void k_gather_lde_rows(const u64* __restrict__ lde, size_t W, int log_N, const u64* __restrict__ idx,
                                   size_t step, u64* __restrict__ out) {
@@ -219,4 +250,86 @@ void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev) {
     const size_t N = b->n_local();
     dim3 grid((unsigned)((n_rows + 31) / 32), (unsigned)((b->W + 31) / 32));
     NLC_LAUNCH(b->ctx, k_leaf_rows, grid, dim3(32, 8), 0, b->lde, b->W, N, row0, n_rows, out_dev);
+}
+
+// ---- the constraint-free parts of quotient_polys (prover.rs:253-358) ----
+std::vector<u64> zero_poly_on_coset_inverses(int log_n, int qdb) {
+    // ZeroPolyOnCoset::new(n_log, rate_bits): Z_H(g w_N^i) = g^n w_{2^qdb}^(i mod 2^qdb) - 1
+    u64 g_pow_n = gl::GENERATOR;
+    for (int i = 0; i < log_n; i++) g_pow_n = gl::h_mul(g_pow_n, g_pow_n);
+    const u64 w = gl::h_root_of_unity(qdb);
+    std::vector<u64> inv((size_t)1 << qdb);
+    u64 x = 1;
+    for (auto& v : inv) {
+        v = gl::h_inv(gl::sub(gl::h_mul(g_pow_n, x), 1));
+        x = gl::h_mul(x, w);
+    }
+    return inv;
+}
+
+void coset_points(nlc_ctx* ctx, int log_size, u64* out_dev) {
+    const size_t size = (size_t)1 << log_size;
+    const unsigned grid = (unsigned)std::min<size_t>((size + 255) / 256, (size_t)ctx->sm_count * 8);
+    NLC_LAUNCH(ctx, k_coset_points, grid, 256, 0, gl::GENERATOR, gl::h_root_of_unity(log_size), size, out_dev);
+}
+
+nlc_batch* quotient_commit_dev(nlc_ctx* ctx, const u64* evals_dev, size_t n_ch, int log_n, int qdb, size_t qdf,
+                               bool divide_by_zh, int rate_bits, int cap_height) {
+    const size_t n = (size_t)1 << log_n, size = n << qdb, keep = n * qdf;
+    const int log_size = log_n + qdb;
+    u64* vals = ctx->dmalloc(n_ch * size);
+    u64* coef = ctx->dmalloc(n_ch * size);
+    u64* scratch = ctx->dmalloc(ntt_scratch_words(n_ch, log_size));
+    u64* small = ctx->dmalloc(((size_t)1 << qdb) + 1); // zh_inv, then the trim flag
+    nlc_batch* b = nullptr;
+    try {
+        int* flag = (int*)(small + ((size_t)1 << qdb));
+        const u64* zh = nullptr;
+        if (divide_by_zh) {
+            const std::vector<u64> inv = zero_poly_on_coset_inverses(log_n, qdb);
+            // pageable source: the runtime stages it before returning, `inv` may go out of scope
+            NLC_CUDA(cudaMemcpyAsync(small, inv.data(), inv.size() * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+            zh = small;
+        }
+        const unsigned grid = (unsigned)std::min<size_t>((size + 255) / 256, (size_t)ctx->sm_count * 8);
+        NLC_LAUNCH(ctx, k_quotient_cols, grid, 256, 0, evals_dev, n_ch, size, zh, (u64)(((size_t)1 << qdb) - 1), vals);
+        NttJob job; // values.coset_ifft(F::coset_shift()), prover.rs:353-357
+        job.src = vals;
+        job.src_stride = size;
+        job.n_cols = n_ch;
+        job.log_n = log_size;
+        job.inverse = true;
+        job.post_shift = gl::h_inv(gl::GENERATOR);
+        job.dst = coef;
+        job.dst_stride = size;
+        job.scratch = scratch;
+        ntt_run(ctx, job);
+        if (keep < size) {
+            NLC_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
+            const size_t total = n_ch * (size - keep);
+            const unsigned g2 = (unsigned)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
+            NLC_LAUNCH(ctx, k_trim_check, g2, 256, 0, coef, n_ch, size, keep, flag);
+            int bad = 0;
+            NLC_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            NLC_CUDA(cudaStreamSynchronize(ctx->stream));
+            NLC_CHECK(bad == 0, "Quotient has failed, the vanishing polynomial is not divisible by Z_H");
+        }
+        // quotient_poly.chunks(degree) (prover.rs:166): polynomial j, chunk c -> column j*qdf + c
+        b = batch_alloc(ctx, n_ch * qdf, log_n, rate_bits, cap_height);
+        NLC_CUDA(cudaMemcpy2DAsync(b->coeffs, keep * sizeof(u64), coef, size * sizeof(u64), keep * sizeof(u64), n_ch,
+                                   cudaMemcpyDeviceToDevice, ctx->stream));
+        batch_lde_and_tree(b);
+    } catch (...) {
+        if (b) batch_release(b);
+        ctx->dfree(small);
+        ctx->dfree(scratch);
+        ctx->dfree(coef);
+        ctx->dfree(vals);
+        throw;
+    }
+    ctx->dfree(small);
+    ctx->dfree(scratch);
+    ctx->dfree(coef);
+    ctx->dfree(vals);
+    return b;
 }

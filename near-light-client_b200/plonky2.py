@@ -576,6 +576,18 @@ def _col_table(cols):
     return table, arrs, n
 
 
+def quotient_domain(degree_log: int, quotient_degree_bits: int, ctx=None):
+    """The tables starkyx's quotient_polys builds before its evaluation loop (prover.rs:278-302):
+    (coset, lagrange_first, lagrange_last, z_h_inverses) with coset[i] = g * w^i over the quotient domain and
+    ZeroPolyOnCoset::eval_inverse(i) = z_h_inverses[i % 2^quotient_degree_bits]."""
+    ctx = ctx or default_context()
+    size = 1 << (degree_log + quotient_degree_bits)
+    x, lf, ll = (np.zeros(size, np.uint64) for _ in range(3))
+    zh = np.zeros(1 << quotient_degree_bits, np.uint64)
+    ctx._check(_ffi.lib().nlc_quotient_domain(ctx._h, degree_log, quotient_degree_bits, _p(x), _p(lf), _p(ll), _p(zh)))
+    return x, lf, ll, zh
+
+
 class PolynomialBatch:
     """plonky2::fri::oracle::PolynomialBatch resident in HBM.  Struct fields (`polynomials`,
     `merkle_tree.{cap,leaves,digests}`) are materialised on first access."""
@@ -659,6 +671,24 @@ class PolynomialBatch:
         ctx._check(_ffi.lib().nlc_commit_from_trace_rows(ctx._h, _p(r), r.shape[1], col0, n_cols, log_n, rate_bits,
                                                          cap_height, C.byref(h)))
         return cls(ctx, h, n_cols, log_n, rate_bits, cap_height)
+
+    @classmethod
+    def from_quotient_values(cls, quotient_values, degree_log: int, quotient_degree_factor: int, rate_bits: int,
+                             cap_height: int, divide_by_zh: bool = False, ctx=None):
+        """What starkyx does with the constraint evaluations (prover.rs:336-357, 158-178):
+        `quotient_values` = size x num_challenges row-major (size = n << log2_ceil(quotient_degree_factor)) ->
+        per challenge coset_ifft(F::coset_shift()), trim_to_len(n * quotient_degree_factor), chunks(n),
+        from_coeffs(chunks, rate_bits, false, cap_height).  divide_by_zh: rows are raw accumulators, multiply by
+        ZeroPolyOnCoset::eval_inverse first.  Panics like the reference when the quotient does not divide."""
+        ctx = ctx or default_context()
+        q = _a(quotient_values)
+        qdb = max(quotient_degree_factor - 1, 0).bit_length()  # log2_ceil
+        if q.ndim != 2 or q.shape[0] != 1 << (degree_log + qdb):
+            raise NlcError("quotient_values must be (n << log2_ceil(quotient_degree_factor)) x num_challenges")
+        h = vp()
+        ctx._check(_ffi.lib().nlc_quotient_commit(ctx._h, _p(q), q.shape[1], degree_log, qdb, quotient_degree_factor,
+                                                  int(divide_by_zh), rate_bits, cap_height, C.byref(h)))
+        return cls(ctx, h, q.shape[1] * quotient_degree_factor, degree_log, rate_bits, cap_height)
 
     # -- fields ---------------------------------------------------------------------------------
     @property

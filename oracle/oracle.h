@@ -58,6 +58,16 @@ void orc_commit_from_values(const uint64_t* values, size_t W, int log_n, int rat
 void orc_commit_from_coeffs(const uint64_t* coeffs, size_t W, int log_n, int rate_bits, int cap_height,
                             uint64_t* leaves, uint64_t* digests, uint64_t* cap);
 
+/* ---- quotient.c : quotient_polys without the AIR evaluation (starkyx prover.rs:253-358, 158-178) ---- */
+/* tables over the quotient domain (size = n << qdb); any output may be NULL; zh_inv has 2^qdb entries */
+void orc_quotient_domain(int log_n, int qdb, uint64_t* coset_x, uint64_t* lagrange_first, uint64_t* lagrange_last,
+                         uint64_t* zh_inv);
+/* evals: size x n_ch row-major.  coeffs_out: (n_ch*qdf) x n chunks; leaves/digests/cap as orc_commit_from_coeffs.
+ * Returns 1 when trim_to_len(n * qdf) fails (a coefficient beyond the degree bound is non-zero). */
+int orc_quotient_commit(const uint64_t* evals, size_t n_ch, int log_n, int qdb, size_t qdf, int divide_by_zh,
+                        int rate_bits, int cap_height, uint64_t* coeffs_out, uint64_t* leaves, uint64_t* digests,
+                        uint64_t* cap);
+
 /* ---- challenger.c : iop/challenger.rs ---- */
 typedef struct {
     uint64_t state[12];

@@ -229,6 +229,34 @@ def commit_from_coeffs(coeffs, rate_bits: int, cap_height: int) -> Batch:
     return Batch(coeffs.copy(), leaves, digests, cap, log_n, rate_bits, cap_height)
 
 
+def quotient_domain(log_n: int, qdb: int):
+    """(coset_x, lagrange_first, lagrange_last, zh_inv) of starkyx prover.rs:278-302 (oracle/quotient.c)."""
+    size = 1 << (log_n + qdb)
+    x, lf, ll = (np.zeros(size, np.uint64) for _ in range(3))
+    zh = np.zeros(1 << qdb, np.uint64)
+    lib().orc_quotient_domain(log_n, qdb, _p(x), _p(lf), _p(ll), _p(zh))
+    return x, lf, ll, zh
+
+
+def quotient_commit(evals, log_n: int, qdb: int, qdf: int, divide_by_zh: bool, rate_bits: int, cap_height: int):
+    """evals: size x n_challenges row-major.  Returns the Batch of the quotient chunks, or None when
+    trim_to_len fails (prover.rs:161-165)."""
+    evals = _a(evals)
+    size, n_ch = evals.shape
+    assert size == 1 << (log_n + qdb)
+    n, W = 1 << log_n, n_ch * qdf
+    N = n << rate_bits
+    coeffs = np.zeros((W, n), np.uint64)
+    leaves = np.zeros((N, W), np.uint64)
+    digests = np.zeros((2 * (N - (1 << cap_height)), 4), np.uint64)
+    cap = np.zeros((1 << cap_height, 4), np.uint64)
+    rc = lib().orc_quotient_commit(_p(evals), C.c_size_t(n_ch), log_n, qdb, C.c_size_t(qdf), int(divide_by_zh),
+                                   rate_bits, cap_height, _p(coeffs), _p(leaves), _p(digests), _p(cap))
+    if rc:
+        return None
+    return Batch(coeffs, leaves, digests, cap, log_n, rate_bits, cap_height)
+
+
 class Challenger:
     def __init__(self):
         self.c = _Challenger()

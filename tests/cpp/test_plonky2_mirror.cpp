@@ -120,6 +120,33 @@ int main() {
     PolynomialBatch quotient_commitment = PolynomialBatch::from_coeffs(all_quotient_chunks, rate_bits, false, cap_height);
     OracleBatch oquot = oracle_commit(oquot_cols, (int)rate_bits, (int)cap_height, false);
     CHECK(quotient_commitment.merkle_tree.cap.flatten() == oquot.capv);
+    {   // the same commit from the row-per-point quotient_values in one call (prover.rs:336-357):
+        // rows = values of the quotient polynomials on the coset, then again as raw accumulators q(x) * Z_H(x)
+        QuotientDomain dom(degree_bits, 1);
+        size_t w = 0;
+        std::vector<F> qcoef[2];
+        for (size_t a = 0; a < num_challenges; a++)
+            for (size_t c = 0; c < quotient_degree_factor; c++, w++)
+                qcoef[a].insert(qcoef[a].end(), all_quotient_chunks[w].coeffs.begin(), all_quotient_chunks[w].coeffs.end());
+        const size_t size = degree * quotient_degree_factor;
+        std::vector<F> rows(size * num_challenges), raw(size * num_challenges);
+        for (size_t a = 0; a < num_challenges; a++) {
+            PolynomialValues v = PolynomialCoeffs(qcoef[a]).coset_fft(COSET_SHIFT);
+            for (size_t i = 0; i < size; i++) {
+                rows[i * num_challenges + a] = v.values[i];
+                const F xn = powmod(dom.coset[i], degree), z_h = xn ? xn - 1 : ORDER - 1;
+                CHECK(mulmod(z_h, dom.eval_inverse(i)) == 1);
+                raw[i * num_challenges + a] = mulmod(v.values[i], z_h);
+            }
+        }
+        PolynomialBatch q1 = PolynomialBatch::from_quotient_values(rows, num_challenges, degree_bits, quotient_degree_factor, rate_bits, cap_height);
+        PolynomialBatch q2 = PolynomialBatch::from_quotient_values(raw, num_challenges, degree_bits, quotient_degree_factor, rate_bits, cap_height, true);
+        CHECK(q1.merkle_tree.cap.flatten() == oquot.capv);
+        CHECK(q2.merkle_tree.cap.flatten() == oquot.capv);
+        std::vector<uint64_t> ox(size), of(size), ol(size), oz(2);
+        orc_quotient_domain((int)degree_bits, 1, ox.data(), of.data(), ol.data(), oz.data());
+        CHECK(dom.coset == ox && dom.lagrange_first.values == of && dom.lagrange_last.values == ol && dom.z_h_inverses == oz);
+    }
     challenger.observe_cap(quotient_commitment.merkle_tree.cap);
     orc_challenger_observe(&och, oquot.capv.data(), oquot.capv.size());
 

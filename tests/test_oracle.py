@@ -179,3 +179,50 @@ def test_fri_golden(O):
     proof = O.prove_openings(O.FriInstance(batches), [t, q], ch, O.fri_params(log_n, r, cap, 7, 6, 2, 3))
     assert np.array_equal(proof, g["proof"])
     assert np.array_equal(np.array(list(ch.c.state), np.uint64), g["challenger_state"])
+
+
+def _quotient_case(O, rng, log_n, qdf, n_ch):
+    """Random quotient polynomials of degree < n*qdf and the raw constraint accumulators c(x) = q(x) Z_H(x)
+    on the quotient coset (what the AIR evaluation of prover.rs:320-334 would have produced)."""
+    qdb = max(qdf - 1, 0).bit_length()
+    n, size = 1 << log_n, 1 << (log_n + qdb)
+    q = np.zeros((n_ch, size), np.uint64)
+    q[:, :n * qdf] = O.random_field(rng, (n_ch, n * qdf))
+    q_vals = np.stack([O.coset_fft(c, 7) for c in q])
+    x, _, _, zh = O.quotient_domain(log_n, qdb)
+    z_h = np.array([(pow(int(v), n, P) - 1) % P for v in x], dtype=object)
+    raw = np.array([[int(q_vals[j, i]) * int(z_h[i]) % P for j in range(n_ch)] for i in range(size)], dtype=np.uint64)
+    return qdb, q, q_vals, raw, zh
+
+
+def test_quotient_domain_tables(O):
+    """oracle/quotient.c against the closed forms: x_i = 7 w^i, L_first(x) = (x^n - 1)/(n (x - 1)),
+    L_last(x) = w_n^-1 (x^n - 1)/(n (x - w_n^-1)), 1/Z_H(x_i) periodic with period 2^qdb."""
+    for log_n, qdb in [(3, 0), (4, 1), (5, 2), (3, 3)]:
+        n, size = 1 << log_n, 1 << (log_n + qdb)
+        x, lf, ll, zh = O.quotient_domain(log_n, qdb)
+        w = pow(7, (P - 1) >> (log_n + qdb), P)
+        last = pow(pow(7, (P - 1) >> log_n, P), P - 2, P) if log_n else 1
+        inv_n = pow(n, P - 2, P)
+        for i in range(size):
+            xi = 7 * pow(w, i, P) % P
+            assert int(x[i]) == xi
+            zhx = (pow(xi, n, P) - 1) % P
+            assert int(zh[i % (1 << qdb)]) * zhx % P == 1
+            assert int(lf[i]) == zhx * inv_n % P * pow((xi - 1) % P, P - 2, P) % P
+            assert int(ll[i]) == last * zhx % P * inv_n % P * pow((xi - last) % P, P - 2, P) % P
+
+
+@pytest.mark.parametrize("log_n,qdf,n_ch,r", [(4, 1, 2, 1), (5, 2, 2, 1), (5, 3, 2, 2), (6, 4, 3, 3), (4, 5, 1, 3)])
+def test_quotient_commit_recovers_the_quotient(O, rng, log_n, qdf, n_ch, r):
+    qdb, q, q_vals, raw, zh = _quotient_case(O, rng, log_n, qdf, n_ch)
+    n = 1 << log_n
+    want = q[:, :n * qdf].reshape(n_ch * qdf, n)  # polynomial j, chunk c -> column j*qdf + c
+    ref = O.commit_from_coeffs(want, r, 2)
+    for divide, evals in ((True, raw), (False, np.ascontiguousarray(q_vals.T))):
+        b = O.quotient_commit(evals, log_n, qdb, qdf, divide, r, 2)
+        assert np.array_equal(b.coeffs, want)
+        assert np.array_equal(b.cap, ref.cap) and np.array_equal(b.digests, ref.digests)
+        assert np.array_equal(b.leaves, ref.leaves)
+    if qdf < (1 << qdb):  # trim_to_len fails on anything that does not divide (prover.rs:161-165)
+        assert O.quotient_commit(O.random_field(rng, raw.shape), log_n, qdb, qdf, True, r, 2) is None

@@ -12,6 +12,11 @@
             each timed end to end through the host mirror (host columns in, FriProof out).  The CPU-oracle leg and
             the bit-exact proof comparison live in bench.py (--workload replay_plonk / replay_stark), the only
             place besides tests/ that may run oracle/.
+  air     : the trace shapes of the AIRs that are actually in the tree (SURVEY.md 8d, config 4 note): ed25519
+            2^16 x 1651 / 2502 (machine/ec/builder.rs:301-303), SHA-256 2^17 x 418 / 912 (sha256/air.rs:221-222),
+            SHA-512 2^16 x 815 / 1782 (sha512/air.rs:223-224), starky standard_fast_config (rate_bits 1, cap 4):
+            resident commit, host-fed commit from pinned columns, and the quotient commit (2 challenges,
+            quotient_degree_factor 2: scale by 1/Z_H, coset_ifft, chunks, from_coeffs -- nlc_quotient_commit_dev).
 bench.py stays the contract line; the output of this tool is committed under profiles/.
 """
 from __future__ import annotations
@@ -79,6 +84,59 @@ def run_sweep(args):
                 torch.cuda.empty_cache()
 
 
+AIR_SHAPES = [("ed25519_2^16x1651", 16, 1651), ("ed25519_2^16x2502", 16, 2502), ("sha256_2^17x418", 17, 418),
+              ("sha256_2^17x912", 17, 912), ("sha512_2^16x815", 16, 815), ("sha512_2^16x1782", 16, 1782)]
+
+
+def run_air(args):
+    import ctypes as C
+    import torch
+    pkg = graft.load_package()
+    P2, ffi = pkg.plonky2, pkg._ffi
+    L = ffi.lib()
+    ctx = P2.Context(0)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    r, cap = 1, 4
+
+    def timed(fn):
+        times = []
+        for it in range(args.warmup + args.steps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            h = ffi.vp()
+            a.record(stream)
+            fn(h)
+            b.record(stream)
+            torch.cuda.synchronize()
+            L.nlc_batch_free(h)
+            if it >= args.warmup:
+                times.append(a.elapsed_time(b))
+        return float(np.median(times))
+
+    for name, log_n, W in AIR_SHAPES:
+        n = 1 << log_n
+        g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + 4)
+        dev = torch.randint(0, 1 << 62, (W, n), dtype=torch.int64, device="cuda", generator=g)
+        ms = timed(lambda h: ctx._check(L.nlc_commit_from_values_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap,
+                                                                     C.byref(h))))
+        host = dev.cpu().pin_memory()
+        table = (ffi.u64p * W)(*[C.cast(host[j].data_ptr(), ffi.u64p) for j in range(W)])
+        ms_host = timed(lambda h: ctx._check(L.nlc_commit_from_values(ctx._h, table, W, log_n, r, cap, C.byref(h))))
+        # quotient: 2 challenges, factor 2 -> size 2n rows; any rows divide when factor == 2^bits
+        ev = torch.randint(0, 1 << 62, (2 * n, 2), dtype=torch.int64, device="cuda", generator=g)
+        ms_q = timed(lambda h: ctx._check(L.nlc_quotient_commit_dev(ctx._h, ffi.vp(ev.data_ptr()), 2, log_n, 1, 2, 1, r,
+                                                                    cap, C.byref(h))))
+        print(json.dumps({"air": name, "rate_bits": r, "cap_height": cap, "commit_resident_ms": ms,
+                          "commit_host_pinned_ms": ms_host, "elements_per_s": W * n / ms * 1e3,
+                          "e2e_elements_per_s": W * n / ms_host * 1e3, "h2d_bytes": 8 * W * n,
+                          "quotient_commit_ms": ms_q}), flush=True)
+        del dev, host, ev
+        torch.cuda.empty_cache()
+
+
 def run_replay(args):
     """GPU side of the proof-shape replay (bench.py --workload replay_* adds the CPU oracle leg and the bit-exact check)."""
     import bench
@@ -88,13 +146,13 @@ def run_replay(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("mode", choices=["sweep", "replay"])
+    ap.add_argument("mode", choices=["sweep", "replay", "air"])
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--min-log", type=int, default=14)
     ap.add_argument("--max-log", type=int, default=22)
     args = ap.parse_args()
-    (run_sweep if args.mode == "sweep" else run_replay)(args)
+    {"sweep": run_sweep, "replay": run_replay, "air": run_air}[args.mode](args)
 
 
 if __name__ == "__main__":
