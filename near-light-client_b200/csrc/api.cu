@@ -116,11 +116,16 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             // chunks on the copy stream and run IFFT + coset NTTs + the sponge blocks of chunk c on the compute
             // stream while chunk c+1 crosses PCIe (inner chunks are whole 8-column sponge blocks; the 12-word
             // sponge states wait in HBM between chunks).  Only the first, short chunk's upload is exposed.
-            // Chunk sizes: 16 columns first, then doubling (each upload hides behind the previous chunk's compute
-            // as long as a column computes at least twice as long as it uploads: true from rate_bits 1 up), tripling
+            // Chunk sizes: 16 columns first, then growing by half (each upload hides behind the previous chunk's compute
+            // as long as a column computes 1.5x as long as it uploads: measured 1.45-1.95x at rate_bits 1), tripling
             // at rate_bits >= 2 where compute is >= 8x the upload, also from pageable memory (fewer, fuller NTT grids).
             const bool stream_hash = W >= 32;
             const size_t chunk = W <= 8 ? W : (W + 4) / 5; // narrow batches: plain fifths, one leaf-hash launch
+            // Growth stops at an eighth of the batch (whole 8-column sponge blocks), but never below what fills the
+            // NTT grids (2^23 elements): once chunk k+1 uploads faster than chunk k computes the compute stream
+            // never waits, and what is exposed at the end is one capped chunk's compute, not half the batch's
+            // (2^16 x 2502 at rate_bits 1: 56.6 -> 48 ms against 47.0 ms resident).
+            const size_t chunk_cap = std::max<size_t>((W / 8 + 7) / 8 * 8, std::max<size_t>(16, ((size_t)1 << 23) >> log_n));
             const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
             DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
@@ -131,7 +136,7 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             std::vector<cudaEvent_t> evs;
             for (size_t c0 = 0, nc = 0; c0 < W; c0 += nc) {
                 size_t want = chunk;
-                if (stream_hash) want = c0 == 0 ? 16 : (rate_bits >= 2 ? 3 * nc : 2 * nc);
+                if (stream_hash) want = c0 == 0 ? 16 : std::min(chunk_cap, rate_bits >= 2 ? 3 * nc : (nc * 3 / 2 + 7) / 8 * 8);
                 nc = W - c0 < want ? W - c0 : want;
                 if (stream_hash && W - c0 - nc < 16) nc = W - c0; // no tiny last chunk
                 for (size_t j = c0; j < c0 + nc; j++) {
