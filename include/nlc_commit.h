@@ -34,8 +34,12 @@ typedef struct nlc_tree nlc_tree;   /* a stand-alone MerkleTree living in HBM */
 /* ---- lifecycle ---------------------------------------------------------------------------- */
 /* device < 0: use the current CUDA device. */
 int nlc_init(int device, nlc_ctx** out);
+/* Every nlc_batch / nlc_tree / nlc_fri_state made on the context must have been freed before (the Rust wrapper's
+ * handles hold an Arc of the context); a handle that outlives its context is dangling. */
 void nlc_destroy(nlc_ctx* ctx);
-const char* nlc_last_error(nlc_ctx* ctx); /* ctx may be NULL: error of the last failed nlc_init */
+/* Message of the CALLING THREAD's last failed call (threads sharing a context each see their own);
+ * ctx may be NULL: error of this thread's last failed nlc_init.  Valid until the thread's next failing call. */
+const char* nlc_last_error(nlc_ctx* ctx);
 int nlc_device(nlc_ctx* ctx);
 /* Launch all work of this context on an existing CUDA stream (a cudaStream_t cast to void*); NULL
  * restores the context's own stream.  Lets a harness time kernels with events on that stream. */

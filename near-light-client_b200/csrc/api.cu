@@ -230,7 +230,7 @@ void nlc_destroy(nlc_ctx* ctx) {
     delete ctx;
 }
 
-const char* nlc_last_error(nlc_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+const char* nlc_last_error(nlc_ctx* ctx) { return ctx ? nlc_thread_error().c_str() : g_init_error.c_str(); }
 int nlc_device(nlc_ctx* ctx) { return ctx ? ctx->device : -1; }
 
 int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream) {

@@ -5,6 +5,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <exception>
 #include <map>
 #include <mutex>
 #include <stdexcept>
@@ -55,7 +56,6 @@ struct nlc_ctx {
         return chunk_events[i];
     }
     std::recursive_mutex mu;
-    std::string err;
     std::atomic<u64> launches{0};
     std::map<TableKey, u64*> tables; // device-resident twiddle / scale tables, built once
     size_t table_bytes = 0;
@@ -107,12 +107,16 @@ struct nlc_ctx {
 struct CtxGuard {
     nlc_ctx* c;
     int prev = -1;
-    explicit CtxGuard(nlc_ctx* ctx) : c(ctx) {
+    int unwinding;
+    explicit CtxGuard(nlc_ctx* ctx) : c(ctx), unwinding(std::uncaught_exceptions()) {
         c->mu.lock();
         cudaGetDevice(&prev);
         if (prev != c->device) cudaSetDevice(c->device);
     }
     ~CtxGuard() {
+        // a call that fails drops its half-filled staging slot while it still holds the context: once the lock is
+        // gone another thread's upload may own the stager
+        if (std::uncaught_exceptions() > unwinding) c->stager.abandon();
         if (prev >= 0 && prev != c->device) cudaSetDevice(prev);
         c->mu.unlock();
     }
@@ -125,6 +129,10 @@ struct CtxGuard {
         NLC_CUDA(cudaGetLastError());                                           \
     } while (0)
 
+inline std::string& nlc_thread_error() {
+    static thread_local std::string e;
+    return e;
+}
 // Every extern "C" entry point wraps its body with this: exceptions become error codes.
 template <class F>
 static inline int nlc_guarded(nlc_ctx* ctx, F&& f) {
@@ -132,10 +140,9 @@ static inline int nlc_guarded(nlc_ctx* ctx, F&& f) {
         f();
         return 0;
     } catch (const std::exception& e) {
-        if (ctx) {
-            ctx->err = e.what();
-            ctx->stager.abandon();
-        }
+        // per calling thread: rayon workers share a context, each reads back its own failure (nlc_last_error)
+        (void)ctx;
+        nlc_thread_error() = e.what();
         cudaGetLastError(); // clear a non-sticky error so later calls can proceed
         return 1;
     }

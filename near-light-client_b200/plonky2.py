@@ -289,9 +289,9 @@ class MerkleTree:
 
     def __del__(self):
         try:
-            if self._h:
+            if self._h and self._ctx._h:  # a handle must not be touched once its context is gone
                 _ffi.lib().nlc_tree_free(self._h)
-                self._h = None
+            self._h = None
         except Exception:
             pass
 
@@ -754,9 +754,9 @@ class PolynomialBatch:
         return FriProof.parse(out, fri_params, [o.n_polys for o in oracles])
 
     def free(self):
-        if self._h:
+        if self._h and self._ctx._h:  # a handle must not be touched once its context is gone
             _ffi.lib().nlc_batch_free(self._h)
-            self._h = None
+        self._h = None
 
     def __del__(self):
         try:
@@ -806,9 +806,9 @@ class FriCommitPhase:
 
     def __del__(self):
         try:
-            if self._h:
+            if self._h and self._ctx._h:
                 _ffi.lib().nlc_fri_state_free(self._h)
-                self._h = None
+            self._h = None
         except Exception:
             pass
 
