@@ -37,6 +37,8 @@ WORKLOADS = {
     "commit_2^16x20_r3_cap4": (16, 20, 3, 4),
     "commit_2^20x400_r1_cap4": (20, 400, 1, 4),   # configs[3] (starkyx trace commitment)
     "commit_2^14x64_r3_cap4": (14, 64, 3, 4),
+    "commit_2^16x2502_r1_cap4": (16, 2502, 1, 4),  # ed25519 AIR trace in the tree (machine/ec/builder.rs:301-303)
+    "commit_2^17x912_r1_cap4": (17, 912, 1, 4),    # SHA-256 AIR trace (sha256/air.rs:221-222)
 }
 DEFAULT_WORKLOAD = "commit_2^16x135_r3_cap4"
 
@@ -297,16 +299,44 @@ def run_ours(args, rank, local_rank, world):
             state["batch"] = None
 
     sharded = bool(args.shard_commit) and world > 1
+    by_rows = sharded and world > (1 << r)  # more ranks than cosets: SURVEY.md 8(e).3
     if sharded:  # ONE commit split by coset over the ranks, cap entries all-gathered over NCCL
-        pkg.sharding.check_plan(r, cap, world)
+        if by_rows:  # column shards for the transforms, one all-to-all, leaf-row shards for the tree
+            pkg.sharding.check_row_plan(cap, world)
+            split = pkg.sharding.column_split(W, world)
+            c0, nc = split[rank]
+            per = N // world
+            my_coeffs = torch.empty((nc, n), dtype=torch.int64, device="cuda")
+            my_lde = torch.empty((nc, N), dtype=torch.int64, device="cuda")
+            send = torch.empty((world, nc, per), dtype=torch.int64, device="cuda")
+            rows = torch.empty((W, per), dtype=torch.int64, device="cuda")
+            out_split, in_split = [c * per for _, c in split], [nc * per] * world
+        else:
+            pkg.sharding.check_plan(r, cap, world)
         cap_local = torch.empty(((1 << cap) // world, 4), dtype=torch.int64, device="cuda")
         cap_full = torch.empty((1 << cap, 4), dtype=torch.int64, device="cuda")
         cudart = C.CDLL("libcudart.so.12")
 
+    def rows_commit(src_cols):
+        """8(e).3 from this rank's columns (device): transforms, pack, all-to-all, tree, cap all-gather."""
+        h = ffi.vp()
+        ctx._check(L.nlc_lde_columns_dev(ctx._h, ffi.vp(src_cols.data_ptr()), nc, log_n, r, 1,
+                                         ffi.vp(my_coeffs.data_ptr()), ffi.vp(my_lde.data_ptr())))
+        send.copy_(my_lde.view(nc, world, per).permute(1, 0, 2))
+        dist.all_to_all_single(rows.view(-1), send.view(-1), output_split_sizes=out_split, input_split_sizes=in_split)
+        ctx._check(L.nlc_commit_from_lde_rows_dev(ctx._h, ffi.vp(rows.data_ptr()), W, log_n, r, cap, rank, world,
+                                                  C.byref(h)))
+        cudart.cudaMemcpyAsync(C.c_void_p(cap_local.data_ptr()), C.c_void_p(L.nlc_batch_cap_dev(h)),
+                               C.c_size_t(cap_local.numel() * 8), 3, C.c_void_p(stream.cuda_stream))
+        dist.all_gather_into_tensor(cap_full, cap_local)
+        return h
+
     def step_resident():
         free_prev()
         h = ffi.vp()
-        if sharded:
+        if by_rows:
+            h = rows_commit(dev[c0:c0 + nc])
+        elif sharded:
             ctx._check(L.nlc_commit_from_values_shard_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, rank, world,
                                                           C.byref(h)))
             # cudaMemcpyAsync(dst, src, bytes, D2D = 3, stream): the shard's cap entries into the all-gather input
@@ -320,7 +350,11 @@ def run_ours(args, rank, local_rank, world):
     def step_e2e():
         free_prev()
         h = ffi.vp()
-        if sharded:
+        if by_rows:  # this rank's columns from pinned host memory, the full cap back on the host
+            h = rows_commit(host[c0:c0 + nc].cuda(non_blocking=True))
+            state["batch"] = h
+            cap_host[:] = cap_full.cpu().numpy().view(np.uint64)
+        elif sharded:
             ctx._check(L.nlc_commit_from_values_shard(ctx._h, col_table, W, log_n, r, cap, rank, world, C.byref(h)))
             state["batch"] = h
             local = np.zeros(((1 << cap) // world, 4), np.uint64)
@@ -441,7 +475,9 @@ def run_ours(args, rank, local_rank, world):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r, "cap_height": cap,
-                           "parallelism": (f"one commit, coset shards x{world} + NCCL all-gather of the cap" if sharded
+                           "parallelism": (f"one commit, column shards x{world} -> NCCL all-to-all -> leaf-row shards + "
+                                           "all-gather of the cap (SURVEY 8e.3)" if by_rows else
+                                           f"one commit, coset shards x{world} + NCCL all-gather of the cap" if sharded
                                            else f"instances x{world}"), "l2": "flushed between timed iterations (256 MiB write)"},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_val, "unit": "elements/s", "h2d_bytes_per_step": 8 * elems,

@@ -92,6 +92,22 @@ int nlc_commit_from_values_shard(nlc_ctx* ctx, const uint64_t* const* cols, size
 int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n,
                                      int rate_bits, int cap_height, size_t shard_idx, size_t n_shards,
                                      nlc_batch** out);
+/* SURVEY.md 8(e).3 -- more GPUs than cosets (starky commits at rate_bits 1 on 4 or 8 GPUs): shard by COLUMN for the
+ * transforms, exchange once, shard by leaf ROW for the tree.
+ *   1. every rank, for the columns it owns: nlc_lde_columns_dev -- iFFT (is_values) and the 2^rate_bits coset NTTs of
+ *      n_cols columns; lde_out_dev = n_cols x N column-major in leaf order (leaf k = LDE row bitrev_N(k)),
+ *      coeffs_out_dev = n_cols x n or NULL.  Device pointers, asynchronous on the context's stream.
+ *   2. all-to-all over NVLink (caller: NCCL all_to_all_single in near-light-client_b200/plonky2.py): rank g receives
+ *      the leaves [g, g+1) * N / n_shards of every column -> n_cols_total x (N / n_shards) column-major.
+ *   3. every rank: nlc_commit_from_lde_rows_dev over what it received -- leaf hashes, the digests of its cap
+ *      subtrees and its 2^cap_height / n_shards cap entries, exactly as a coset shard (same concatenation rule); then
+ *      the all-gather of the cap entries.  The batch does NOT copy lde_rows_dev: the buffer must outlive it.  It holds
+ *      no coefficients (nlc_batch_coeffs / nlc_batch_eval fail on it; the column owners kept them in step 1).
+ * n_shards: a power of two, at most 2^cap_height. */
+int nlc_lde_columns_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, int log_n, int rate_bits, int is_values,
+                        uint64_t* coeffs_out_dev, uint64_t* lde_out_dev);
+int nlc_commit_from_lde_rows_dev(nlc_ctx* ctx, uint64_t* lde_rows_dev, size_t n_cols, int log_n, int rate_bits,
+                                 int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out);
 int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards);
 void nlc_batch_free(nlc_batch* b);
 

@@ -58,6 +58,9 @@ SIGNATURES = {
                                                C.c_size_t, C.POINTER(vp)]),
     "nlc_commit_from_values_shard_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                                    C.c_size_t, C.POINTER(vp)]),
+    "nlc_lde_columns_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, vp, vp]),
+    "nlc_commit_from_lde_rows_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
+                                               C.POINTER(vp)]),
     "nlc_batch_shard": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "nlc_commit_from_coeffs_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_trace_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,

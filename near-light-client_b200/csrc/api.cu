@@ -331,6 +331,30 @@ int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, s
         *out = commit_dev(ctx, values_dev, true, n_cols, log_n, rate_bits, cap_height, sl, shard_idx);
     });
 }
+// ---- 8e.3: column shards for the transforms, exchange (caller), leaf-row shards for the tree ----
+int nlc_lde_columns_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, int log_n, int rate_bits, int is_values,
+                        uint64_t* coeffs_out_dev, uint64_t* lde_out_dev) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(src_dev && lde_out_dev, "null argument");
+        NLC_CHECK(n_cols > 0, "PolynomialBatch: at least one polynomial required");
+        NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
+        lde_columns_dev(ctx, src_dev, n_cols, log_n, rate_bits, is_values != 0, coeffs_out_dev, lde_out_dev);
+    });
+}
+int nlc_commit_from_lde_rows_dev(nlc_ctx* ctx, uint64_t* lde_rows_dev, size_t n_cols, int log_n, int rate_bits,
+                                 int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && lde_rows_dev, "null argument");
+        *out = nullptr;
+        const int sl = shard_log_of(n_shards);
+        NLC_CHECK(sl >= 0, "n_shards must be a power of two");
+        *out = commit_from_lde_rows_dev(ctx, lde_rows_dev, n_cols, log_n, rate_bits, cap_height, sl, shard_idx);
+    });
+}
 int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards) {
     if (!b) return 1;
     if (shard_idx) *shard_idx = b->shard_idx;
@@ -383,6 +407,7 @@ int nlc_batch_coeffs(nlc_batch* b, uint64_t* const* out_cols) {
         CtxGuard g(b->ctx);
         const size_t n = (size_t)1 << b->log_n;
         NLC_CHECK(out_cols != nullptr, "null column table");
+        NLC_CHECK(b->coeffs != nullptr, "a leaf-row shard holds no coefficients: they stay with the column owners");
         if (b->W * n * sizeof(u64) >= ((size_t)1 << 20) && HostStager::pageable(out_cols[0])) {
             std::vector<HostStager::Seg> segs; // W separate Vecs on the host, one contiguous matrix on the device
             for (size_t j = 0; j < b->W; j++) segs.push_back({out_cols[j], n * sizeof(u64)});
@@ -461,6 +486,7 @@ int nlc_batch_eval(nlc_batch* b, const uint64_t z[2], uint64_t* out) {
     return nlc_guarded(b->ctx, [&] {
         nlc_ctx* ctx = b->ctx;
         CtxGuard g(ctx);
+        NLC_CHECK(b->coeffs != nullptr, "a leaf-row shard holds no coefficients: they stay with the column owners");
         DevBuf res(ctx, 2 * b->W);
         batch_eval_ext(b, z, res.p);
         d2h(ctx, out, res.p, 2 * b->W * sizeof(u64));

@@ -16,6 +16,10 @@ struct nlc_batch {
     // i.e. 2^(rate_bits - shard_log) whole cosets and 2^(cap_height - shard_log) whole cap subtrees.
     int shard_log = 0;
     size_t shard_idx = 0;
+    // Leaf-row shard: same leaf range as a coset shard, but the rows arrived over
+    // the all-to-all: the LDE lives in the caller's receive buffer (not owned) and the coefficients stay with the
+    // ranks that own the columns (coeffs == nullptr here).
+    bool owns_lde = true;
     size_t n_local() const { return ((size_t)1 << (log_n + rate_bits)) >> shard_log; }
     int cap_local() const { return cap_height - shard_log; }
 };
@@ -46,6 +50,11 @@ void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
 // rows [row0, row0+n_rows) of the leaf matrix, row-major, into out_dev (n_rows x W): plonky2's merkle_tree.leaves
 void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);
 
+// transforms of a column shard (no tree), and the tree over a leaf-row shard
+void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n, int rate_bits, bool is_values,
+                     u64* coeffs_out_dev, u64* lde_out_dev);
+nlc_batch* commit_from_lde_rows_dev(nlc_ctx* ctx, u64* lde_rows_dev, size_t W, int log_n, int rate_bits, int cap_height,
+                                    int shard_log, size_t shard_idx);
 // SURVEY.md 8f.1 (prover.rs:253-358 without the AIR evaluation)
 std::vector<u64> zero_poly_on_coset_inverses(int log_n, int qdb);
 void coset_points(nlc_ctx* ctx, int log_size, u64* out_dev);

@@ -152,7 +152,7 @@ void batch_release(nlc_batch* b) {
     if (!b) return;
     nlc_ctx* ctx = b->ctx;
     ctx->dfree(b->coeffs);
-    ctx->dfree(b->lde);
+    if (b->owns_lde) ctx->dfree(b->lde);
     ctx->dfree(b->digests);
     ctx->dfree(b->cap);
     delete b;
@@ -331,5 +331,64 @@ nlc_batch* quotient_commit_dev(nlc_ctx* ctx, const u64* evals_dev, size_t n_ch, 
     ctx->dfree(scratch);
     ctx->dfree(coef);
     ctx->dfree(vals);
+    return b;
+}
+
+// ---- column shards for the transforms, leaf-row shards for the tree ----
+// "IFFT" + "FFT + blinding" of from_values / from_coeffs for the columns one rank owns: lde_out = n_cols x N
+// column-major in leaf order (what batch_lde_cols writes), no tree.
+void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n, int rate_bits, bool is_values,
+                     u64* coeffs_out_dev, u64* lde_out_dev) {
+    const size_t n = (size_t)1 << log_n;
+    nlc_batch view; // a window over the caller's buffers: only the fields the two column passes read
+    view.ctx = ctx;
+    view.W = n_cols;
+    view.log_n = log_n;
+    view.rate_bits = rate_bits;
+    u64* own = coeffs_out_dev ? nullptr : ctx->dmalloc(n_cols * n);
+    view.coeffs = coeffs_out_dev ? coeffs_out_dev : own;
+    view.lde = lde_out_dev;
+    try {
+        if (is_values)
+            batch_ifft_cols(&view, src_dev, 0, n_cols);
+        else if (view.coeffs != src_dev)
+            NLC_CUDA(cudaMemcpyAsync(view.coeffs, src_dev, n_cols * n * sizeof(u64), cudaMemcpyDeviceToDevice, ctx->stream));
+        batch_lde_cols(&view, 0, n_cols);
+    } catch (...) {
+        ctx->dfree(own);
+        throw;
+    }
+    ctx->dfree(own);
+}
+
+// The tree over the leaves [shard_idx, shard_idx + 1) * N >> shard_log, whose rows (all W columns) sit column-major in
+// lde_rows_dev: digests of the shard's cap subtrees and its 2^(cap_height - shard_log) cap entries.
+nlc_batch* commit_from_lde_rows_dev(nlc_ctx* ctx, u64* lde_rows_dev, size_t W, int log_n, int rate_bits, int cap_height,
+                                    int shard_log, size_t shard_idx) {
+    NLC_CHECK(W > 0, "PolynomialBatch: at least one polynomial required");
+    NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
+    NLC_CHECK(cap_height >= 0 && cap_height <= log_n + rate_bits, "cap_height should be at most log2(leaves.len())");
+    NLC_CHECK(shard_log >= 0 && shard_log <= cap_height, "leaf-row sharding needs n_shards <= 2^cap_height");
+    NLC_CHECK(shard_idx < ((size_t)1 << shard_log), "shard index out of range");
+    nlc_batch* b = new nlc_batch();
+    b->ctx = ctx;
+    b->W = W;
+    b->log_n = log_n;
+    b->rate_bits = rate_bits;
+    b->cap_height = cap_height;
+    b->shard_log = shard_log;
+    b->shard_idx = shard_idx;
+    b->lde = lde_rows_dev;
+    b->owns_lde = false;
+    const size_t N = b->n_local();
+    try {
+        b->n_digest_words = 8 * (N - ((size_t)1 << b->cap_local()));
+        b->digests = ctx->dmalloc(b->n_digest_words);
+        b->cap = ctx->dmalloc((size_t)4 << b->cap_local());
+        batch_tree(b);
+    } catch (...) {
+        batch_release(b);
+        throw;
+    }
     return b;
 }

@@ -315,6 +315,7 @@ nlc_fri_state* fri_state_new(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_bat
     for (int o = 0; o < n_oracles; o++) {
         NLC_CHECK(oracles[o] && oracles[o]->ctx == ctx, "oracle belongs to another context");
         NLC_CHECK(oracles[o]->shard_log == 0, "prove_openings needs whole batches, not coset shards");
+        NLC_CHECK(oracles[o]->coeffs != nullptr, "prove_openings needs the coefficients: not a leaf-row shard");
         NLC_CHECK(oracles[o]->log_n == log_n && oracles[o]->rate_bits == p->rate_bits &&
                       oracles[o]->cap_height == p->cap_height,
                   "oracle degree / rate_bits / cap_height do not match the FriParams");

@@ -651,6 +651,76 @@ class PolynomialBatch:
             b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
         return b
 
+    @staticmethod
+    def lde_columns(src, rate_bits: int, is_values: bool = True, ctx=None):
+        """Step 1 of the row-sharded commit: src = (nc, n) int64 CUDA tensor holding this rank's
+        columns; returns (coeffs (nc, n), lde (nc, N) in leaf order) as CUDA tensors.  Asynchronous."""
+        import torch
+        ctx = ctx or default_context()
+        nc, n = src.shape
+        log_n = _log2_strict(n)
+        coeffs = torch.empty((nc, n), dtype=torch.int64, device=src.device)
+        lde = torch.empty((nc, n << rate_bits), dtype=torch.int64, device=src.device)
+        ctx._check(_ffi.lib().nlc_lde_columns_dev(ctx._h, vp(src.data_ptr()), nc, log_n, rate_bits, int(is_values),
+                                                  vp(coeffs.data_ptr()), vp(lde.data_ptr())))
+        return coeffs, lde
+
+    @classmethod
+    def from_lde_rows(cls, rows, degree_log: int, rate_bits: int, cap_height: int, shard_idx: int, n_shards: int,
+                      ctx=None):
+        """Step 3: the tree over the leaf rows [shard_idx, shard_idx+1) * N / n_shards; rows = (W, N / n_shards) int64
+        CUDA tensor (column-major leaves, what sharding.exchange_rows returns).  The batch reads the tensor in place
+        and keeps it alive; it is a shard: merkle_tree.local_cap / leaves / digests are the shard's part."""
+        ctx = ctx or default_context()
+        W, per = rows.shape
+        if per * n_shards != 1 << (degree_log + rate_bits) or not rows.is_contiguous():
+            raise NlcError("rows must be a contiguous (W, N / n_shards) tensor")
+        h = vp()
+        ctx._check(_ffi.lib().nlc_commit_from_lde_rows_dev(ctx._h, vp(rows.data_ptr()), W, degree_log, rate_bits,
+                                                           cap_height, shard_idx, n_shards, C.byref(h)))
+        b = cls(ctx, h, W, degree_log, rate_bits, cap_height)
+        b.shard_idx, b.n_shards = shard_idx, n_shards
+        b._keepalive = rows
+        return b
+
+    @classmethod
+    def from_values_row_sharded(cls, values, rate_bits: int, blinding: bool, cap_height: int, group=None, ctx=None,
+                                is_values: bool = True):
+        """one commit over more GPUs than it has cosets (starky: rate_bits 1 on 4 / 8 GPUs).
+        Every rank passes the same `values`; rank p transforms the columns sharding.column_split(W, G)[p]
+        (lde_columns), one NCCL all-to-all hands rank g the leaves [g, g+1) * N / G of all columns, rank g builds its
+        cap subtrees (from_lde_rows), and the cap entries are all-gathered.  The returned batch is a leaf-row shard:
+        merkle_tree.cap is the full MerkleCap, merkle_tree.leaves / digests the shard's part, `column_coeffs` the
+        coefficients of this rank's columns `column_range`."""
+        import torch
+        from . import sharding
+        if blinding:
+            raise NlcError("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)")
+        g, G = sharding.rank_and_world(group)
+        sharding.check_row_plan(cap_height, G)
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(values)
+        W, log_n = len(arrs), _log2_strict(n)
+        c0, nc = sharding.column_split(W, G)[g]
+        if nc == 0:
+            raise NlcError("fewer columns than ranks: shard independent commits instead")
+        dev = torch.device("cuda", ctx.device)
+        stream = torch.cuda.current_stream(dev)
+        ctx.set_stream(stream.cuda_stream)  # the exchange runs on torch's stream: keep the kernels in the same order
+        try:
+            mine = np.stack([np.asarray(arrs[j]).view(np.int64) for j in range(c0, c0 + nc)])
+            src = torch.from_numpy(mine).pin_memory().to(dev, non_blocking=True)
+            coeffs, lde = cls.lde_columns(src, rate_bits, is_values, ctx)
+            rows = sharding.exchange_rows(sharding.pack_rows(lde, G), W, group)
+            del lde
+            b = cls.from_lde_rows(rows, log_n, rate_bits, cap_height, g, G, ctx)
+            b.column_range, b.column_coeffs = (c0, nc), coeffs
+            b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
+            stream.synchronize()
+        finally:
+            ctx.set_stream(None)
+        return b
+
     @classmethod
     def from_device(cls, dev_ptr: int, n_polys: int, degree_log: int, rate_bits: int, cap_height: int,
                     is_values: bool = True, ctx=None):

@@ -5,6 +5,12 @@ contiguous leaf range [bitrev_r(k) * n, +n), so rank g of G = 2^s ranks owns the
 2^(rate_bits - s) whole cosets and 2^(cap_height - s) whole cap subtrees.  Each rank computes its shard with
 nlc_commit_from_values_shard (no communication), and the only exchange on the path is the all-gather of the
 cap entries, 32 bytes each: NCCL over NVLink on GPUs, gloo in the CPU tests of this logic.
+
+When there are more ranks than cosets (starky commits at rate_bits 1 on 4 or 8 GPUs) the commit
+shards twice: by COLUMN for the transforms (rank p owns the columns column_split(W, G)[p]: nlc_lde_columns_dev), then
+one all-to-all hands rank g the leaf rows [g, g+1) * N / G of every column, and the tree is built by leaf ROW exactly
+as for a coset shard (nlc_commit_from_lde_rows_dev).  pack_rows / exchange_rows below are that exchange:
+8 * W * N * (G-1) / G bytes in total, uniform all-to-all through NVSwitch.
 """
 from __future__ import annotations
 
@@ -26,6 +32,51 @@ def check_plan(rate_bits: int, cap_height: int, n_shards: int) -> int:
     if s > cap_height:
         raise ShardPlanError(f"coset sharding needs n_shards <= 2^cap_height = {1 << cap_height} (got {n_shards})")
     return s
+
+
+def check_row_plan(cap_height: int, n_shards: int) -> int:
+    """Leaf-row sharding (8e.3) only needs whole cap subtrees per shard; returns log2(n_shards)."""
+    if n_shards < 1 or n_shards & (n_shards - 1):
+        raise ShardPlanError(f"n_shards = {n_shards} must be a power of two")
+    s = n_shards.bit_length() - 1
+    if s > cap_height:
+        raise ShardPlanError(f"leaf-row sharding needs n_shards <= 2^cap_height = {1 << cap_height} (got {n_shards})")
+    return s
+
+
+def column_split(W: int, n_shards: int):
+    """[(first column, count)] per rank: contiguous, in rank order, sizes differing by at most one."""
+    base, extra = divmod(W, n_shards)
+    out, c0 = [], 0
+    for p in range(n_shards):
+        nc = base + (1 if p < extra else 0)
+        out.append((c0, nc))
+        c0 += nc
+    return out
+
+
+def pack_rows(lde_cols, n_shards: int):
+    """lde_cols: this rank's columns, (nc, N) in leaf order (torch tensor or ndarray).  Returns the send buffer of the
+    all-to-all: (n_shards, nc, N / n_shards) contiguous, block g = the leaves of shard g."""
+    nc, N = lde_cols.shape
+    v = lde_cols.reshape(nc, n_shards, N // n_shards)
+    if isinstance(v, np.ndarray):
+        return np.ascontiguousarray(v.transpose(1, 0, 2))
+    return v.permute(1, 0, 2).contiguous()
+
+
+def exchange_rows(send, W: int, group=None):
+    """all_to_all of pack_rows' buffers (torch tensors on the backend's device).  Returns (W, N / G): every column's
+    leaves of this rank's shard, column-major -- the layout nlc_commit_from_lde_rows_dev hashes."""
+    import torch
+    import torch.distributed as dist
+    G = dist.get_world_size(group)
+    per = send.shape[2]
+    split = column_split(W, G)
+    recv = torch.empty((W, per), dtype=send.dtype, device=send.device)
+    dist.all_to_all_single(recv.view(-1), send.view(-1), output_split_sizes=[nc * per for _, nc in split],
+                           input_split_sizes=[send.shape[1] * per] * G, group=group)
+    return recv
 
 
 def leaf_range(log_n: int, rate_bits: int, shard_idx: int, n_shards: int):

@@ -26,3 +26,47 @@ def test_shard_limits(P2, O, rng):
     values = O.random_field(rng, (2, 16))
     with pytest.raises(Exception):
         P2.PolynomialBatch.from_values_sharded(list(values), 1, False, 4, shard_idx=0, n_shards=4)
+
+
+@pytest.mark.parametrize("W,log_n,r,cap,G", [(5, 6, 1, 3, 4), (9, 10, 1, 4, 8), (135, 11, 1, 4, 8), (418, 10, 1, 4, 4),
+                                             (3, 7, 0, 2, 4), (20, 9, 3, 4, 16), (7, 8, 1, 4, 2), (6, 5, 1, 2, 1)])
+def test_row_shards_assemble_to_the_commit(P2, O, rng, W, log_n, r, cap, G):
+    """8(e).3 on one GPU: the G ranks' work done one after the other on cuda:0 -- column shards through
+    nlc_lde_columns_dev, the all-to-all replaced by concatenating the packed blocks, leaf-row shards through
+    nlc_commit_from_lde_rows_dev -- gives exactly the single-GPU commit = the oracle's."""
+    import torch
+    import __graft_entry__ as graft
+    S = graft.load_package().sharding
+    if W < G:
+        pytest.skip("fewer columns than ranks")
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, r, cap)
+    dev = torch.device("cuda", 0)
+    sends, coeffs = [], []
+    for c0, nc in S.column_split(W, G):
+        src = torch.from_numpy(values[c0:c0 + nc].view(np.int64)).to(dev)
+        cf, lde = P2.PolynomialBatch.lde_columns(src, r)
+        torch.cuda.synchronize()
+        # the column owner's LDE in leaf order = the oracle's leaves of those columns
+        assert np.array_equal(lde.cpu().numpy().view(np.uint64), ref.leaves[:, c0:c0 + nc].T)
+        sends.append(S.pack_rows(lde, G))
+        coeffs.append(cf.cpu().numpy().view(np.uint64))
+    assert np.array_equal(np.concatenate(coeffs), ref.coeffs)
+    shards = []
+    for g in range(G):
+        rows = torch.cat([s[g] for s in sends]).contiguous()  # what rank g receives, in source-rank order
+        shards.append(P2.PolynomialBatch.from_lde_rows(rows, log_n, r, cap, g, G))
+    assert np.array_equal(S.assemble(s.merkle_tree.local_cap for s in shards), ref.cap)
+    assert np.array_equal(S.assemble(s.merkle_tree.digests for s in shards), ref.digests)
+    assert np.array_equal(S.assemble(s.merkle_tree.leaves for s in shards), ref.leaves)
+    with pytest.raises(P2.NlcError, match="no coefficients"):
+        shards[0].coeff_matrix  # noqa: B018 -- the coefficients stay with the column owners
+
+
+def test_row_shard_limits(P2, O, rng):
+    import torch
+    rows = torch.zeros((2, 8), dtype=torch.int64, device="cuda")
+    with pytest.raises(P2.NlcError):
+        P2.PolynomialBatch.from_lde_rows(rows, 4, 1, 1, 0, 4)  # 4 shards, 2 cap subtrees
+    with pytest.raises(P2.NlcError):
+        P2.PolynomialBatch.from_lde_rows(rows, 4, 1, 2, 0, 2)  # wrong row count for 2 shards

@@ -76,3 +76,59 @@ def test_gather_cap_gloo_world2():
         assert p.exitcode == 0
     assert [x[1] for x in res] == [True, True]
     assert (res[0][2], res[0][3], res[1][2], res[1][3]) == (0, 128, 128, 256)
+
+
+def test_column_split_and_row_plan():
+    S = graft.load_package().sharding
+    assert S.column_split(10, 4) == [(0, 3), (3, 3), (6, 2), (8, 2)]
+    assert S.column_split(8, 8) == [(j, 1) for j in range(8)]
+    assert S.column_split(3, 4) == [(0, 1), (1, 1), (2, 1), (3, 0)]
+    assert S.check_row_plan(4, 8) == 3  # rate_bits does not matter: starky's rate_bits 1 on 8 GPUs
+    with pytest.raises(S.ShardPlanError):
+        S.check_row_plan(2, 8)
+    with pytest.raises(S.ShardPlanError):
+        S.check_row_plan(4, 6)
+
+
+def _row_worker(rank, world, port, q):
+    """8e.3 host logic over gloo: the oracle plays the kernels; the exchange (pack_rows + all_to_all_single with
+    ragged column splits) must hand every rank exactly its leaf rows, and the gathered cap is the commit's."""
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        S = graft.load_package().sharding
+        O = graft.load_oracle()
+        rng = np.random.default_rng(11)
+        W, log_n, r, cap = 7, 6, 1, 3  # 7 columns over 2 ranks: 4 + 3
+        values = O.random_field(rng, (W, 1 << log_n))
+        ref = O.commit_from_values(values, r, cap)
+        g, G = S.rank_and_world()
+        S.check_row_plan(cap, G)
+        c0, nc = S.column_split(W, G)[g]
+        lde_cols = np.ascontiguousarray(ref.leaves[:, c0:c0 + nc].T)  # what nlc_lde_columns_dev returns
+        send = torch.from_numpy(S.pack_rows(lde_cols, G).view(np.int64))
+        rows = S.exchange_rows(send, W).numpy().view(np.uint64)
+        lo, hi = S.leaf_range(log_n, r, g, G)
+        ok_rows = bool(np.array_equal(rows, ref.leaves[lo:hi].T))
+        # the tree over the shard (oracle in place of nlc_commit_from_lde_rows_dev), then the all-gather
+        _, local_cap = O.merkle_new(np.ascontiguousarray(rows.T), cap - (G.bit_length() - 1))
+        full = S.gather_cap(local_cap, cap)
+        q.put((rank, ok_rows, bool(np.array_equal(full, ref.cap))))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_exchange_gloo_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_row_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res == [(0, True, True), (1, True, True)]
