@@ -705,20 +705,23 @@ class PolynomialBatch:
         if nc == 0:
             raise NlcError("fewer columns than ranks: shard independent commits instead")
         dev = torch.device("cuda", ctx.device)
-        stream = torch.cuda.current_stream(dev)
-        ctx.set_stream(stream.cuda_stream)  # the exchange runs on torch's stream: keep the kernels in the same order
+        # kernels (library) and exchange (torch / NCCL) must share ONE real stream: torch's default stream is the
+        # NULL stream, which the C ABI reads as "use your own", so make a stream current for the whole commit
+        stream = torch.cuda.Stream(dev)
+        ctx.set_stream(stream.cuda_stream)
         try:
-            mine = np.stack([np.asarray(arrs[j]).view(np.int64) for j in range(c0, c0 + nc)])
-            src = torch.from_numpy(mine).pin_memory().to(dev, non_blocking=True)
-            coeffs, lde = cls.lde_columns(src, rate_bits, is_values, ctx)
-            rows = sharding.exchange_rows(sharding.pack_rows(lde, G), W, group)
-            del lde
-            b = cls.from_lde_rows(rows, log_n, rate_bits, cap_height, g, G, ctx)
-            b.column_range, b.column_coeffs = (c0, nc), coeffs
-            b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
-            stream.synchronize()
+            with torch.cuda.stream(stream):
+                mine = np.stack([np.asarray(arrs[j]).view(np.int64) for j in range(c0, c0 + nc)])
+                src = torch.from_numpy(mine).pin_memory().to(dev, non_blocking=True)
+                coeffs, lde = cls.lde_columns(src, rate_bits, is_values, ctx)
+                rows = sharding.exchange_rows(sharding.pack_rows(lde, G), W, group)
+                b = cls.from_lde_rows(rows, log_n, rate_bits, cap_height, g, G, ctx)
+                b.column_range, b.column_coeffs = (c0, nc), coeffs
+                stream.synchronize()
+                del lde, src
         finally:
             ctx.set_stream(None)
+        b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
         return b
 
     @classmethod
