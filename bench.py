@@ -414,6 +414,15 @@ def run_ours(args, rank, local_rank, world):
                 "ncu_pipes_pct_of_peak": ncu_pipes(args.workload, "k_leaf_hash"),
                 "peak_source": peak_src, "ms_per_launch": leaf_ms,
                 "poseidon_perms_per_s": perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None}
+    # The pipe that actually bounds the hash: the busiest integer pipe of the committed ncu capture.  Its utilisation IS
+    # the fraction of the pipe-bound rate; peak = the permutation rate the same instruction stream would reach at 100 %.
+    pipes = roofline["ncu_pipes_pct_of_peak"] or {}
+    busiest = max(((v, k) for k, v in pipes.items() if k in ("alu", "fmaheavy (IMAD)")), default=None)
+    if busiest and roofline["poseidon_perms_per_s"]:
+        roofline["int_pipe"] = {"bound": busiest[1], "achieved": roofline["poseidon_perms_per_s"],
+                                "peak": roofline["poseidon_perms_per_s"] * 100.0 / busiest[0], "unit": "permutations/s",
+                                "frac": busiest[0] / 100.0,
+                                "source": "ncu pipe-active cycles of profiles/traffic.json (capture of this kernel, this workload)"}
     roofline_ntt = {"bound": "hbm", "kernel": "k_ntt_* (iFFT + 2^r coset NTTs into leaf rows)",
                     "achieved": ab["ntt"] / (ntt_ms * 1e-3) / 1e9 if ntt_ms > 0 else 0.0, "peak": peak, "unit": "GB/s",
                     "ms": ntt_ms}
