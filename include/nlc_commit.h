@@ -108,6 +108,22 @@ int nlc_lde_columns_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, in
                         uint64_t* coeffs_out_dev, uint64_t* lde_out_dev);
 int nlc_commit_from_lde_rows_dev(nlc_ctx* ctx, uint64_t* lde_rows_dev, size_t n_cols, int log_n, int rate_bits,
                                  int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out);
+/* Steps 1 and 2 fused: the last NTT pass stores each leaf where its row shard lives instead of into a local LDE.
+ *   peer_rows == NULL: send_dev = [n_shards][n_cols][N / n_shards], the all-to-all's send buffer (no re-blocking pass);
+ *   peer_rows != NULL: n_shards device pointers (host array), peer_rows[g] = rank g's receive buffer
+ *     (n_cols_total x N / n_shards, opened with nlc_peer_open; this rank's own buffer for g = its rank): local column j
+ *     is written to peer_rows[g] + (col0 + j) * (N / n_shards) over NVLink while the transform is still running --
+ *     no send buffer, no NCCL call; the caller separates the transforms from the tree with one barrier.
+ * n_shards <= 16. */
+int nlc_lde_columns_scatter_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, int log_n, int rate_bits,
+                                int is_values, uint64_t* coeffs_out_dev, uint64_t* send_dev, size_t n_shards,
+                                uint64_t* const* peer_rows, size_t col0);
+/* Receive buffers that other processes on the node can write (cudaMalloc + CUDA IPC).  handle: 64 bytes to pass to
+ * the peers (any transport); nlc_peer_open maps a peer's buffer into this process (peer access enabled lazily). */
+int nlc_peer_alloc(nlc_ctx* ctx, size_t words, uint64_t** ptr_out, unsigned char handle_out[64]);
+int nlc_peer_open(nlc_ctx* ctx, const unsigned char handle[64], uint64_t** ptr_out);
+int nlc_peer_close(nlc_ctx* ctx, uint64_t* ptr);
+int nlc_peer_free(nlc_ctx* ctx, uint64_t* ptr);
 int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards);
 void nlc_batch_free(nlc_batch* b);
 

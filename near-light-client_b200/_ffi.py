@@ -61,6 +61,12 @@ SIGNATURES = {
     "nlc_lde_columns_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, vp, vp]),
     "nlc_commit_from_lde_rows_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
                                                C.POINTER(vp)]),
+    "nlc_lde_columns_scatter_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, vp, vp, C.c_size_t,
+                                              C.POINTER(vp), C.c_size_t]),
+    "nlc_peer_alloc": (C.c_int, [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]),
+    "nlc_peer_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),
+    "nlc_peer_close": (C.c_int, [vp, vp]),
+    "nlc_peer_free": (C.c_int, [vp, vp]),
     "nlc_batch_shard": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "nlc_commit_from_coeffs_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_trace_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,

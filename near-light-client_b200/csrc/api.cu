@@ -343,6 +343,76 @@ int nlc_lde_columns_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, in
         lde_columns_dev(ctx, src_dev, n_cols, log_n, rate_bits, is_values != 0, coeffs_out_dev, lde_out_dev);
     });
 }
+int nlc_lde_columns_scatter_dev(nlc_ctx* ctx, const uint64_t* src_dev, size_t n_cols, int log_n, int rate_bits,
+                                int is_values, uint64_t* coeffs_out_dev, uint64_t* send_dev, size_t n_shards,
+                                uint64_t* const* peer_rows, size_t col0) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(src_dev && (send_dev || peer_rows), "null argument");
+        NLC_CHECK(n_cols > 0, "PolynomialBatch: at least one polynomial required");
+        NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
+        const int sl = shard_log_of(n_shards);
+        NLC_CHECK(sl >= 0 && n_shards <= 16, "n_shards must be a power of two, at most 16");
+        NLC_CHECK(sl <= log_n + rate_bits, "more shards than leaves");
+        NttScatter sc;
+        sc.log_per = log_n + rate_bits - sl;
+        sc.shard_stride = n_cols << sc.log_per;
+        if (peer_rows)
+            for (size_t p = 0; p < n_shards; p++) {
+                NLC_CHECK(peer_rows[p] != nullptr, "null peer buffer");
+                sc.peer[p] = peer_rows[p];
+            }
+        lde_columns_dev(ctx, src_dev, n_cols, log_n, rate_bits, is_values != 0, coeffs_out_dev, send_dev, &sc,
+                        peer_rows ? col0 : 0);
+    });
+}
+// receive buffers other processes can write: plain cudaMalloc memory (stream-ordered pools cannot be exported)
+int nlc_peer_alloc(nlc_ctx* ctx, size_t words, uint64_t** ptr_out, unsigned char handle_out[64]) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(ptr_out && handle_out && words, "null argument");
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+        void* p = nullptr;
+        NLC_CUDA(cudaMalloc(&p, words * sizeof(u64)));
+        cudaIpcMemHandle_t h;
+        cudaError_t e = cudaIpcGetMemHandle(&h, p);
+        if (e != cudaSuccess) {
+            cudaFree(p);
+            NLC_CUDA(e);
+        }
+        memcpy(handle_out, &h, 64);
+        *ptr_out = (u64*)p;
+    });
+}
+int nlc_peer_open(nlc_ctx* ctx, const unsigned char handle[64], uint64_t** ptr_out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(ptr_out && handle, "null argument");
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handle, 64);
+        void* p = nullptr;
+        NLC_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        *ptr_out = (u64*)p;
+    });
+}
+int nlc_peer_close(nlc_ctx* ctx, uint64_t* ptr) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        if (ptr) NLC_CUDA(cudaIpcCloseMemHandle(ptr));
+    });
+}
+int nlc_peer_free(nlc_ctx* ctx, uint64_t* ptr) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ptr) NLC_CUDA(cudaFree(ptr));
+    });
+}
 int nlc_commit_from_lde_rows_dev(nlc_ctx* ctx, uint64_t* lde_rows_dev, size_t n_cols, int log_n, int rate_bits,
                                  int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out) {
     if (!ctx) return 1;

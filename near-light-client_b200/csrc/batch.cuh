@@ -41,7 +41,7 @@ void batch_release(nlc_batch* b);
 void batch_ifft_values(nlc_batch* b, const u64* values_dev);
 void batch_lde_and_tree(nlc_batch* b);
 void batch_ifft_cols(nlc_batch* b, const u64* values_dev, size_t c0, size_t nc);
-void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc);
+void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc, const NttScatter* sc = nullptr);
 void batch_tree(nlc_batch* b);
 void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
                           u64* out_dev);
@@ -52,7 +52,7 @@ void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);
 
 // transforms of a column shard (no tree), and the tree over a leaf-row shard
 void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n, int rate_bits, bool is_values,
-                     u64* coeffs_out_dev, u64* lde_out_dev);
+                     u64* coeffs_out_dev, u64* lde_out_dev, const NttScatter* sc = nullptr, size_t col0 = 0);
 nlc_batch* commit_from_lde_rows_dev(nlc_ctx* ctx, u64* lde_rows_dev, size_t W, int log_n, int rate_bits, int cap_height,
                                     int shard_log, size_t shard_idx);
 // SURVEY.md 8f.1 (prover.rs:253-358 without the AIR evaluation)

@@ -161,7 +161,7 @@ void batch_release(nlc_batch* b) {
 // "FFT + blinding" (+ "transpose LDEs" + reverse_index_bits, which never happen) of from_coeffs for the columns
 // [c0, c0 + nc): columns are independent until the leaf hash, so a host-fed commit can run this on one chunk while
 // the next chunk is still crossing PCIe.
-void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc) {
+void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc, const NttScatter* sc) {
     nlc_ctx* ctx = b->ctx;
     const int log_n = b->log_n, r = b->rate_bits;
     const size_t n = (size_t)1 << log_n, N = b->n_local();
@@ -187,6 +187,10 @@ void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc) {
         job.row_base = (kr - kr0) * n;
         job.col0 = c0;
         job.scratch = scratch;
+        if (sc) { // re-blocked by leaf-row shard: columns are 2^log_per apart inside a shard's block
+            job.scatter = *sc;
+            job.dst_stride = (size_t)1 << sc->log_per;
+        }
         ntt_run(ctx, job);
     }
     ctx->phase_end();
@@ -338,7 +342,7 @@ nlc_batch* quotient_commit_dev(nlc_ctx* ctx, const u64* evals_dev, size_t n_ch, 
 // "IFFT" + "FFT + blinding" of from_values / from_coeffs for the columns one rank owns: lde_out = n_cols x N
 // column-major in leaf order (what batch_lde_cols writes), no tree.
 void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n, int rate_bits, bool is_values,
-                     u64* coeffs_out_dev, u64* lde_out_dev) {
+                     u64* coeffs_out_dev, u64* lde_out_dev, const NttScatter* sc, size_t col0) {
     const size_t n = (size_t)1 << log_n;
     nlc_batch view; // a window over the caller's buffers: only the fields the two column passes read
     view.ctx = ctx;
@@ -353,7 +357,14 @@ void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n,
             batch_ifft_cols(&view, src_dev, 0, n_cols);
         else if (view.coeffs != src_dev)
             NLC_CUDA(cudaMemcpyAsync(view.coeffs, src_dev, n_cols * n * sizeof(u64), cudaMemcpyDeviceToDevice, ctx->stream));
-        batch_lde_cols(&view, 0, n_cols);
+        if (sc && col0) { // peers address columns globally: shift the base so that local column j lands at col0 + j
+            NttScatter shifted = *sc;
+            for (auto& p : shifted.peer)
+                if (p) p += col0 << sc->log_per;
+            batch_lde_cols(&view, 0, n_cols, &shifted);
+        } else {
+            batch_lde_cols(&view, 0, n_cols, sc);
+        }
     } catch (...) {
         ctx->dfree(own);
         throw;

@@ -159,6 +159,14 @@ static inline int ilog2(size_t n) {
 // ROWS: out is a row-major (rows x row_width) matrix; row = row_base + bitrev order position, column
 //       offset col0.  COLS: the same matrix stored column-major (column stride dst_stride).
 //       NATURAL: out is column-contiguous, natural order.
+// COLS output re-blocked by leaf-row shard: leaf k of column c goes to
+//   base(k >> log_per) + c * dst_stride + (k & (2^log_per - 1)),  base(g) = peer[g] if peers are given (the receive
+// buffers of the other GPUs, written over NVLink) else dst + g * shard_stride (the send buffer of an all-to-all).
+struct NttScatter {
+    int log_per = -1; // < 0: off
+    size_t shard_stride = 0;
+    u64* peer[16] = {};
+};
 struct NttJob {
     const u64* src = nullptr;
     size_t src_stride = 0;
@@ -175,6 +183,7 @@ struct NttJob {
     size_t row_base = 0;       // ROWS / COLS: first row (bit-reversed position)
     size_t col0 = 0;           // ROWS / COLS: first column
     u64* scratch = nullptr;    // n_cols * 2^log_n words, needed when log_n > one digit
+    NttScatter scatter;        // COLS only
 };
 void ntt_run(nlc_ctx* ctx, const NttJob& job);
 size_t ntt_scratch_words(size_t n_cols, int log_n);

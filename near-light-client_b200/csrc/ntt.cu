@@ -168,13 +168,13 @@ k_ntt_hi(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, 
 // columns (transform g = gb*Gc + gc).  smem: [Gb*Gc][pitch].
 //   COLS / ROWS : the Gb blocks are consecutive; NATURAL : Gc = 1 and the blocks are the bit-reversal-related
 //   ones whose outputs interleave into contiguous Gb-element segments.
-enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2 };
+enum { OUT_NATURAL = 0, OUT_ROWS = 1, OUT_COLS = 2, OUT_SCATTER = 3 }; // SCATTER: COLS re-blocked by leaf-row shard
 template <int MODE, bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int log_Gb, int log_Gc, u32 plan,
          size_t n_cols, const u64* __restrict__ pre, const u64* __restrict__ post, u64 scale,
          const u64* __restrict__ roots, u64* __restrict__ dst, size_t dst_stride, size_t row_width, size_t row_base,
-         size_t col0) {
+         size_t col0, const NttScatter sc) {
     extern __shared__ u64 sm[];
     const int log_G = log_Gb + log_Gc;
     const u32 len = 1u << S, pitch = pad16(len) + 1;
@@ -197,7 +197,7 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
     }
     __syncthreads();
     fft_tile<false, INV>(sm, S, plan, log_G, pitch, roots);
-    if (MODE == OUT_COLS) { // column-major, index-bit-reversed: the tile is contiguous in its column
+    if (MODE == OUT_COLS || MODE == OUT_SCATTER) { // column-major, index-bit-reversed: the tile is contiguous in its column
         _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
             const u32 g = idx >> S, q = idx & (len - 1);
             const size_t col = ((size_t)blockIdx.y << log_Gc) + (g & Gc_mask);
@@ -205,7 +205,14 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
             const size_t blk = ((size_t)blockIdx.x << log_Gb) + (g >> log_Gc);
             u64 v = sm[g * pitch + pad16(q)];
             if (scale != 1) v = gl::mul(v, scale);
-            dst[(col0 + col) * dst_stride + row_base + (blk << S) + q] = v;
+            const size_t leaf = row_base + (blk << S) + q;
+            if (MODE == OUT_COLS) {
+                dst[(col0 + col) * dst_stride + leaf] = v;
+            } else { // re-blocked by leaf-row shard, possibly straight into a peer GPU's buffer
+                const size_t gd = leaf >> sc.log_per;
+                u64* base = sc.peer[0] ? sc.peer[gd] : dst + gd * sc.shard_stride;
+                base[(col0 + col) * dst_stride + (leaf & (((size_t)1 << sc.log_per) - 1))] = v;
+            }
         }
     } else if (MODE == OUT_ROWS) { // row-major: the Gc columns of a row are adjacent words
         _Pragma("unroll 4") for (u32 idx = threadIdx.x; idx < total; idx += NTT_THREADS) {
@@ -295,6 +302,7 @@ void ensure_attrs(nlc_ctx* ctx) {
     NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_ROWS, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_COLS, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_COLS, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    NLC_CUDA(cudaFuncSetAttribute((k_ntt_lo<OUT_SCATTER, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     ctx->ntt_attrs = true;
 }
 
@@ -359,16 +367,21 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
         if (log_Gb > log_nb) log_Gb = log_nb;
         dim3 grid((unsigned)((n >> S) >> log_Gb), (unsigned)((job.n_cols + ((size_t)1 << log_Gc) - 1) >> log_Gc));
         size_t smem = ((size_t)1 << (log_Gb + log_Gc)) * pitch * sizeof(u64);
-        if (job.cols) {
+        if (job.cols && job.scatter.log_per >= 0) {
+            NLC_CHECK(!inv, "scatter output is for forward transforms"); // the shard is picked per element: tiles may span shards
+            NLC_LAUNCH(ctx, (k_ntt_lo<OUT_SCATTER, false>), grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb,
+                       log_Gc, plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst,
+                       job.dst_stride, (size_t)0, job.row_base, job.col0, job.scatter);
+        } else if (job.cols) {
             auto k_lo = inv ? k_ntt_lo<OUT_COLS, true> : k_ntt_lo<OUT_COLS, false>;
             NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
                        plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, job.dst_stride,
-                       (size_t)0, job.row_base, job.col0);
+                       (size_t)0, job.row_base, job.col0, job.scatter);
         } else {
             auto k_lo = inv ? k_ntt_lo<OUT_ROWS, true> : k_ntt_lo<OUT_ROWS, false>;
             NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_Gb, log_Gc,
                        plan_steps(S), job.n_cols, lo_pre, (const u64*)nullptr, scale, roots, job.dst, (size_t)0,
-                       job.row_width, job.row_base, job.col0);
+                       job.row_width, job.row_base, job.col0, NttScatter());
         }
     } else {
         NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
@@ -378,6 +391,6 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
         auto k_lo = inv ? k_ntt_lo<OUT_NATURAL, true> : k_ntt_lo<OUT_NATURAL, false>;
         NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, 0,
                    plan_steps(S), job.n_cols, lo_pre, post, scale, roots, job.dst, job.dst_stride, (size_t)0,
-                   (size_t)0, (size_t)0);
+                   (size_t)0, (size_t)0, NttScatter());
     }
 }

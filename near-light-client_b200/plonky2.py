@@ -665,6 +665,28 @@ class PolynomialBatch:
                                                   vp(coeffs.data_ptr()), vp(lde.data_ptr())))
         return coeffs, lde
 
+    @staticmethod
+    def lde_columns_scatter(src, rate_bits: int, n_shards: int, is_values: bool = True, ctx=None, peer_ptrs=None,
+                            col0: int = 0):
+        """lde_columns with the exchange layout fused into the last NTT pass (nlc_lde_columns_scatter_dev).
+        peer_ptrs None: returns (coeffs, send) with send = (n_shards, nc, N / n_shards), the all-to-all's send buffer.
+        peer_ptrs = the n_shards receive buffers (sharding.PeerRows.ptrs): stores go to the peers; returns (coeffs, None)."""
+        import torch
+        ctx = ctx or default_context()
+        nc, n = src.shape
+        log_n = _log2_strict(n)
+        per = (n << rate_bits) // n_shards
+        coeffs = torch.empty((nc, n), dtype=torch.int64, device=src.device)
+        send, table = None, None
+        if peer_ptrs is None:
+            send = torch.empty((n_shards, nc, per), dtype=torch.int64, device=src.device)
+        else:
+            table = (vp * n_shards)(*[vp(p) for p in peer_ptrs])
+        ctx._check(_ffi.lib().nlc_lde_columns_scatter_dev(
+            ctx._h, vp(src.data_ptr()), nc, log_n, rate_bits, int(is_values), vp(coeffs.data_ptr()),
+            vp(send.data_ptr()) if send is not None else None, n_shards, table, col0))
+        return coeffs, send
+
     @classmethod
     def from_lde_rows(cls, rows, degree_log: int, rate_bits: int, cap_height: int, shard_idx: int, n_shards: int,
                       ctx=None):
@@ -672,11 +694,15 @@ class PolynomialBatch:
         CUDA tensor (column-major leaves, what sharding.exchange_rows returns).  The batch reads the tensor in place
         and keeps it alive; it is a shard: merkle_tree.local_cap / leaves / digests are the shard's part."""
         ctx = ctx or default_context()
-        W, per = rows.shape
-        if per * n_shards != 1 << (degree_log + rate_bits) or not rows.is_contiguous():
-            raise NlcError("rows must be a contiguous (W, N / n_shards) tensor")
+        if isinstance(rows, tuple):  # (device pointer, W, keepalive): a sharding.PeerRows buffer
+            ptr, W, rows = rows
+        else:
+            W, per = rows.shape
+            if per * n_shards != 1 << (degree_log + rate_bits) or not rows.is_contiguous():
+                raise NlcError("rows must be a contiguous (W, N / n_shards) tensor")
+            ptr = rows.data_ptr()
         h = vp()
-        ctx._check(_ffi.lib().nlc_commit_from_lde_rows_dev(ctx._h, vp(rows.data_ptr()), W, degree_log, rate_bits,
+        ctx._check(_ffi.lib().nlc_commit_from_lde_rows_dev(ctx._h, vp(ptr), W, degree_log, rate_bits,
                                                            cap_height, shard_idx, n_shards, C.byref(h)))
         b = cls(ctx, h, W, degree_log, rate_bits, cap_height)
         b.shard_idx, b.n_shards = shard_idx, n_shards
@@ -685,7 +711,7 @@ class PolynomialBatch:
 
     @classmethod
     def from_values_row_sharded(cls, values, rate_bits: int, blinding: bool, cap_height: int, group=None, ctx=None,
-                                is_values: bool = True):
+                                is_values: bool = True, exchange: str = "nccl"):
         """one commit over more GPUs than it has cosets (starky: rate_bits 1 on 4 / 8 GPUs).
         Every rank passes the same `values`; rank p transforms the columns sharding.column_split(W, G)[p]
         (lde_columns), one NCCL all-to-all hands rank g the leaves [g, g+1) * N / G of all columns, rank g builds its
@@ -713,12 +739,24 @@ class PolynomialBatch:
             with torch.cuda.stream(stream):
                 mine = np.stack([np.asarray(arrs[j]).view(np.int64) for j in range(c0, c0 + nc)])
                 src = torch.from_numpy(mine).pin_memory().to(dev, non_blocking=True)
-                coeffs, lde = cls.lde_columns(src, rate_bits, is_values, ctx)
-                rows = sharding.exchange_rows(sharding.pack_rows(lde, G), W, group)
-                b = cls.from_lde_rows(rows, log_n, rate_bits, cap_height, g, G, ctx)
+                if exchange == "p2p":
+                    # exchange fused into the transform: the last NTT pass stores into the peers' buffers over NVLink
+                    peers = sharding.PeerRows(ctx, W * ((n << rate_bits) // G), group)
+                    coeffs, _ = cls.lde_columns_scatter(src, rate_bits, G, is_values, ctx, peers.ptrs, c0)
+                    sharding.stream_barrier(dev, group)
+                    stream.synchronize()
+                    peers.close_peers()  # before the cap all-gather: nobody maps a buffer whose owner has returned
+                    b = cls.from_lde_rows((peers.own, W, peers), log_n, rate_bits, cap_height, g, G, ctx)
+                elif exchange == "nccl":
+                    coeffs, send = cls.lde_columns_scatter(src, rate_bits, G, is_values, ctx)
+                    rows = sharding.exchange_rows(send, W, group)
+                    b = cls.from_lde_rows(rows, log_n, rate_bits, cap_height, g, G, ctx)
+                    del send
+                else:
+                    raise NlcError("exchange must be 'nccl' or 'p2p'")
                 b.column_range, b.column_coeffs = (c0, nc), coeffs
                 stream.synchronize()
-                del lde, src
+                del src
         finally:
             ctx.set_stream(None)
         b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)

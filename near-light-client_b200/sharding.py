@@ -10,7 +10,10 @@ When there are more ranks than cosets (starky commits at rate_bits 1 on 4 or 8 G
 shards twice: by COLUMN for the transforms (rank p owns the columns column_split(W, G)[p]: nlc_lde_columns_dev), then
 one all-to-all hands rank g the leaf rows [g, g+1) * N / G of every column, and the tree is built by leaf ROW exactly
 as for a coset shard (nlc_commit_from_lde_rows_dev).  pack_rows / exchange_rows below are that exchange:
-8 * W * N * (G-1) / G bytes in total, uniform all-to-all through NVSwitch.
+8 * W * N * (G-1) / G bytes in total, uniform all-to-all through NVSwitch.  Two fused forms skip work:
+nlc_lde_columns_scatter_dev stores the last NTT pass straight into the send layout (no pack_rows pass), or -- with
+PeerRows -- straight into the other GPUs' receive buffers over NVLink (no send buffer, no NCCL all-to-all; one
+stream_barrier separates the transforms from the tree).
 """
 from __future__ import annotations
 
@@ -122,6 +125,61 @@ def gather_cap(local_cap: np.ndarray, cap_height: int, group=None, device=None) 
     out = torch.empty((world * per, 4), dtype=torch.int64, device=t.device)
     dist.all_gather_into_tensor(out, t, group=group)
     return out.cpu().numpy().view(np.uint64).reshape(1 << cap_height, 4)
+
+
+class PeerRows:
+    """The receive buffers of a row-sharded commit, writable by every rank of the node over NVLink (CUDA IPC).
+    Collective over `group`: every rank allocates W * per words, the 64-byte handles travel by all_gather_object,
+    every rank maps the others' buffers.  ptrs[g] = rank g's buffer as seen from this process (own buffer for own
+    rank).  close_peers() unmaps the others' buffers (after the transforms); free() releases the own one."""
+
+    def __init__(self, ctx, words: int, group=None):
+        import ctypes as C
+        import torch.distributed as dist
+        from . import _ffi
+        self._ctx, self._ffi = ctx, _ffi
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        own, handle = _ffi.vp(), C.create_string_buffer(64)
+        ctx._check(_ffi.lib().nlc_peer_alloc(ctx._h, words, C.byref(own), handle))
+        self.own = own.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self.ptrs, self._opened = [], []
+        for g, h in enumerate(handles):
+            if g == self.rank:
+                self.ptrs.append(self.own)
+                continue
+            p = _ffi.vp()
+            ctx._check(_ffi.lib().nlc_peer_open(ctx._h, h, C.byref(p)))
+            self.ptrs.append(p.value)
+            self._opened.append(p.value)
+
+    def close_peers(self):
+        for p in self._opened:
+            self._ctx._check(self._ffi.lib().nlc_peer_close(self._ctx._h, self._ffi.vp(p)))
+        self._opened = []
+
+    def free(self):
+        self.close_peers()
+        if self.own and self._ctx._h:
+            self._ffi.lib().nlc_peer_free(self._ctx._h, self._ffi.vp(self.own))
+        self.own = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def stream_barrier(device, group=None):
+    """A barrier in stream order (a 1-word all-reduce on the current stream): what every rank enqueued before it
+    has completed on every rank when it completes."""
+    import torch
+    import torch.distributed as dist
+    t = torch.zeros(1, dtype=torch.int32, device=device)
+    dist.all_reduce(t, group=group)
+    return t
 
 
 def assemble(parts):

@@ -31,12 +31,16 @@ for W, log_n, r, cap in [(9, 8, 1, 4), (135, 10, 3, 4), (418, 9, 1, 4), (world, 
     ref = O.commit_from_values(values, r, cap)
     lo, hi = S.leaf_range(log_n, r, rank, world)
     dlo, dhi = (ref.digests.shape[0] // world) * rank, (ref.digests.shape[0] // world) * (rank + 1)
-    b = P2.PolynomialBatch.from_values_row_sharded(list(values), r, False, cap, ctx=ctx)
-    assert np.array_equal(b.merkle_tree.cap, ref.cap), ("rows cap", W, log_n, r)
-    assert np.array_equal(b.merkle_tree.leaves, ref.leaves[lo:hi]), ("rows leaves", W, log_n, r)
-    assert np.array_equal(b.merkle_tree.digests, ref.digests[dlo:dhi]), ("rows digests", W, log_n, r)
-    c0, nc = b.column_range
-    assert np.array_equal(b.column_coeffs.cpu().numpy().view(np.uint64), ref.coeffs[c0:c0 + nc])
+    for exchange in ("nccl", "p2p"):  # all-to-all of the scattered send buffer / NTT stores into the peers' buffers
+        b = P2.PolynomialBatch.from_values_row_sharded(list(values), r, False, cap, ctx=ctx, exchange=exchange)
+        assert np.array_equal(b.merkle_tree.cap, ref.cap), ("rows cap", exchange, W, log_n, r)
+        assert np.array_equal(b.merkle_tree.leaves, ref.leaves[lo:hi]), ("rows leaves", exchange, W, log_n, r)
+        assert np.array_equal(b.merkle_tree.digests, ref.digests[dlo:dhi]), ("rows digests", exchange, W, log_n, r)
+        c0, nc = b.column_range
+        assert np.array_equal(b.column_coeffs.cpu().numpy().view(np.uint64), ref.coeffs[c0:c0 + nc])
+        b.free()
+        del b
+        dist.barrier()
     if world <= 1 << r:
         c = P2.PolynomialBatch.from_values_sharded(list(values), r, False, cap, ctx=ctx)
         assert np.array_equal(c.merkle_tree.cap, ref.cap), ("coset cap", W, log_n, r)

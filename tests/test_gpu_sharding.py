@@ -51,6 +51,10 @@ def test_row_shards_assemble_to_the_commit(P2, O, rng, W, log_n, r, cap, G):
         assert np.array_equal(lde.cpu().numpy().view(np.uint64), ref.leaves[:, c0:c0 + nc].T)
         sends.append(S.pack_rows(lde, G))
         coeffs.append(cf.cpu().numpy().view(np.uint64))
+        # the fused form: the last NTT pass stores straight into the send layout
+        cf2, send2 = P2.PolynomialBatch.lde_columns_scatter(src, r, G)
+        torch.cuda.synchronize()
+        assert torch.equal(send2, sends[-1]) and torch.equal(cf2, cf)
     assert np.array_equal(np.concatenate(coeffs), ref.coeffs)
     shards = []
     for g in range(G):
@@ -70,3 +74,39 @@ def test_row_shard_limits(P2, O, rng):
         P2.PolynomialBatch.from_lde_rows(rows, 4, 1, 1, 0, 4)  # 4 shards, 2 cap subtrees
     with pytest.raises(P2.NlcError):
         P2.PolynomialBatch.from_lde_rows(rows, 4, 1, 2, 0, 2)  # wrong row count for 2 shards
+
+
+@pytest.mark.parametrize("W,log_n,r,cap,G", [(5, 6, 1, 3, 4), (9, 10, 1, 4, 8), (135, 11, 1, 4, 8), (20, 9, 3, 4, 16),
+                                             (7, 8, 1, 4, 2)])
+def test_row_shards_through_peer_buffers(P2, pkg, O, rng, W, log_n, r, cap, G):
+    """The P2P form of 8(e).3 on one GPU: G receive buffers from nlc_peer_alloc stand for the G ranks' buffers, every
+    column owner's last NTT pass stores into all of them (nlc_lde_columns_scatter_dev with peer pointers and its
+    global column offset), and the tree over each buffer is the oracle's shard."""
+    import ctypes as C
+    import torch
+    S, ffi = pkg.sharding, pkg._ffi
+    ctx = P2.default_context()
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, r, cap)
+    per = (1 << (log_n + r)) // G
+    bufs = []
+    for _ in range(G):
+        ptr, handle = ffi.vp(), C.create_string_buffer(64)
+        ctx._check(ffi.lib().nlc_peer_alloc(ctx._h, W * per, C.byref(ptr), handle))
+        bufs.append(ptr.value)
+    try:
+        for c0, nc in S.column_split(W, G):
+            src = torch.from_numpy(values[c0:c0 + nc].view(np.int64)).cuda()
+            cf, none = P2.PolynomialBatch.lde_columns_scatter(src, r, G, peer_ptrs=bufs, col0=c0)
+            assert none is None
+            assert np.array_equal(cf.cpu().numpy().view(np.uint64), ref.coeffs[c0:c0 + nc])
+        torch.cuda.synchronize()
+        shards = [P2.PolynomialBatch.from_lde_rows((bufs[g], W, None), log_n, r, cap, g, G) for g in range(G)]
+        assert np.array_equal(S.assemble(s.merkle_tree.local_cap for s in shards), ref.cap)
+        assert np.array_equal(S.assemble(s.merkle_tree.digests for s in shards), ref.digests)
+        assert np.array_equal(S.assemble(s.merkle_tree.leaves for s in shards), ref.leaves)
+        for s in shards:
+            s.free()
+    finally:
+        for p in bufs:
+            ffi.lib().nlc_peer_free(ctx._h, ffi.vp(p))
