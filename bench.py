@@ -307,9 +307,15 @@ def run_ours(args, rank, local_rank, world):
             c0, nc = split[rank]
             per = N // world
             my_coeffs = torch.empty((nc, n), dtype=torch.int64, device="cuda")
-            my_lde = torch.empty((nc, N), dtype=torch.int64, device="cuda")
-            send = torch.empty((world, nc, per), dtype=torch.int64, device="cuda")
-            rows = torch.empty((W, per), dtype=torch.int64, device="cuda")
+            if args.exchange == "p2p":  # receive buffers every rank can write, registered once (like NCCL's own)
+                peers = pkg.sharding.PeerRows(ctx, W * per)
+                peer_table = (ffi.vp * world)(*[ffi.vp(p) for p in peers.ptrs])
+                tiny = torch.zeros(1, dtype=torch.int32, device="cuda")
+            else:
+                if args.exchange == "nccl-pack":
+                    my_lde = torch.empty((nc, N), dtype=torch.int64, device="cuda")
+                send = torch.empty((world, nc, per), dtype=torch.int64, device="cuda")
+                rows = torch.empty((W, per), dtype=torch.int64, device="cuda")
             out_split, in_split = [c * per for _, c in split], [nc * per] * world
         else:
             pkg.sharding.check_plan(r, cap, world)
@@ -318,14 +324,27 @@ def run_ours(args, rank, local_rank, world):
         cudart = C.CDLL("libcudart.so.12")
 
     def rows_commit(src_cols):
-        """8(e).3 from this rank's columns (device): transforms, pack, all-to-all, tree, cap all-gather."""
+        """8(e).3 from this rank's columns (device): transforms (+ exchange), tree, cap all-gather."""
         h = ffi.vp()
-        ctx._check(L.nlc_lde_columns_dev(ctx._h, ffi.vp(src_cols.data_ptr()), nc, log_n, r, 1,
-                                         ffi.vp(my_coeffs.data_ptr()), ffi.vp(my_lde.data_ptr())))
-        send.copy_(my_lde.view(nc, world, per).permute(1, 0, 2))
-        dist.all_to_all_single(rows.view(-1), send.view(-1), output_split_sizes=out_split, input_split_sizes=in_split)
-        ctx._check(L.nlc_commit_from_lde_rows_dev(ctx._h, ffi.vp(rows.data_ptr()), W, log_n, r, cap, rank, world,
-                                                  C.byref(h)))
+        if args.exchange == "p2p":  # the last NTT pass stores into the peers' receive buffers over NVLink
+            ctx._check(L.nlc_lde_columns_scatter_dev(ctx._h, ffi.vp(src_cols.data_ptr()), nc, log_n, r, 1,
+                                                     ffi.vp(my_coeffs.data_ptr()), None, world, peer_table, c0))
+            dist.all_reduce(tiny)  # barrier in stream order: every rank's stores have landed
+            rows_ptr = peers.own
+        elif args.exchange == "nccl":  # ... into the send layout, then one all-to-all
+            ctx._check(L.nlc_lde_columns_scatter_dev(ctx._h, ffi.vp(src_cols.data_ptr()), nc, log_n, r, 1,
+                                                     ffi.vp(my_coeffs.data_ptr()), ffi.vp(send.data_ptr()), world, None, 0))
+            dist.all_to_all_single(rows.view(-1), send.view(-1), output_split_sizes=out_split,
+                                   input_split_sizes=in_split)
+            rows_ptr = rows.data_ptr()
+        else:  # "nccl-pack": plain LDE, a re-blocking pass, all-to-all (the unfused baseline)
+            ctx._check(L.nlc_lde_columns_dev(ctx._h, ffi.vp(src_cols.data_ptr()), nc, log_n, r, 1,
+                                             ffi.vp(my_coeffs.data_ptr()), ffi.vp(my_lde.data_ptr())))
+            send.copy_(my_lde.view(nc, world, per).permute(1, 0, 2))
+            dist.all_to_all_single(rows.view(-1), send.view(-1), output_split_sizes=out_split,
+                                   input_split_sizes=in_split)
+            rows_ptr = rows.data_ptr()
+        ctx._check(L.nlc_commit_from_lde_rows_dev(ctx._h, ffi.vp(rows_ptr), W, log_n, r, cap, rank, world, C.byref(h)))
         cudart.cudaMemcpyAsync(C.c_void_p(cap_local.data_ptr()), C.c_void_p(L.nlc_batch_cap_dev(h)),
                                C.c_size_t(cap_local.numel() * 8), 3, C.c_void_p(stream.cuda_stream))
         dist.all_gather_into_tensor(cap_full, cap_local)
@@ -484,8 +503,8 @@ def run_ours(args, rank, local_rank, world):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "u64", "data": "synthetic",
                 "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": r, "cap_height": cap,
-                           "parallelism": (f"one commit, column shards x{world} -> NCCL all-to-all -> leaf-row shards + "
-                                           "all-gather of the cap (SURVEY 8e.3)" if by_rows else
+                           "parallelism": (f"one commit, column shards x{world} -> exchange over NVLink -> leaf-row shards + "
+                                           f"all-gather of the cap (SURVEY 8e.3; exchange={args.exchange})" if by_rows else
                                            f"one commit, coset shards x{world} + NCCL all-gather of the cap" if sharded
                                            else f"instances x{world}"), "l2": "flushed between timed iterations (256 MiB write)"},
                 "clocks": clocks, "gpu_launches": int(launches),
@@ -512,6 +531,8 @@ def main():
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
                          "of one independent commit per rank")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl", "nccl-pack"],
+                    help="--shard-commit with more ranks than cosets (SURVEY 8e.3): how leaf rows reach their shard")
     ap.add_argument("--ref-sample-log-rows", type=int, default=13,
                     help="reference arm: rows of the bounded sample (log2); throughput is per input element")
     args = ap.parse_args()
