@@ -223,14 +223,40 @@ def run_replay_workload(args):
     print(json.dumps(out), flush=True)
 
 
+def oracle_quality(O):
+    """Single-thread rates of the CPU port, so that the quality of the baseline is on record beside every GPU/CPU
+    factor: Poseidon permutations/s/core (fast partial rounds, as upstream runs them) and FFT butterflies/s/core."""
+    rng = np.random.default_rng(3)
+    threads = O.get_threads()
+    O.set_threads(1)
+    leaves = O.random_field(rng, (1 << 10, 135))
+    O.merkle_new(leaves[:16], 0)
+    t0 = time.perf_counter()
+    O.merkle_new(leaves, 4)
+    dt = time.perf_counter() - t0
+    perms = (1 << 10) * 17 + (1 << 10) - 16
+    col = O.random_field(rng, (1 << 16,))
+    O.fft(col)
+    t0 = time.perf_counter()
+    for _ in range(4):
+        O.fft(col)
+    df = (time.perf_counter() - t0) / 4
+    O.set_threads(threads)
+    return {"poseidon_perms_per_s_per_core": perms / dt, "fft_butterflies_per_s_per_core": 16 * (1 << 15) / df,
+            "note": "C restatement (scalar 64-bit mulq, fast partial rounds, OpenMP); NOT plonky2's AVX2/asm build"}
+
+
 def run_reference(args, rank, world):
-    """The reference's CPU algorithm for the path (oracle port; plonky2 itself cannot be built here)."""
+    """The reference's CPU algorithm for the path (oracle port; plonky2 itself cannot be built here), on the
+    WORKLOAD'S OWN SIZE by default; --ref-sample-log-rows N is an explicit opt-in to a bounded row sample."""
     if rank != 0:
         return
     O = graft.load_oracle()
     log_n, W, r, cap = WORKLOADS[args.workload]
     full_log_n = log_n
-    log_n = min(log_n, args.ref_sample_log_rows)  # bounded sample: same columns / rate / cap, fewer rows
+    sampled = args.ref_sample_log_rows is not None and args.ref_sample_log_rows < log_n
+    if sampled:
+        log_n = args.ref_sample_log_rows  # bounded sample: same columns / rate / cap, fewer rows
     n = 1 << log_n
     values = synth_values(W, n, 0xC0FFEE + 1)
     # torchrun exports OMP_NUM_THREADS=1 to every rank: the reference arm runs on rank 0 alone and takes every core
@@ -243,14 +269,18 @@ def run_reference(args, rank, world):
         O.commit_from_values(values, r, cap)
     dt = (time.perf_counter() - t0) / args.steps
     val = W * n / dt
+    config = {"workload": args.workload, "rows": 1 << full_log_n, "cols": W, "rate_bits": r, "cap_height": cap}
+    sample = f"{args.steps} full commits of {args.workload} (OpenMP over columns/rows/subtrees)"
+    if sampled:
+        config["sample_rows"] = n
+        sample = (f"{args.steps} commits of 2^{log_n} of the workload's 2^{full_log_n} rows x {W} cols, rate_bits {r} "
+                  f"(same per-row work; OpenMP over columns/rows/subtrees)")
     line = {"impl": "reference", "metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": val,
             "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
-            "data": "synthetic", "config": {"workload": args.workload, "rows": 1 << full_log_n, "cols": W, "rate_bits": r,
-                                            "cap_height": cap, "sample_rows": n},
-            "cpu_baseline": {"value": val, "unit": "elements/s", "cores": cores, "kind": "port",
-                             "sample": f"{args.steps} commits of 2^{log_n} of the workload's 2^{full_log_n} rows x {W} cols, "
-                                       f"rate_bits {r} (same per-row work; OpenMP over columns/rows/subtrees)"},
+            "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": val, "unit": "elements/s", "cores": cores, "kind": "port", "sample": sample,
+                             "port_quality": oracle_quality(O)},
             "e2e": {"value": val, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -495,7 +525,8 @@ def run_ours(args, rank, local_rank, world):
         dt = time.perf_counter() - t0
         ok = bool(np.array_equal(ref.cap, cap_host))
         cpu_baseline = {"value": elems / dt, "unit": "elements/s", "cores": O.get_threads(), "kind": "port",
-                        "sample": f"1 full commit of {args.workload} ({dt:.2f} s); cap equals the GPU's: {ok}"}
+                        "sample": f"1 full commit of {args.workload} ({dt:.2f} s); cap equals the GPU's: {ok}",
+                        "port_quality": oracle_quality(O)}
 
     if rank == 0:
         line = {"metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": value,
@@ -533,8 +564,8 @@ def main():
                          "of one independent commit per rank")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl", "nccl-pack"],
                     help="--shard-commit with more ranks than cosets (SURVEY 8e.3): how leaf rows reach their shard")
-    ap.add_argument("--ref-sample-log-rows", type=int, default=13,
-                    help="reference arm: rows of the bounded sample (log2); throughput is per input element")
+    ap.add_argument("--ref-sample-log-rows", type=int, default=None,
+                    help="reference arm: opt in to a bounded row sample (log2 rows); default = the workload's own size")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))

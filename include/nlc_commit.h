@@ -32,7 +32,7 @@ typedef struct nlc_batch nlc_batch; /* a committed PolynomialBatch living in HBM
 typedef struct nlc_tree nlc_tree;   /* a stand-alone MerkleTree living in HBM */
 
 /* ---- lifecycle ---------------------------------------------------------------------------- */
-/* device < 0: use the current CUDA device. */
+/* device < 0: the device named by the environment variable NLC_DEVICE if set, else the current CUDA device. */
 int nlc_init(int device, nlc_ctx** out);
 /* Every nlc_batch / nlc_tree / nlc_fri_state made on the context must have been freed before (the Rust wrapper's
  * handles hold an Arc of the context); a handle that outlives its context is dangling. */
@@ -45,6 +45,15 @@ int nlc_device(nlc_ctx* ctx);
  * restores the context's own stream.  Lets a harness time kernels with events on that stream. */
 int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream);
 int nlc_synchronize(nlc_ctx* ctx);
+/* STREAM AND LIFETIME CONTRACT of every *_dev entry point (nlc_commit_from_values_dev, nlc_commit_from_coeffs_dev,
+ * nlc_commit_from_values_shard_dev, nlc_lde_columns[_scatter]_dev, nlc_commit_from_lde_rows_dev,
+ * nlc_quotient_commit_dev, nlc_air_eval_dev): they only ENQUEUE work on the context's stream and return.  That stream is
+ * created cudaStreamNonBlocking: it does NOT order against the legacy NULL stream or any other stream.  The caller must
+ * (a) order the producer of the input buffer before the call -- nlc_wait_stream(ctx, producer) does it with one event
+ * (NULL = the legacy default stream), or run the library on the producer's stream with nlc_set_stream -- and
+ * (b) keep input and output device buffers alive and unmodified until nlc_synchronize(ctx) or a later synchronising
+ * accessor (nlc_batch_cap, ...) has returned. */
+int nlc_wait_stream(nlc_ctx* ctx, void* producer_stream);
 /* Number of kernels this library has launched on ctx since creation (bench.py's gpu_launches). */
 uint64_t nlc_launch_count(nlc_ctx* ctx);
 
@@ -81,6 +90,14 @@ int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t 
  * the serial column split of trace/mod.rs:270-285: rows x width host matrix, columns [col0, col0+n_cols). */
 int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols,
                                int log_n, int rate_bits, int cap_height, nlc_batch** out);
+/* SURVEY.md section 5 (checkpoint / resume): bring a PolynomialBatch that was built and serialised earlier back onto
+ * the GPU -- plonky2x serialises circuit data incl. constants_sigmas_commitment (/root/reference/scripts/
+ * build-circuit.sh:10-18), which is oracle 0 of every plonk prove_openings.  coeff_cols = `polynomials` (n_cols host
+ * vectors of n coefficients).  The LDE and the tree are RECOMPUTED from them (bit-identical by construction, no 8x larger
+ * upload); expect_cap (2^cap_height x 4) and expect_digests (2*(N - 2^cap_height) x 4), when non-NULL, are the
+ * serialised merkle_tree.cap / .digests: a mismatch fails loudly (non-zero, message in nlc_last_error). */
+int nlc_batch_import(nlc_ctx* ctx, const uint64_t* const* coeff_cols, size_t n_cols, int log_n, int rate_bits,
+                     int cap_height, const uint64_t* expect_cap, const uint64_t* expect_digests, nlc_batch** out);
 /* SURVEY.md 8(e).2 -- one GPU's share of a commit, split by LDE coset.  n_shards (a power of two, at most
  * 2^rate_bits and at most 2^cap_height) ranks each call this with their shard_idx: the batch then holds the
  * leaves [shard_idx, shard_idx + 1) * N / n_shards (whole cosets = whole cap subtrees), their digests, and
@@ -140,6 +157,10 @@ int nlc_batch_leaves(nlc_batch* b, uint64_t* out);
 int nlc_batch_digests(nlc_batch* b, uint64_t* out);
 /* a6: get_lde_values(i, step) = leaves[bitrev_N(i*step)] for i in idx (prover.rs:289-294): m x n_cols. */
 int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step, uint64_t* out);
+/* The same for the stripe i = i_start .. i_start + count - 1 in ONE launch and ONE D2H (count x n_cols): what a
+ * host-side quotient loop (prover.rs:306-352 calls get_lde_values_packed(i, step) for every P::WIDTH points, twice)
+ * uses while the AIR is still evaluated on the CPU; with nlc_air_eval_dev the rows never leave the GPU. */
+int nlc_batch_lde_rows_range(nlc_batch* b, size_t i_start, size_t count, size_t step, uint64_t* out);
 /* merkle_tree.get(leaf_index) and merkle_tree.prove(leaf_index): row (n_cols) and siblings
  * ((log N - cap_height) x 4, bottom-up). Either output may be NULL. */
 int nlc_batch_open(nlc_batch* b, size_t leaf_index, uint64_t* row_out, uint64_t* siblings_out);
@@ -227,6 +248,7 @@ int nlc_challenger_get(nlc_ctx* ctx, nlc_challenger* c, size_t n, uint64_t* out)
 /* FriParams { config: FriConfig { rate_bits, cap_height, proof_of_work_bits, num_query_rounds, .. },
  * hiding = false, degree_bits, reduction_arity_bits } (plonky2::fri::{FriConfig,FriParams});
  * knobs set at vendor/starkyx/starkyx/src/plonky2/stark/config.rs:64-70. */
+#define NLC_MAX_FRI_ROUNDS 32 /* degree_bits <= 32 (two-adicity) and every round removes >= 1 bit */
 typedef struct {
     int degree_bits;
     int rate_bits;
@@ -234,10 +256,11 @@ typedef struct {
     int proof_of_work_bits;
     int num_query_rounds;
     int n_reduction_rounds;
-    int reduction_arity_bits[16];
+    int reduction_arity_bits[NLC_MAX_FRI_ROUNDS];
 } nlc_fri_params;
 /* FriConfig::fri_params(degree_bits, false) with FriReductionStrategy::ConstantArityBits(arity_bits,
- * final_poly_bits) (config.rs:68 uses (4, 5); config.rs:75-77). */
+ * final_poly_bits) (config.rs:68 uses (4, 5); config.rs:75-77).  Upstream's loop is unbounded; this one fails
+ * (non-zero) rather than truncate if it would need more than NLC_MAX_FRI_ROUNDS rounds. */
 int nlc_fri_params_constant_arity(nlc_fri_params* p, int degree_bits, int rate_bits, int cap_height,
                                   int proof_of_work_bits, int num_query_rounds, int arity_bits,
                                   int final_poly_bits);

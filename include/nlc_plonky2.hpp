@@ -378,6 +378,31 @@ class PolynomialBatch {
         return commit(cols, polynomials.empty() ? 0 : polynomials[0].len(), lens_equal(polynomials), rate_bits, blinding,
                       cap_height, false);
     }
+    // A PolynomialBatch read back from serialised circuit data (plonky2's Read::read_polynomial_batch; circuits are
+    // serialised by /root/reference/scripts/build-circuit.sh:10-18): `polynomials` + the serialised MerkleCap.  The LDE
+    // and the tree are recomputed on the GPU from the coefficients and the cap must match (panics otherwise).
+    static PolynomialBatch from_serialized(const std::vector<PolynomialCoeffs>& polynomials, size_t rate_bits,
+                                           size_t cap_height, const MerkleCap* cap = nullptr) {
+        if (polynomials.empty()) throw Panic("PolynomialBatch: at least one polynomial required");
+        if (!lens_equal(polynomials)) throw Panic("All polynomials in a batch must have the same length");
+        if (cap && cap->hashes.size() != ((size_t)1 << cap_height)) throw Panic("serialised cap has the wrong size");
+        std::vector<const uint64_t*> cols;
+        for (const auto& p : polynomials) cols.push_back(p.coeffs.data());
+        Context& c = Context::current();
+        nlc_batch* h = nullptr;
+        const int log_n = (int)log2_strict(polynomials[0].len());
+        c.check(nlc_batch_import(c.raw(), cols.data(), cols.size(), log_n, (int)rate_bits, (int)cap_height,
+                                 cap ? cap->hashes[0].elements : nullptr, nullptr, &h));
+        PolynomialBatch b;
+        b.h_.reset(h, nlc_batch_free);
+        b.n_polys_ = cols.size();
+        b.degree_log = (size_t)log_n;
+        b.rate_bits = rate_bits;
+        b.cap_height_ = cap_height;
+        b.merkle_tree.cap.hashes.resize((size_t)1 << cap_height);
+        c.check(nlc_batch_cap(h, b.merkle_tree.cap.hashes[0].elements));
+        return b;
+    }
     // SURVEY.md 8f.1 -- what prover.rs:336-357 and :158-178 do with the constraint evaluations: `quotient_values` is
     // the row-per-point Vec<Vec<F>> (num_challenges values per row, size = n << log2_ceil(quotient_degree_factor)
     // rows) flattened; per challenge coset_ifft(F::coset_shift()), trim_to_len(n * factor).expect("Quotient has

@@ -32,7 +32,7 @@ class CTiming(C.Structure):
 class CFriParams(C.Structure):
     _fields_ = [("degree_bits", C.c_int), ("rate_bits", C.c_int), ("cap_height", C.c_int),
                 ("proof_of_work_bits", C.c_int), ("num_query_rounds", C.c_int), ("n_reduction_rounds", C.c_int),
-                ("reduction_arity_bits", C.c_int * 16)]
+                ("reduction_arity_bits", C.c_int * 32)]  # NLC_MAX_FRI_ROUNDS
 
 
 class CFriInstance(C.Structure):
@@ -48,6 +48,7 @@ SIGNATURES = {
     "nlc_device": (C.c_int, [vp]),
     "nlc_set_stream": (C.c_int, [vp, vp]),
     "nlc_synchronize": (C.c_int, [vp]),
+    "nlc_wait_stream": (C.c_int, [vp, vp]),
     "nlc_launch_count": (C.c_uint64, [vp]),
     "nlc_timing_enable": (C.c_int, [vp, C.c_int]),
     "nlc_timing_read": (C.c_int, [vp, C.POINTER(CTiming)]),
@@ -83,6 +84,8 @@ SIGNATURES = {
     "nlc_batch_leaves": (C.c_int, [vp, u64p]),
     "nlc_batch_digests": (C.c_int, [vp, u64p]),
     "nlc_batch_lde_rows": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, u64p]),
+    "nlc_batch_lde_rows_range": (C.c_int, [vp, C.c_size_t, C.c_size_t, C.c_size_t, u64p]),
+    "nlc_batch_import": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, u64p, u64p, C.POINTER(vp)]),
     "nlc_batch_open": (C.c_int, [vp, C.c_size_t, u64p, u64p]),
     "nlc_batch_lde_dev": (vp, [vp]),
     "nlc_batch_coeffs_dev": (vp, [vp]),

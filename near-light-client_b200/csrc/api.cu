@@ -3,6 +3,8 @@
 // Every entry point: lock the context, select its device, run on its stream, turn C++ exceptions into
 // a non-zero return code + nlc_last_error.  There is no CPU implementation behind any of them: if no
 // CUDA device is usable nlc_init fails and no other call can be made.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "batch.cuh"
@@ -133,6 +135,7 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream)); // buffers allocated on the compute stream
             NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
             NLC_CHECK(cols != nullptr, "null column table");
+            for (size_t j = 0; j < W; j++) NLC_CHECK(cols[j] != nullptr, "null column pointer"); // before any upload is issued
             std::vector<cudaEvent_t> evs;
             for (size_t c0 = 0, nc = 0; c0 < W; c0 += nc) {
                 size_t want = chunk;
@@ -163,6 +166,12 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             batch_tree(b);
             sync(ctx);
         } catch (...) {
+            // uploads of earlier chunks may still be in flight on the copy stream into `vals` / b->coeffs: the
+            // stream-ordered frees below are ordered on the compute stream only, so drain the copies first or the
+            // pool could hand this memory to the next commit while a stale DMA lands in it
+            ctx->stager.abandon();
+            cudaStreamSynchronize(ctx->copy_stream);
+            cudaStreamSynchronize(ctx->stream);
             batch_release(b);
             throw;
         }
@@ -184,7 +193,17 @@ int nlc_init(int device, nlc_ctx** out) {
         if (e != cudaSuccess || count == 0)
             throw NlcError(std::string("nlc_init: no CUDA device (") + cudaGetErrorString(e) +
                            "); this library has no CPU fallback");
-        if (device < 0) NLC_CUDA(cudaGetDevice(&device));
+        if (device < 0) { // NLC_DEVICE: pick the GPU without touching the caller's code, else the current one
+            const char* e = getenv("NLC_DEVICE");
+            if (e && *e) {
+                char* end = nullptr;
+                const long d = strtol(e, &end, 10);
+                NLC_CHECK(end && *end == 0 && d >= 0, "NLC_DEVICE must be a non-negative device index");
+                device = (int)d;
+            } else {
+                NLC_CUDA(cudaGetDevice(&device));
+            }
+        }
         NLC_CHECK(device < count, "device index out of range");
         int prev = 0;
         cudaGetDevice(&prev);
@@ -239,6 +258,17 @@ int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream) {
         CtxGuard g(ctx);
         NLC_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    });
+}
+int nlc_wait_stream(nlc_ctx* ctx, void* producer_stream) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        if ((cudaStream_t)producer_stream == ctx->stream) return;
+        // cudaEventRecord on stream 0 records on the legacy NULL stream (torch's default), which the context's
+        // non-blocking stream does not order against by itself
+        NLC_CUDA(cudaEventRecord(ctx->ev_ready, (cudaStream_t)producer_stream));
+        NLC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_ready, 0));
     });
 }
 int nlc_synchronize(nlc_ctx* ctx) {
@@ -442,12 +472,77 @@ int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width,
         NLC_CHECK(n_cols > 0 && col0 + n_cols <= width, "column range outside the trace");
         NLC_CHECK(log_n >= 0 && log_n <= 32, "bad shape");
         const size_t n = (size_t)1 << log_n;
-        DevBuf rows_dev(ctx, n * width), vals(ctx, n * n_cols);
-        h2d(ctx, rows_dev.p, rows, n * width * sizeof(u64));
-        transpose_trace_cols(ctx, rows_dev.p, width, col0, n_cols, n, vals.p);
-        *out = commit_dev(ctx, vals.p, true, n_cols, log_n, rate_bits, cap_height);
-        sync(ctx);
+        // Only the [col0, col0 + n_cols) strip of each row crosses PCIe (ed25519: 1 651 of 4 153 columns), in row
+        // chunks on the copy stream; the compute stream transposes chunk k into the column-major value matrix while
+        // chunk k+1 uploads.  Two strip buffers alternate.
+        size_t chunk_rows = ((size_t)32 << 20) / (n_cols * sizeof(u64)); // ~32 MiB per chunk
+        chunk_rows = std::max<size_t>(chunk_rows / 32 * 32, 32);
+        if (chunk_rows > n) chunk_rows = n;
+        DevBuf strip0(ctx, chunk_rows * n_cols), strip1(ctx, chunk_rows * n_cols), vals(ctx, n * n_cols);
+        u64* strip[2] = {strip0.p, strip1.p};
+        const bool pageable = HostStager::pageable(rows);
+        try {
+            NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream));
+            NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
+            size_t k = 0;
+            for (size_t r0 = 0; r0 < n; r0 += chunk_rows, k++) {
+                const size_t nr = n - r0 < chunk_rows ? n - r0 : chunk_rows;
+                if (k >= 2) // the transpose that last read this strip buffer must be done before it is overwritten
+                    NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->chunk_event(2 * (k - 2) + 1), 0));
+                const u64* src = rows + r0 * width + col0;
+                if (pageable) {
+                    ctx->stager.upload_rows(ctx->copy_stream, strip[k & 1], src, width * sizeof(u64), n_cols * sizeof(u64), nr);
+                    ctx->stager.flush(ctx->copy_stream);
+                } else {
+                    NLC_CUDA(cudaMemcpy2DAsync(strip[k & 1], n_cols * sizeof(u64), src, width * sizeof(u64),
+                                               n_cols * sizeof(u64), nr, cudaMemcpyHostToDevice, ctx->copy_stream));
+                }
+                NLC_CUDA(cudaEventRecord(ctx->chunk_event(2 * k), ctx->copy_stream));
+                NLC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_event(2 * k), 0));
+                transpose_trace_cols(ctx, strip[k & 1], n_cols, 0, n_cols, nr, vals.p + r0, n);
+                NLC_CUDA(cudaEventRecord(ctx->chunk_event(2 * k + 1), ctx->stream));
+            }
+            *out = commit_dev(ctx, vals.p, true, n_cols, log_n, rate_bits, cap_height);
+            sync(ctx);
+        } catch (...) {
+            ctx->stager.abandon();
+            cudaStreamSynchronize(ctx->copy_stream);
+            cudaStreamSynchronize(ctx->stream);
+            throw;
+        }
     });
+}
+
+// SURVEY.md section 5 "checkpoint / resume": a PolynomialBatch that was built earlier and serialised (circuit data:
+// constants_sigmas_commitment).  The LDE and the tree are recomputed from the coefficients (bit-identical by
+// construction, a few ms) and checked against what the serialised struct carried.
+int nlc_batch_import(nlc_ctx* ctx, const uint64_t* const* coeff_cols, size_t n_cols, int log_n, int rate_bits,
+                     int cap_height, const uint64_t* expect_cap, const uint64_t* expect_digests, nlc_batch** out) {
+    if (!ctx) return 1;
+    nlc_batch* b = nullptr;
+    int rc = commit_host(ctx, coeff_cols, n_cols, log_n, rate_bits, cap_height, false, &b);
+    if (rc) return rc;
+    rc = nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out != nullptr, "null output handle");
+        *out = nullptr;
+        if (expect_cap) {
+            const size_t words = (size_t)4 << cap_height;
+            DevBuf e(ctx, words);
+            h2d(ctx, e.p, expect_cap, words * sizeof(u64));
+            NLC_CHECK(!device_words_differ(ctx, e.p, b->cap, words),
+                      "PolynomialBatch import: the MerkleCap recomputed from the coefficients differs from the serialised one");
+        }
+        if (expect_digests && b->n_digest_words) {
+            DevBuf e(ctx, b->n_digest_words);
+            h2d(ctx, e.p, expect_digests, b->n_digest_words * sizeof(u64));
+            NLC_CHECK(!device_words_differ(ctx, e.p, b->digests, b->n_digest_words),
+                      "PolynomialBatch import: the digests recomputed from the coefficients differ from the serialised ones");
+        }
+        *out = b;
+    });
+    if (rc) nlc_batch_free(b);
+    return rc;
 }
 void nlc_batch_free(nlc_batch* b) {
     if (!b) return;
@@ -524,8 +619,22 @@ int nlc_batch_lde_rows(nlc_batch* b, const uint64_t* idx, size_t m, size_t step,
         if (!m) return;
         DevBuf idx_dev(ctx, m), rows(ctx, m * b->W);
         h2d(ctx, idx_dev.p, idx, m * sizeof(u64));
-        batch_gather_lde_rows(b, idx_dev.p, m, step, rows.p);
+        batch_gather_lde_rows(b, idx_dev.p, 0, m, step, rows.p);
         d2h(ctx, out, rows.p, m * b->W * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_batch_lde_rows_range(nlc_batch* b, size_t i_start, size_t count, size_t step, uint64_t* out) {
+    if (!b) return 1;
+    return nlc_guarded(b->ctx, [&] {
+        nlc_ctx* ctx = b->ctx;
+        CtxGuard g(ctx);
+        NLC_CHECK(b->shard_log == 0, "get_lde_values on a coset shard: rows of other shards live on other GPUs");
+        NLC_CHECK(out || !count, "null argument");
+        if (!count) return;
+        DevBuf rows(ctx, count * b->W);
+        batch_gather_lde_rows(b, nullptr, i_start, count, step, rows.p);
+        d2h(ctx, out, rows.p, count * b->W * sizeof(u64));
         sync(ctx);
     });
 }
@@ -876,7 +985,8 @@ int nlc_fri_params_constant_arity(nlc_fri_params* p, int degree_bits, int rate_b
     // FriReductionStrategy::ConstantArityBits: keep reducing while the result stays above the final
     // polynomial size and the round's tree still has at least 2^cap_height leaves
     int d = degree_bits;
-    while (d > final_poly_bits && d + rate_bits - arity_bits >= cap_height && p->n_reduction_rounds < 16) {
+    while (d > final_poly_bits && d + rate_bits - arity_bits >= cap_height) {
+        if (p->n_reduction_rounds == NLC_MAX_FRI_ROUNDS) return 1; // never hand back fewer rounds than plonky2 computes
         p->reduction_arity_bits[p->n_reduction_rounds++] = arity_bits;
         d -= arity_bits;
     }

@@ -43,9 +43,11 @@ void batch_lde_and_tree(nlc_batch* b);
 void batch_ifft_cols(nlc_batch* b, const u64* values_dev, size_t c0, size_t nc);
 void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc, const NttScatter* sc = nullptr);
 void batch_tree(nlc_batch* b);
-void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
-                          u64* out_dev);
-void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev);
+void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n_rows,
+                          u64* out_dev, size_t out_stride);
+void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, u64 i_start, size_t m, size_t step, u64* out_dev);
+// true when the two device arrays differ (one small kernel + a 4-byte D2H; synchronises the stream)
+bool device_words_differ(nlc_ctx* ctx, const u64* a_dev, const u64* b_dev, size_t words);
 void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
 // rows [row0, row0+n_rows) of the leaf matrix, row-major, into out_dev (n_rows x W): plonky2's merkle_tree.leaves
 void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);

@@ -17,12 +17,14 @@
 // after the index bit reversal coset k is the contiguous leaf range [bitrev_r(k)*n, +n).  So each
 // coset is one size-n NTT of coeff_j*(7 w_N^k)^j written straight into that range of every column: no zero
 // padding, no size-N transform, no transpose or bit-reversal pass.
+#include <algorithm>
+
 #include "batch.cuh"
 
 namespace {
 
 __global__ void k_transpose_cols(const u64* __restrict__ rows, size_t width, size_t col0, size_t n_cols, size_t n,
-                                 u64* __restrict__ out) {
+                                 u64* __restrict__ out, size_t out_stride) {
     __shared__ u64 tile[32][33];
     const size_t r0 = (size_t)blockIdx.x * 32, c0 = (size_t)blockIdx.y * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -32,7 +34,7 @@ __global__ void k_transpose_cols(const u64* __restrict__ rows, size_t width, siz
     __syncthreads();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         size_t c = c0 + i, r = r0 + threadIdx.x;
-        if (r < n && c < n_cols) out[c * n + r] = tile[threadIdx.x][i];
+        if (r < n && c < n_cols) out[c * out_stride + r] = tile[threadIdx.x][i];
     }
 }
 
@@ -68,10 +70,11 @@ __global__ void k_coset_points(u64 shift, u64 w, size_t size, u64* __restrict__ 
 }
 
 // out[i*W + j] = lde[j*N + bitrev_N(idx[i]*step)]
+// idx == nullptr: the arithmetic stripe idx[i] = i_start + i (get_lde_values_packed over a whole range, one launch)
 __global__ void k_gather_lde_rows(const u64* __restrict__ lde, size_t W, int log_N, const u64* __restrict__ idx,
-                                  size_t step, u64* __restrict__ out) {
+                                  u64 i_start, size_t step, u64* __restrict__ out) {
     const size_t i = blockIdx.x;
-    const u64 pt = (idx[i] * step) & (((u64)1 << log_N) - 1);
+    const u64 pt = ((idx ? idx[i] : i_start + i) * step) & (((u64)1 << log_N) - 1);
     const u64 row = log_N ? (__brevll(pt) >> (64 - log_N)) : 0;
     for (size_t j = threadIdx.x; j < W; j += blockDim.x) out[i * W + j] = lde[(j << log_N) + row];
 }
@@ -90,6 +93,13 @@ __global__ void k_leaf_rows(const u64* __restrict__ lde, size_t W, size_t N, siz
         size_t r = r0 + i, c = c0 + threadIdx.x;
         if (r < n_rows && c < W) out[r * W + c] = tile[threadIdx.x][i];
     }
+}
+
+__global__ void k_words_differ(const u64* __restrict__ a, const u64* __restrict__ b, size_t words, int* __restrict__ flag) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    int any = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += stride) any |= a[i] != b[i];
+    if (__syncthreads_or(any) && threadIdx.x == 0) atomicOr(flag, 1);
 }
 
 // One block per polynomial: sum_j c_j z^j over F_{p^2}.
@@ -232,16 +242,36 @@ void batch_ifft_cols(nlc_batch* b, const u64* values_dev, size_t c0, size_t nc) 
 }
 void batch_ifft_values(nlc_batch* b, const u64* values_dev) { batch_ifft_cols(b, values_dev, 0, b->W); }
 
-void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n,
-                          u64* out_dev) {
-    dim3 grid((unsigned)((n + 31) / 32), (unsigned)((n_cols + 31) / 32));
-    NLC_LAUNCH(ctx, k_transpose_cols, grid, dim3(32, 8), 0, rows_dev, width, col0, n_cols, n, out_dev);
+// rows_dev: n_rows x width row-major; columns [col0, col0 + n_cols) -> out_dev[c * out_stride + r]
+void transpose_trace_cols(nlc_ctx* ctx, const u64* rows_dev, size_t width, size_t col0, size_t n_cols, size_t n_rows,
+                          u64* out_dev, size_t out_stride) {
+    if (!n_rows || !n_cols) return;
+    dim3 grid((unsigned)((n_rows + 31) / 32), (unsigned)((n_cols + 31) / 32));
+    NLC_LAUNCH(ctx, k_transpose_cols, grid, dim3(32, 8), 0, rows_dev, width, col0, n_cols, n_rows, out_dev, out_stride);
 }
 
-void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, size_t m, size_t step, u64* out_dev) {
+void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, u64 i_start, size_t m, size_t step, u64* out_dev) {
     if (!m) return;
-    NLC_LAUNCH(b->ctx, k_gather_lde_rows, (unsigned)m, 128, 0, b->lde, b->W, b->log_n + b->rate_bits, idx_dev, step,
-               out_dev);
+    NLC_LAUNCH(b->ctx, k_gather_lde_rows, (unsigned)m, 128, 0, b->lde, b->W, b->log_n + b->rate_bits, idx_dev, i_start,
+               step, out_dev);
+}
+
+bool device_words_differ(nlc_ctx* ctx, const u64* a_dev, const u64* b_dev, size_t words) {
+    if (!words) return false;
+    int* flag = (int*)ctx->dmalloc(1);
+    int bad = 0;
+    try {
+        NLC_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
+        const unsigned grid = (unsigned)std::min<size_t>((words + 255) / 256, (size_t)ctx->sm_count * 8);
+        NLC_LAUNCH(ctx, k_words_differ, grid, 256, 0, a_dev, b_dev, words, flag);
+        NLC_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        NLC_CUDA(cudaStreamSynchronize(ctx->stream));
+    } catch (...) {
+        ctx->dfree(flag);
+        throw;
+    }
+    ctx->dfree(flag);
+    return bad != 0;
 }
 
 void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev) {

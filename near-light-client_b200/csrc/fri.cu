@@ -309,7 +309,7 @@ nlc_fri_state* fri_state_new(nlc_ctx* ctx, const nlc_fri_instance* inst, nlc_bat
     NLC_CHECK(n_oracles > 0 && inst && p, "prove_openings: no oracles");
     const int log_n = p->degree_bits, log_N = log_n + p->rate_bits;
     NLC_CHECK(log_n >= 0 && log_N <= 32, "degree_bits + rate_bits out of range");
-    NLC_CHECK(p->n_reduction_rounds >= 0 && p->n_reduction_rounds <= 16, "too many reduction rounds");
+    NLC_CHECK(p->n_reduction_rounds >= 0 && p->n_reduction_rounds <= NLC_MAX_FRI_ROUNDS, "too many reduction rounds");
     NLC_CHECK(total_arity(*p) <= log_n, "reduction arities exceed the degree");
     NLC_CHECK(p->num_query_rounds >= 0 && p->proof_of_work_bits >= 0 && p->proof_of_work_bits < 64, "bad FriConfig");
     for (int o = 0; o < n_oracles; o++) {

@@ -88,7 +88,11 @@ struct HostStager {
         char* dst;
         const char* src;
         size_t len;
+        size_t rows = 1, src_pitch = 0; // rows > 1: `rows` pieces of `len` bytes, src_pitch apart, packed at dst
     };
+    static void run_granule(const Granule& g) {
+        for (size_t r = 0; r < g.rows; r++) memcpy(g.dst + r * g.len, g.src + r * g.src_pitch, g.len);
+    }
     std::vector<Granule> pending;
     CopyPool* pool = nullptr;
 
@@ -132,7 +136,7 @@ struct HostStager {
     // flush slot[cur]: memcpy the pending granules in parallel, one async H2D, move to the next slot
     void flush(cudaStream_t stream) {
         if (fill == 0) return;
-        pool->parallel_for(pending.size(), [&](size_t i) { memcpy(pending[i].dst, pending[i].src, pending[i].len); });
+        pool->parallel_for(pending.size(), [&](size_t i) { run_granule(pending[i]); });
         pending.clear();
         if (cudaMemcpyAsync(dst_base, slot[cur], fill, cudaMemcpyHostToDevice, stream) != cudaSuccess)
             throw std::runtime_error("HostStager: cudaMemcpyAsync failed");
@@ -166,6 +170,39 @@ struct HostStager {
             d += take;
             s += take;
             bytes -= take;
+        }
+    }
+
+    // `n_rows` strips of `row_bytes` bytes, `src_pitch` apart in pageable memory (a column range of a row-major
+    // trace matrix), packed back to back at device address `dst`
+    void upload_rows(cudaStream_t stream, void* dst, const void* src, size_t src_pitch, size_t row_bytes, size_t n_rows) {
+        init();
+        char* d = (char*)dst;
+        const char* s = (const char*)src;
+        if (row_bytes == 0 || row_bytes > SLOT_BYTES) { // degenerate shapes: row by row
+            for (size_t r = 0; r < n_rows; r++) upload(stream, d + r * row_bytes, s + r * src_pitch, row_bytes);
+            return;
+        }
+        const size_t rows_per_granule = GRANULE / row_bytes ? GRANULE / row_bytes : 1;
+        while (n_rows) {
+            if (fill && (dst_base + fill != d || SLOT_BYTES - fill < row_bytes)) flush(stream);
+            if (fill == 0) {
+                if (busy[cur]) {
+                    cudaEventSynchronize(ev[cur]);
+                    busy[cur] = false;
+                }
+                dst_base = d;
+            }
+            size_t take = (SLOT_BYTES - fill) / row_bytes;
+            if (take > n_rows) take = n_rows;
+            for (size_t o = 0; o < take; o += rows_per_granule) {
+                const size_t k = take - o < rows_per_granule ? take - o : rows_per_granule;
+                pending.push_back({(char*)slot[cur] + fill + o * row_bytes, s + o * src_pitch, row_bytes, k, src_pitch});
+            }
+            fill += take * row_bytes;
+            d += take * row_bytes;
+            s += take * src_pitch;
+            n_rows -= take;
         }
     }
 
@@ -214,7 +251,7 @@ struct HostStager {
                 seg_off += take;
                 if (seg_off == g.len) seg_i++, seg_off = 0;
             }
-            pool->parallel_for(pending.size(), [&](size_t i) { memcpy(pending[i].dst, pending[i].src, pending[i].len); });
+            pool->parallel_for(pending.size(), [&](size_t i) { run_granule(pending[i]); });
             pending.clear();
             drained += len_of[tail];
             tail = (tail + 1) % N_SLOTS;

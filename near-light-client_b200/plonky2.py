@@ -65,6 +65,19 @@ class Context:
     def synchronize(self):
         self._check(_ffi.lib().nlc_synchronize(self._h))
 
+    def wait_stream(self, producer_stream: int | None = None):
+        """Order the context's (non-blocking) stream after everything enqueued so far on `producer_stream`
+        (a cudaStream_t as int; 0 / None = the legacy default stream).  See the *_dev contract in nlc_commit.h."""
+        self._check(_ffi.lib().nlc_wait_stream(self._h, vp(producer_stream or 0)))
+
+    def wait_torch(self):
+        """wait_stream on torch's current stream of this device, if torch has been imported and CUDA is up: the
+        device-pointer entry points take buffers a torch op may still be producing on another stream."""
+        import sys
+        torch = sys.modules.get("torch")
+        if torch is not None and torch.cuda.is_available() and torch.cuda.is_initialized():
+            self.wait_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
     def launch_count(self) -> int:
         return int(_ffi.lib().nlc_launch_count(self._h))
 
@@ -470,7 +483,7 @@ class FriConfig:
                                                       self.reduction_strategy.arity_bits,
                                                       self.reduction_strategy.final_poly_bits)
         if rc:
-            raise NlcError("bad FriConfig")
+            raise NlcError("bad FriConfig (arity_bits in 1..8; at most 32 reduction rounds)")
         return FriParams(self, hiding, degree_bits, [p.reduction_arity_bits[i] for i in range(p.n_reduction_rounds)])
 
 
@@ -661,6 +674,7 @@ class PolynomialBatch:
         log_n = _log2_strict(n)
         coeffs = torch.empty((nc, n), dtype=torch.int64, device=src.device)
         lde = torch.empty((nc, n << rate_bits), dtype=torch.int64, device=src.device)
+        ctx.wait_torch()  # `src` may still be in flight on torch's stream
         ctx._check(_ffi.lib().nlc_lde_columns_dev(ctx._h, vp(src.data_ptr()), nc, log_n, rate_bits, int(is_values),
                                                   vp(coeffs.data_ptr()), vp(lde.data_ptr())))
         return coeffs, lde
@@ -682,6 +696,7 @@ class PolynomialBatch:
             send = torch.empty((n_shards, nc, per), dtype=torch.int64, device=src.device)
         else:
             table = (vp * n_shards)(*[vp(p) for p in peer_ptrs])
+        ctx.wait_torch()
         ctx._check(_ffi.lib().nlc_lde_columns_scatter_dev(
             ctx._h, vp(src.data_ptr()), nc, log_n, rate_bits, int(is_values), vp(coeffs.data_ptr()),
             vp(send.data_ptr()) if send is not None else None, n_shards, table, col0))
@@ -702,6 +717,7 @@ class PolynomialBatch:
                 raise NlcError("rows must be a contiguous (W, N / n_shards) tensor")
             ptr = rows.data_ptr()
         h = vp()
+        ctx.wait_torch()
         ctx._check(_ffi.lib().nlc_commit_from_lde_rows_dev(ctx._h, vp(ptr), W, degree_log, rate_bits,
                                                            cap_height, shard_idx, n_shards, C.byref(h)))
         b = cls(ctx, h, W, degree_log, rate_bits, cap_height)
@@ -765,12 +781,35 @@ class PolynomialBatch:
     @classmethod
     def from_device(cls, dev_ptr: int, n_polys: int, degree_log: int, rate_bits: int, cap_height: int,
                     is_values: bool = True, ctx=None):
-        """Input already in HBM as an n_polys x n column-major matrix (asynchronous: no host sync)."""
+        """Input already in HBM as an n_polys x n column-major matrix (asynchronous: no host sync).  The commit is
+        ordered after torch's current stream (Context.wait_torch); the caller keeps the buffer alive until a
+        synchronising accessor (merkle_tree.cap, ...) or ctx.synchronize() has returned."""
         ctx = ctx or default_context()
+        ctx.wait_torch()
         h = vp()
         fn = _ffi.lib().nlc_commit_from_values_dev if is_values else _ffi.lib().nlc_commit_from_coeffs_dev
         ctx._check(fn(ctx._h, vp(dev_ptr), n_polys, degree_log, rate_bits, cap_height, C.byref(h)))
         return cls(ctx, h, n_polys, degree_log, rate_bits, cap_height)
+
+    @classmethod
+    def import_serialized(cls, polynomials, rate_bits: int, cap_height: int, cap=None, digests=None, ctx=None):
+        """A PolynomialBatch deserialised from circuit data (constants_sigmas_commitment of
+        /root/reference/scripts/build-circuit.sh:10-18): the LDE and the tree are recomputed on the GPU from
+        `polynomials`; `cap` / `digests` (the serialised merkle_tree fields), when given, must match or this raises."""
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(polynomials)
+        log_n = _log2_strict(n)
+        cap_a = None if cap is None else _a(cap).reshape(-1)
+        dig_a = None if digests is None else _a(digests).reshape(-1)
+        if cap_a is not None and cap_a.size != 4 << cap_height:
+            raise NlcError("serialised cap has the wrong size")
+        if dig_a is not None and dig_a.size != 8 * ((n << rate_bits) - (1 << cap_height)):
+            raise NlcError("serialised digests have the wrong size")
+        h = vp()
+        ctx._check(_ffi.lib().nlc_batch_import(ctx._h, table, len(arrs), log_n, rate_bits, cap_height,
+                                               None if cap_a is None else _p(cap_a),
+                                               None if dig_a is None else _p(dig_a), C.byref(h)))
+        return cls(ctx, h, len(arrs), log_n, rate_bits, cap_height)
 
     @classmethod
     def from_trace_rows(cls, rows, col0: int, n_cols: int, rate_bits: int, cap_height: int, ctx=None):
@@ -832,9 +871,15 @@ class PolynomialBatch:
         self._ctx._check(_ffi.lib().nlc_batch_lde_rows(self._h, _p(idx), idx.size, step, _p(out)))
         return out
 
+    def get_lde_rows_range(self, index_start: int, count: int, step: int = 1) -> np.ndarray:
+        """get_lde_values(i, step) for i = index_start .. index_start + count - 1 in one launch and one D2H."""
+        out = np.zeros((count, self.n_polys), np.uint64)
+        self._ctx._check(_ffi.lib().nlc_batch_lde_rows_range(self._h, index_start, count, step, _p(out)))
+        return out
+
     def get_lde_values_packed(self, index_start: int, step: int, width: int = 1) -> np.ndarray:
         """P::WIDTH consecutive rows, transposed to n_polys x width like PackedField::from_slice per poly."""
-        return self.get_lde_rows(np.arange(index_start, index_start + width), step).T.copy()
+        return self.get_lde_rows_range(index_start, width, step).T.copy()
 
     def eval_at(self, z) -> np.ndarray:
         """Every polynomial at the extension point z -> (n_polys, 2) (StarkOpeningSet::new, proof.rs:307-310)."""

@@ -101,6 +101,81 @@ def test_from_trace_rows(P2, O, rng):
     check_batch(b, ref)
 
 
+@pytest.mark.parametrize("pinned", [False, True])
+def test_from_trace_rows_strip_chunks(P2, O, rng, pinned):
+    """Only the column strip crosses PCIe, in row chunks (32 MiB) overlapped with the transpose: several chunks, a
+    ragged last one is impossible (powers of two) but strip != width and col0 != 0 are; pageable and pinned hosts."""
+    import torch
+    n, width, col0, nc = 1 << 16, 150, 7, 130  # 130 cols * 8 B -> 32 256 rows per chunk -> 3 chunks
+    trace = O.random_field(rng, (n, width))
+    host = trace
+    if pinned:
+        t = torch.empty((n, width), dtype=torch.int64).pin_memory()
+        t.numpy().view(np.uint64)[:] = trace
+        host = t.numpy().view(np.uint64)
+    b = P2.PolynomialBatch.from_trace_rows(host, col0, nc, 1, 4)
+    ref = O.commit_from_values(np.ascontiguousarray(trace[:, col0:col0 + nc].T), 1, 4)
+    assert np.array_equal(b.merkle_tree.cap, ref.cap)
+    assert np.array_equal(b.coeff_matrix, ref.coeffs)
+    assert np.array_equal(b.merkle_tree.digests, ref.digests)
+
+
+def test_import_serialized(P2, pkg, O, rng):
+    """SURVEY.md section 5 checkpoint row: a deserialised PolynomialBatch (coefficients + cap [+ digests]) comes back
+    onto the GPU by recommitting; a wrong cap or digest fails loudly."""
+    W, log_n, r, cap = 21, 10, 3, 4
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, r, cap)
+    b = P2.PolynomialBatch.import_serialized(list(ref.coeffs), r, cap, cap=ref.cap, digests=ref.digests)
+    check_batch(b, ref)
+    b2 = P2.PolynomialBatch.import_serialized(list(ref.coeffs), r, cap)  # nothing to verify against: still the same batch
+    assert np.array_equal(b2.merkle_tree.cap, ref.cap)
+    bad_cap = ref.cap.copy()
+    bad_cap[3, 1] ^= np.uint64(1)
+    with pytest.raises(pkg.NlcError, match="MerkleCap recomputed"):
+        P2.PolynomialBatch.import_serialized(list(ref.coeffs), r, cap, cap=bad_cap)
+    bad_dig = ref.digests.copy()
+    bad_dig[-1, 0] ^= np.uint64(1)
+    with pytest.raises(pkg.NlcError, match="digests recomputed"):
+        P2.PolynomialBatch.import_serialized(list(ref.coeffs), r, cap, cap=ref.cap, digests=bad_dig)
+    with pytest.raises(pkg.NlcError, match="wrong size"):
+        P2.PolynomialBatch.import_serialized(list(ref.coeffs), r, cap, cap=ref.cap[:8])
+
+
+def test_lde_rows_range(P2, O, rng):
+    """nlc_batch_lde_rows_range: a whole stripe of get_lde_values(i, step) in one launch + one D2H."""
+    W, log_n, r, cap = 13, 9, 2, 3
+    values = O.random_field(rng, (W, 1 << log_n))
+    b = P2.PolynomialBatch.from_values(list(values), r, False, cap)
+    ref = O.commit_from_values(values, r, cap)
+    N, log_N = 1 << (log_n + r), log_n + r
+    br = lambda x: int(format(x, f"0{log_N}b")[::-1], 2)
+    for i0, count, step in [(0, N, 1), (5, 100, 2), (N - 3, 9, 4), (17, 1, 1)]:  # wraps mod N like the reference
+        got = b.get_lde_rows_range(i0, count, step)
+        want = np.stack([ref.leaves[br(((i0 + k) * step) % N)] for k in range(count)])
+        assert np.array_equal(got, want)
+    assert b.get_lde_rows_range(0, 0, 1).shape == (0, W)
+
+
+def test_from_device_orders_after_the_producer_stream(P2, O, rng):
+    """a tensor produced on torch's default stream must not race with the commit on the context's own
+    (non-blocking) stream -- from_device waits on the producer (nlc_wait_stream)."""
+    import torch
+    W, log_n, r, cap = 64, 14, 1, 4
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, r, cap)
+    ctx = P2.default_context()
+    src = torch.from_numpy(values.view(np.int64)).pin_memory()
+    for _ in range(3):
+        spin = torch.empty(64 << 20, dtype=torch.int64, device="cuda")
+        for _k in range(8):
+            spin.add_(1)  # keep the default stream busy so the copy below is genuinely late
+        dev = src.to("cuda", non_blocking=True)
+        b = P2.PolynomialBatch.from_device(dev.data_ptr(), W, log_n, r, cap, ctx=ctx)
+        assert np.array_equal(b.merkle_tree.cap, ref.cap)
+        b.free()
+
+
 def test_errors(P2, pkg, O, rng):
     v = O.random_field(rng, (2, 16))
     with pytest.raises(pkg.NlcError):
@@ -124,3 +199,17 @@ def test_golden_fixtures(P2):
         assert np.array_equal(b.merkle_tree.cap, g[key + ":cap"])
         assert np.array_equal(b.get_lde_rows([0, 1, 5], 1), g[key + ":lde_rows"])
         assert np.array_equal(b.coeff_matrix[:, :4], g[key + ":coeffs_head"])
+
+
+def test_nlc_device_env(P2, pkg, monkeypatch):
+    """nlc_init(device < 0) honours NLC_DEVICE: the GPU is chosen without touching the caller."""
+    monkeypatch.setenv("NLC_DEVICE", "0")
+    c = P2.Context(-1)
+    assert c.device == 0
+    c.close()
+    monkeypatch.setenv("NLC_DEVICE", "4096")
+    with pytest.raises(pkg.NlcError, match="device index out of range"):
+        P2.Context(-1)
+    monkeypatch.setenv("NLC_DEVICE", "gpu0")
+    with pytest.raises(pkg.NlcError, match="NLC_DEVICE"):
+        P2.Context(-1)

@@ -1,6 +1,9 @@
-"""BASELINE.json's full sizes: configs[1] bit-exact against the oracle, configs[3] through size-independent
-properties (LDE = polynomial evaluation on the coset, Merkle paths verify to the cap, iFFT . FFT = id), and the
-pageable-host staging path (csrc/staging.h) against pinned host memory.
+"""BASELINE.json's full sizes, bit-exact against the oracle: configs[1] (2^16 x 135, rate_bits 3), configs[3]
+(2^20 x 400, rate_bits 1) and the AIR trace shapes that are in the reference tree (ed25519 2^16 x 2502,
+vendor/starkyx/starkyx/src/machine/ec/builder.rs:301-303; SHA-256 2^17 x 912, machine/hash/sha/sha256/air.rs:221-222),
+for BOTH the resident path (one k_leaf_hash launch) and the host-fed path (chunked upload + k_leaf_absorb).
+configs[3] additionally through size-independent properties (LDE = polynomial evaluation on the coset, Merkle paths
+verify to the cap, iFFT . FFT = id), and the pageable-host staging path (csrc/staging.h) against pinned host memory.
 """
 import numpy as np
 import pytest
@@ -28,6 +31,54 @@ def test_config2_full_commit_bit_exact(P2, O):
     rows = np.array([0, 1, 2, 12345, N // 2, N - 2, N - 1])
     got = b.get_lde_rows([bitrev(int(i), log_n + r) for i in rows], 1)  # get_lde_values(i) = leaves[bitrev(i)]
     assert np.array_equal(got, ref.leaves[rows])
+
+
+FULL_SHAPES = {
+    # id: (W, log_n, rate_bits, cap_height)
+    "config4_2^20x400_r1": (400, 20, 1, 4),        # BASELINE.json configs[3]
+    "ed25519_2^16x2502_r1": (2502, 16, 1, 4),      # machine/ec/builder.rs:301-303 (EXTENDED_COLUMNS)
+    "sha256_2^17x912_r1": (912, 17, 1, 4),         # machine/hash/sha/sha256/air.rs:221-222
+}
+
+
+@pytest.mark.parametrize("shape", sorted(FULL_SHAPES))
+def test_fullsize_commit_bit_exact(P2, O, shape):
+    """Whole-commit parity at the sizes BASELINE.json / the in-tree AIRs name: the full cap, every digest, the
+    whole coefficient matrix and 2048 random leaf rows (+ the corners) against the oracle, for the resident
+    (nlc_commit_from_values_dev: one leaf-hash launch) and the host-fed (nlc_commit_from_values: column chunks,
+    k_leaf_absorb) paths."""
+    import os
+
+    import torch
+    W, log_n, r, cap = FULL_SHAPES[shape]
+    n, log_N = 1 << log_n, log_n + r
+    N = 1 << log_N
+    rng = np.random.default_rng(0xC0FFEE + 3 + W)
+    values = O.random_field(rng, (W, n))
+    O.set_threads(len(os.sched_getaffinity(0)))
+    ref = O.commit_from_values(values, r, cap)
+    rows = np.unique(np.concatenate([rng.integers(0, N, size=2048), [0, 1, N // 2 - 1, N // 2, N - 2, N - 1]]))
+    pts = [bitrev(int(k), log_N) for k in rows]  # get_lde_values(i) = leaves[bitrev(i)]
+    want_rows = ref.leaves[rows]
+
+    def check(b, what):
+        assert np.array_equal(b.merkle_tree.cap, ref.cap), (shape, what, "cap")
+        assert np.array_equal(b.merkle_tree.digests, ref.digests), (shape, what, "digests")
+        got = b.get_lde_rows(pts, 1)
+        assert np.array_equal(got, want_rows), (shape, what, "leaf rows")
+        cm = b.coeff_matrix
+        assert np.array_equal(cm, ref.coeffs), (shape, what, "coefficients")
+        b.free()
+
+    # host-fed: W separate pageable host vectors in, like Vec<PolynomialValues>
+    check(P2.PolynomialBatch.from_values(list(values), r, False, cap), "host-fed")
+    # resident: the same matrix already in HBM
+    dev = torch.from_numpy(values.view(np.int64)).cuda()
+    ctx = P2.default_context()
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    check(P2.PolynomialBatch.from_device(dev.data_ptr(), W, log_n, r, cap, ctx=ctx), "resident")
+    del dev
 
 
 def test_config4_properties(P2, O):
