@@ -209,6 +209,61 @@ int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_ch
                             int quotient_degree_bits, size_t quotient_degree_factor, int divide_by_zh, int rate_bits,
                             int cap_height, nlc_batch** out);
 
+/* ---- "next" row SURVEY.md 8f.3: AIR constraint evaluation on the device -------------------------------------- */
+/* Replaces the evaluation loop of starkyx's quotient_polys (vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:306-352):
+ * per point of the quotient domain, local/next rows from every trace commitment (get_lde_values_packed,
+ * prover.rs:289-294), `stark.air().eval(&mut parser)` (prover.rs:334) into a ConstraintConsumer
+ * (plonky2/parser/consumer.rs:54-78).  The AIR is handed over as a straight-line BYTECODE that the caller obtains by
+ * running its `air.eval` once against a RECORDING AirParser (air/parser.rs: Var = virtual register id; the way
+ * RecursiveStarkParser, plonky2/parser/mod.rs:30-38, records a circuit): any AIR written against the AirParser trait --
+ * Chip<L> constraint lists (chip/mod.rs:58-66), ArithmeticConstraint (chip/arithmetic/mod.rs:13-50), the field
+ * instructions (chip/field/add.rs, mul.rs, ...) -- compiles unchanged.  One instruction = 4 x uint32 {op, dst, a, b}: */
+#define NLC_AIR_LOCAL 0                  /* dst = local_slice()[a]      (a indexes the columns of all trace commitments, concatenated) */
+#define NLC_AIR_NEXT 1                   /* dst = next_slice()[a] */
+#define NLC_AIR_PUBLIC 2                 /* dst = public_slice()[a] */
+#define NLC_AIR_GLOBAL 3                 /* dst = global_slice()[a] */
+#define NLC_AIR_CHALLENGE 4              /* dst = challenge_slice()[a] */
+#define NLC_AIR_CONST 5                  /* dst = constant(pool[a]) */
+#define NLC_AIR_ADD 6                    /* dst = add(reg a, reg b) */
+#define NLC_AIR_SUB 7
+#define NLC_AIR_MUL 8
+#define NLC_AIR_NEG 9                    /* dst = neg(reg a) */
+#define NLC_AIR_MUL_CONST 10             /* dst = mul_const(reg a, pool[b]) */
+#define NLC_AIR_ADD_CONST 11
+#define NLC_AIR_SUB_CONST 12
+#define NLC_AIR_CONSTRAINT 13            /* constraint(reg a) */
+#define NLC_AIR_CONSTRAINT_TRANSITION 14 /* constraint_transition(reg a): * z_last = x - g^(n-1) */
+#define NLC_AIR_CONSTRAINT_FIRST_ROW 15  /* constraint_first_row(reg a): * lagrange_basis_first */
+#define NLC_AIR_CONSTRAINT_LAST_ROW 16   /* constraint_last_row(reg a):  * lagrange_basis_last */
+typedef struct {
+    const uint32_t* code; /* n_ops x 4 */
+    uint32_t n_ops;
+    uint32_t n_regs;      /* virtual registers (a register is written before it is read; registers may be reused) */
+    const uint64_t* pool; /* n_pool 64-bit field constants */
+    uint32_t n_pool;
+    uint32_t n_public;    /* lengths of the public / global / challenge slices the program may index */
+    uint32_t n_global;
+    uint32_t n_challenge;
+} nlc_air_program;
+/* constraint_accs of every point, NOT yet multiplied by 1/Z_H: evals_out_dev = size x n_alphas row-major in the natural
+ * order of the quotient domain (size = n << quotient_degree_bits) -- exactly what nlc_quotient_commit_dev takes with
+ * divide_by_zh = 1.  trace_data: the commitments whose LDE rows are concatenated into local/next vars (prover.rs:289-294);
+ * all must share degree and rate_bits.  alphas: config.num_challenges values (prover.rs:262), at most 8.  Asynchronous
+ * (see the *_dev contract above); nlc_air_eval is the same with the accumulators copied to the host. */
+int nlc_air_eval_dev(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                     const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                     const uint64_t* alphas, size_t n_alphas, int quotient_degree_bits, uint64_t* evals_out_dev);
+int nlc_air_eval(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                 const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                 const uint64_t* alphas, size_t n_alphas, int quotient_degree_bits, uint64_t* evals_out);
+/* quotient_polys + the quotient commitment (prover.rs:144-178) without a host round trip: evaluate the AIR, scale by
+ * 1/Z_H, per-alpha coset_ifft(F::coset_shift()), trim_to_len / chunks(degree), PolynomialBatch::from_coeffs(chunks,
+ * rate_bits, false, cap_height).  quotient_degree_factor = stark.air().quotient_degree_factor(). */
+int nlc_stark_quotient_commit(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                              const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                              const uint64_t* alphas, size_t n_alphas, size_t quotient_degree_factor, int cap_height,
+                              nlc_batch** out);
+
 /* ---- a4: Poseidon (plonky2::hash::{poseidon,hashing}) -------------------------------------- */
 /* PoseidonPermutation::permute on `count` independent 12-lane states (in place). */
 int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count);

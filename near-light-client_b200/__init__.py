@@ -8,3 +8,4 @@ from . import _ffi  # noqa: F401
 from ._ffi import NlcError  # noqa: F401
 from . import plonky2  # noqa: F401
 from . import sharding  # noqa: F401
+from . import starky  # noqa: F401

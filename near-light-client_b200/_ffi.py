@@ -35,6 +35,11 @@ class CFriParams(C.Structure):
                 ("reduction_arity_bits", C.c_int * 32)]  # NLC_MAX_FRI_ROUNDS
 
 
+class CAirProgram(C.Structure):
+    _fields_ = [("code", u32p), ("n_ops", C.c_uint32), ("n_regs", C.c_uint32), ("pool", u64p), ("n_pool", C.c_uint32),
+                ("n_public", C.c_uint32), ("n_global", C.c_uint32), ("n_challenge", C.c_uint32)]
+
+
 class CFriInstance(C.Structure):
     _fields_ = [("n_batches", C.c_int), ("points", u64p), ("batch_offsets", u32p), ("poly_oracle", u32p),
                 ("poly_index", u32p)]
@@ -77,6 +82,12 @@ SIGNATURES = {
                                       C.POINTER(vp)]),
     "nlc_quotient_commit_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int,
                                           C.c_int, C.POINTER(vp)]),
+    "nlc_air_eval_dev": (C.c_int, [vp, C.POINTER(CAirProgram), C.POINTER(vp), C.c_int, u64p, u64p, u64p, u64p, C.c_size_t,
+                                   C.c_int, vp]),
+    "nlc_air_eval": (C.c_int, [vp, C.POINTER(CAirProgram), C.POINTER(vp), C.c_int, u64p, u64p, u64p, u64p, C.c_size_t,
+                               C.c_int, u64p]),
+    "nlc_stark_quotient_commit": (C.c_int, [vp, C.POINTER(CAirProgram), C.POINTER(vp), C.c_int, u64p, u64p, u64p, u64p,
+                                            C.c_size_t, C.c_size_t, C.c_int, C.POINTER(vp)]),
     "nlc_batch_free": (None, [vp]),
     "nlc_batch_info": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nlc_batch_cap": (C.c_int, [vp, u64p]),

@@ -723,6 +723,12 @@ int nlc_lde_onto_coset(nlc_ctx* ctx, const uint64_t* in, uint64_t* out, size_t n
 }
 
 // ---- quotient_polys without the AIR evaluation (prover.rs:253-358, 158-178) ----
+static void quotient_check(size_t n_ch, int log_n, int qdb, size_t qdf, int rate_bits) {
+    NLC_CHECK(n_ch > 0, "no challenges");
+    NLC_CHECK(log_n >= 0 && qdb >= 0 && log_n + qdb <= 32, "log_n + quotient_degree_bits out of range");
+    NLC_CHECK(qdb <= rate_bits, "Having constraints of degree higher than the rate is not supported yet.");
+    NLC_CHECK(qdf >= 1 && qdf <= ((size_t)1 << qdb), "quotient_degree_factor exceeds 2^quotient_degree_bits");
+}
 int nlc_quotient_domain(nlc_ctx* ctx, int log_n, int quotient_degree_bits, uint64_t* coset_x, uint64_t* lagrange_first,
                         uint64_t* lagrange_last, uint64_t* zh_inv) {
     if (!ctx) return 1;
@@ -778,12 +784,6 @@ int nlc_quotient_domain(nlc_ctx* ctx, int log_n, int quotient_degree_bits, uint6
     });
 }
 
-static void quotient_check(size_t n_ch, int log_n, int qdb, size_t qdf, int rate_bits) {
-    NLC_CHECK(n_ch > 0, "no challenges");
-    NLC_CHECK(log_n >= 0 && qdb >= 0 && log_n + qdb <= 32, "log_n + quotient_degree_bits out of range");
-    NLC_CHECK(qdb <= rate_bits, "Having constraints of degree higher than the rate is not supported yet.");
-    NLC_CHECK(qdf >= 1 && qdf <= ((size_t)1 << qdb), "quotient_degree_factor exceeds 2^quotient_degree_bits");
-}
 int nlc_quotient_commit(nlc_ctx* ctx, const uint64_t* evals, size_t n_challenges, int log_n, int quotient_degree_bits,
                         size_t quotient_degree_factor, int divide_by_zh, int rate_bits, int cap_height,
                         nlc_batch** out) {
@@ -812,6 +812,54 @@ int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_ch
         quotient_check(n_challenges, log_n, quotient_degree_bits, quotient_degree_factor, rate_bits);
         *out = quotient_commit_dev(ctx, evals_dev, n_challenges, log_n, quotient_degree_bits, quotient_degree_factor,
                                    divide_by_zh != 0, rate_bits, cap_height);
+    });
+}
+
+// ---- AIR evaluation on the device (prover.rs:306-352) ----
+int nlc_air_eval_dev(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                     const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                     const uint64_t* alphas, size_t n_alphas, int quotient_degree_bits, uint64_t* evals_out_dev) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(evals_out_dev != nullptr, "null argument");
+        air_eval_dev(ctx, air, trace_data, n_trace_data, public_inputs, global_values, challenges, alphas, n_alphas,
+                     quotient_degree_bits, evals_out_dev);
+    });
+}
+int nlc_air_eval(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                 const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                 const uint64_t* alphas, size_t n_alphas, int quotient_degree_bits, uint64_t* evals_out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(evals_out && trace_data && n_trace_data > 0 && trace_data[0], "null argument");
+        NLC_CHECK(quotient_degree_bits >= 0 && quotient_degree_bits <= 32, "quotient_degree_bits out of range");
+        const size_t words = n_alphas << (trace_data[0]->log_n + quotient_degree_bits);
+        DevBuf ev(ctx, words);
+        air_eval_dev(ctx, air, trace_data, n_trace_data, public_inputs, global_values, challenges, alphas, n_alphas,
+                     quotient_degree_bits, ev.p);
+        d2h(ctx, evals_out, ev.p, words * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_stark_quotient_commit(nlc_ctx* ctx, const nlc_air_program* air, nlc_batch* const* trace_data, int n_trace_data,
+                              const uint64_t* public_inputs, const uint64_t* global_values, const uint64_t* challenges,
+                              const uint64_t* alphas, size_t n_alphas, size_t quotient_degree_factor, int cap_height,
+                              nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && trace_data && n_trace_data > 0 && trace_data[0], "null argument");
+        *out = nullptr;
+        int qdb = 0;
+        while (((size_t)1 << qdb) < quotient_degree_factor) qdb++; // log2_ceil (prover.rs:266)
+        const int log_n = trace_data[0]->log_n, rate_bits = trace_data[0]->rate_bits;
+        quotient_check(n_alphas, log_n, qdb, quotient_degree_factor, rate_bits);
+        DevBuf ev(ctx, n_alphas << (log_n + qdb));
+        air_eval_dev(ctx, air, trace_data, n_trace_data, public_inputs, global_values, challenges, alphas, n_alphas, qdb, ev.p);
+        *out = quotient_commit_dev(ctx, ev.p, n_alphas, log_n, qdb, quotient_degree_factor, true, rate_bits, cap_height);
+        sync(ctx);
     });
 }
 

@@ -63,6 +63,11 @@ void coset_points(nlc_ctx* ctx, int log_size, u64* out_dev);
 nlc_batch* quotient_commit_dev(nlc_ctx* ctx, const u64* evals_dev, size_t n_ch, int log_n, int qdb, size_t qdf,
                                bool divide_by_zh, int rate_bits, int cap_height);
 
+// ---- air.cu ----
+void quotient_tables_dev(nlc_ctx* ctx, int log_n, int qdb, const u64** x, const u64** lf, const u64** ll);
+void air_eval_dev(nlc_ctx* ctx, const nlc_air_program* prog, nlc_batch* const* batches, int n_batches, const u64* publics,
+                  const u64* globals, const u64* challenges, const u64* alphas, size_t n_alphas, int qdb, u64* out_dev);
+
 // ---- fri.cu ----
 void challenger_observe_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, const u64* elems_dev, size_t n);
 void challenger_get_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, size_t n, u64* out_dev);

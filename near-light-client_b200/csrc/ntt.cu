@@ -34,12 +34,12 @@ __global__ void k_pow_table(u64* out, size_t n, u64 base, u64 scale) {
     if (i < n) out[i] = gl::mul(scale, gl::pow(base, i));
 }
 // tw[pos << L | i_low] = root^(bitrev_S(pos) * i_low), root = w_{2^m}^{+-1}
-__global__ void k_tw_table(u64* out, int m, int S, u64 root) {
+__global__ void k_tw_table(u64* out, int m, int S, u64 root, u64 scale) {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= ((size_t)1 << m)) return;
     const int L = m - S;
     u64 pos = i >> L, low = i & (((u64)1 << L) - 1);
-    out[i] = gl::pow(root, (u64)brev((u32)pos, S) * low);
+    out[i] = gl::mul(scale, gl::pow(root, (u64)brev((u32)pos, S) * low));
 }
 
 // ---- the 2^S-point transform of a tile held in shared memory ---------------------------------------------
@@ -238,6 +238,162 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fast path (digits of 4..8 bits = two register steps R1 + R2, 4096-element tiles, 256 threads).  Same pass
+// structure and the same HBM layouts as the generic kernels above, but every index is a compile-time constant plus
+// one per-thread base, and the data makes ONE shared-memory round trip per pass instead of three:
+//   hi: global -> registers (the first register step works on exactly the elements a thread gathers: tile index
+//       tau + k * TASKS) -> twiddle -> shared -> registers (second step) -> inter-digit twiddle -> global;
+//   lo: global -> registers -> twiddle -> shared -> registers -> shared (in place: a thread owns its 2^R2 slots)
+//       -> coalesced global stores.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr u32 F_TILE_LOG = 12, F_TILE = 1u << F_TILE_LOG;
+
+template <int R>
+__device__ __forceinline__ constexpr u32 brev_c(u32 k) {
+    u32 r = 0;
+    for (int i = 0; i < R; i++) r |= ((k >> i) & 1u) << (R - 1 - i);
+    return r;
+}
+
+template <int R1, int R2, bool INV>
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
+k_ntt_hi_f(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, size_t dst_stride, int m,
+           const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots, int canon_in) {
+    constexpr int S = R1 + R2, LOG_T = F_TILE_LOG - S;
+    constexpr u32 T = 1u << LOG_T, TASKS1 = F_TILE >> R1, TASKS2 = F_TILE >> R2;
+    extern __shared__ u64 sm[]; // [2^S][T], t fastest
+    const int L = m - S;
+    const size_t tile = blockIdx.x;
+    const size_t base = (tile >> (L - LOG_T)) << m;
+    const u32 low0 = ((u32)tile & ((1u << (L - LOG_T)) - 1)) << LOG_T;
+    const u64* s = src + blockIdx.y * src_stride + base + low0;
+    u64* d = dst + blockIdx.y * dst_stride + base + low0;
+    const u64* pr = pre ? pre + base + low0 : nullptr;
+    const u64* twp = tw + low0;
+    const size_t kstride = (size_t)1 << (L + R2);
+
+#pragma unroll
+    for (u32 j = 0; j < TASKS1 / NTT_THREADS; j++) {
+        const u32 tau = threadIdx.x + j * NTT_THREADS;
+        const u32 t = tau & (T - 1), b = tau >> LOG_T; // b < 2^R2
+        const size_t off0 = ((size_t)b << L) + t;
+        u64 v[1 << R1];
+#pragma unroll
+        for (int k = 0; k < (1 << R1); k++) v[k] = s[off0 + k * kstride];
+        if (pr) {
+#pragma unroll
+            for (int k = 0; k < (1 << R1); k++) v[k] = gl::mul(v[k], __ldg(pr + off0 + k * kstride));
+        } else if (canon_in) { // caller data may be any representative; later passes read their own canonical output
+#pragma unroll
+            for (int k = 0; k < (1 << R1); k++) v[k] = gl::dcanon(v[k]);
+        }
+        dft_regs<R1, INV>(v);
+#pragma unroll
+        for (int k = 1; k < (1 << R1); k++) v[k] = gl::mul(v[k], __ldg(roots + b * brev_c<R1>(k)));
+#pragma unroll
+        for (int k = 0; k < (1 << R1); k++) sm[tau + k * TASKS1] = v[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (u32 j = 0; j < TASKS2 / NTT_THREADS; j++) {
+        const u32 tau = threadIdx.x + j * NTT_THREADS;
+        const u32 t = tau & (T - 1), p = tau >> LOG_T; // p < 2^R1: which sub-problem
+        const u32 i0 = (p << (R2 + LOG_T)) + t;
+        u64 v[1 << R2];
+#pragma unroll
+        for (int k = 0; k < (1 << R2); k++) v[k] = sm[i0 + (k << LOG_T)];
+        dft_regs<R2, INV>(v);
+        const size_t off0 = ((size_t)(p << R2) << L) + t;
+        const size_t pstride = (size_t)1 << L;
+#pragma unroll
+        for (int k = 0; k < (1 << R2); k++) d[off0 + k * pstride] = gl::mul(v[k], __ldg(twp + off0 + k * pstride));
+    }
+}
+
+// lo-pass shared layout: transform g at sm[g * pitch + pidx(e)], two pad words per 16 (keeps 16-byte alignment of
+// every 16-element run and makes both the strided and the contiguous register steps conflict-free)
+template <int S>
+struct LoGeom {
+    static constexpr u32 pitch = (1u << S) + (S >= 4 ? (1u << (S - 3)) : 0) + 2;
+    __device__ __forceinline__ static u32 pidx(u32 e) { return e + 2 * (e >> 4); }
+};
+
+template <int R1, int R2, int MODE, bool INV>
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
+k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64* __restrict__ post, u64 scale,
+           const u64* __restrict__ roots, u64* __restrict__ dst, size_t dst_stride, size_t row_base, size_t col0,
+           const NttScatter sc) {
+    constexpr int S = R1 + R2, LOG_G = F_TILE_LOG - S;
+    constexpr u32 G = 1u << LOG_G, LEN = 1u << S, TASKS1 = F_TILE >> R1, TASKS2 = F_TILE >> R2;
+    constexpr u32 pitch = LoGeom<S>::pitch;
+    extern __shared__ u64 sm[];
+    const int log_nb = log_n - S;
+    const u64* s = src + blockIdx.y * src_stride;
+
+#pragma unroll
+    for (u32 j = 0; j < TASKS1 / NTT_THREADS; j++) {
+        const u32 tau = threadIdx.x + j * NTT_THREADS;
+        const u32 b = tau & ((1u << R2) - 1), g = tau >> R2;
+        size_t blk = ((size_t)blockIdx.x << LOG_G) + g;
+        if (MODE == OUT_NATURAL) blk = brev((u32)blk, log_nb);
+        const u64* in = s + (blk << S) + b;
+        u64 v[1 << R1];
+#pragma unroll
+        for (int k = 0; k < (1 << R1); k++) v[k] = in[k << R2]; // an earlier pass of this transform wrote it: canonical
+        dft_regs<R1, INV>(v);
+#pragma unroll
+        for (int k = 1; k < (1 << R1); k++) v[k] = gl::mul(v[k], __ldg(roots + b * brev_c<R1>(k)));
+#pragma unroll
+        for (int k = 0; k < (1 << R1); k++) sm[g * pitch + LoGeom<S>::pidx(b + (k << R2))] = v[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (u32 j = 0; j < TASKS2 / NTT_THREADS; j++) {
+        const u32 tau = threadIdx.x + j * NTT_THREADS;
+        const u32 p = tau & ((1u << R1) - 1), g = tau >> R1;
+        u64* row = sm + g * pitch;
+        u64 v[1 << R2];
+#pragma unroll
+        for (int k = 0; k < (1 << R2); k++) v[k] = row[LoGeom<S>::pidx((p << R2) + k)];
+        dft_regs<R2, INV>(v);
+#pragma unroll
+        for (int k = 0; k < (1 << R2); k++) row[LoGeom<S>::pidx((p << R2) + k)] = v[k]; // in place: the thread owns these slots
+    }
+    __syncthreads();
+    if (MODE == OUT_COLS || MODE == OUT_SCATTER) {
+        u64* out = dst + (col0 + blockIdx.y) * dst_stride;
+#pragma unroll
+        for (u32 j = 0; j < F_TILE / NTT_THREADS; j++) {
+            const u32 idx = threadIdx.x + j * NTT_THREADS;
+            const u32 g = idx >> S, q = idx & (LEN - 1);
+            u64 v = sm[g * pitch + LoGeom<S>::pidx(q)];
+            if (scale != 1) v = gl::mul(v, scale);
+            const size_t leaf = row_base + ((((size_t)blockIdx.x << LOG_G) + g) << S) + q;
+            if (MODE == OUT_COLS) {
+                out[leaf] = v;
+            } else { // re-blocked by leaf-row shard, possibly straight into a peer GPU's buffer
+                const size_t gd = leaf >> sc.log_per;
+                u64* pbase = sc.peer[0] ? sc.peer[gd] : dst + gd * sc.shard_stride;
+                pbase[(col0 + blockIdx.y) * dst_stride + (leaf & (((size_t)1 << sc.log_per) - 1))] = v;
+            }
+        }
+    } else { // natural order: output k = bitrev_S(q) * 2^log_nb + block index, contiguous over the G blocks
+        u64* out = dst + blockIdx.y * dst_stride + ((size_t)blockIdx.x << LOG_G);
+#pragma unroll
+        for (u32 j = 0; j < F_TILE / NTT_THREADS; j++) {
+            const u32 idx = threadIdx.x + j * NTT_THREADS;
+            const u32 g = idx & (G - 1), q = idx >> LOG_G;
+            u64 v = sm[g * pitch + LoGeom<S>::pidx(q)];
+            if (scale != 1) v = gl::mul(v, scale);
+            const size_t k = ((size_t)brev(q, S) << log_nb) + g;
+            if (post) v = gl::mul(v, __ldg(post + ((size_t)blockIdx.x << LOG_G) + k));
+            out[k] = v;
+        }
+    }
+}
+
 u64* get_table(nlc_ctx* ctx, const TableKey& key, size_t words) {
     auto it = ctx->tables.find(key);
     if (it != ctx->tables.end()) return it->second;
@@ -258,14 +414,15 @@ u64* roots_table(nlc_ctx* ctx, int S, bool inv) {
     NLC_LAUNCH(ctx, k_pow_table, (unsigned)((words + 255) / 256), 256, 0, p, words, w, (u64)1);
     return p;
 }
-u64* tw_table(nlc_ctx* ctx, int m, int S, bool inv) {
-    TableKey key{KIND_TW, m, S, inv ? 1 : 0, 0, 0};
+// scale != 1: the 1/n of an inverse transform rides on the first inter-digit twiddle (every element meets it once)
+u64* tw_table(nlc_ctx* ctx, int m, int S, bool inv, u64 scale = 1) {
+    TableKey key{KIND_TW, m, S, inv ? 1 : 0, 0, scale};
     size_t words = (size_t)1 << m;
     if (u64* p = get_table(ctx, key, words)) return p;
     u64* p = ctx->tables[key];
     u64 w = gl::h_root_of_unity(m);
     if (inv) w = gl::h_inv(w);
-    NLC_LAUNCH(ctx, k_tw_table, (unsigned)((words + 255) / 256), 256, 0, p, m, S, w);
+    NLC_LAUNCH(ctx, k_tw_table, (unsigned)((words + 255) / 256), 256, 0, p, m, S, w, scale);
     return p;
 }
 u64* pw_table(nlc_ctx* ctx, int log_n, u64 base, u64 scale) {
@@ -312,7 +469,98 @@ size_t ntt_scratch_words(size_t n_cols, int log_n) {
     return plan_digits(log_n).size() > 1 ? n_cols << log_n : 0;
 }
 
+// ---- fast path dispatch ----
+namespace {
+std::vector<int> plan_digits_fast(int log_n) { // digits of 4..8 bits, smaller ones first (the last digit is >= 6)
+    const int d = (log_n + 7) / 8;
+    std::vector<int> v(d, log_n / d);
+    for (int i = 0; i < log_n % d; i++) v[d - 1 - i]++;
+    return v;
+}
+
+template <bool INV>
+void launch_hi_f(nlc_ctx* ctx, int S, dim3 grid, const u64* src, size_t src_stride, u64* dst, size_t dst_stride, int m,
+                 const u64* pre, const u64* tw, const u64* roots, int canon_in) {
+    const size_t smem = (size_t)F_TILE * sizeof(u64);
+    switch (S) {
+    case 4: NLC_LAUNCH(ctx, (k_ntt_hi_f<2, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    case 5: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    case 6: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    case 7: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    default: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 4, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    }
+}
+template <int MODE, bool INV>
+void launch_lo_f(nlc_ctx* ctx, int S, dim3 grid, const u64* src, size_t src_stride, int log_n, const u64* post, u64 scale,
+                 const u64* roots, u64* dst, size_t dst_stride, size_t row_base, size_t col0, const NttScatter& sc) {
+    switch (S) {
+    case 6: NLC_LAUNCH(ctx, (k_ntt_lo_f<3, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 6) * LoGeom<6>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
+    case 7: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 7) * LoGeom<7>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
+    default: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 4, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 8) * LoGeom<8>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
+    }
+}
+
+void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
+    const int log_n = job.log_n;
+    const size_t n = (size_t)1 << log_n;
+    const std::vector<int> digits = plan_digits_fast(log_n);
+    const int d = (int)digits.size();
+    const bool inv = job.inverse;
+    u64 scale = inv ? gl::h_inv(gl::canon((u64)(n % gl::P))) : 1;
+    const u64* pre = nullptr;
+    if (gl::canon(job.pre_shift) != 1) pre = pw_table(ctx, log_n, gl::canon(job.pre_shift), 1);
+    const u64* post = nullptr;
+    if (!job.cols && gl::canon(job.post_shift) != 1) post = pw_table(ctx, log_n, gl::canon(job.post_shift), 1);
+    NLC_CHECK(job.scratch != nullptr, "ntt_run: scratch required for multi-digit transform");
+
+    const u64* cur = job.src;
+    size_t cur_stride = job.src_stride;
+    int m = log_n;
+    for (int lvl = 0; lvl + 1 < d; lvl++) {
+        const int S = digits[lvl], L = m - S, log_T = (int)F_TILE_LOG - S;
+        NLC_CHECK(L >= log_T, "ntt fast path: tile wider than the stride");
+        const u64* tw = tw_table(ctx, m, S, inv, lvl == 0 ? scale : 1); // 1/n folded into the first inter-digit twiddle
+        const u64* roots = roots_table(ctx, S, inv);
+        dim3 grid((unsigned)((n >> m) << (L - log_T)), (unsigned)job.n_cols);
+        if (inv)
+            launch_hi_f<true>(ctx, S, grid, cur, cur_stride, job.scratch, n, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0);
+        else
+            launch_hi_f<false>(ctx, S, grid, cur, cur_stride, job.scratch, n, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0);
+        cur = job.scratch;
+        cur_stride = n;
+        m = L;
+    }
+    scale = 1;
+    const int S = digits[d - 1];
+    const u64* roots = roots_table(ctx, S, inv);
+    dim3 grid((unsigned)(n >> F_TILE_LOG), (unsigned)job.n_cols);
+    if (job.cols && job.scatter.log_per >= 0) {
+        NLC_CHECK(!inv, "scatter output is for forward transforms");
+        launch_lo_f<OUT_SCATTER, false>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst, job.dst_stride,
+                                        job.row_base, job.col0, job.scatter);
+    } else if (job.cols) {
+        if (inv)
+            launch_lo_f<OUT_COLS, true>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst, job.dst_stride,
+                                        job.row_base, job.col0, job.scatter);
+        else
+            launch_lo_f<OUT_COLS, false>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst,
+                                         job.dst_stride, job.row_base, job.col0, job.scatter);
+    } else {
+        NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
+        if (inv)
+            launch_lo_f<OUT_NATURAL, true>(ctx, S, grid, cur, cur_stride, log_n, post, scale, roots, job.dst, job.dst_stride,
+                                           0, 0, NttScatter());
+        else
+            launch_lo_f<OUT_NATURAL, false>(ctx, S, grid, cur, cur_stride, log_n, post, scale, roots, job.dst,
+                                            job.dst_stride, 0, 0, NttScatter());
+    }
+}
+} // namespace
+
 void ntt_run(nlc_ctx* ctx, const NttJob& job) {
+    NLC_CHECK(job.log_n >= 0 && job.log_n <= 32, "log_n out of range (two-adicity is 32)");
+    NLC_CHECK(job.n_cols > 0 && job.n_cols <= 65535u, "column count out of range");
+    if (job.log_n >= 12 && !job.rows) return ntt_run_fast(ctx, job);
     ensure_attrs(ctx);
     const int log_n = job.log_n;
     const size_t n = (size_t)1 << log_n;

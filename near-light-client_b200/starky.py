@@ -1,0 +1,718 @@
+"""Host-side mirror of the starkyx interfaces that sit on the constraint-evaluation side of the hot path
+(SURVEY.md 8f.3), over the C ABI of libnlc_commit.so -- no compute happens in Python.
+
+Mirrors, name for name (reference files under /root/reference/vendor/starkyx/starkyx/src):
+  air/parser.rs:6-75              AirParser (the trait an AIR's `eval` is written against)
+  polynomial/parser.rs            PolynomialParser's default methods (poly_add, poly_sub, poly_mul, ...)
+  plonky2/parser/mod.rs:16-28     StarkParser -- here `BytecodeParser`: Var = a virtual register id; running
+                                  `air.eval(parser)` ONCE records the straight-line program that the device
+                                  interpreter (csrc/air.cu) then runs for every point of the quotient domain
+  air/fibonacci.rs                FibonacciAir (the in-tree test AIR, plonky2/stark/mod.rs:243-265)
+  chip/arithmetic/*.rs            ArithmeticExpression(Slice) / ArithmeticConstraint::{First,Last,Transition,All}
+  chip/register/memory.rs         MemorySlice
+  chip/field/mul.rs, util.rs      FpMulInstruction<Fp25519> (one field-arithmetic chip: 31 degree-2 constraints)
+  plonky2/stark/prover.rs:50-225  StarkyProver::{generate_trace, prove_with_trace, quotient_polys}
+  plonky2/stark/proof.rs:300-345  StarkOpeningSet::{new, to_fri_openings};  plonky2/stark/mod.rs:56-96 fri_instance
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _ffi
+from . import plonky2 as P2
+from ._ffi import NlcError, u32p, u64p, vp
+
+P = 0xFFFFFFFF00000001
+
+OP = {name: i for i, name in enumerate(
+    ["LOCAL", "NEXT", "PUBLIC", "GLOBAL", "CHALLENGE", "CONST", "ADD", "SUB", "MUL", "NEG", "MUL_CONST", "ADD_CONST",
+     "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW"])}
+
+
+# ---------------------------------------------------------------------------------------------
+# air/parser.rs: the recording parser
+# ---------------------------------------------------------------------------------------------
+class AirProgram:
+    """The bytecode of one AIR (nlc_air_program): code (n_ops x 4 uint32), constant pool, register count."""
+
+    def __init__(self, code: np.ndarray, pool: np.ndarray, n_regs: int, n_public: int, n_global: int, n_challenge: int,
+                 n_columns: int, n_constraints: int):
+        self.code, self.pool, self.n_regs = np.ascontiguousarray(code, np.uint32), np.ascontiguousarray(pool, np.uint64), n_regs
+        self.n_public, self.n_global, self.n_challenge = n_public, n_global, n_challenge
+        self.n_columns, self.n_constraints = n_columns, n_constraints
+
+    @property
+    def n_ops(self) -> int:
+        return self.code.shape[0]
+
+    def to_c(self) -> _ffi.CAirProgram:
+        p = _ffi.CAirProgram()
+        p.code = self.code.ctypes.data_as(u32p)
+        p.n_ops, p.n_regs = self.n_ops, self.n_regs
+        p.pool = self.pool.ctypes.data_as(u64p) if self.pool.size else None
+        p.n_pool = self.pool.size
+        p.n_public, p.n_global, p.n_challenge = self.n_public, self.n_global, self.n_challenge
+        return p
+
+
+class BytecodeParser:
+    """AirParser with Var = SSA value id.  `finish()` assigns physical registers by liveness (a value's register is
+    recycled after its last use) and returns the AirProgram."""
+
+    def __init__(self, n_columns: int, n_public: int = 0, n_global: int = 0, n_challenge: int = 0):
+        self.n_columns, self.n_public, self.n_global, self.n_challenge = n_columns, n_public, n_global, n_challenge
+        self.ops: list[tuple] = []   # (op, dst_value or None, a, b) with a/b value ids or immediates
+        self._n_values = 0
+        self._pool: dict[int, int] = {}
+        self._slices: dict[str, list[int]] = {}
+        self.n_constraints = 0
+
+    # -- values --
+    def _new(self, op, a=0, b=0) -> int:
+        v = self._n_values
+        self._n_values += 1
+        self.ops.append((OP[op], v, a, b))
+        return v
+
+    def _const_index(self, value: int) -> int:
+        value = int(value) % P
+        return self._pool.setdefault(value, len(self._pool))
+
+    def _slice(self, kind: str, op: str, length: int) -> list[int]:
+        if kind not in self._slices:  # loaded lazily, in index order, on first access of the slice
+            self._slices[kind] = [None] * length
+        return _LazySlice(self, self._slices[kind], op)
+
+    def local_slice(self):
+        return self._slice("local", "LOCAL", self.n_columns)
+
+    def next_slice(self):
+        return self._slice("next", "NEXT", self.n_columns)
+
+    def challenge_slice(self):
+        return self._slice("challenge", "CHALLENGE", self.n_challenge)
+
+    def global_slice(self):
+        return self._slice("global", "GLOBAL", self.n_global)
+
+    def public_slice(self):
+        return self._slice("public", "PUBLIC", self.n_public)
+
+    # -- constraints (plonky2/parser/mod.rs:72-86 -> consumer.rs:54-78) --
+    def _emit_constraint(self, op: str, c: int):
+        self.ops.append((OP[op], None, c, 0))
+        self.n_constraints += 1
+
+    def constraint(self, c):
+        self._emit_constraint("CONSTRAINT", c)
+
+    def constraint_transition(self, c):
+        self._emit_constraint("CONSTRAINT_TRANSITION", c)
+
+    def constraint_first_row(self, c):
+        self._emit_constraint("CONSTRAINT_FIRST_ROW", c)
+
+    def constraint_last_row(self, c):
+        self._emit_constraint("CONSTRAINT_LAST_ROW", c)
+
+    # -- arithmetic --
+    def constant(self, value):
+        return self._new("CONST", self._const_index(value))
+
+    def add(self, a, b):
+        return self._new("ADD", a, b)
+
+    def sub(self, a, b):
+        return self._new("SUB", a, b)
+
+    def neg(self, a):
+        return self._new("NEG", a)
+
+    def mul(self, a, b):
+        return self._new("MUL", a, b)
+
+    def add_const(self, a, c):
+        return self._new("ADD_CONST", a, self._const_index(c))
+
+    def sub_const(self, a, c):
+        return self._new("SUB_CONST", a, self._const_index(c))
+
+    def mul_const(self, a, c):
+        return self._new("MUL_CONST", a, self._const_index(c))
+
+    def one(self):
+        return self.constant(1)
+
+    def zero(self):
+        return self.constant(0)
+
+    def sum(self, elements):
+        acc = self.zero()
+        for x in elements:
+            acc = self.add(acc, x)
+        return acc
+
+    def assert_eq(self, a, b):
+        self.constraint(self.sub(a, b))
+
+    def assert_eq_transition(self, a, b):
+        self.constraint_transition(self.sub(a, b))
+
+    # -- register allocation --
+    def finish(self) -> AirProgram:
+        reads_reg = {OP[k] for k in ("ADD", "SUB", "MUL")}
+        reads_a = {OP[k] for k in ("NEG", "MUL_CONST", "ADD_CONST", "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION",
+                                   "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW")}
+        last_use: dict[int, int] = {}
+        for pc, (op, dst, a, b) in enumerate(self.ops):
+            if op in reads_reg:
+                last_use[a] = pc
+                last_use[b] = pc
+            elif op in reads_a:
+                last_use[a] = pc
+        reg_of: dict[int, int] = {}
+        free: list[int] = []
+        n_regs = 0
+        code = np.zeros((len(self.ops), 4), np.uint32)
+        kept = 0
+        for pc, (op, dst, a, b) in enumerate(self.ops):
+            if dst is not None and dst not in last_use:
+                continue  # a value nobody reads (e.g. an unused slice element): no instruction
+            ra, rb = a, b
+            dying = []
+            if op in reads_reg:
+                ra, rb = reg_of[a], reg_of[b]
+                dying = [v for v in {a, b} if last_use[v] == pc]
+            elif op in reads_a:
+                ra = reg_of[a]
+                dying = [a] if last_use[a] == pc else []
+            for v in dying:  # operands are read before the destination is written: the register can be reused now
+                free.append(reg_of.pop(v))
+            rd = 0
+            if dst is not None:
+                if free:
+                    rd = free.pop()
+                else:
+                    rd = n_regs
+                    n_regs += 1
+                reg_of[dst] = rd
+            code[kept] = (op, rd, ra, rb)
+            kept += 1
+        pool = np.zeros(len(self._pool), np.uint64)
+        for value, idx in self._pool.items():
+            pool[idx] = value
+        return AirProgram(code[:kept].copy(), pool, max(n_regs, 1), self.n_public, self.n_global, self.n_challenge,
+                          self.n_columns, self.n_constraints)
+
+
+class _LazySlice:
+    """&[Var]: element i is loaded (one LOCAL / NEXT / ... instruction) the first time it is indexed."""
+
+    def __init__(self, parser: BytecodeParser, store: list, op: str):
+        self._p, self._s, self._op = parser, store, op
+
+    def __len__(self):
+        return len(self._s)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self._s)))]
+        if i < 0:
+            i += len(self._s)
+        if self._s[i] is None:
+            self._s[i] = self._p._new(self._op, i)
+        return self._s[i]
+
+
+def compile_air(air, n_challenge: int = 0) -> AirProgram:
+    """`stark.air().eval(&mut parser)` (prover.rs:334) against the recording parser."""
+    parser = BytecodeParser(air.width(), air.num_public_inputs(), air.num_global_values(), n_challenge)
+    air.eval(parser)
+    return parser.finish()
+
+
+# ---------------------------------------------------------------------------------------------
+# polynomial/parser.rs: PolynomialParser default methods (free functions over any AirParser)
+# ---------------------------------------------------------------------------------------------
+def constant_poly(parser, coefficients):
+    return [parser.constant(c) for c in coefficients]
+
+
+def _zip_longest(a, b):
+    for i in range(max(len(a), len(b))):
+        yield (a[i] if i < len(a) else None), (b[i] if i < len(b) else None)
+
+
+def poly_add(parser, a, b):
+    return [x if y is None else y if x is None else parser.add(x, y) for x, y in _zip_longest(a, b)]
+
+
+def poly_sub(parser, a, b):
+    return [x if y is None else parser.neg(y) if x is None else parser.sub(x, y) for x, y in _zip_longest(a, b)]
+
+
+def poly_scalar_mul(parser, a, s):
+    return [parser.mul(x, s) for x in a]
+
+
+def poly_scalar_sub(parser, a, s):
+    return [parser.sub(x, s) for x in a]
+
+
+def poly_mul(parser, a, b):
+    result = [parser.zero()] * (len(a) + len(b) - 1)  # vec![self.zero(); len]: ONE zero var, copied
+    for i, x in enumerate(a):
+        for j, y in enumerate(b):
+            ab = parser.mul(x, y)
+            result[i + j] = parser.add(result[i + j], ab)
+    return result
+
+
+def poly_mul_poly_const(parser, a, b_const):
+    result = [parser.zero()] * (len(a) + len(b_const) - 1)
+    for i, x in enumerate(a):
+        for j, c in enumerate(b_const):
+            ab = parser.mul_const(x, c)
+            result[i + j] = parser.add(result[i + j], ab)
+    return result
+
+
+# ---------------------------------------------------------------------------------------------
+# air/mod.rs RAirData + air/fibonacci.rs
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class RoundDatum:
+    num_columns: int
+    global_values_range: tuple
+    num_challenges: int
+
+
+class RAirData:
+    def constraint_degree(self) -> int:
+        raise NotImplementedError
+
+    def width(self) -> int:
+        raise NotImplementedError
+
+    def round_data(self):
+        return [RoundDatum(self.width(), (0, 0), 0)]
+
+    def num_public_inputs(self) -> int:
+        return 0
+
+    def num_global_values(self) -> int:
+        return sum(d.global_values_range[1] - d.global_values_range[0] for d in self.round_data())
+
+    def quotient_degree_factor(self) -> int:
+        return max(1, self.constraint_degree() - 1)
+
+
+class FibonacciAir(RAirData):
+    """air/fibonacci.rs:11-97."""
+
+    def constraint_degree(self):
+        return 1
+
+    def width(self):
+        return 2
+
+    def round_data(self):
+        return [RoundDatum(2, (0, 3), 0)]
+
+    def num_public_inputs(self):
+        return 3
+
+    @staticmethod
+    def fibonacci(n: int, x0: int, x1: int) -> int:
+        for _ in range(n):
+            x0, x1 = x1, (x0 + x1) % P
+        return x1
+
+    @staticmethod
+    def generate_trace(x0: int, x1: int, num_rows: int) -> np.ndarray:
+        """AirTrace (row-major, num_rows x 2)."""
+        rows = np.zeros((num_rows, 2), np.uint64)
+        for r in range(num_rows):
+            rows[r] = (x0, x1)
+            x0, x1 = x1, (x0 + x1) % P
+        return rows
+
+    def eval(self, parser):
+        pis_constraints = [parser.sub(parser.local_slice()[0], parser.public_slice()[0]),
+                           parser.sub(parser.local_slice()[1], parser.public_slice()[1])]
+        parser.constraint_first_row(pis_constraints[0])
+        parser.constraint_first_row(pis_constraints[1])
+        first_col_constraint = parser.sub(parser.next_slice()[0], parser.local_slice()[1])  # x0' <- x1
+        parser.constraint_transition(first_col_constraint)
+        tmp = parser.sub(parser.next_slice()[1], parser.local_slice()[0])                    # x1' <- x0 + x1
+        parser.constraint_transition(parser.sub(tmp, parser.local_slice()[1]))
+
+    def eval_global(self, parser):
+        pass
+
+
+# ---------------------------------------------------------------------------------------------
+# chip/register/memory.rs, chip/arithmetic/{expression_slice,expression,mod}.rs
+# ---------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class MemorySlice:
+    kind: str   # "Local" | "Next" | "Public" | "Global" | "Challenge"
+    index: int
+    length: int
+
+    def next(self):
+        if self.kind != "Local":
+            raise NlcError("Invalid register type for the next register")
+        return MemorySlice("Next", self.index, self.length)
+
+    def eval_slice(self, parser):
+        s = {"Local": parser.local_slice, "Next": parser.next_slice, "Public": parser.public_slice,
+             "Global": parser.global_slice, "Challenge": parser.challenge_slice}[self.kind]()
+        return s[self.index:self.index + self.length]
+
+
+@dataclass
+class ArithmeticExpression:
+    """ArithmeticExpression { expression: ArithmeticExpressionSlice, size }; node = (tag, ...)."""
+    node: tuple
+    size: int
+
+    @classmethod
+    def from_register(cls, m: MemorySlice):
+        return cls(("Input", m), m.length)
+
+    @classmethod
+    def from_constant_vec(cls, constants):
+        return cls(("Const", [int(c) % P for c in constants]), len(constants))
+
+    @classmethod
+    def from_constant(cls, c):
+        return cls.from_constant_vec([c])
+
+    def _bin(self, tag, rhs):
+        if isinstance(rhs, (list, tuple)):
+            rhs = ArithmeticExpression.from_constant_vec(rhs)
+        if self.size != rhs.size:
+            raise NlcError("Cannot combine arithmetic expressions of different sizes")
+        return ArithmeticExpression((tag, self.node, rhs.node), self.size)
+
+    def __add__(self, rhs):
+        return self._bin("Add", rhs)
+
+    def __sub__(self, rhs):
+        return self._bin("Sub", rhs)
+
+    def __mul__(self, rhs):
+        if isinstance(rhs, int):
+            return ArithmeticExpression(("ConstMul", rhs % P, self.node), self.size)
+        if rhs.size == 1 and self.size != 1:
+            return ArithmeticExpression(("ScalarMul", rhs.node, self.node), self.size)
+        if self.size == 1 and rhs.size != 1:
+            return ArithmeticExpression(("ScalarMul", self.node, rhs.node), rhs.size)
+        if self.size != rhs.size:
+            raise NlcError("Cannot multiply arithmetic expressions of different sizes")
+        return ArithmeticExpression(("Mul", self.node, rhs.node), self.size)
+
+    def eval(self, parser):
+        return _eval_slice(self.node, parser)
+
+
+def _eval_slice(node, parser):
+    tag = node[0]
+    if tag == "Input":
+        return list(node[1].eval_slice(parser))
+    if tag == "Const":
+        return [parser.constant(c) for c in node[1]]
+    if tag == "Add":
+        left, right = _eval_slice(node[1], parser), _eval_slice(node[2], parser)
+        return [parser.add(l, r) for l, r in zip(left, right)]
+    if tag == "Sub":
+        left, right = _eval_slice(node[1], parser), _eval_slice(node[2], parser)
+        return [parser.sub(l, r) for l, r in zip(left, right)]
+    if tag == "ConstMul":
+        return [parser.mul_const(x, node[1]) for x in _eval_slice(node[2], parser)]
+    if tag == "ScalarMul":
+        scalar = _eval_slice(node[1], parser)[0]
+        return [parser.mul(x, scalar) for x in _eval_slice(node[2], parser)]
+    if tag == "Mul":
+        left, right = _eval_slice(node[1], parser), _eval_slice(node[2], parser)
+        return [parser.mul(l, r) for l, r in zip(left, right)]
+    raise NlcError(f"unknown expression node {tag}")
+
+
+@dataclass
+class ArithmeticConstraint:
+    """chip/arithmetic/mod.rs:13-50."""
+    kind: str   # "First" | "Last" | "Transition" | "All"
+    expression: ArithmeticExpression
+
+    def eval(self, parser):
+        emit = {"First": parser.constraint_first_row, "Last": parser.constraint_last_row,
+                "Transition": parser.constraint_transition, "All": parser.constraint}[self.kind]
+        for c in self.expression.eval(parser):
+            emit(c)
+
+
+# ---------------------------------------------------------------------------------------------
+# chip/field: FpMulInstruction<Fp25519> (mul.rs:70-98, util.rs:8-38, parameters.rs:44-62)
+# ---------------------------------------------------------------------------------------------
+class Fp25519:
+    NB_BITS_PER_LIMB = 16
+    NB_LIMBS = 16
+    NB_WITNESS_LIMBS = 2 * 16 - 2
+    MODULUS = [65517] + [65535] * 14 + [32767]
+    WITNESS_OFFSET = 1 << 21
+
+    @classmethod
+    def modulus(cls) -> int:
+        return (1 << 255) - 19
+
+
+@dataclass
+class FpMulInstruction:
+    """a * b = result (mod p) on 16-bit limbs: p_a p_b - p_result - p_carry p_modulus = (x - 2^16) p_witness."""
+    a: MemorySlice
+    b: MemorySlice
+    result: MemorySlice
+    carry: MemorySlice
+    witness_low: MemorySlice
+    witness_high: MemorySlice
+    params: type = Fp25519
+
+    def eval(self, parser):
+        p_a, p_b = list(self.a.eval_slice(parser)), list(self.b.eval_slice(parser))
+        p_result, p_carry = list(self.result.eval_slice(parser)), list(self.carry.eval_slice(parser))
+        p_a_mul_b = poly_mul(parser, p_a, p_b)
+        p_a_mul_b_minus_result = poly_sub(parser, p_a_mul_b, p_result)
+        p_limbs = constant_poly(parser, self.params.MODULUS[:self.params.NB_LIMBS])
+        p_mul_times_carry = poly_mul(parser, p_carry, p_limbs)
+        p_vanishing = poly_sub(parser, p_a_mul_b_minus_result, p_mul_times_carry)
+        p_witness_low = list(self.witness_low.eval_slice(parser))
+        p_witness_high = list(self.witness_high.eval_slice(parser))
+        eval_field_operation(parser, self.params, p_vanishing, p_witness_low, p_witness_high)
+
+    def write(self, a_int: int, b_int: int) -> dict:
+        """Instruction::write (mul.rs:101-145): the limbs of result / carry / witness for one row."""
+        pr = self.params
+        modulus = pr.modulus()
+        result = a_int * b_int % modulus
+        carry = (a_int * b_int - result) // modulus
+        limbs = lambda v: [(v >> (16 * i)) & 0xFFFF for i in range(pr.NB_LIMBS)]
+        p_a, p_b, p_res, p_carry, p_mod = limbs(a_int), limbs(b_int), limbs(result), limbs(carry), limbs(modulus)
+        van = [0] * (2 * pr.NB_LIMBS - 1)
+        for i in range(pr.NB_LIMBS):
+            for j in range(pr.NB_LIMBS):
+                van[i + j] += p_a[i] * p_b[j] - p_carry[i] * p_mod[j]
+            van[i] -= p_res[i]
+        # compute_root_quotient_and_shift (util.rs:48-84): vanishing(x) / (x - 2^16), shifted by WITNESS_OFFSET
+        q = [0] * (len(van) - 1)
+        acc = 0
+        for i in range(len(van) - 1, 0, -1):
+            acc = van[i] + (acc << 16)
+            q[i - 1] = acc
+        assert van[0] + (q[0] << 16) == 0, "vanishing polynomial does not vanish at 2^16"
+        w = [x + pr.WITNESS_OFFSET for x in q]
+        assert all(0 <= x < 1 << 32 for x in w)
+        return {"result": p_res, "carry": p_carry, "witness_low": [x & 0xFFFF for x in w],
+                "witness_high": [x >> 16 for x in w]}
+
+
+def eval_field_operation(parser, params, p_vanishing, p_witness_low, p_witness_high):
+    """chip/field/util.rs:8-38."""
+    limb_field = 1 << 16
+    limb = parser.constant(limb_field)
+    p_witness_high_mul_limb = poly_scalar_mul(parser, p_witness_high, limb)
+    p_witness_shifted = poly_add(parser, p_witness_low, p_witness_high_mul_limb)
+    offset = parser.constant(params.WITNESS_OFFSET)
+    p_witness = poly_scalar_sub(parser, p_witness_shifted, offset)
+    root_monomial = [(-limb_field) % P, 1]
+    p_witness_mul_root = poly_mul_poly_const(parser, p_witness, root_monomial)
+    for constr in poly_sub(parser, p_vanishing, p_witness_mul_root):
+        parser.constraint(constr)
+
+
+class FpMulChip(RAirData):
+    """A one-instruction Chip (chip/mod.rs:58-66): columns a | b | result | carry | witness_low | witness_high = 124,
+    the arithmetic columns of chip/field/mul.rs `FpMulTest` (NUM_ARITHMETIC_COLUMNS = 124)."""
+
+    def __init__(self):
+        L, Wn = Fp25519.NB_LIMBS, Fp25519.NB_WITNESS_LIMBS
+        o = 0
+        regs = []
+        for ln in (L, L, L, L, Wn, Wn):
+            regs.append(MemorySlice("Local", o, ln))
+            o += ln
+        self.instruction = FpMulInstruction(*regs)
+        self._width = o
+
+    def constraint_degree(self):
+        return 2
+
+    def width(self):
+        return self._width
+
+    def eval(self, parser):
+        self.instruction.eval(parser)
+
+    def eval_global(self, parser):
+        pass
+
+    def generate_trace(self, rng, num_rows: int) -> np.ndarray:
+        """Row-major AirTrace (num_rows x 124) of random multiplications mod 2^255 - 19 (mul.rs test_fpmul)."""
+        p = Fp25519.modulus()
+        rows = np.zeros((num_rows, self._width), np.uint64)
+        ins = self.instruction
+        for r in range(num_rows):
+            a_int = int.from_bytes(rng.bytes(32), "little") % p
+            b_int = int.from_bytes(rng.bytes(32), "little") % p
+            w = ins.write(a_int, b_int)
+            row = [(a_int >> (16 * i)) & 0xFFFF for i in range(16)] + [(b_int >> (16 * i)) & 0xFFFF for i in range(16)]
+            row += w["result"] + w["carry"] + w["witness_low"] + w["witness_high"]
+            rows[r] = row
+        return rows
+
+
+# ---------------------------------------------------------------------------------------------
+# plonky2/stark: config, opening set, prover
+# ---------------------------------------------------------------------------------------------
+@dataclass
+class StarkyConfig:
+    """plonky2/stark/config.rs:38-77: standard_fast_config(num_rows)."""
+    degree_bits: int
+    num_challenges: int = 2
+    fri_config: P2.FriConfig = field(default_factory=P2.FriConfig.standard_fast_config)
+
+    @classmethod
+    def standard_fast_config(cls, num_rows: int):
+        return cls((num_rows - 1).bit_length() if num_rows > 1 else 0)
+
+    def fri_params(self) -> P2.FriParams:
+        return self.fri_config.fri_params(self.degree_bits, False)
+
+
+@dataclass
+class StarkOpeningSet:
+    local_values: np.ndarray     # (num_columns, 2)
+    next_values: np.ndarray
+    quotient_polys: np.ndarray
+
+    @classmethod
+    def new(cls, zeta, g: int, trace_commitments, quotient_commitment):
+        zeta_next = (int(zeta[0]) * g % P, int(zeta[1]) * g % P)
+        local_values = np.concatenate([t.eval_at(zeta) for t in trace_commitments])
+        next_values = np.concatenate([t.eval_at(zeta_next) for t in trace_commitments])
+        return cls(local_values, next_values, quotient_commitment.eval_at(zeta))
+
+    def to_fri_openings(self):
+        """[zeta batch: local ++ quotient, zeta_next batch: next] (proof.rs:330-345)."""
+        return [np.concatenate([self.local_values, self.quotient_polys]), self.next_values]
+
+
+@dataclass
+class StarkProof:
+    trace_caps: list
+    quotient_polys_cap: np.ndarray
+    openings: StarkOpeningSet
+    opening_proof: P2.FriProof
+    global_values: list
+
+
+class Starky:
+    def __init__(self, air):
+        self.air = air
+        self._program = None
+
+    def program(self, n_challenge: int = 0) -> AirProgram:
+        if self._program is None:
+            self._program = compile_air(self.air, n_challenge)
+        return self._program
+
+    def fri_instance(self, zeta, g: int, config: StarkyConfig) -> P2.FriInstanceInfo:
+        """plonky2/stark/mod.rs:56-96."""
+        trace_info, n_oracles = [], 0
+        for rd in self.air.round_data():
+            trace_info += P2.FriPolynomialInfo.from_range(n_oracles, range(rd.num_columns))
+            n_oracles += 1
+        num_quotient_polys = self.air.quotient_degree_factor() * config.num_challenges
+        quotient_info = P2.FriPolynomialInfo.from_range(n_oracles, range(num_quotient_polys))
+        zeta_next = (int(zeta[0]) * g % P, int(zeta[1]) * g % P)
+        return P2.FriInstanceInfo([], [P2.FriBatchInfo(tuple(int(z) for z in zeta), trace_info + quotient_info),
+                                       P2.FriBatchInfo(zeta_next, trace_info)])
+
+
+def _u64(a):
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.uint64).reshape(-1))
+    return a, (a.ctypes.data_as(u64p) if a.size else None)
+
+
+class StarkyProver:
+    """plonky2/stark/prover.rs: the part of StarkyProver that lives on the commitment path."""
+
+    @staticmethod
+    def air_eval(stark: Starky, trace_data, challenges, global_values, public_inputs, alphas,
+                 quotient_degree_bits: int | None = None) -> np.ndarray:
+        """The constraint accumulators of prover.rs:306-335 for every point of the quotient domain, BEFORE the
+        multiplication by 1/Z_H: (size, num_challenges), natural order."""
+        ctx = trace_data[0]._ctx
+        prog = stark.program(len(challenges))
+        if quotient_degree_bits is None:
+            quotient_degree_bits = max(stark.air.quotient_degree_factor() - 1, 0).bit_length()
+        handles = (vp * len(trace_data))(*[b._h for b in trace_data])
+        cp = prog.to_c()
+        (_pa, pub), (_ga, glob), (_ca, chal), (al, alp) = _u64(public_inputs), _u64(global_values), _u64(challenges), _u64(alphas)
+        out = np.zeros((1 << (trace_data[0].degree_log + quotient_degree_bits), al.size), np.uint64)
+        ctx._check(_ffi.lib().nlc_air_eval(ctx._h, C.byref(cp), handles, len(trace_data), pub, glob, chal, alp, al.size,
+                                           quotient_degree_bits, out.ctypes.data_as(u64p)))
+        return out
+
+    @staticmethod
+    def quotient_commitment(stark: Starky, config: StarkyConfig, trace_data, challenges, global_values, public_inputs,
+                            challenger: P2.Challenger) -> P2.PolynomialBatch:
+        """quotient_polys (prover.rs:253-358) + trim / chunks / from_coeffs (prover.rs:157-178), all on the device."""
+        alphas = challenger.get_n_challenges(config.num_challenges)
+        ctx = trace_data[0]._ctx
+        prog = stark.program(len(challenges))
+        handles = (vp * len(trace_data))(*[b._h for b in trace_data])
+        cp = prog.to_c()
+        (_pa, pub), (_ga, glob), (_ca, chal), (al, alp) = _u64(public_inputs), _u64(global_values), _u64(challenges), _u64(alphas)
+        qdf = stark.air.quotient_degree_factor()
+        h = vp()
+        ctx._check(_ffi.lib().nlc_stark_quotient_commit(ctx._h, C.byref(cp), handles, len(trace_data), pub, glob, chal,
+                                                        alp, al.size, qdf, config.fri_config.cap_height, C.byref(h)))
+        return P2.PolynomialBatch(ctx, h, al.size * qdf, trace_data[0].degree_log, config.fri_config.rate_bits,
+                                  config.fri_config.cap_height)
+
+    @staticmethod
+    def prove(config: StarkyConfig, stark: Starky, trace_rows: np.ndarray, public_inputs, ctx=None) -> StarkProof:
+        """generate_trace + prove_with_trace for a single-round AIR (prover.rs:50-225): row-major AirTrace in,
+        StarkProof out; every commitment, the AIR evaluation and the FRI proof run on the GPU."""
+        fc = config.fri_config
+        challenger = P2.Challenger(ctx)
+        global_values = [0] * stark.air.num_global_values()
+        challenger.observe_elements(public_inputs)
+        rounds = stark.air.round_data()
+        if len(rounds) != 1:
+            raise NlcError("StarkyProver.prove mirrors single-round AIRs; multi-round AIRs drive the steps themselves")
+        rd = rounds[0]
+        commitment = P2.PolynomialBatch.from_trace_rows(trace_rows, 0, rd.num_columns, fc.rate_bits, fc.cap_height, ctx=ctx)
+        id0, id1 = rd.global_values_range
+        challenger.observe_elements(global_values[id0:id1])
+        challenger.observe_cap(commitment.merkle_tree.cap)
+        challenges = challenger.get_n_challenges(rd.num_challenges)
+        trace_commitments = [commitment]
+        fri_params = config.fri_params()
+        quotient_commitment = StarkyProver.quotient_commitment(stark, config, trace_commitments, challenges, global_values,
+                                                               public_inputs, challenger)
+        quotient_polys_cap = quotient_commitment.merkle_tree.cap
+        challenger.observe_cap(quotient_polys_cap)
+        zeta = challenger.get_extension_challenge()
+        g = pow(1753635133440165772, 1 << (32 - config.degree_bits), P)
+        openings = StarkOpeningSet.new(zeta, g, trace_commitments, quotient_commitment)
+        for batch in openings.to_fri_openings():
+            challenger.observe_extension_elements(batch)
+        opening_proof = P2.PolynomialBatch.prove_openings(stark.fri_instance(zeta, g, config),
+                                                          trace_commitments + [quotient_commitment], challenger, fri_params)
+        return StarkProof([commitment.merkle_tree.cap], quotient_polys_cap, openings, opening_proof, global_values)

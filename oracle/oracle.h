@@ -137,6 +137,13 @@ void orc_eval_poly_ext(const uint64_t* coeffs, size_t n, const uint64_t* z2, uin
 void orc_set_threads(int n);
 int orc_get_threads(void);
 
+/* ---- vec.c: element-wise field arithmetic over arrays (the packed-field ops of an AIR parser) ---- */
+void orc_vec_add(const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+void orc_vec_sub(const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+void orc_vec_mul(const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
+void orc_vec_neg(const uint64_t* a, uint64_t* out, size_t n);
+void orc_vec_mul_scalar_add(const uint64_t* a, uint64_t s, const uint64_t* c, uint64_t* out, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,7 +17,8 @@ from dataclasses import dataclass, field
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SRCS = ["poseidon.c", "fft.c", "merkle.c", "commit.c", "challenger.c", "fri.c", "oracle.h", "gl.h", "poseidon_fast.h"]
+_SRCS = ["poseidon.c", "fft.c", "merkle.c", "commit.c", "quotient.c", "challenger.c", "fri.c", "vec.c", "oracle.h", "gl.h",
+         "poseidon_fast.h"]
 P = 0xFFFFFFFF00000001
 
 u64p = C.POINTER(C.c_uint64)

