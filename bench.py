@@ -131,6 +131,26 @@ def ncu_pipes(workload: str, kernel: str):
         return None
 
 
+def kernel_source_hash(files):
+    """sha256 over the kernel sources a committed ncu capture describes: a capture whose hash differs from the tree's
+    is reported as stale instead of being passed off as a measurement of the current kernel."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in files:
+        with open(os.path.join(ROOT, "near-light-client_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_capture_meta(workload: str, kernel: str):
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            d = json.load(f)[workload][kernel]
+        return d.get("source_files"), d.get("source_sha256_16"), d.get("capture")
+    except Exception:
+        return None, None, None
+
+
 def algorithmic_bytes(log_n, W, r, cap):
     n, N = 1 << log_n, 1 << (log_n + r)
     return {
@@ -283,6 +303,247 @@ def run_reference(args, rank, world):
                              "port_quality": oracle_quality(O)},
             "e2e": {"value": val, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+class Strong:
+    """ONE commit split over all ranks (strong scaling), measured inside the same process group as the weak-scaling
+    line so that the driver's SCALE record carries it: CUDA-event timed, L2 flushed, own clock sample.
+      coset  (world <= 2^rate_bits): rank p uploads + inverse-transforms its columns only, the iFFT's
+             stores put the coefficients into every rank's matrix over NVLink, barrier, every rank extends + hashes its
+             cosets, cap entries all-gathered;
+      rows   (world > 2^rate_bits): column shards for the transforms, last NTT pass stores into the
+             peers' leaf-row buffers over NVLink, barrier, leaf-row shards for the tree, cap all-gather."""
+
+    def __init__(self, pkg, ctx, stream, rank, world, workload, flush):
+        import ctypes as C
+        import torch
+        self.C, self.torch = C, torch
+        self.pkg, self.ctx, self.stream, self.rank, self.world, self.flush = pkg, ctx, stream, rank, world, flush
+        self.ffi, self.L = pkg._ffi, pkg._ffi.lib()
+        self.workload = workload
+        self.log_n, self.W, self.r, self.cap = WORKLOADS[workload]
+        self.n, self.N = 1 << self.log_n, 1 << (self.log_n + self.r)
+        self.by_rows = world > (1 << self.r)
+        S = pkg.sharding
+        if self.by_rows:
+            S.check_row_plan(self.cap, world)
+            self.split = S.column_split(self.W, world)
+            self.per_rows = self.N // world
+            self.peers = S.PeerRows(ctx, self.W * self.per_rows)
+        else:
+            S.check_plan(self.r, self.cap, world)
+            self.per_cols, self.split = S.uniform_column_split(self.W, world)
+            self.peers = S.PeerRows(ctx, world * self.per_cols * self.n)
+        self.c0, self.nc = self.split[rank]
+        self.peer_table = (self.ffi.vp * world)(*[self.ffi.vp(p) for p in self.peers.ptrs])
+        self.tiny = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.cap_local = torch.empty(((1 << self.cap) // world, 4), dtype=torch.int64, device="cuda")
+        self.cap_full = torch.empty((1 << self.cap, 4), dtype=torch.int64, device="cuda")
+        self.cudart = C.CDLL("libcudart.so.12")
+        # every rank holds the same trace (seed without the rank); only this rank's columns are ever touched
+        full = synth_values(self.W, self.n, 0xC0FFEE + 1)
+        self.host_mine = torch.empty((max(self.nc, 1), self.n), dtype=torch.int64).pin_memory()
+        if self.nc:
+            self.host_mine.numpy().view(np.uint64)[:self.nc] = full[self.c0:self.c0 + self.nc]
+        self.dev_mine = self.host_mine.cuda(non_blocking=True)
+        self.my_coeffs = torch.empty((max(self.nc, 1), self.n), dtype=torch.int64, device="cuda") if self.by_rows else None
+        self.full_values = full
+        self.batch = None
+
+    def free_prev(self):
+        if self.batch is not None:
+            self.L.nlc_batch_free(self.batch)
+            self.batch = None
+
+    def commit(self, src_cols):
+        import torch.distributed as dist
+        C, ffi, L, ctx = self.C, self.ffi, self.L, self.ctx
+        self.free_prev()
+        h = ffi.vp()
+        if self.by_rows:
+            ctx._check(L.nlc_lde_columns_scatter_dev(ctx._h, ffi.vp(src_cols.data_ptr()), self.nc, self.log_n, self.r, 1,
+                                                     ffi.vp(self.my_coeffs.data_ptr()), None, self.world, self.peer_table,
+                                                     self.c0))
+            dist.all_reduce(self.tiny)  # barrier in stream order: every rank's stores have landed
+            ctx._check(L.nlc_commit_from_lde_rows_dev(ctx._h, ffi.vp(self.peers.own), self.W, self.log_n, self.r, self.cap,
+                                                      self.rank, self.world, C.byref(h)))
+        else:
+            if self.nc:
+                ctx._check(L.nlc_ifft_columns_bcast_dev(ctx._h, ffi.vp(src_cols.data_ptr()), self.nc, self.log_n, self.c0,
+                                                        self.world, self.peer_table))
+            dist.all_reduce(self.tiny)
+            ctx._check(L.nlc_commit_from_coeffs_shard_dev(ctx._h, ffi.vp(self.peers.own), self.W, self.log_n, self.r,
+                                                          self.cap, self.rank, self.world, C.byref(h)))
+        self.batch = h
+        self.cudart.cudaMemcpyAsync(C.c_void_p(self.cap_local.data_ptr()), C.c_void_p(L.nlc_batch_cap_dev(h)),
+                                    C.c_size_t(self.cap_local.numel() * 8), 3, C.c_void_p(self.stream.cuda_stream))
+        dist.all_gather_into_tensor(self.cap_full, self.cap_local)  # also the "buffers free" barrier for the next commit
+
+    def step_resident(self):
+        self.commit(self.dev_mine)
+
+    def step_e2e(self):
+        """this rank's columns from pinned host memory over PCIe, the full cap back on the host"""
+        self.commit(self.host_mine.cuda(non_blocking=True))
+        return self.cap_full.cpu().numpy().view(np.uint64)
+
+    def measure(self, steps):
+        import torch.distributed as dist
+        torch = self.torch
+        for _ in range(3):
+            self.flush.zero_()
+            self.step_resident()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(torch.cuda.current_device())
+        sampler.start()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        dist.barrier()
+        torch.cuda.synchronize()
+        for a, b in evs:
+            self.flush.zero_()
+            a.record(self.stream)
+            self.step_resident()
+            b.record(self.stream)
+        torch.cuda.synchronize()
+        dist.barrier()
+        clocks = sampler.stop()
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        # phases (this rank's CUDA events; max over ranks per phase)
+        self.ctx.timing_enable(True)
+        self.ctx.timing_read()
+        for _ in range(3):
+            self.flush.zero_()
+            self.step_resident()
+        ph = self.ctx.timing_read()
+        self.ctx.timing_enable(False)
+        k = max(ph["commits"], 1)
+        names = ["IFFT", "FFT + blinding", "leaf hashing", "digest levels"]
+        pt = torch.tensor([ph[nm] / k for nm in names], dtype=torch.float64, device="cuda")
+        dist.all_reduce(pt, op=dist.ReduceOp.MAX)
+        phases = {nm: float(v) for nm, v in zip(names, pt.tolist())}
+        # e2e: host columns in, cap out
+        for _ in range(2):
+            self.step_e2e()
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            cap_host = self.step_e2e()
+        torch.cuda.synchronize()
+        te = torch.tensor([(time.perf_counter() - t0) / steps * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        self.free_prev()
+        return ms, phases, float(te.item()), clocks, cap_host
+
+
+def n1_resident_ms(pkg, ctx, stream, workload, flush, values, steps=3):
+    """The same commit on ONE GPU, resident input, in this process: the denominator of the strong-scaling factor."""
+    import ctypes as C
+    import torch
+    ffi, L = pkg._ffi, pkg._ffi.lib()
+    log_n, W, r, cap = WORKLOADS[workload]
+    dev = torch.from_numpy(values.view(np.int64)).cuda()
+    torch.cuda.synchronize()
+    h = [None]
+
+    def step():
+        if h[0] is not None:
+            L.nlc_batch_free(h[0])
+        hh = ffi.vp()
+        ctx._check(L.nlc_commit_from_values_dev(ctx._h, ffi.vp(dev.data_ptr()), W, log_n, r, cap, C.byref(hh)))
+        h[0] = hh
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in evs:
+        flush.zero_()
+        a.record(stream)
+        step()
+        b.record(stream)
+    torch.cuda.synchronize()
+    cap_host = np.zeros((1 << cap, 4), np.uint64)
+    ctx._check(L.nlc_batch_cap(h[0], cap_host.ctypes.data_as(ffi.u64p)))
+    L.nlc_batch_free(h[0])
+    del dev
+    torch.cuda.empty_cache()
+    return sum(a.elapsed_time(b) for a, b in evs) / steps, cap_host
+
+
+def strong_scaling_block(pkg, ctx, stream, rank, world, flush, steps):
+    """`strong` of the bench line at N > 1: configs[1] and configs[3] as ONE commit over all ranks."""
+    import torch
+    import torch.distributed as dist
+    out = {}
+    for name in ("commit_2^16x135_r3_cap4", "commit_2^20x400_r1_cap4"):
+        log_n, W, r, cap = WORKLOADS[name]
+        if not (world > (1 << r) or world <= (1 << min(r, cap))):
+            continue
+        st = Strong(pkg, ctx, stream, rank, world, name, flush)
+        ms, phases, e2e_ms, clocks, cap_sharded = st.measure(max(3, min(steps, 10)))
+        n1_ms, cap_n1 = n1_resident_ms(pkg, ctx, stream, name, flush, st.full_values)
+        same = torch.tensor([int(np.array_equal(cap_sharded, cap_n1))], dtype=torch.int32, device="cuda")
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        resid = max(phases, key=phases.get)
+        accounted = sum(phases.values())
+        out[name] = {"split": ("column shards -> NTT stores into peers over NVLink -> leaf-row shards (8e.3)" if st.by_rows else
+                               "column-sharded upload + iFFT, coefficient all-gather by the iFFT's NVLink stores, coset shards (8e.2)"),
+                     "ms_per_commit": ms, "phases_ms_max_over_ranks": phases,
+                     "unaccounted_ms (barriers, cap all-gather, launch gaps)": ms - accounted,
+                     "e2e_ms": e2e_ms, "e2e_h2d_bytes_per_rank": 8 * st.nc * st.n, "n1_resident_ms_same_process": n1_ms,
+                     "speedup_vs_1gpu": n1_ms / ms, "efficiency": n1_ms / ms / world, "largest_phase": resid,
+                     "cap_equals_1gpu_commit_on_every_rank": bool(same.item()), "clocks": clocks}
+        st.peers.free()
+        del st
+        torch.cuda.empty_cache()
+        dist.barrier()
+    return out
+
+
+def sharded_parity_block(pkg, ctx, rank, world):
+    """Multi-GPU parity where the driver has the GPUs (tests/test_gpu_multi.py is skipped on its 1-GPU test box): one
+    coset-sharded (both forms) and one row-sharded (p2p and nccl) commit of small traces against the ORACLE (checker
+    leg, after every timed region): cap on every rank, this rank's leaves and digests."""
+    import torch
+    import torch.distributed as dist
+    O = graft.load_oracle()
+    P2, S = pkg.plonky2, pkg.sharding
+    res = {}
+    rng = np.random.default_rng(5)
+    cases = {"coset": (135, 12, 3, 4), "coset_bcast": (135, 12, 3, 4), "rows_p2p": (418, 12, 1, 4), "rows_nccl": (418, 12, 1, 4)}
+    refs = {}
+    for key, (W, log_n, r, cap) in cases.items():
+        shape = (W, log_n, r, cap)
+        if shape not in refs:
+            values = O.random_field(rng, (W, 1 << log_n))
+            refs[shape] = (values, O.commit_from_values(values, r, cap))
+        values, ref = refs[shape]
+        lo, hi = S.leaf_range(log_n, r, rank, world)
+        per_d = ref.digests.shape[0] // world
+        ok = True
+        try:
+            if key.startswith("coset"):
+                if world > (1 << r):
+                    res[key] = None
+                    continue
+                f = P2.PolynomialBatch.from_values_sharded if key == "coset" else P2.PolynomialBatch.from_values_coset_sharded
+                b = f(list(values), r, False, cap, ctx=ctx)
+            else:
+                b = P2.PolynomialBatch.from_values_row_sharded(list(values), r, False, cap, ctx=ctx, exchange=key.split("_")[1])
+            ok = (np.array_equal(b.merkle_tree.cap, ref.cap) and np.array_equal(b.merkle_tree.leaves, ref.leaves[lo:hi])
+                  and np.array_equal(b.merkle_tree.digests, ref.digests[per_d * rank:per_d * (rank + 1)]))
+            b.free()
+            del b
+        except Exception as e:  # a failing rank must not hang the others in a collective: report, then fail below
+            print(f"[rank {rank}] sharded parity {key}: {e!r}", file=sys.stderr, flush=True)
+            ok = False
+        t = torch.tensor([int(ok)], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        res[key] = bool(t.item())
+        dist.barrier()
+    return res
 
 
 def run_ours(args, rank, local_rank, world):
@@ -472,6 +733,10 @@ def run_ours(args, rank, local_rank, world):
                                 "peak": roofline["poseidon_perms_per_s"] * 100.0 / busiest[0], "unit": "permutations/s",
                                 "frac": busiest[0] / 100.0,
                                 "source": "ncu pipe-active cycles of profiles/traffic.json (capture of this kernel, this workload)"}
+        files, sha, cap_name = ncu_capture_meta(args.workload, "k_leaf_hash")
+        roofline["int_pipe"]["capture"] = cap_name
+        # the fraction is a property of the CAPTURED kernel: flag it when the kernel sources have changed since
+        roofline["int_pipe"]["stale_capture"] = (sha is None) or (kernel_source_hash(files) != sha)
     roofline_ntt = {"bound": "hbm", "kernel": "k_ntt_* (iFFT + 2^r coset NTTs into leaf rows)",
                     "achieved": ab["ntt"] / (ntt_ms * 1e-3) / 1e9 if ntt_ms > 0 else 0.0, "peak": peak, "unit": "GB/s",
                     "ms": ntt_ms}
@@ -528,6 +793,13 @@ def run_ours(args, rank, local_rank, world):
                         "sample": f"1 full commit of {args.workload} ({dt:.2f} s); cap equals the GPU's: {ok}",
                         "port_quality": oracle_quality(O)}
 
+    strong = parity = None
+    if world > 1 and not sharded and not args.no_strong:
+        strong = strong_scaling_block(pkg, ctx, stream, rank, world, flush, args.steps)
+        ctx.set_stream(None)  # the mirror's sharded commits bring their own stream
+        parity = sharded_parity_block(pkg, ctx, rank, world)
+        ctx.set_stream(stream.cuda_stream)
+
     if rank == 0:
         line = {"metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": value,
                 "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -546,9 +818,16 @@ def run_ours(args, rank, local_rank, world):
                 "commit_algorithmic_gbs": commit_gbs, "commit_frac_of_hbm": commit_gbs / peak,
                 "phases_ms": {kk: (v / k if kk != "commits" else v) for kk, v in phases.items()},
                 "cpu_baseline": cpu_baseline}
+        if strong is not None:
+            line["strong"] = strong
+            line["sharded_parity"] = parity
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and any(v is False for v in parity.values()):
+        raise SystemExit(f"bench.py: sharded parity FAILED: {parity}")
+    if strong is not None and not all(v["cap_equals_1gpu_commit_on_every_rank"] for v in strong.values()):
+        raise SystemExit("bench.py: a sharded commit's cap differs from the single-GPU commit")
 
 
 def main():
@@ -562,6 +841,7 @@ def main():
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
                          "of one independent commit per rank")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the single-commit strong-scaling block")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl", "nccl-pack"],
                     help="--shard-commit with more ranks than cosets (SURVEY 8e.3): how leaf rows reach their shard")
     ap.add_argument("--ref-sample-log-rows", type=int, default=None,

@@ -81,6 +81,16 @@ int nlc_commit_from_values(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_c
  * call site vendor/starkyx/starkyx/src/plonky2/stark/prover.rs:171-178. */
 int nlc_commit_from_coeffs(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
                            int cap_height, nlc_batch** out);
+/* from_values that ALSO fills the host images of the struct fields a patched plonky2 keeps, with the
+ * device->host traffic hidden under the commit: coeffs_out_cols = `polynomials` (n_cols host vectors of n, what
+ * proof.rs:307-310 reads), leaves_out = merkle_tree.leaves flattened (N x n_cols row-major), digests_out =
+ * merkle_tree.digests, cap_out = merkle_tree.cap; any of them may be NULL.  The coefficients of a column chunk cross PCIe
+ * as soon as its iFFT is done, its slab of leaf rows behind its coset NTTs -- both while later chunks upload / transform
+ * and while the leaves are hashed -- and the digests + cap at the end.  Same results as nlc_commit_from_values followed by
+ * nlc_batch_coeffs / _leaves / _digests / _cap (which pay the copies after the commit). */
+int nlc_commit_from_values_materialised(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                                        int cap_height, uint64_t* const* coeffs_out_cols, uint64_t* leaves_out,
+                                        uint64_t* digests_out, uint64_t* cap_out, nlc_batch** out);
 /* Same, input already resident in HBM as one n_cols x n matrix (column j at values_dev + j*n). */
 int nlc_commit_from_values_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n, int rate_bits,
                                int cap_height, nlc_batch** out);
@@ -109,6 +119,16 @@ int nlc_commit_from_values_shard(nlc_ctx* ctx, const uint64_t* const* cols, size
 int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n,
                                      int rate_bits, int cap_height, size_t shard_idx, size_t n_shards,
                                      nlc_batch** out);
+/* The same split without replicating the iFFT or the upload (SURVEY.md 8e.2 "column-sharded iFFT + all-gather of the
+ * coefficient matrix"): rank p uploads and inverse-transforms ONLY its columns [col0, col0 + n_cols) and the transform's
+ * own stores put every coefficient into all n_peers coefficient matrices (peer_coeffs[q] = rank q's n_cols_total x n
+ * buffer, nlc_peer_alloc / nlc_peer_open; this rank's own buffer included) -- the all-gather rides on the last NTT pass
+ * over NVLink, no NCCL call.  After one barrier in stream order every rank holds the whole matrix and calls
+ * nlc_commit_from_coeffs_shard_dev for its cosets; the batch reads coeffs_dev in place (it must outlive the batch). */
+int nlc_ifft_columns_bcast_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n, size_t col0,
+                               size_t n_peers, uint64_t* const* peer_coeffs);
+int nlc_commit_from_coeffs_shard_dev(nlc_ctx* ctx, uint64_t* coeffs_dev, size_t n_cols, int log_n, int rate_bits,
+                                     int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out);
 /* SURVEY.md 8(e).3 -- more GPUs than cosets (starky commits at rate_bits 1 on 4 or 8 GPUs): shard by COLUMN for the
  * transforms, exchange once, shard by leaf ROW for the tree.
  *   1. every rank, for the columns it owns: nlc_lde_columns_dev -- iFFT (is_values) and the 2^rate_bits coset NTTs of

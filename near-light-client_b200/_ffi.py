@@ -59,11 +59,16 @@ SIGNATURES = {
     "nlc_timing_read": (C.c_int, [vp, C.POINTER(CTiming)]),
     "nlc_commit_from_values": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_coeffs": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
+    "nlc_commit_from_values_materialised": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int,
+                                                      C.POINTER(u64p), u64p, u64p, u64p, C.POINTER(vp)]),
     "nlc_commit_from_values_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]),
     "nlc_commit_from_values_shard": (C.c_int, [vp, C.POINTER(u64p), C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                                C.c_size_t, C.POINTER(vp)]),
     "nlc_commit_from_values_shard_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                                    C.c_size_t, C.POINTER(vp)]),
+    "nlc_ifft_columns_bcast_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_size_t, C.c_size_t, C.POINTER(vp)]),
+    "nlc_commit_from_coeffs_shard_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
+                                                   C.POINTER(vp)]),
     "nlc_lde_columns_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, vp, vp]),
     "nlc_commit_from_lde_rows_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t,
                                                C.POINTER(vp)]),

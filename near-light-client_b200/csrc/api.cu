@@ -103,13 +103,66 @@ nlc_batch* commit_dev(nlc_ctx* ctx, const u64* src_dev, bool is_values, size_t W
     return b;
 }
 
+// Host images of the struct fields, filled WHILE the commit runs (all optional)
+struct Materialise {
+    u64* const* coeffs_cols = nullptr; // polynomials: W host vectors of n
+    u64* leaves = nullptr;             // merkle_tree.leaves flattened: N x W row-major
+    u64* digests = nullptr;            // merkle_tree.digests
+    u64* cap = nullptr;                // merkle_tree.cap
+    bool any() const { return coeffs_cols || leaves || digests || cap; }
+};
+
+// out[r * nc + (c - c0)] = lde[c * N + r] for c in [c0, c0 + nc): the row-major slab of a column range
+__global__ void k_leaf_rows_cols(const u64* __restrict__ lde, size_t N, size_t c0, size_t nc, u64* __restrict__ out) {
+    __shared__ u64 tile[32][33];
+    const size_t r0 = (size_t)blockIdx.x * 32, cc0 = (size_t)blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t c = cc0 + i, r = r0 + threadIdx.x;
+        if (r < N && c < nc) tile[i][threadIdx.x] = lde[(c0 + c) * N + r];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        size_t r = r0 + i, c = cc0 + threadIdx.x;
+        if (r < N && c < nc) out[r * nc + c] = tile[threadIdx.x][i];
+    }
+}
+
+// Runs on the downloader thread: D2H of `bytes` contiguous device bytes into host segments / a strided host matrix,
+// after `after` has completed; pinned destinations take plain asynchronous copies, pageable ones the stager.
+void dl_wait(nlc_ctx* ctx, cudaEvent_t after) { NLC_CUDA(cudaStreamWaitEvent(ctx->dl_stream, after, 0)); }
+void dl_segments(nlc_ctx* ctx, const u64* src, const std::vector<HostStager::Seg>& segs) {
+    if (segs.empty()) return;
+    if (HostStager::pageable(segs[0].dst)) {
+        ctx->dl_stager.download(ctx->dl_stream, src, segs);
+    } else {
+        const char* s = (const char*)src;
+        for (const auto& g : segs) {
+            NLC_CUDA(cudaMemcpyAsync(g.dst, s, g.len, cudaMemcpyDeviceToHost, ctx->dl_stream));
+            s += g.len;
+        }
+        NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
+    }
+}
+void dl_rows(nlc_ctx* ctx, const u64* src_packed, u64* dst, size_t dst_pitch, size_t row_bytes, size_t n_rows) {
+    if (HostStager::pageable(dst)) {
+        ctx->dl_stager.download_rows(ctx->dl_stream, src_packed, dst, dst_pitch, row_bytes, n_rows);
+    } else {
+        NLC_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src_packed, row_bytes, row_bytes, n_rows, cudaMemcpyDeviceToHost, ctx->dl_stream));
+        NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
+    }
+}
+
 int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int rate_bits, int cap_height,
-                bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0) {
+                bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0, const Materialise* mat = nullptr) {
     if (!ctx) return 1;
     return nlc_guarded(ctx, [&] {
         CtxGuard g(ctx);
         NLC_CHECK(out != nullptr, "null output handle");
         *out = nullptr;
+        const bool want = mat && mat->any();
+        size_t n_dl_ev = 0;
+        u64* slab = nullptr; // row-major slab of one column chunk (leaves materialisation), reused chunk after chunk
+        if (want) ctx->downloader.start(ctx->device);
         NLC_CHECK(W > 0 && log_n >= 0 && log_n <= 32, "bad shape");
         const size_t n = (size_t)1 << log_n;
         nlc_batch* b = batch_alloc(ctx, W, log_n, rate_bits, cap_height, shard_log, shard_idx);
@@ -131,6 +184,59 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
             DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
+            size_t slab_cols = 0;
+            if (want && mat->leaves) { // the widest chunk the loop below can form
+                slab_cols = stream_hash ? std::min(W, std::max<size_t>(chunk_cap + 16, 16)) : std::min(W, chunk);
+                slab = ctx->dmalloc(N * slab_cols);
+            }
+            // jobs for the downloader thread (it owns dl_stream): after `ev`, drain one piece
+            auto after_compute = [&]() {
+                cudaEvent_t e = ctx->dl_event(n_dl_ev++);
+                NLC_CUDA(cudaEventRecord(e, ctx->stream));
+                return e;
+            };
+            auto dl_coeffs = [&](size_t c0, size_t nc) {
+                if (!want || !mat->coeffs_cols) return;
+                cudaEvent_t e = after_compute();
+                std::vector<HostStager::Seg> segs;
+                for (size_t j = c0; j < c0 + nc; j++) segs.push_back({mat->coeffs_cols[j], n * sizeof(u64)});
+                const u64* src = b->coeffs + c0 * n;
+                ctx->downloader.submit([ctx, e, src, segs] {
+                    dl_wait(ctx, e);
+                    dl_segments(ctx, src, segs);
+                });
+            };
+            auto dl_leaves = [&](size_t c0, size_t nc) {
+                if (!want || !mat->leaves) return;
+                NLC_CHECK(nc <= slab_cols, "leaf slab too narrow");
+                cudaEvent_t e = after_compute();
+                const u64* lde = b->lde;
+                u64* dst = mat->leaves + c0;
+                u64* sl = slab;
+                ctx->downloader.submit([ctx, e, lde, N, c0, nc, W, sl, dst] {
+                    dl_wait(ctx, e);
+                    dim3 grid((unsigned)((N + 31) / 32), (unsigned)((nc + 31) / 32));
+                    k_leaf_rows_cols<<<grid, dim3(32, 8), 0, ctx->dl_stream>>>(lde, N, c0, nc, sl);
+                    ctx->launches.fetch_add(1, std::memory_order_relaxed);
+                    NLC_CUDA(cudaGetLastError());
+                    dl_rows(ctx, sl, dst, W * sizeof(u64), nc * sizeof(u64), N);
+                });
+            };
+            auto dl_tree = [&]() {
+                if (!want || (!mat->digests && !mat->cap)) return;
+                cudaEvent_t e = after_compute();
+                const u64 *dg = b->digests, *cp = b->cap;
+                const size_t dw = b->n_digest_words, cw = (size_t)4 << b->cap_local();
+                u64 *dgo = mat->digests, *cpo = mat->cap;
+                ctx->downloader.submit([ctx, e, dg, cp, dw, cw, dgo, cpo] {
+                    dl_wait(ctx, e);
+                    if (dgo && dw) dl_segments(ctx, dg, {{dgo, dw * sizeof(u64)}});
+                    if (cpo) {
+                        NLC_CUDA(cudaMemcpyAsync(cpo, cp, cw * sizeof(u64), cudaMemcpyDeviceToHost, ctx->dl_stream));
+                        NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
+                    }
+                });
+            };
             u64* stage = is_values ? vals.p : b->coeffs;
             NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream)); // buffers allocated on the compute stream
             NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
@@ -152,20 +258,31 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                 NLC_CUDA(cudaEventRecord(e, ctx->copy_stream));
                 NLC_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0));
                 if (is_values) batch_ifft_cols(b, vals.p + c0 * n, c0, nc);
+                dl_coeffs(c0, nc); // the coefficients of this chunk cross PCIe while later chunks compute
                 batch_lde_cols(b, c0, nc);
+                dl_leaves(c0, nc); // ... and so does its slab of leaf rows, under the hashing
                 if (stream_hash)
                     merkle_leaf_absorb(ctx, b->lde, N, N, c0, nc, c0 == 0, c0 + nc == W, sponge.p, b->cap_local(),
                                        b->digests, b->cap);
             }
-            if (stream_hash) {
+            if (stream_hash)
                 merkle_levels(ctx, N, b->cap_local(), b->digests, b->cap);
-                sync(ctx);
-                *out = b;
-                return;
-            }
-            batch_tree(b);
+            else
+                batch_tree(b);
+            dl_tree();
             sync(ctx);
+            if (want) ctx->downloader.drain();
+            ctx->dfree(slab);
+            slab = nullptr;
         } catch (...) {
+            if (want) {
+                try {
+                    ctx->downloader.drain();
+                } catch (...) {
+                }
+                cudaStreamSynchronize(ctx->dl_stream);
+            }
+            ctx->dfree(slab);
             // uploads of earlier chunks may still be in flight on the copy stream into `vals` / b->coeffs: the
             // stream-ordered frees below are ordered on the compute stream only, so drain the copies first or the
             // pool could hand this memory to the next commit while a stale DMA lands in it
@@ -217,6 +334,7 @@ int nlc_init(int device, nlc_ctx** out) {
         NLC_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
         ctx->stream = ctx->own_stream;
         NLC_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        NLC_CUDA(cudaStreamCreateWithFlags(&ctx->dl_stream, cudaStreamNonBlocking));
         NLC_CUDA(cudaEventCreateWithFlags(&ctx->ev_ready, cudaEventDisableTiming));
         cudaMemPool_t pool;
         NLC_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -240,7 +358,11 @@ void nlc_destroy(nlc_ctx* ctx) {
         cudaStreamSynchronize(ctx->stream);
         for (auto& kv : ctx->tables) cudaFree(kv.second);
         if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->downloader.shutdown();
         ctx->stager.destroy();
+        ctx->dl_stager.destroy();
+        if (ctx->dl_stream) cudaStreamDestroy(ctx->dl_stream);
+        for (cudaEvent_t e : ctx->dl_events) cudaEventDestroy(e);
         if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
         if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
         if (ctx->ev_ready) cudaEventDestroy(ctx->ev_ready);
@@ -336,6 +458,16 @@ int nlc_commit_from_coeffs_dev(nlc_ctx* ctx, const uint64_t* coeffs_dev, size_t 
         *out = commit_dev(ctx, coeffs_dev, false, n_cols, log_n, rate_bits, cap_height);
     });
 }
+int nlc_commit_from_values_materialised(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
+                                        int cap_height, uint64_t* const* coeffs_out_cols, uint64_t* leaves_out,
+                                        uint64_t* digests_out, uint64_t* cap_out, nlc_batch** out) {
+    Materialise m;
+    m.coeffs_cols = coeffs_out_cols;
+    m.leaves = leaves_out;
+    m.digests = digests_out;
+    m.cap = cap_out;
+    return commit_host(ctx, cols, n_cols, log_n, rate_bits, cap_height, true, out, 0, 0, &m);
+}
 // ---- 8e.2: one coset shard of a commit ----
 static int shard_log_of(size_t n_shards) {
     int l = 0;
@@ -359,6 +491,31 @@ int nlc_commit_from_values_shard_dev(nlc_ctx* ctx, const uint64_t* values_dev, s
         const int sl = shard_log_of(n_shards);
         NLC_CHECK(sl >= 0, "n_shards must be a power of two");
         *out = commit_dev(ctx, values_dev, true, n_cols, log_n, rate_bits, cap_height, sl, shard_idx);
+    });
+}
+int nlc_ifft_columns_bcast_dev(nlc_ctx* ctx, const uint64_t* values_dev, size_t n_cols, int log_n, size_t col0,
+                               size_t n_peers, uint64_t* const* peer_coeffs) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(values_dev && peer_coeffs, "null argument");
+        NLC_CHECK(n_cols > 0, "PolynomialBatch: at least one polynomial required");
+        NLC_CHECK(log_n >= 0 && log_n <= 32, "log_n out of range (two-adicity is 32)");
+        NLC_CHECK(n_peers >= 1 && n_peers <= 16, "1..16 coefficient buffers");
+        for (size_t p = 0; p < n_peers; p++) NLC_CHECK(peer_coeffs[p] != nullptr, "null peer buffer");
+        ifft_columns_bcast_dev(ctx, values_dev, n_cols, log_n, col0, n_peers, peer_coeffs);
+    });
+}
+int nlc_commit_from_coeffs_shard_dev(nlc_ctx* ctx, uint64_t* coeffs_dev, size_t n_cols, int log_n, int rate_bits,
+                                     int cap_height, size_t shard_idx, size_t n_shards, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out && coeffs_dev, "null argument");
+        *out = nullptr;
+        const int sl = shard_log_of(n_shards);
+        NLC_CHECK(sl >= 0, "n_shards must be a power of two");
+        *out = commit_from_coeffs_shard_dev(ctx, coeffs_dev, n_cols, log_n, rate_bits, cap_height, sl, shard_idx);
     });
 }
 // ---- 8e.3: column shards for the transforms, exchange (caller), leaf-row shards for the tree ----

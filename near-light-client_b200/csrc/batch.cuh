@@ -20,6 +20,8 @@ struct nlc_batch {
     // the all-to-all: the LDE lives in the caller's receive buffer (not owned) and the coefficients stay with the
     // ranks that own the columns (coeffs == nullptr here).
     bool owns_lde = true;
+    // Coefficients that live in a caller-owned buffer (the all-gathered coefficient matrix of a coset-sharded commit)
+    bool owns_coeffs = true;
     size_t n_local() const { return ((size_t)1 << (log_n + rate_bits)) >> shard_log; }
     int cap_local() const { return cap_height - shard_log; }
 };
@@ -57,6 +59,12 @@ void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n,
                      u64* coeffs_out_dev, u64* lde_out_dev, const NttScatter* sc = nullptr, size_t col0 = 0);
 nlc_batch* commit_from_lde_rows_dev(nlc_ctx* ctx, u64* lde_rows_dev, size_t W, int log_n, int rate_bits, int cap_height,
                                     int shard_log, size_t shard_idx);
+// iFFT of the columns one rank owns, every result stored into all n_peers coefficient matrices
+void ifft_columns_bcast_dev(nlc_ctx* ctx, const u64* values_dev, size_t n_cols, int log_n, size_t col0, size_t n_peers,
+                            u64* const* peer_coeffs);
+// ... and this rank's coset shard of from_coeffs over the gathered matrix (read in place, not copied)
+nlc_batch* commit_from_coeffs_shard_dev(nlc_ctx* ctx, u64* coeffs_dev, size_t W, int log_n, int rate_bits, int cap_height,
+                                        int shard_log, size_t shard_idx);
 // SURVEY.md 8f.1 (prover.rs:253-358 without the AIR evaluation)
 std::vector<u64> zero_poly_on_coset_inverses(int log_n, int qdb);
 void coset_points(nlc_ctx* ctx, int log_size, u64* out_dev);

@@ -161,7 +161,7 @@ nlc_batch* batch_alloc(nlc_ctx* ctx, size_t W, int log_n, int rate_bits, int cap
 void batch_release(nlc_batch* b) {
     if (!b) return;
     nlc_ctx* ctx = b->ctx;
-    ctx->dfree(b->coeffs);
+    if (b->owns_coeffs) ctx->dfree(b->coeffs);
     if (b->owns_lde) ctx->dfree(b->lde);
     ctx->dfree(b->digests);
     ctx->dfree(b->cap);
@@ -400,6 +400,66 @@ void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n,
         throw;
     }
     ctx->dfree(own);
+}
+
+void ifft_columns_bcast_dev(nlc_ctx* ctx, const u64* values_dev, size_t n_cols, int log_n, size_t col0, size_t n_peers,
+                            u64* const* peer_coeffs) {
+    const size_t n = (size_t)1 << log_n;
+    u64* scratch = nullptr;
+    const size_t sw = ntt_scratch_words(n_cols, log_n);
+    if (sw) scratch = ctx->dmalloc(sw);
+    NttJob job;
+    job.src = values_dev;
+    job.src_stride = n;
+    job.n_cols = n_cols;
+    job.log_n = log_n;
+    job.inverse = true;
+    job.dst = peer_coeffs[0] + col0 * n; // unused by the stores, kept for the out-of-place check
+    job.dst_stride = n;
+    job.scratch = scratch;
+    job.scatter.n_bcast = (int)n_peers;
+    for (size_t p = 0; p < n_peers; p++) job.scatter.peer[p] = peer_coeffs[p] + col0 * n;
+    ctx->phase_begin(0);
+    try {
+        ntt_run(ctx, job);
+    } catch (...) {
+        ctx->dfree(scratch);
+        throw;
+    }
+    ctx->phase_end();
+    ctx->dfree(scratch);
+}
+
+nlc_batch* commit_from_coeffs_shard_dev(nlc_ctx* ctx, u64* coeffs_dev, size_t W, int log_n, int rate_bits, int cap_height,
+                                        int shard_log, size_t shard_idx) {
+    NLC_CHECK(W > 0, "PolynomialBatch: at least one polynomial required");
+    NLC_CHECK(log_n >= 0 && rate_bits >= 0 && log_n + rate_bits <= 32, "degree_log + rate_bits exceeds the two-adicity");
+    NLC_CHECK(cap_height >= 0 && cap_height <= log_n + rate_bits, "cap_height should be at most log2(leaves.len())");
+    NLC_CHECK(shard_log >= 0 && shard_log <= rate_bits && shard_log <= cap_height,
+              "coset sharding needs n_shards <= 2^rate_bits and n_shards <= 2^cap_height");
+    NLC_CHECK(shard_idx < ((size_t)1 << shard_log), "shard index out of range");
+    nlc_batch* b = new nlc_batch();
+    b->ctx = ctx;
+    b->W = W;
+    b->log_n = log_n;
+    b->rate_bits = rate_bits;
+    b->cap_height = cap_height;
+    b->shard_log = shard_log;
+    b->shard_idx = shard_idx;
+    b->coeffs = coeffs_dev;
+    b->owns_coeffs = false;
+    const size_t N = b->n_local();
+    try {
+        b->lde = ctx->dmalloc(W * N);
+        b->n_digest_words = 8 * (N - ((size_t)1 << b->cap_local()));
+        b->digests = ctx->dmalloc(b->n_digest_words);
+        b->cap = ctx->dmalloc((size_t)4 << b->cap_local());
+        batch_lde_and_tree(b);
+    } catch (...) {
+        batch_release(b);
+        throw;
+    }
+    return b;
 }
 
 // The tree over the leaves [shard_idx, shard_idx + 1) * N >> shard_log, whose rows (all W columns) sit column-major in

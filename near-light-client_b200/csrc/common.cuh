@@ -61,6 +61,21 @@ struct nlc_ctx {
     size_t table_bytes = 0;
     // small pinned staging area + device scratch for transcript-sized transfers
     HostStager stager; // pageable host columns -> HBM through pinned slots (staging.h)
+    // a commit that also materialises struct fields on the host (nlc_commit_from_values_materialised): device -> host
+    // traffic runs on its own stream, through its own stager, driven by a worker thread while the caller's thread
+    // keeps feeding the compute stream
+    HostStager dl_stager;
+    Downloader downloader;
+    cudaStream_t dl_stream = nullptr;
+    std::vector<cudaEvent_t> dl_events;
+    cudaEvent_t dl_event(size_t i) {
+        while (dl_events.size() <= i) {
+            cudaEvent_t e;
+            NLC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            dl_events.push_back(e);
+        }
+        return dl_events[i];
+    }
     u64* pinned = nullptr;
     size_t pinned_words = 0;
     int sm_count = 148;
@@ -166,6 +181,9 @@ struct NttScatter {
     int log_per = -1; // < 0: off
     size_t shard_stride = 0;
     u64* peer[16] = {};
+    // NATURAL output only: store every result into n_bcast buffers (peer[0..n_bcast), same offsets) instead of dst --
+    // the all-gather of a column-sharded iFFT done by the transform's own stores over NVLink
+    int n_bcast = 0;
 };
 struct NttJob {
     const u64* src = nullptr;

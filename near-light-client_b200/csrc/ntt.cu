@@ -233,7 +233,11 @@ k_ntt_lo(const u64* __restrict__ src, size_t src_stride, int log_n, int S, int l
             if (scale != 1) v = gl::mul(v, scale);
             const size_t k = ((size_t)brev(q, S) << log_nb) + ((size_t)blockIdx.x << log_G) + g;
             if (post) v = gl::mul(v, post[k]);
-            dst[blockIdx.y * dst_stride + k] = v;
+            if (sc.n_bcast == 0) {
+                dst[blockIdx.y * dst_stride + k] = v;
+            } else {
+                for (int p = 0; p < sc.n_bcast; p++) sc.peer[p][blockIdx.y * dst_stride + k] = v;
+            }
         }
     }
 }
@@ -389,7 +393,12 @@ k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64*
             if (scale != 1) v = gl::mul(v, scale);
             const size_t k = ((size_t)brev(q, S) << log_nb) + g;
             if (post) v = gl::mul(v, __ldg(post + ((size_t)blockIdx.x << LOG_G) + k));
-            out[k] = v;
+            if (sc.n_bcast == 0) {
+                out[k] = v;
+            } else { // every rank's coefficient matrix receives this rank's columns (local store + NVLink stores)
+                const size_t off = blockIdx.y * dst_stride + ((size_t)blockIdx.x << LOG_G) + k;
+                for (int p = 0; p < sc.n_bcast; p++) sc.peer[p][off] = v;
+            }
         }
     }
 }
@@ -546,13 +555,13 @@ void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
             launch_lo_f<OUT_COLS, false>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst,
                                          job.dst_stride, job.row_base, job.col0, job.scatter);
     } else {
-        NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
+        NLC_CHECK((const void*)cur != (const void*)job.dst || job.scatter.n_bcast, "ntt_run: NATURAL output must be out of place");
         if (inv)
             launch_lo_f<OUT_NATURAL, true>(ctx, S, grid, cur, cur_stride, log_n, post, scale, roots, job.dst, job.dst_stride,
-                                           0, 0, NttScatter());
+                                           0, 0, job.scatter);
         else
             launch_lo_f<OUT_NATURAL, false>(ctx, S, grid, cur, cur_stride, log_n, post, scale, roots, job.dst,
-                                            job.dst_stride, 0, 0, NttScatter());
+                                            job.dst_stride, 0, 0, job.scatter);
     }
 }
 } // namespace
@@ -632,13 +641,13 @@ void ntt_run(nlc_ctx* ctx, const NttJob& job) {
                        job.row_width, job.row_base, job.col0, NttScatter());
         }
     } else {
-        NLC_CHECK((const void*)cur != (const void*)job.dst, "ntt_run: NATURAL output must be out of place");
+        NLC_CHECK((const void*)cur != (const void*)job.dst || job.scatter.n_bcast, "ntt_run: NATURAL output must be out of place");
         if (log_G > log_nb) log_G = log_nb;
         dim3 grid((unsigned)((n >> S) >> log_G), (unsigned)job.n_cols);
         size_t smem = ((size_t)1 << log_G) * pitch * sizeof(u64);
         auto k_lo = inv ? k_ntt_lo<OUT_NATURAL, true> : k_ntt_lo<OUT_NATURAL, false>;
         NLC_LAUNCH(ctx, k_lo, grid, NTT_THREADS, smem, cur, cur_stride, log_n, S, log_G, 0,
                    plan_steps(S), job.n_cols, lo_pre, post, scale, roots, job.dst, job.dst_stride, (size_t)0,
-                   (size_t)0, (size_t)0, NttScatter());
+                   (size_t)0, (size_t)0, job.scatter);
     }
 }

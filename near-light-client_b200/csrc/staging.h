@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 
 #include <condition_variable>
+#include <deque>
+#include <exception>
 #include <cstdlib>
 #include <cstring>
 #include <functional>
@@ -88,10 +90,12 @@ struct HostStager {
         char* dst;
         const char* src;
         size_t len;
-        size_t rows = 1, src_pitch = 0; // rows > 1: `rows` pieces of `len` bytes, src_pitch apart, packed at dst
+        size_t rows = 1, src_pitch = 0; // rows > 1: `rows` pieces of `len` bytes, src_pitch apart (0: packed) ...
+        size_t dst_pitch = 0;           // ... written dst_pitch apart (0: packed)
     };
     static void run_granule(const Granule& g) {
-        for (size_t r = 0; r < g.rows; r++) memcpy(g.dst + r * g.len, g.src + r * g.src_pitch, g.len);
+        const size_t sp = g.src_pitch ? g.src_pitch : g.len, dp = g.dst_pitch ? g.dst_pitch : g.len;
+        for (size_t r = 0; r < g.rows; r++) memcpy(g.dst + r * dp, g.src + r * sp, g.len);
     }
     std::vector<Granule> pending;
     CopyPool* pool = nullptr;
@@ -206,6 +210,49 @@ struct HostStager {
         }
     }
 
+    // device -> pageable host, strided destination: n_rows packed rows of row_bytes at device address `src` go to
+    // dst + r * dst_pitch (a column range of a row-major host matrix).  Synchronous, pipelined like download().
+    void download_rows(cudaStream_t stream, const void* src, void* dst, size_t dst_pitch, size_t row_bytes, size_t n_rows) {
+        init();
+        flush(stream);
+        if (!row_bytes || !n_rows) return;
+        const size_t rows_per_slot = SLOT_BYTES / row_bytes;
+        if (rows_per_slot == 0) throw std::runtime_error("HostStager: row wider than a staging slot");
+        const size_t rows_per_granule = GRANULE / row_bytes ? GRANULE / row_bytes : 1;
+        const char* s = (const char*)src;
+        size_t issued = 0, drained = 0;
+        int head = cur, tail = cur;
+        size_t rows_of[N_SLOTS] = {}, first_of[N_SLOTS] = {};
+        while (drained < n_rows) {
+            while (issued < n_rows && !(issued > drained && head == tail)) {
+                if (busy[head]) {
+                    cudaEventSynchronize(ev[head]);
+                    busy[head] = false;
+                }
+                const size_t take = n_rows - issued < rows_per_slot ? n_rows - issued : rows_per_slot;
+                if (cudaMemcpyAsync(slot[head], s + issued * row_bytes, take * row_bytes, cudaMemcpyDeviceToHost, stream) != cudaSuccess)
+                    throw std::runtime_error("HostStager: cudaMemcpyAsync (D2H) failed");
+                cudaEventRecord(ev[head], stream);
+                rows_of[head] = take;
+                first_of[head] = issued;
+                issued += take;
+                head = (head + 1) % N_SLOTS;
+            }
+            cudaEventSynchronize(ev[tail]);
+            pending.clear();
+            for (size_t o = 0; o < rows_of[tail]; o += rows_per_granule) {
+                const size_t k = rows_of[tail] - o < rows_per_granule ? rows_of[tail] - o : rows_per_granule;
+                pending.push_back({(char*)dst + (first_of[tail] + o) * dst_pitch, (const char*)slot[tail] + o * row_bytes,
+                                   row_bytes, k, 0, dst_pitch});
+            }
+            pool->parallel_for(pending.size(), [&](size_t i) { run_granule(pending[i]); });
+            pending.clear();
+            drained += rows_of[tail];
+            tail = (tail + 1) % N_SLOTS;
+        }
+        cur = head;
+    }
+
     // device -> pageable host: `segs` lists the host destinations of consecutive device bytes starting at `src`
     // (one segment = one Vec of the caller).  DMA into slot k+1 overlaps the host threads scattering slot k.
     // Synchronous: the data is in place on return.
@@ -257,5 +304,71 @@ struct HostStager {
             tail = (tail + 1) % N_SLOTS;
         }
         cur = head;
+    }
+};
+
+// A worker thread that runs device->host materialisation jobs in FIFO order while the calling thread keeps feeding the
+// compute stream (a commit that also hands back `polynomials` / `leaves` / `digests`): each job typically waits for a
+// CUDA event on the worker's own stream, then drains a buffer through the worker's own HostStager.
+struct Downloader {
+    std::thread worker;
+    std::mutex mu;
+    std::condition_variable cv_job, cv_idle;
+    std::deque<std::function<void()>> jobs;
+    bool stop = false, busy = false;
+    std::exception_ptr error;
+    int device = 0;
+
+    void start(int dev) {
+        if (worker.joinable()) return;
+        device = dev;
+        worker = std::thread([this] { run(); });
+    }
+    void run() {
+        cudaSetDevice(device);
+        std::unique_lock<std::mutex> l(mu);
+        for (;;) {
+            cv_job.wait(l, [&] { return stop || !jobs.empty(); });
+            if (stop && jobs.empty()) return;
+            std::function<void()> f = std::move(jobs.front());
+            jobs.pop_front();
+            busy = true;
+            l.unlock();
+            try {
+                if (!error) f(); // after a failure the remaining jobs of the call are dropped
+            } catch (...) {
+                std::lock_guard<std::mutex> g(mu);
+                if (!error) error = std::current_exception();
+            }
+            l.lock();
+            busy = false;
+            if (jobs.empty()) cv_idle.notify_all();
+        }
+    }
+    void submit(std::function<void()> f) {
+        {
+            std::lock_guard<std::mutex> l(mu);
+            jobs.push_back(std::move(f));
+        }
+        cv_job.notify_one();
+    }
+    // waits until every submitted job has run; rethrows the first failure
+    void drain() {
+        std::unique_lock<std::mutex> l(mu);
+        cv_idle.wait(l, [&] { return jobs.empty() && !busy; });
+        if (error) {
+            std::exception_ptr e = error;
+            error = nullptr;
+            std::rethrow_exception(e);
+        }
+    }
+    void shutdown() {
+        if (!worker.joinable()) return;
+        {
+            std::lock_guard<std::mutex> l(mu);
+            stop = true;
+        }
+        cv_job.notify_all();
+        worker.join();
     }
 };

@@ -665,6 +665,69 @@ class PolynomialBatch:
         return b
 
     @staticmethod
+    def ifft_columns_bcast(src, col0: int, peer_ptrs, ctx=None):
+        """Step 1 of the coset-sharded commit without replication: src = (nc, n) int64 CUDA tensor, this
+        rank's trace columns [col0, col0 + nc); their coefficients are stored into EVERY buffer of `peer_ptrs` (each a
+        device pointer to an n_cols_total x n matrix; remote ones over NVLink).  Asynchronous."""
+        ctx = ctx or default_context()
+        nc, n = src.shape
+        table = (vp * len(peer_ptrs))(*[vp(p) for p in peer_ptrs])
+        ctx.wait_torch()
+        ctx._check(_ffi.lib().nlc_ifft_columns_bcast_dev(ctx._h, vp(src.data_ptr()), nc, _log2_strict(n), col0,
+                                                         len(peer_ptrs), table))
+
+    @classmethod
+    def from_coeffs_shard_dev(cls, coeffs_ptr: int, n_polys: int, degree_log: int, rate_bits: int, cap_height: int,
+                              shard_idx: int, n_shards: int, ctx=None, keepalive=None):
+        """Step 2: this rank's coset shard over the gathered coefficient matrix (read in place)."""
+        ctx = ctx or default_context()
+        h = vp()
+        ctx.wait_torch()
+        ctx._check(_ffi.lib().nlc_commit_from_coeffs_shard_dev(ctx._h, vp(coeffs_ptr), n_polys, degree_log, rate_bits,
+                                                               cap_height, shard_idx, n_shards, C.byref(h)))
+        b = cls(ctx, h, n_polys, degree_log, rate_bits, cap_height)
+        b.shard_idx, b.n_shards = shard_idx, n_shards
+        b._keepalive = keepalive
+        return b
+
+    @classmethod
+    def from_values_coset_sharded(cls, values, rate_bits: int, blinding: bool, cap_height: int, group=None, ctx=None):
+        """SURVEY.md 8e.2 as written: rank p uploads and inverse-transforms only ITS columns, the iFFT's stores put the
+        coefficients into every rank's matrix over NVLink (no replicated iFFT, no replicated upload, no NCCL
+        all-gather of 8*W*n bytes), one barrier in stream order, then every rank extends and hashes its cosets and the
+        cap entries are all-gathered.  Every rank passes the same `values`."""
+        import torch
+        from . import sharding
+        if blinding:
+            raise NlcError("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)")
+        g, G = sharding.rank_and_world(group)
+        sharding.check_plan(rate_bits, cap_height, G)
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(values)
+        W, log_n = len(arrs), _log2_strict(n)
+        per, split = sharding.uniform_column_split(W, G)
+        c0, nc = split[g]
+        dev = torch.device("cuda", ctx.device)
+        stream = torch.cuda.Stream(dev)
+        ctx.set_stream(stream.cuda_stream)
+        try:
+            with torch.cuda.stream(stream):
+                peers = sharding.PeerRows(ctx, G * per * n, group)
+                if nc:
+                    mine = np.stack([np.asarray(arrs[j]).view(np.int64) for j in range(c0, c0 + nc)])
+                    src = torch.from_numpy(mine).pin_memory().to(dev, non_blocking=True)
+                    cls.ifft_columns_bcast(src, c0, peers.ptrs, ctx)
+                sharding.stream_barrier(dev, group)
+                stream.synchronize()
+                peers.close_peers()
+                b = cls.from_coeffs_shard_dev(peers.own, W, log_n, rate_bits, cap_height, g, G, ctx, keepalive=peers)
+                stream.synchronize()
+        finally:
+            ctx.set_stream(None)
+        b.merkle_tree._cap = sharding.gather_cap(b.merkle_tree.local_cap, cap_height, group, device=ctx.device)
+        return b
+
+    @staticmethod
     def lde_columns(src, rate_bits: int, is_values: bool = True, ctx=None):
         """Step 1 of the row-sharded commit: src = (nc, n) int64 CUDA tensor holding this rank's
         columns; returns (coeffs (nc, n), lde (nc, N) in leaf order) as CUDA tensors.  Asynchronous."""

@@ -58,6 +58,14 @@ def column_split(W: int, n_shards: int):
     return out
 
 
+def uniform_column_split(W: int, n_shards: int):
+    """[(first column, count)] per rank with EQUAL strides: rank p owns [p * per, min(W, (p + 1) * per)), per =
+    ceil(W / n_shards) -- the layout of the gathered coefficient matrix of a coset-sharded commit (n_shards * per
+    columns, the tail padding unused).  Returns (per, split)."""
+    per = -(-W // n_shards)
+    return per, [(min(W, p * per), max(0, min(W, (p + 1) * per) - min(W, p * per))) for p in range(n_shards)]
+
+
 def pack_rows(lde_cols, n_shards: int):
     """lde_cols: this rank's columns, (nc, N) in leaf order (torch tensor or ndarray).  Returns the send buffer of the
     all-to-all: (n_shards, nc, N / n_shards) contiguous, block g = the leaves of shard g."""

@@ -46,6 +46,15 @@ for W, log_n, r, cap in [(9, 8, 1, 4), (135, 10, 3, 4), (418, 9, 1, 4), (world, 
         assert np.array_equal(c.merkle_tree.cap, ref.cap), ("coset cap", W, log_n, r)
         assert np.array_equal(c.merkle_tree.leaves, ref.leaves[lo:hi])
         assert np.array_equal(c.merkle_tree.digests, ref.digests[dlo:dhi])
+        # the same split with column-sharded upload + iFFT and the coefficient all-gather done by the iFFT's stores
+        c2 = P2.PolynomialBatch.from_values_coset_sharded(list(values), r, False, cap, ctx=ctx)
+        assert np.array_equal(c2.merkle_tree.cap, ref.cap), ("coset bcast cap", W, log_n, r)
+        assert np.array_equal(c2.merkle_tree.leaves, ref.leaves[lo:hi])
+        assert np.array_equal(c2.merkle_tree.digests, ref.digests[dlo:dhi])
+        assert np.array_equal(c2.coeff_matrix, ref.coeffs)
+        c2.free()
+        del c2
+        dist.barrier()
 dist.barrier()
 if rank == 0:
     print("multi-gpu parity ok, world", world)

@@ -110,3 +110,42 @@ def test_row_shards_through_peer_buffers(P2, pkg, O, rng, W, log_n, r, cap, G):
     finally:
         for p in bufs:
             ffi.lib().nlc_peer_free(ctx._h, ffi.vp(p))
+
+
+@pytest.mark.parametrize("W,log_n,r,cap,G", [(5, 6, 2, 3, 2), (9, 12, 3, 4, 8), (135, 12, 3, 4, 4), (3, 7, 2, 2, 4),
+                                             (17, 13, 1, 4, 2), (4, 5, 2, 2, 1)])
+def test_coset_shards_from_broadcast_coefficients(P2, pkg, O, rng, W, log_n, r, cap, G):
+    """8(e).2 without the replicated iFFT, on one GPU: G coefficient matrices from nlc_peer_alloc stand for the G ranks'
+    buffers; every column owner's iFFT stores its coefficients into all of them (nlc_ifft_columns_bcast_dev), and each
+    rank's coset shard over its own matrix (nlc_commit_from_coeffs_shard_dev) is the oracle's shard.  W < G leaves some
+    ranks without columns; W not a multiple of G leaves padding columns at the end of the matrix."""
+    import ctypes as C
+    import torch
+    S, ffi = pkg.sharding, pkg._ffi
+    ctx = P2.default_context()
+    n = 1 << log_n
+    values = O.random_field(rng, (W, n))
+    ref = O.commit_from_values(values, r, cap)
+    per, split = S.uniform_column_split(W, G)
+    assert sum(nc for _, nc in split) == W and all(c0 == min(W, p * per) for p, (c0, _) in enumerate(split))
+    bufs = []
+    for _ in range(G):
+        ptr, handle = ffi.vp(), C.create_string_buffer(64)
+        ctx._check(ffi.lib().nlc_peer_alloc(ctx._h, G * per * n, C.byref(ptr), handle))
+        bufs.append(ptr.value)
+    try:
+        for c0, nc in split:
+            if nc:
+                src = torch.from_numpy(values[c0:c0 + nc].view(np.int64)).cuda()
+                P2.PolynomialBatch.ifft_columns_bcast(src, c0, bufs)
+        ctx.synchronize()
+        shards = [P2.PolynomialBatch.from_coeffs_shard_dev(bufs[g], W, log_n, r, cap, g, G) for g in range(G)]
+        assert np.array_equal(S.assemble(s.merkle_tree.local_cap for s in shards), ref.cap)
+        assert np.array_equal(S.assemble(s.merkle_tree.digests for s in shards), ref.digests)
+        assert np.array_equal(S.assemble(s.merkle_tree.leaves for s in shards), ref.leaves)
+        for s in shards:
+            assert np.array_equal(s.coeff_matrix, ref.coeffs)  # every rank holds the whole coefficient matrix
+            s.free()
+    finally:
+        for p in bufs:
+            ffi.lib().nlc_peer_free(ctx._h, ffi.vp(p))

@@ -90,6 +90,19 @@ def test_column_split_and_row_plan():
         S.check_row_plan(4, 6)
 
 
+def test_uniform_column_split():
+    """The gathered coefficient matrix of the broadcast coset-sharded commit: equal strides, padding at the end."""
+    S = graft.load_package().sharding
+    assert S.uniform_column_split(135, 8) == (17, [(17 * p, 17) for p in range(7)] + [(119, 16)])
+    assert S.uniform_column_split(3, 4) == (1, [(0, 1), (1, 1), (2, 1), (3, 0)])
+    assert S.uniform_column_split(9, 8) == (2, [(0, 2), (2, 2), (4, 2), (6, 2), (8, 1), (9, 0), (9, 0), (9, 0)])
+    for W in range(1, 40):
+        for G in (1, 2, 4, 8):
+            per, split = S.uniform_column_split(W, G)
+            assert sum(nc for _, nc in split) == W and per * G >= W
+            assert all(c0 + nc <= W and (nc == 0 or c0 == p * per) for p, (c0, nc) in enumerate(split))
+
+
 def _row_worker(rank, world, port, q):
     """8e.3 host logic over gloo: the oracle plays the kernels; the exchange (pack_rows + all_to_all_single with
     ragged column splits) must hand every rank exactly its leaf rows, and the gathered cap is the commit's."""
