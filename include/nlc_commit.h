@@ -85,9 +85,10 @@ int nlc_commit_from_coeffs(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_c
  * device->host traffic hidden under the commit: coeffs_out_cols = `polynomials` (n_cols host vectors of n, what
  * proof.rs:307-310 reads), leaves_out = merkle_tree.leaves flattened (N x n_cols row-major), digests_out =
  * merkle_tree.digests, cap_out = merkle_tree.cap; any of them may be NULL.  The coefficients of a column chunk cross PCIe
- * as soon as its iFFT is done, its slab of leaf rows behind its coset NTTs -- both while later chunks upload / transform
- * and while the leaves are hashed -- and the digests + cap at the end.  Same results as nlc_commit_from_values followed by
- * nlc_batch_coeffs / _leaves / _digests / _cap (which pay the copies after the commit). */
+ * as soon as its iFFT is done, while later chunks upload and transform; the leaf rows (whole only once every column is
+ * extended) cross slab by slab under the leaf hashing and the digest levels; the digests + cap at the end.  Same results
+ * as nlc_commit_from_values followed by nlc_batch_coeffs / _leaves / _digests / _cap (which pay the copies after the
+ * commit). */
 int nlc_commit_from_values_materialised(nlc_ctx* ctx, const uint64_t* const* cols, size_t n_cols, int log_n, int rate_bits,
                                         int cap_height, uint64_t* const* coeffs_out_cols, uint64_t* leaves_out,
                                         uint64_t* digests_out, uint64_t* cap_out, nlc_batch** out);

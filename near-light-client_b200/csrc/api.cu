@@ -112,21 +112,6 @@ struct Materialise {
     bool any() const { return coeffs_cols || leaves || digests || cap; }
 };
 
-// out[r * nc + (c - c0)] = lde[c * N + r] for c in [c0, c0 + nc): the row-major slab of a column range
-__global__ void k_leaf_rows_cols(const u64* __restrict__ lde, size_t N, size_t c0, size_t nc, u64* __restrict__ out) {
-    __shared__ u64 tile[32][33];
-    const size_t r0 = (size_t)blockIdx.x * 32, cc0 = (size_t)blockIdx.y * 32;
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        size_t c = cc0 + i, r = r0 + threadIdx.x;
-        if (r < N && c < nc) tile[i][threadIdx.x] = lde[(c0 + c) * N + r];
-    }
-    __syncthreads();
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        size_t r = r0 + i, c = cc0 + threadIdx.x;
-        if (r < N && c < nc) out[r * nc + c] = tile[threadIdx.x][i];
-    }
-}
-
 // Runs on the downloader thread: D2H of `bytes` contiguous device bytes into host segments / a strided host matrix,
 // after `after` has completed; pinned destinations take plain asynchronous copies, pageable ones the stager.
 void dl_wait(nlc_ctx* ctx, cudaEvent_t after) { NLC_CUDA(cudaStreamWaitEvent(ctx->dl_stream, after, 0)); }
@@ -143,15 +128,6 @@ void dl_segments(nlc_ctx* ctx, const u64* src, const std::vector<HostStager::Seg
         NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
     }
 }
-void dl_rows(nlc_ctx* ctx, const u64* src_packed, u64* dst, size_t dst_pitch, size_t row_bytes, size_t n_rows) {
-    if (HostStager::pageable(dst)) {
-        ctx->dl_stager.download_rows(ctx->dl_stream, src_packed, dst, dst_pitch, row_bytes, n_rows);
-    } else {
-        NLC_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src_packed, row_bytes, row_bytes, n_rows, cudaMemcpyDeviceToHost, ctx->dl_stream));
-        NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
-    }
-}
-
 int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int rate_bits, int cap_height,
                 bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0, const Materialise* mat = nullptr) {
     if (!ctx) return 1;
@@ -174,7 +150,12 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             // Chunk sizes: 16 columns first, then growing by half (each upload hides behind the previous chunk's compute
             // as long as a column computes 1.5x as long as it uploads: measured 1.45-1.95x at rate_bits 1), tripling
             // at rate_bits >= 2 where compute is >= 8x the upload, also from pageable memory (fewer, fuller NTT grids).
-            const bool stream_hash = W >= 32;
+            // When the host wants merkle_tree.leaves (N x W row-major, the largest field by far) the sponge is NOT
+            // streamed: rows are whole only once every column is extended, so all transforms run first, and the rows
+            // then cross PCIe slab by slab (contiguous on both sides) under the one leaf-hash launch and the digest
+            // levels -- 8x the coefficients' bytes hidden under ~85 % of the commit's compute.
+            const bool want_leaves = want && mat->leaves;
+            const bool stream_hash = W >= 32 && !want_leaves;
             const size_t chunk = W <= 8 ? W : (W + 4) / 5; // narrow batches: plain fifths, one leaf-hash launch
             // Growth stops at an eighth of the batch (whole 8-column sponge blocks), but never below what fills the
             // NTT grids (2^23 elements): once chunk k+1 uploads faster than chunk k computes the compute stream
@@ -184,10 +165,10 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
             DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
-            size_t slab_cols = 0;
-            if (want && mat->leaves) { // the widest chunk the loop below can form
-                slab_cols = stream_hash ? std::min(W, std::max<size_t>(chunk_cap + 16, 16)) : std::min(W, chunk);
-                slab = ctx->dmalloc(N * slab_cols);
+            size_t slab_rows = 0;
+            if (want_leaves) { // ~64 MiB of rows per slab, as nlc_batch_leaves
+                slab_rows = std::min(N, std::max<size_t>(32, ((size_t)8 << 20) / W));
+                slab = ctx->dmalloc(slab_rows * W);
             }
             // jobs for the downloader thread (it owns dl_stream): after `ev`, drain one piece
             auto after_compute = [&]() {
@@ -206,20 +187,18 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                     dl_segments(ctx, src, segs);
                 });
             };
-            auto dl_leaves = [&](size_t c0, size_t nc) {
-                if (!want || !mat->leaves) return;
-                NLC_CHECK(nc <= slab_cols, "leaf slab too narrow");
+            auto dl_leaves = [&]() { // after the last column's LDE: row slabs, transposed on dl_stream, contiguous D2H
+                if (!want_leaves) return;
                 cudaEvent_t e = after_compute();
-                const u64* lde = b->lde;
-                u64* dst = mat->leaves + c0;
+                u64* dst = mat->leaves;
                 u64* sl = slab;
-                ctx->downloader.submit([ctx, e, lde, N, c0, nc, W, sl, dst] {
+                ctx->downloader.submit([ctx, e, b, N, W, sl, slab_rows, dst] {
                     dl_wait(ctx, e);
-                    dim3 grid((unsigned)((N + 31) / 32), (unsigned)((nc + 31) / 32));
-                    k_leaf_rows_cols<<<grid, dim3(32, 8), 0, ctx->dl_stream>>>(lde, N, c0, nc, sl);
-                    ctx->launches.fetch_add(1, std::memory_order_relaxed);
-                    NLC_CUDA(cudaGetLastError());
-                    dl_rows(ctx, sl, dst, W * sizeof(u64), nc * sizeof(u64), N);
+                    for (size_t r0 = 0; r0 < N; r0 += slab_rows) {
+                        const size_t nr = std::min(slab_rows, N - r0);
+                        batch_leaf_rows(b, r0, nr, sl, ctx->dl_stream);
+                        dl_segments(ctx, sl, {{dst + r0 * W, nr * W * sizeof(u64)}}); // returns when the slab is on the host
+                    }
                 });
             };
             auto dl_tree = [&]() {
@@ -260,11 +239,11 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                 if (is_values) batch_ifft_cols(b, vals.p + c0 * n, c0, nc);
                 dl_coeffs(c0, nc); // the coefficients of this chunk cross PCIe while later chunks compute
                 batch_lde_cols(b, c0, nc);
-                dl_leaves(c0, nc); // ... and so does its slab of leaf rows, under the hashing
                 if (stream_hash)
                     merkle_leaf_absorb(ctx, b->lde, N, N, c0, nc, c0 == 0, c0 + nc == W, sponge.p, b->cap_local(),
                                        b->digests, b->cap);
             }
+            dl_leaves(); // every column is extended: the leaf rows cross PCIe under the hashing below
             if (stream_hash)
                 merkle_levels(ctx, N, b->cap_local(), b->digests, b->cap);
             else

@@ -52,7 +52,7 @@ void batch_gather_lde_rows(nlc_batch* b, const u64* idx_dev, u64 i_start, size_t
 bool device_words_differ(nlc_ctx* ctx, const u64* a_dev, const u64* b_dev, size_t words);
 void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev);
 // rows [row0, row0+n_rows) of the leaf matrix, row-major, into out_dev (n_rows x W): plonky2's merkle_tree.leaves
-void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev);
+void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev, cudaStream_t on = nullptr); // on: default = the context's stream
 
 // transforms of a column shard (no tree), and the tree over a leaf-row shard
 void lde_columns_dev(nlc_ctx* ctx, const u64* src_dev, size_t n_cols, int log_n, int rate_bits, bool is_values,

@@ -279,11 +279,13 @@ void batch_eval_ext(nlc_batch* b, const u64 z[2], u64* out_dev) {
     NLC_LAUNCH(b->ctx, k_eval_ext, (unsigned)b->W, 256, 0, b->coeffs, (size_t)1 << b->log_n, ze, out_dev);
 }
 
-void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev) {
+void batch_leaf_rows(nlc_batch* b, size_t row0, size_t n_rows, u64* out_dev, cudaStream_t on) {
     if (!n_rows) return;
     const size_t N = b->n_local();
     dim3 grid((unsigned)((n_rows + 31) / 32), (unsigned)((b->W + 31) / 32));
-    NLC_LAUNCH(b->ctx, k_leaf_rows, grid, dim3(32, 8), 0, b->lde, b->W, N, row0, n_rows, out_dev);
+    k_leaf_rows<<<grid, dim3(32, 8), 0, on ? on : b->ctx->stream>>>(b->lde, b->W, N, row0, n_rows, out_dev);
+    b->ctx->launches.fetch_add(1, std::memory_order_relaxed);
+    NLC_CUDA(cudaGetLastError());
 }
 
 // ---- the constraint-free parts of quotient_polys (prover.rs:253-358) ----

@@ -59,6 +59,8 @@ struct nlc_ctx {
     std::atomic<u64> launches{0};
     std::map<TableKey, u64*> tables; // device-resident twiddle / scale tables, built once
     size_t table_bytes = 0;
+    std::vector<TableKey> pw_lru; // caller-keyed power tables, least recently used first (ntt.cu:pw_table)
+    size_t pw_bytes = 0;
     // small pinned staging area + device scratch for transcript-sized transfers
     HostStager stager; // pageable host columns -> HBM through pinned slots (staging.h)
     // a commit that also materialises struct fields on the host (nlc_commit_from_values_materialised): device -> host

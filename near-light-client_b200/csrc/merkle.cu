@@ -41,40 +41,54 @@ __device__ __forceinline__ u64* node_slot(u64* digests, u64* cap, TreeGeom g, in
 //   COLS  (leaf_stride 1, elem_stride N): the column-major LDE of a PolynomialBatch, exactly as the NTT left it --
 //         the 8 loads of a sponge block are 8 fully coalesced 256-byte warp requests, nothing is transposed;
 //   !COLS (leaf_stride leaf_len, elem_stride 1): row-major leaves (FRI round trees, nlc_merkle_new).
-// Leaves are dealt to warps round-robin (grid-stride) so that a grid of a few warps per SM sub-partition
-// keeps every multiplier busy without a ragged last wave.
+// Leaves are dealt to warps in units of 32 consecutive leaves.  A warp starts on unit = its global warp index and then
+// claims the next unit from a device counter (one atomicAdd per warp per unit, i.e. per >= 32 x ceil(W/8) permutations):
+// with a static grid-stride deal the last round ran on the CTAs with the lowest indices only, 3 of them on some SMs and
+// 2 on others, and the SMs with 2 idled for the difference (ncu: SMs active 95.8 % of the kernel); claimed units even
+// that out and let warps drift apart, so that they do not all sit in the S-box (multiplier) phase at the same time.
+__device__ __forceinline__ size_t next_unit(u32* __restrict__ ctr, u32 n_warps) {
+    u32 nx = 0;
+    if ((threadIdx.x & 31) == 0) nx = atomicAdd(ctr, 1u);
+    return (size_t)n_warps + __shfl_sync(0xffffffffu, nx, 0);
+}
+
 template <bool COLS>
 __global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, size_t leaf_stride, size_t elem_stride,
-            TreeGeom g, u64* digests, u64* cap) {
-    const size_t step = (size_t)gridDim.x * HASH_THREADS;
-    for (size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x; row < n_leaves; row += step) {
-        const u64* in = leaves + row * (COLS ? 1 : leaf_stride);
-        const size_t es = COLS ? elem_stride : 1;
-        u64 s[poseidon::WIDTH];
+            TreeGeom g, u64* digests, u64* cap, u32* __restrict__ ctr) {
+    const u32 n_warps = gridDim.x * (HASH_THREADS / 32);
+    const size_t n_units = (n_leaves + 31) >> 5;
+    for (size_t unit = blockIdx.x * (size_t)(HASH_THREADS / 32) + (threadIdx.x >> 5); unit < n_units;
+         unit = next_unit(ctr, n_warps)) {
+        const size_t row = (unit << 5) + (threadIdx.x & 31);
+        if (row < n_leaves) { // whole warps reach next_unit together
+            const u64* in = leaves + row * (COLS ? 1 : leaf_stride);
+            const size_t es = COLS ? elem_stride : 1;
+            u64 s[poseidon::WIDTH];
 #pragma unroll
-        for (int i = 0; i < poseidon::WIDTH; i++) s[i] = 0;
-        if (leaf_len <= 4) { // hash_or_noop: short rows are copied, zero padded
+            for (int i = 0; i < poseidon::WIDTH; i++) s[i] = 0;
+            if (leaf_len <= 4) { // hash_or_noop: short rows are copied, zero padded
 #pragma unroll
-            for (int i = 0; i < 4; i++)
-                if ((size_t)i < leaf_len) s[i] = gl::canon(in[i * es]);
-        } else {
-            // one call site for the permutation (its two round bodies are ~29 KB of code: a second inlined copy
-            // for the ragged last block would not fit the instruction cache beside the first)
+                for (int i = 0; i < 4; i++)
+                    if ((size_t)i < leaf_len) s[i] = gl::canon(in[i * es]);
+            } else {
+                // one call site for the permutation (its two round bodies are ~29 KB of code: a second inlined copy
+                // for the ragged last block would not fit the instruction cache beside the first)
 #pragma unroll 1
-            for (size_t off = 0; off < leaf_len; off += poseidon::RATE) {
-                const size_t rem = leaf_len - off;
+                for (size_t off = 0; off < leaf_len; off += poseidon::RATE) {
+                    const size_t rem = leaf_len - off;
 #pragma unroll
-                for (int i = 0; i < poseidon::RATE; i++)
-                    if ((size_t)i < rem) s[i] = in[(off + i) * es]; // overwrite mode
-                poseidon::permute_nc(s);
+                    for (int i = 0; i < poseidon::RATE; i++)
+                        if ((size_t)i < rem) s[i] = in[(off + i) * es]; // overwrite mode
+                    poseidon::permute_nc(s);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++) s[i] = gl::canon(s[i]);
             }
-#pragma unroll
-            for (int i = 0; i < 4; i++) s[i] = gl::canon(s[i]);
+            u64* out = node_slot(digests, cap, g, 0, row);
+            reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(s[0], s[1]);
+            reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(s[2], s[3]);
         }
-        u64* out = node_slot(digests, cap, g, 0, row);
-        reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(s[0], s[1]);
-        reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(s[2], s[3]);
     }
 }
 
@@ -84,28 +98,33 @@ k_leaf_hash(const u64* __restrict__ leaves, size_t n_leaves, size_t leaf_len, si
 // Same permutations, same order, same result as k_leaf_hash<true> over all columns (leaf_len > 4 only).
 __global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, size_t col0, size_t n_cols, bool first,
-              bool last, u64* __restrict__ state, TreeGeom g, u64* digests, u64* cap) {
-    const size_t step = (size_t)gridDim.x * HASH_THREADS;
-    for (size_t row = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x; row < n_leaves; row += step) {
-        const u64* in = lde + col0 * elem_stride + row;
-        u64 s[poseidon::WIDTH];
+              bool last, u64* __restrict__ state, TreeGeom g, u64* digests, u64* cap, u32* __restrict__ ctr) {
+    const u32 n_warps = gridDim.x * (HASH_THREADS / 32);
+    const size_t n_units = (n_leaves + 31) >> 5;
+    for (size_t unit = blockIdx.x * (size_t)(HASH_THREADS / 32) + (threadIdx.x >> 5); unit < n_units;
+         unit = next_unit(ctr, n_warps)) {
+        const size_t row = (unit << 5) + (threadIdx.x & 31);
+        if (row < n_leaves) {
+            const u64* in = lde + col0 * elem_stride + row;
+            u64 s[poseidon::WIDTH];
 #pragma unroll
-        for (int i = 0; i < poseidon::WIDTH; i++) s[i] = first ? 0 : state[i * n_leaves + row];
+            for (int i = 0; i < poseidon::WIDTH; i++) s[i] = first ? 0 : state[i * n_leaves + row];
 #pragma unroll 1
-        for (size_t off = 0; off < n_cols; off += poseidon::RATE) { // a ragged block only ends the last chunk
-            const size_t rem = n_cols - off;
+            for (size_t off = 0; off < n_cols; off += poseidon::RATE) { // a ragged block only ends the last chunk
+                const size_t rem = n_cols - off;
 #pragma unroll
-            for (int i = 0; i < poseidon::RATE; i++)
-                if ((size_t)i < rem) s[i] = in[(off + i) * elem_stride];
-            poseidon::permute_nc(s);
-        }
-        if (last) {
-            u64* out = node_slot(digests, cap, g, 0, row);
-            reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
-            reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
-        } else {
+                for (int i = 0; i < poseidon::RATE; i++)
+                    if ((size_t)i < rem) s[i] = in[(off + i) * elem_stride];
+                poseidon::permute_nc(s);
+            }
+            if (last) {
+                u64* out = node_slot(digests, cap, g, 0, row);
+                reinterpret_cast<ulonglong2*>(out)[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
+                reinterpret_cast<ulonglong2*>(out)[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
+            } else {
 #pragma unroll
-            for (int i = 0; i < poseidon::WIDTH; i++) state[i * n_leaves + row] = s[i];
+                for (int i = 0; i < poseidon::WIDTH; i++) state[i * n_leaves + row] = s[i];
+            }
         }
     }
 }
@@ -192,10 +211,16 @@ __global__ void k_two_to_one_many(const u64* l, const u64* r, size_t count, u64*
 
 } // namespace
 
-// Leaves are dealt grid-stride to HASH_MINB CTAs per SM.  The kernel is bound by each SM's integer pipes, not by
-// thread count: when n / threads is not an integer the last round simply runs with fewer warps per SM at (almost)
-// the same SM throughput, and every SM still gets the same number of leaves -- measured: 5 CTAs/SM (5.5 leaves per
-// thread) 7.41 ms, 4 CTAs/SM (6.9 leaves per thread, the "less ragged" choice) 7.51 ms, 3 CTAs/SM 7.75 ms.
+// unit counter of one leaf-hash launch: stream-ordered, so concurrent launches on different streams never share one
+static u32* unit_counter(nlc_ctx* ctx) {
+    u32* c = (u32*)ctx->dmalloc(1);
+    NLC_CUDA(cudaMemsetAsync(c, 0, sizeof(u32), ctx->stream));
+    return c;
+}
+
+// Grid: HASH_MINB CTAs per SM (all resident at once), each warp claiming 32-leaf units until none are left.  The kernel
+// is bound by each SM's integer pipes, not by thread count -- measured with the static deal: 5 CTAs/SM 7.41 ms,
+// 4 CTAs/SM 7.51 ms, 3 CTAs/SM 7.75 ms for config 2.
 static unsigned leaf_grid(nlc_ctx* ctx, size_t n_leaves) {
     const size_t want = (n_leaves + HASH_THREADS - 1) / HASH_THREADS;
     const size_t full = (size_t)ctx->sm_count * HASH_MINB;
@@ -232,14 +257,16 @@ void merkle_levels(nlc_ctx* ctx, size_t n_leaves, int cap_height, u64* digests, 
 void merkle_build(nlc_ctx* ctx, const u64* leaves, size_t n_leaves, size_t leaf_len, size_t elem_stride, int cap_height,
                   u64* digests, u64* cap) {
     const TreeGeom g = tree_geom(n_leaves, cap_height);
+    u32* ctr = unit_counter(ctx);
     ctx->phase_begin(2);
     if (elem_stride)
         NLC_LAUNCH(ctx, k_leaf_hash<true>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
-                   (size_t)1, elem_stride, g, digests, cap);
+                   (size_t)1, elem_stride, g, digests, cap, ctr);
     else
         NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, leaves, n_leaves, leaf_len,
-                   leaf_len, (size_t)1, g, digests, cap);
+                   leaf_len, (size_t)1, g, digests, cap, ctr);
     ctx->phase_end();
+    ctx->dfree(ctr);
     merkle_levels(ctx, n_leaves, cap_height, digests, cap);
 }
 
@@ -248,10 +275,12 @@ void merkle_leaf_absorb(nlc_ctx* ctx, const u64* lde, size_t n_leaves, size_t el
                         bool first, bool last, u64* state, int cap_height, u64* digests, u64* cap) {
     NLC_CHECK(last || n_cols % poseidon::RATE == 0, "leaf absorb: inner chunks must be whole sponge blocks");
     const TreeGeom g = tree_geom(n_leaves, cap_height);
+    u32* ctr = unit_counter(ctx);
     ctx->phase_begin(4);
     NLC_LAUNCH(ctx, k_leaf_absorb, leaf_grid(ctx, n_leaves), HASH_THREADS, 0, lde, n_leaves, elem_stride, col0, n_cols,
-               first, last, state, g, digests, cap);
+               first, last, state, g, digests, cap, ctr);
     ctx->phase_end();
+    ctx->dfree(ctr);
 }
 
 void merkle_open_many(nlc_ctx* ctx, const u64* leaves, const u64* digests, size_t n_leaves, size_t leaf_len,
@@ -281,8 +310,10 @@ void hash_many(nlc_ctx* ctx, const u64* in_dev, size_t count, size_t len, bool o
     g.sub_height = 0;
     g.sub_digests = 0;
     if (or_noop || len > 4) {
+        u32* ctr = unit_counter(ctx);
         NLC_LAUNCH(ctx, k_leaf_hash<false>, leaf_grid(ctx, count), HASH_THREADS, 0, in_dev, count, len, len, (size_t)1, g,
-                   (u64*)nullptr, out_dev);
+                   (u64*)nullptr, out_dev, ctr);
+        ctx->dfree(ctr);
     } else {
         // short hash_no_pad: pad into full states, permute, take 4 lanes
         u64* st = ctx->dmalloc(count * 12);

@@ -434,11 +434,36 @@ u64* tw_table(nlc_ctx* ctx, int m, int S, bool inv, u64 scale = 1) {
     NLC_LAUNCH(ctx, k_tw_table, (unsigned)((words + 255) / 256), 256, 0, p, m, S, w, scale);
     return p;
 }
+// Power tables are keyed by a shift the CALLER may choose (nlc_coset_fft / nlc_coset_ifft take any shift): they are kept
+// least-recently-used within a byte budget, so a caller that walks through many shifts cannot grow the context without
+// bound.  The library's own shifts (7, 7 w_N^k, 7^-1, the FRI round shifts) are a fixed small set that fits the budget and
+// therefore stays resident; an evicted table is simply rebuilt on its next use.  cudaFree synchronises the device, so no
+// kernel in flight can still be reading an evicted table.
+constexpr size_t PW_BUDGET_BYTES = (size_t)1 << 30;
 u64* pw_table(nlc_ctx* ctx, int log_n, u64 base, u64 scale) {
     TableKey key{KIND_PW, log_n, 0, 0, base, scale};
     size_t words = (size_t)1 << log_n;
-    if (u64* p = get_table(ctx, key, words)) return p;
+    auto& lru = ctx->pw_lru;
+    for (size_t i = 0; i < lru.size(); i++)
+        if (lru[i] == key) { // hit: most recently used goes to the back
+            lru.erase(lru.begin() + i);
+            lru.push_back(key);
+            return ctx->tables[key];
+        }
+    while (!lru.empty() && ctx->pw_bytes + words * sizeof(u64) > PW_BUDGET_BYTES) {
+        const TableKey old = lru.front();
+        lru.erase(lru.begin());
+        auto it = ctx->tables.find(old);
+        const size_t old_bytes = sizeof(u64) << std::get<1>(old);
+        cudaFree(it->second);
+        ctx->tables.erase(it);
+        ctx->pw_bytes -= old_bytes;
+        ctx->table_bytes -= old_bytes;
+    }
+    get_table(ctx, key, words);
     u64* p = ctx->tables[key];
+    lru.push_back(key);
+    ctx->pw_bytes += words * sizeof(u64);
     NLC_LAUNCH(ctx, k_pow_table, (unsigned)((words + 255) / 256), 256, 0, p, words, base, scale);
     return p;
 }

@@ -632,6 +632,40 @@ class PolynomialBatch:
         return cls._commit("nlc_commit_from_values", values, rate_bits, blinding, cap_height, ctx)
 
     @classmethod
+    def from_values_materialised(cls, values, rate_bits: int, blinding: bool, cap_height: int,
+                                 fields=("polynomials", "leaves", "digests", "cap"), ctx=None):
+        """from_values that also fills the host images of the struct fields a patched plonky2 keeps -- `polynomials`
+        (proof.rs:307-310 reads them), `merkle_tree.leaves`, `merkle_tree.digests`, `merkle_tree.cap` -- while the
+        commit runs (nlc_commit_from_values_materialised): the device->host copies ride under the hashing instead
+        of following it.  `fields` picks which images to fill; the others stay lazy."""
+        if blinding:
+            raise NlcError("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)")
+        ctx = ctx or default_context()
+        table, arrs, n = _col_table(values)
+        W, log_n = len(arrs), _log2_strict(n)
+        N = n << rate_bits
+        if not 0 <= cap_height <= log_n + rate_bits:
+            raise NlcError("cap_height should be at most log2(leaves.len())")
+        coeffs = np.zeros((W, n), np.uint64) if "polynomials" in fields else None
+        leaves = np.zeros((N, W), np.uint64) if "leaves" in fields else None
+        digests = np.zeros((2 * (N - (1 << cap_height)), 4), np.uint64) if "digests" in fields else None
+        cap = np.zeros((1 << cap_height, 4), np.uint64) if "cap" in fields else None
+        ctab = (u64p * W)(*[_p(coeffs[j]) for j in range(W)]) if coeffs is not None else None
+        h = vp()
+        ctx._check(_ffi.lib().nlc_commit_from_values_materialised(
+            ctx._h, table, W, log_n, rate_bits, cap_height, ctab, _p(leaves) if leaves is not None else None,
+            _p(digests) if digests is not None and digests.size else None, _p(cap) if cap is not None else None,
+            C.byref(h)))
+        b = cls(ctx, h, W, log_n, rate_bits, cap_height)
+        if coeffs is not None:
+            b._coeff_matrix = coeffs
+            b._polys = [PolynomialCoeffs(coeffs[j]) for j in range(W)]
+        b.merkle_tree._leaves, b.merkle_tree._digests = leaves, digests
+        if cap is not None:
+            b.merkle_tree._cap = b.merkle_tree._local_cap = cap
+        return b
+
+    @classmethod
     def from_coeffs(cls, polynomials, rate_bits: int, blinding: bool, cap_height: int, timing=None,
                     fft_root_table=None, ctx=None):
         """PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)."""

@@ -39,6 +39,52 @@ def test_from_values(P2, O, rng, W, log_n, rate_bits, cap_height):
     assert commitment.degree_log == log_n and len(commitment.polynomials) == W
 
 
+@pytest.mark.parametrize("W,log_n,rate_bits,cap_height", SHAPES[1::2] + [(135, 13, 3, 4), (418, 10, 1, 4)])
+def test_from_values_materialised(P2, O, rng, W, log_n, rate_bits, cap_height):
+    """nlc_commit_from_values_materialised: the struct fields a patched plonky2 keeps on the host (`polynomials`,
+    merkle_tree.leaves / digests / cap) written back WHILE the commit runs equal the oracle's -- and so
+    does what the handle still serves afterwards (the copies must not disturb the resident batch)."""
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, rate_bits, cap_height)
+    b = P2.PolynomialBatch.from_values_materialised([P2.PolynomialValues(v) for v in values], rate_bits, False, cap_height)
+    assert b._polys is not None and b.merkle_tree._leaves is not None and b.merkle_tree._digests is not None
+    check_batch(b, ref)
+    log_N = log_n + rate_bits
+    rows = rng.integers(0, 1 << log_N, 16)
+    br = lambda x: int(format(x, f"0{log_N}b")[::-1], 2) if log_N else 0
+    assert np.array_equal(b.get_lde_rows(rows), ref.leaves[[br(int(i)) for i in rows]])
+    # any subset of the fields; the others stay lazy and are served by the handle
+    b2 = P2.PolynomialBatch.from_values_materialised(list(values), rate_bits, False, cap_height, fields=("polynomials", "cap"))
+    assert b2.merkle_tree._leaves is None and b2.merkle_tree._digests is None
+    check_batch(b2, ref)
+    b3 = P2.PolynomialBatch.from_values_materialised(list(values), rate_bits, False, cap_height, fields=("leaves",))
+    assert b3._polys is None
+    check_batch(b3, ref)
+
+
+def test_from_values_materialised_pinned_outputs(P2, pkg, O, rng):
+    """Pinned destinations take plain asynchronous copies instead of the pageable stager: same bytes."""
+    import ctypes as C
+    import torch
+    ffi = pkg._ffi
+    W, log_n, r, cap = 40, 12, 2, 3
+    n, N = 1 << log_n, 1 << (log_n + r)
+    values = O.random_field(rng, (W, n))
+    ref = O.commit_from_values(values, r, cap)
+    ctx = P2.default_context()
+    pin = lambda shape: torch.zeros(shape, dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+    coeffs, leaves, digests, capo = pin((W, n)), pin((N, W)), pin((2 * (N - (1 << cap)), 4)), pin((1 << cap, 4))
+    tab = (ffi.u64p * W)(*[values[j].ctypes.data_as(ffi.u64p) for j in range(W)])
+    ctab = (ffi.u64p * W)(*[coeffs[j].ctypes.data_as(ffi.u64p) for j in range(W)])
+    h = ffi.vp()
+    ctx._check(ffi.lib().nlc_commit_from_values_materialised(
+        ctx._h, tab, W, log_n, r, cap, ctab, leaves.ctypes.data_as(ffi.u64p), digests.ctypes.data_as(ffi.u64p),
+        capo.ctypes.data_as(ffi.u64p), C.byref(h)))
+    ffi.lib().nlc_batch_free(h)
+    assert np.array_equal(coeffs, ref.coeffs) and np.array_equal(leaves, ref.leaves)
+    assert np.array_equal(digests, ref.digests) and np.array_equal(capo, ref.cap)
+
+
 @pytest.mark.parametrize("W,log_n,rate_bits,cap_height", SHAPES[::3])
 def test_from_coeffs(P2, O, rng, W, log_n, rate_bits, cap_height):
     coeffs = O.random_field(rng, (W, 1 << log_n))

@@ -42,3 +42,21 @@ def test_lde_onto_coset(P2, O, rng, log_n, rate_bits):
     assert np.array_equal(got, np.stack([O.lde_onto_coset(c, rate_bits) for c in v]))
     sel = P2.PolynomialValues.selector(1 << log_n, 0).lde_onto_coset(rate_bits)  # prover.rs:280-284
     assert np.array_equal(sel.values, O.lde_onto_coset(np.eye(1, 1 << log_n, 0, dtype=np.uint64)[0], rate_bits))
+
+
+def test_many_caller_shifts_stay_within_the_table_budget(P2, O, rng):
+    """nlc_coset_fft takes any shift; its power table is cached least-recently-used within a byte budget (1 GiB), so a
+    caller that walks through 160 distinct shifts at 2^20 (8 MiB of table each, 1.25 GiB in all) makes the cache evict --
+    and every transform, including one whose table was evicted and rebuilt, still equals the oracle's."""
+    log_n = 20
+    c = O.random_field(rng, 1 << log_n)
+    shifts = [int(s) for s in rng.integers(2, 1 << 62, 160)]
+    outs = {}
+    for i, s in enumerate(shifts):
+        v = P2.coset_fft(c, s)
+        if i in (0, 1, 80, 159):
+            outs[s] = v
+    for s, v in outs.items():
+        assert np.array_equal(v, O.coset_fft(c, s))
+    assert np.array_equal(P2.coset_fft(c, shifts[0]), outs[shifts[0]])  # evicted by now: rebuilt, same answer
+    assert np.array_equal(P2.coset_ifft(P2.coset_fft(c, shifts[5]), shifts[5]), c)
