@@ -137,7 +137,7 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
         *out = nullptr;
         const bool want = mat && mat->any();
         size_t n_dl_ev = 0;
-        u64* slab = nullptr; // row-major slab of one column chunk (leaves materialisation), reused chunk after chunk
+        u64* slab = nullptr; // row-major image of the LDE (leaves materialisation)
         if (want) ctx->downloader.start(ctx->device);
         NLC_CHECK(W > 0 && log_n >= 0 && log_n <= 32, "bad shape");
         const size_t n = (size_t)1 << log_n;
@@ -151,9 +151,11 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             // as long as a column computes 1.5x as long as it uploads: measured 1.45-1.95x at rate_bits 1), tripling
             // at rate_bits >= 2 where compute is >= 8x the upload, also from pageable memory (fewer, fuller NTT grids).
             // When the host wants merkle_tree.leaves (N x W row-major, the largest field by far) the sponge is NOT
-            // streamed: rows are whole only once every column is extended, so all transforms run first, and the rows
-            // then cross PCIe slab by slab (contiguous on both sides) under the one leaf-hash launch and the digest
-            // levels -- 8x the coefficients' bytes hidden under ~85 % of the commit's compute.
+            // streamed: rows are whole only once every column is extended, so all transforms run first; one transpose
+            // pass then writes the row-major image into a second HBM buffer (0.2 ms for config 2), and the copy engine
+            // moves it to the host under the one leaf-hash launch and the digest levels.  (Transposing slab by slab on
+            // the download stream would wait for the hash to END: its CTAs hold every SM's registers until no unit
+            // is left.)
             const bool want_leaves = want && mat->leaves;
             const bool stream_hash = W >= 32 && !want_leaves;
             const size_t chunk = W <= 8 ? W : (W + 4) / 5; // narrow batches: plain fifths, one leaf-hash launch
@@ -165,11 +167,7 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
             DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
-            size_t slab_rows = 0;
-            if (want_leaves) { // ~64 MiB of rows per slab, as nlc_batch_leaves
-                slab_rows = std::min(N, std::max<size_t>(32, ((size_t)8 << 20) / W));
-                slab = ctx->dmalloc(slab_rows * W);
-            }
+            if (want_leaves) slab = ctx->dmalloc(N * W); // row-major image of the LDE, freed once it is on the host
             // jobs for the downloader thread (it owns dl_stream): after `ev`, drain one piece
             auto after_compute = [&]() {
                 cudaEvent_t e = ctx->dl_event(n_dl_ev++);
@@ -187,18 +185,16 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
                     dl_segments(ctx, src, segs);
                 });
             };
-            auto dl_leaves = [&]() { // after the last column's LDE: row slabs, transposed on dl_stream, contiguous D2H
+            auto dl_leaves = [&]() { // after the last column's LDE
                 if (!want_leaves) return;
+                batch_leaf_rows(b, 0, N, slab);
                 cudaEvent_t e = after_compute();
                 u64* dst = mat->leaves;
-                u64* sl = slab;
-                ctx->downloader.submit([ctx, e, b, N, W, sl, slab_rows, dst] {
+                const u64* src = slab;
+                const size_t bytes = N * W * sizeof(u64);
+                ctx->downloader.submit([ctx, e, src, dst, bytes] {
                     dl_wait(ctx, e);
-                    for (size_t r0 = 0; r0 < N; r0 += slab_rows) {
-                        const size_t nr = std::min(slab_rows, N - r0);
-                        batch_leaf_rows(b, r0, nr, sl, ctx->dl_stream);
-                        dl_segments(ctx, sl, {{dst + r0 * W, nr * W * sizeof(u64)}}); // returns when the slab is on the host
-                    }
+                    dl_segments(ctx, src, {{dst, bytes}});
                 });
             };
             auto dl_tree = [&]() {

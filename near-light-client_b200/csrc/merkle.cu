@@ -132,7 +132,7 @@ k_leaf_absorb(const u64* __restrict__ lde, size_t n_leaves, size_t elem_stride, 
 // layer (i) -> layer (i+1): one thread per parent.
 __global__ void __launch_bounds__(HASH_THREADS, HASH_MINB)
 k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) {
-    const size_t j = blockIdx.x * (size_t)HASH_THREADS + threadIdx.x;
+    const size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (j >= n_parents) return;
     const u64* kids = node_slot(digests, cap, g, layer, 2 * j); // the sibling pair is contiguous
     u64 l[4], r[4], o[4];
@@ -152,7 +152,13 @@ k_merkle_level(u64* digests, u64* cap, TreeGeom g, int layer, size_t n_parents) 
 // the one-thread form (measured: 32 us per layer with one thread per parent, 36 us with all of a subtree's
 // half-warps crowded onto one SM).
 constexpr int COOP_THREADS = 128;
-constexpr size_t COOP_MAX_PARENTS = 8192;
+// measured per layer (ncu, config 2): one thread per parent 23.8 us at 16384 parents; half-warp form 42 / 27 / 17 / 13 us
+// at 8192 / 4096 / 2048 / <= 1024 parents -- a lone warp per sub-partition finishes its permutations in ~19 us, so the
+// half-warp form only pays below 4096 parents
+#ifndef NLC_COOP_MAX_PARENTS
+#define NLC_COOP_MAX_PARENTS 2048
+#endif
+constexpr size_t COOP_MAX_PARENTS = NLC_COOP_MAX_PARENTS;
 __global__ void __launch_bounds__(COOP_THREADS) k_merkle_level_coop(u64* digests, u64* cap, TreeGeom g, int layer,
                                                                      size_t n_parents) {
     const int lane = threadIdx.x & 31, l16 = lane & 15;
@@ -244,10 +250,12 @@ void merkle_levels(nlc_ctx* ctx, size_t n_leaves, int cap_height, u64* digests, 
     ctx->phase_begin(3);
     for (int layer = 0; layer < g.sub_height; layer++) {
         const size_t parents = n_leaves >> (layer + 1);
-        if (parents > COOP_MAX_PARENTS)
-            NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + HASH_THREADS - 1) / HASH_THREADS), HASH_THREADS, 0,
-                       digests, cap, g, layer, parents);
-        else
+        if (parents > COOP_MAX_PARENTS) {
+            // fewer parents than the GPU has lanes: one-warp CTAs, so every warp gets a sub-partition of its own
+            const int threads = parents >= (size_t)ctx->sm_count * 4 * 32 * 4 ? HASH_THREADS : 32;
+            NLC_LAUNCH(ctx, k_merkle_level, (unsigned)((parents + threads - 1) / threads), threads, 0, digests, cap, g,
+                       layer, parents);
+        } else
             NLC_LAUNCH(ctx, k_merkle_level_coop, (unsigned)((parents * 16 + COOP_THREADS - 1) / COOP_THREADS),
                        COOP_THREADS, 0, digests, cap, g, layer, parents);
     }
