@@ -243,6 +243,94 @@ def run_replay_workload(args):
     print(json.dumps(out), flush=True)
 
 
+def run_stark_proof(args):
+    """--workload stark_proof_fpmul: ONE WHOLE starky proof (prover.rs:50-225) of a field-arithmetic chip
+    (chip/field/mul.rs FpMulInstruction<Fp25519>: 124 columns, 31 degree-2 constraints) at 2^16 rows under
+    standard_fast_config -- trace commit from the row-major AirTrace, AIR evaluation over the quotient domain ON THE
+    DEVICE (csrc/air.cu), quotient commit, openings, prove_openings -- against the same sequence driven through the CPU
+    oracle (direct AIR evaluation, oracle/air.py).  The `air_eval` leg is timed alone on both sides."""
+    import torch
+    from oracle import air as OA
+    pkg = graft.load_package()
+    P2, S = pkg.plonky2, pkg.starky
+    O = graft.load_oracle()
+    O.set_threads(len(os.sched_getaffinity(0)))
+    log_n = 16
+    n = 1 << log_n
+    rng = np.random.default_rng(0xC0FFEE + 20)
+    chip = S.FpMulChip()
+    base = chip.generate_trace(rng, 1 << 10)
+    trace = np.ascontiguousarray(np.tile(base, (n // base.shape[0], 1)))  # rows are independent: repetition stays valid
+    stark = S.Starky(chip)
+    cfg = S.StarkyConfig.standard_fast_config(n)
+    fc = cfg.fri_config
+
+    def gpu_once():
+        t0 = time.perf_counter()
+        proof = S.StarkyProver.prove(cfg, stark, trace, [])
+        return time.perf_counter() - t0, proof
+    gpu_once()
+    runs = [gpu_once() for _ in range(max(args.steps, 1))]
+    t_gpu = float(np.median([r[0] for r in runs]))
+    proof = runs[-1][1]
+    # the AIR evaluation alone (accumulators of every alpha for all 2^17 points, result left on the host)
+    tb = P2.PolynomialBatch.from_trace_rows(trace, 0, chip.width(), fc.rate_bits, fc.cap_height)
+    alphas = [3, 5]
+    S.StarkyProver.air_eval(stark, [tb], [], [], [], alphas)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        acc_gpu = S.StarkyProver.air_eval(stark, [tb], [], [], [], alphas)
+    t_air_gpu = (time.perf_counter() - t0) / 3
+    # -- the oracle-driven proof, in the order of prover.rs:50-225
+    t0 = time.perf_counter()
+    ch = O.Challenger()
+    ch.observe_elements([])
+    tref = O.commit_from_values(np.ascontiguousarray(trace.T), fc.rate_bits, fc.cap_height)
+    t_commit_cpu = time.perf_counter() - t0
+    ch.observe_cap(tref.cap)
+    al = ch.get_n_challenges(cfg.num_challenges)
+    t1 = time.perf_counter()
+    qdf = chip.quotient_degree_factor()
+    qdb = max(qdf - 1, 0).bit_length()
+    qv = OA.quotient_values(chip, [tref], [], [], [], al, log_n, fc.rate_bits)
+    t_air_cpu = time.perf_counter() - t1
+    qref = O.quotient_commit(qv, log_n, qdb, qdf, False, fc.rate_bits, fc.cap_height)
+    ch.observe_cap(qref.cap)
+    zeta = ch.get_extension_challenge()
+    g = pow(1753635133440165772, 1 << (32 - log_n), P)
+    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
+    ev = lambda b, z: [O.eval_poly_ext(c, np.array(z, np.uint64)) for c in b.coeffs]
+    local, nxt, quot = ev(tref, zeta), ev(tref, zeta_next), ev(qref, zeta)
+    for batch in (local + quot, nxt):
+        ch.observe_elements([c for e in batch for c in e])
+    params = O.fri_params(log_n, fc.rate_bits, fc.cap_height, fc.proof_of_work_bits, fc.num_query_rounds, 4, 5)
+    W, Q = chip.width(), qref.coeffs.shape[0]
+    inst = O.FriInstance([(zeta, [(0, i) for i in range(W)] + [(1, i) for i in range(Q)]), (zeta_next, [(0, i) for i in range(W)])])
+    oproof = O.prove_openings(inst, [tref, qref], ch, params)
+    t_cpu = time.perf_counter() - t0
+    acc_cpu = OA.quotient_values(chip, [tref], [], [], [], alphas, log_n, fc.rate_bits, divide_by_zh=False)
+    same = {"trace_cap": bool(np.array_equal(proof.trace_caps[0], tref.cap)),
+            "quotient_cap": bool(np.array_equal(proof.quotient_polys_cap, qref.cap)),
+            "opening_proof": bool(np.array_equal(np.asarray(proof.opening_proof.flat), np.asarray(oproof))),
+            "air_accumulators": bool(np.array_equal(acc_gpu, acc_cpu))}
+    prog = stark.program(0)
+    out = {"metric": "STARK proof time (trace rows in, StarkProof out)", "value": t_gpu, "unit": "s", "n_gpus": 1,
+           "steps": args.steps, "warmup": 1, "ms_per_step": t_gpu * 1e3, "higher_is_better": False, "scaling": "weak",
+           "vs_baseline": None, "dtype": "u64", "data": "synthetic (valid FpMul trace: 2^10 random multiplications mod 2^255-19, tiled)",
+           "config": {"workload": args.workload, "rows": n, "cols": W, "rate_bits": fc.rate_bits, "cap_height": fc.cap_height,
+                      "num_challenges": cfg.num_challenges, "queries": fc.num_query_rounds, "constraints": prog.n_constraints,
+                      "bytecode_ops": prog.n_ops, "bytecode_registers": prog.n_regs},
+           "air_eval": {"gpu_s": t_air_gpu, "cpu_oracle_s": t_air_cpu, "points": n << qdb,
+                        "note": "GPU: nlc_air_eval incl. the D2H of the accumulators; oracle: numpy/C vector ops over the whole domain"},
+           "cpu_baseline": {"value": t_cpu, "unit": "s", "cores": O.get_threads(), "kind": "port",
+                            "sample": f"the same proof once through the oracle: trace commit {t_commit_cpu:.2f} s, AIR evaluation {t_air_cpu:.2f} s, total {t_cpu:.2f} s",
+                            "bit_exact": same}}
+    print(json.dumps(out), flush=True)
+    if not all(same.values()):
+        raise SystemExit(f"bench.py: stark proof differs from the oracle's: {same}")
+
+
 def oracle_quality(O):
     """Single-thread rates of the CPU port, so that the quality of the baseline is on record beside every GPU/CPU
     factor: Poseidon permutations/s/core (fast partial rounds, as upstream runs them) and FFT butterflies/s/core."""
@@ -314,14 +402,16 @@ class Strong:
       rows   (world > 2^rate_bits): column shards for the transforms, last NTT pass stores into the
              peers' leaf-row buffers over NVLink, barrier, leaf-row shards for the tree, cap all-gather."""
 
-    def __init__(self, pkg, ctx, stream, rank, world, workload, flush):
+    def __init__(self, pkg, ctx, stream, rank, world, workload, flush, device_values=False):
+        """workload: a WORKLOADS name or a (log_n, W, rate_bits, cap_height) tuple; device_values: this rank's columns
+        are drawn on the device (tools/sweep.py: cells too large to generate on every rank's host; no 1-GPU check)."""
         import ctypes as C
         import torch
         self.C, self.torch = C, torch
         self.pkg, self.ctx, self.stream, self.rank, self.world, self.flush = pkg, ctx, stream, rank, world, flush
         self.ffi, self.L = pkg._ffi, pkg._ffi.lib()
         self.workload = workload
-        self.log_n, self.W, self.r, self.cap = WORKLOADS[workload]
+        self.log_n, self.W, self.r, self.cap = WORKLOADS[workload] if isinstance(workload, str) else workload
         self.n, self.N = 1 << self.log_n, 1 << (self.log_n + self.r)
         self.by_rows = world > (1 << self.r)
         S = pkg.sharding
@@ -340,14 +430,19 @@ class Strong:
         self.cap_local = torch.empty(((1 << self.cap) // world, 4), dtype=torch.int64, device="cuda")
         self.cap_full = torch.empty((1 << self.cap, 4), dtype=torch.int64, device="cuda")
         self.cudart = C.CDLL("libcudart.so.12")
-        # every rank holds the same trace (seed without the rank); only this rank's columns are ever touched
-        full = synth_values(self.W, self.n, 0xC0FFEE + 1)
-        self.host_mine = torch.empty((max(self.nc, 1), self.n), dtype=torch.int64).pin_memory()
-        if self.nc:
-            self.host_mine.numpy().view(np.uint64)[:self.nc] = full[self.c0:self.c0 + self.nc]
-        self.dev_mine = self.host_mine.cuda(non_blocking=True)
+        if device_values:
+            g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + 4 + rank)
+            self.dev_mine = torch.randint(0, 1 << 62, (max(self.nc, 1), self.n), dtype=torch.int64, device="cuda", generator=g)
+            self.host_mine, self.full_values = None, None
+        else:
+            # every rank holds the same trace (seed without the rank); only this rank's columns are ever touched
+            full = synth_values(self.W, self.n, 0xC0FFEE + 1)
+            self.host_mine = torch.empty((max(self.nc, 1), self.n), dtype=torch.int64).pin_memory()
+            if self.nc:
+                self.host_mine.numpy().view(np.uint64)[:self.nc] = full[self.c0:self.c0 + self.nc]
+            self.dev_mine = self.host_mine.cuda(non_blocking=True)
+            self.full_values = full
         self.my_coeffs = torch.empty((max(self.nc, 1), self.n), dtype=torch.int64, device="cuda") if self.by_rows else None
-        self.full_values = full
         self.batch = None
 
     def free_prev(self):
@@ -423,6 +518,9 @@ class Strong:
         pt = torch.tensor([ph[nm] / k for nm in names], dtype=torch.float64, device="cuda")
         dist.all_reduce(pt, op=dist.ReduceOp.MAX)
         phases = {nm: float(v) for nm, v in zip(names, pt.tolist())}
+        if self.host_mine is None:  # sweep cells drawn on the device: resident figures only
+            self.free_prev()
+            return ms, phases, None, clocks, None
         # e2e: host columns in, cap out
         for _ in range(2):
             self.step_e2e()
@@ -901,7 +999,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark", "stark_proof_fpmul"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
@@ -918,6 +1016,9 @@ def main():
     if args.workload.startswith("replay_"):
         if rank == 0:
             run_replay_workload(args)
+    elif args.workload == "stark_proof_fpmul":
+        if rank == 0:
+            run_stark_proof(args)
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

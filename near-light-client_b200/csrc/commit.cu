@@ -175,11 +175,31 @@ void batch_lde_cols(nlc_batch* b, size_t c0, size_t nc, const NttScatter* sc) {
     nlc_ctx* ctx = b->ctx;
     const int log_n = b->log_n, r = b->rate_bits;
     const size_t n = (size_t)1 << log_n, N = b->n_local();
+    const u64 w_N = gl::h_root_of_unity(log_n + r);
+    const size_t cosets_local = ((size_t)1 << r) >> b->shard_log, kr0 = b->shard_idx * cosets_local;
+    if (!sc && ntt_can_batch_cosets(log_n)) {
+        // all of this shard's cosets in one launch per pass, in place on the LDE columns (no scratch): 2 launches
+        // instead of 2 * 2^r, each with 2^r times the CTAs
+        NttJob job;
+        job.src = b->coeffs + c0 * n;
+        job.src_stride = n;
+        job.n_cols = nc;
+        job.log_n = log_n;
+        job.cols = true;
+        job.dst = b->lde;
+        job.dst_stride = N;
+        job.row_base = 0;
+        job.col0 = c0;
+        job.log_cosets = r - b->shard_log;
+        job.pre_tables = ntt_coset_tables(ctx, log_n, r, kr0, cosets_local);
+        ctx->phase_begin(1);
+        ntt_run(ctx, job);
+        ctx->phase_end();
+        return;
+    }
     u64* scratch = nullptr;
     const size_t sw = ntt_scratch_words(nc, log_n);
     if (sw) scratch = ctx->dmalloc(sw);
-    const u64 w_N = gl::h_root_of_unity(log_n + r);
-    const size_t cosets_local = ((size_t)1 << r) >> b->shard_log, kr0 = b->shard_idx * cosets_local;
     ctx->phase_begin(1);
     for (size_t k = 0; k < ((size_t)1 << r); k++) {
         size_t kr = 0; // bitrev_r(k): coset k is the leaf range [kr*n, (kr+1)*n)

@@ -187,6 +187,14 @@ struct NttScatter {
     // the all-gather of a column-sharded iFFT done by the transform's own stores over NVLink
     int n_bcast = 0;
 };
+// Several forward transforms of the SAME source columns in one launch per pass (the 2^r cosets of an LDE; fast path,
+// COLS output): transform z multiplies its input by pre + z * z_pre (one power table per coset, back to back), and lands
+// at leaf rows row_base + z * z_dst.  The passes before the last one run in place on the destination columns, so no
+// scratch is needed and a launch carries 2^log_z times the CTAs (narrow batches fill the GPU; launch ramps amortise).
+struct NttCosets {
+    int log_z = 0;
+    size_t z_src = 0, z_dst = 0, z_pre = 0;
+};
 struct NttJob {
     const u64* src = nullptr;
     size_t src_stride = 0;
@@ -204,8 +212,14 @@ struct NttJob {
     size_t col0 = 0;           // ROWS / COLS: first column
     u64* scratch = nullptr;    // n_cols * 2^log_n words, needed when log_n > one digit
     NttScatter scatter;        // COLS only
+    // COLS, forward, no scatter: 2^log_cosets transforms at once; pre_tables = their power tables back to back (device,
+    // 2^log_n words each, replaces pre_shift), coset z at leaf rows row_base + z * 2^log_n
+    int log_cosets = 0;
+    const u64* pre_tables = nullptr;
 };
 void ntt_run(nlc_ctx* ctx, const NttJob& job);
+const u64* ntt_coset_tables(nlc_ctx* ctx, int log_n, int rate_bits, size_t kr0, size_t count);
+bool ntt_can_batch_cosets(int log_n);
 size_t ntt_scratch_words(size_t n_cols, int log_n);
 
 // ---- merkle.cu ----

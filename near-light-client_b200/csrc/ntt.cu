@@ -264,17 +264,21 @@ __device__ __forceinline__ constexpr u32 brev_c(u32 k) {
 template <int R1, int R2, bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_hi_f(const u64* __restrict__ src, size_t src_stride, u64* __restrict__ dst, size_t dst_stride, int m,
-           const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots, int canon_in) {
+           const u64* __restrict__ pre, const u64* __restrict__ tw, const u64* __restrict__ roots, int canon_in,
+           const NttCosets cz) {
     constexpr int S = R1 + R2, LOG_T = F_TILE_LOG - S;
     constexpr u32 T = 1u << LOG_T, TASKS1 = F_TILE >> R1, TASKS2 = F_TILE >> R2;
     extern __shared__ u64 sm[]; // [2^S][T], t fastest
     const int L = m - S;
-    const size_t tile = blockIdx.x;
+    // several transforms of the same columns in one launch (the 2^r cosets of an LDE): the coset index is the FASTEST
+    // part of blockIdx.x, so the CTAs that read the same coefficient tile run together and share it through L2
+    const size_t z = blockIdx.x & (((size_t)1 << cz.log_z) - 1);
+    const size_t tile = blockIdx.x >> cz.log_z;
     const size_t base = (tile >> (L - LOG_T)) << m;
     const u32 low0 = ((u32)tile & ((1u << (L - LOG_T)) - 1)) << LOG_T;
-    const u64* s = src + blockIdx.y * src_stride + base + low0;
-    u64* d = dst + blockIdx.y * dst_stride + base + low0;
-    const u64* pr = pre ? pre + base + low0 : nullptr;
+    const u64* s = src + blockIdx.y * src_stride + z * cz.z_src + base + low0;
+    u64* d = dst + blockIdx.y * dst_stride + z * cz.z_dst + base + low0;
+    const u64* pr = pre ? pre + z * cz.z_pre + base + low0 : nullptr;
     const u64* twp = tw + low0;
     const size_t kstride = (size_t)1 << (L + R2);
 
@@ -328,19 +332,22 @@ template <int R1, int R2, int MODE, bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, NTT_MINB)
 k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64* __restrict__ post, u64 scale,
            const u64* __restrict__ roots, u64* __restrict__ dst, size_t dst_stride, size_t row_base, size_t col0,
-           const NttScatter sc) {
+           const NttScatter sc, const NttCosets cz) {
     constexpr int S = R1 + R2, LOG_G = F_TILE_LOG - S;
     constexpr u32 G = 1u << LOG_G, LEN = 1u << S, TASKS1 = F_TILE >> R1, TASKS2 = F_TILE >> R2;
     constexpr u32 pitch = LoGeom<S>::pitch;
     extern __shared__ u64 sm[];
     const int log_nb = log_n - S;
-    const u64* s = src + blockIdx.y * src_stride;
+    const size_t z = blockIdx.x & (((size_t)1 << cz.log_z) - 1); // coset of a batched LDE (COLS only; 0 otherwise)
+    const size_t bx = blockIdx.x >> cz.log_z;
+    const u64* s = src + blockIdx.y * src_stride + z * cz.z_src;
+    row_base += z * cz.z_dst;
 
 #pragma unroll
     for (u32 j = 0; j < TASKS1 / NTT_THREADS; j++) {
         const u32 tau = threadIdx.x + j * NTT_THREADS;
         const u32 b = tau & ((1u << R2) - 1), g = tau >> R2;
-        size_t blk = ((size_t)blockIdx.x << LOG_G) + g;
+        size_t blk = (bx << LOG_G) + g;
         if (MODE == OUT_NATURAL) blk = brev((u32)blk, log_nb);
         const u64* in = s + (blk << S) + b;
         u64 v[1 << R1];
@@ -374,7 +381,7 @@ k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64*
             const u32 g = idx >> S, q = idx & (LEN - 1);
             u64 v = sm[g * pitch + LoGeom<S>::pidx(q)];
             if (scale != 1) v = gl::mul(v, scale);
-            const size_t leaf = row_base + ((((size_t)blockIdx.x << LOG_G) + g) << S) + q;
+            const size_t leaf = row_base + (((bx << LOG_G) + g) << S) + q;
             if (MODE == OUT_COLS) {
                 out[leaf] = v;
             } else { // re-blocked by leaf-row shard, possibly straight into a peer GPU's buffer
@@ -384,7 +391,7 @@ k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64*
             }
         }
     } else { // natural order: output k = bitrev_S(q) * 2^log_nb + block index, contiguous over the G blocks
-        u64* out = dst + blockIdx.y * dst_stride + ((size_t)blockIdx.x << LOG_G);
+        u64* out = dst + blockIdx.y * dst_stride + (bx << LOG_G);
 #pragma unroll
         for (u32 j = 0; j < F_TILE / NTT_THREADS; j++) {
             const u32 idx = threadIdx.x + j * NTT_THREADS;
@@ -392,11 +399,11 @@ k_ntt_lo_f(const u64* __restrict__ src, size_t src_stride, int log_n, const u64*
             u64 v = sm[g * pitch + LoGeom<S>::pidx(q)];
             if (scale != 1) v = gl::mul(v, scale);
             const size_t k = ((size_t)brev(q, S) << log_nb) + g;
-            if (post) v = gl::mul(v, __ldg(post + ((size_t)blockIdx.x << LOG_G) + k));
+            if (post) v = gl::mul(v, __ldg(post + (bx << LOG_G) + k));
             if (sc.n_bcast == 0) {
                 out[k] = v;
             } else { // every rank's coefficient matrix receives this rank's columns (local store + NVLink stores)
-                const size_t off = blockIdx.y * dst_stride + ((size_t)blockIdx.x << LOG_G) + k;
+                const size_t off = blockIdx.y * dst_stride + (bx << LOG_G) + k;
                 for (int p = 0; p < sc.n_bcast; p++) sc.peer[p][off] = v;
             }
         }
@@ -514,23 +521,24 @@ std::vector<int> plan_digits_fast(int log_n) { // digits of 4..8 bits, smaller o
 
 template <bool INV>
 void launch_hi_f(nlc_ctx* ctx, int S, dim3 grid, const u64* src, size_t src_stride, u64* dst, size_t dst_stride, int m,
-                 const u64* pre, const u64* tw, const u64* roots, int canon_in) {
+                 const u64* pre, const u64* tw, const u64* roots, int canon_in, const NttCosets& cz) {
     const size_t smem = (size_t)F_TILE * sizeof(u64);
     switch (S) {
-    case 4: NLC_LAUNCH(ctx, (k_ntt_hi_f<2, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
-    case 5: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
-    case 6: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
-    case 7: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
-    default: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 4, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in); break;
+    case 4: NLC_LAUNCH(ctx, (k_ntt_hi_f<2, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in, cz); break;
+    case 5: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 2, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in, cz); break;
+    case 6: NLC_LAUNCH(ctx, (k_ntt_hi_f<3, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in, cz); break;
+    case 7: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 3, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in, cz); break;
+    default: NLC_LAUNCH(ctx, (k_ntt_hi_f<4, 4, INV>), grid, NTT_THREADS, smem, src, src_stride, dst, dst_stride, m, pre, tw, roots, canon_in, cz); break;
     }
 }
 template <int MODE, bool INV>
 void launch_lo_f(nlc_ctx* ctx, int S, dim3 grid, const u64* src, size_t src_stride, int log_n, const u64* post, u64 scale,
-                 const u64* roots, u64* dst, size_t dst_stride, size_t row_base, size_t col0, const NttScatter& sc) {
+                 const u64* roots, u64* dst, size_t dst_stride, size_t row_base, size_t col0, const NttScatter& sc,
+                 const NttCosets& cz = NttCosets()) {
     switch (S) {
-    case 6: NLC_LAUNCH(ctx, (k_ntt_lo_f<3, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 6) * LoGeom<6>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
-    case 7: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 7) * LoGeom<7>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
-    default: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 4, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 8) * LoGeom<8>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc); break;
+    case 6: NLC_LAUNCH(ctx, (k_ntt_lo_f<3, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 6) * LoGeom<6>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc, cz); break;
+    case 7: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 3, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 7) * LoGeom<7>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc, cz); break;
+    default: NLC_LAUNCH(ctx, (k_ntt_lo_f<4, 4, MODE, INV>), grid, NTT_THREADS, (size_t)(F_TILE >> 8) * LoGeom<8>::pitch * 8, src, src_stride, log_n, post, scale, roots, dst, dst_stride, row_base, col0, sc, cz); break;
     }
 }
 
@@ -541,12 +549,23 @@ void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
     const int d = (int)digits.size();
     const bool inv = job.inverse;
     u64 scale = inv ? gl::h_inv(gl::canon((u64)(n % gl::P))) : 1;
+    const bool batched = job.log_cosets > 0 || job.pre_tables;
+    if (batched)
+        NLC_CHECK(job.cols && !inv && job.scatter.log_per < 0 && job.pre_tables, "coset batches: forward COLS transforms only");
     const u64* pre = nullptr;
-    if (gl::canon(job.pre_shift) != 1) pre = pw_table(ctx, log_n, gl::canon(job.pre_shift), 1);
+    if (batched) pre = job.pre_tables;
+    else if (gl::canon(job.pre_shift) != 1) pre = pw_table(ctx, log_n, gl::canon(job.pre_shift), 1);
     const u64* post = nullptr;
     if (!job.cols && gl::canon(job.post_shift) != 1) post = pw_table(ctx, log_n, gl::canon(job.post_shift), 1);
-    NLC_CHECK(job.scratch != nullptr, "ntt_run: scratch required for multi-digit transform");
+    NLC_CHECK(batched || job.scratch != nullptr, "ntt_run: scratch required for multi-digit transform");
 
+    // a coset batch works in place on its destination columns (the lo pass reads a tile whole before it writes it)
+    u64* work = batched ? job.dst + job.col0 * job.dst_stride + job.row_base : job.scratch;
+    const size_t work_stride = batched ? job.dst_stride : n;
+    NttCosets cz;
+    cz.log_z = job.log_cosets;
+    cz.z_dst = n;
+    cz.z_pre = n;
     const u64* cur = job.src;
     size_t cur_stride = job.src_stride;
     int m = log_n;
@@ -555,19 +574,21 @@ void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
         NLC_CHECK(L >= log_T, "ntt fast path: tile wider than the stride");
         const u64* tw = tw_table(ctx, m, S, inv, lvl == 0 ? scale : 1); // 1/n folded into the first inter-digit twiddle
         const u64* roots = roots_table(ctx, S, inv);
-        dim3 grid((unsigned)((n >> m) << (L - log_T)), (unsigned)job.n_cols);
+        dim3 grid((unsigned)(((n >> m) << (L - log_T)) << cz.log_z), (unsigned)job.n_cols);
+        cz.z_src = lvl == 0 ? 0 : n; // every coset reads the same coefficients, then its own block of the destination
         if (inv)
-            launch_hi_f<true>(ctx, S, grid, cur, cur_stride, job.scratch, n, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0);
+            launch_hi_f<true>(ctx, S, grid, cur, cur_stride, work, work_stride, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0, cz);
         else
-            launch_hi_f<false>(ctx, S, grid, cur, cur_stride, job.scratch, n, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0);
-        cur = job.scratch;
-        cur_stride = n;
+            launch_hi_f<false>(ctx, S, grid, cur, cur_stride, work, work_stride, m, lvl == 0 ? pre : nullptr, tw, roots, lvl == 0, cz);
+        cur = work;
+        cur_stride = work_stride;
         m = L;
     }
     scale = 1;
     const int S = digits[d - 1];
     const u64* roots = roots_table(ctx, S, inv);
-    dim3 grid((unsigned)(n >> F_TILE_LOG), (unsigned)job.n_cols);
+    dim3 grid((unsigned)((n >> F_TILE_LOG) << cz.log_z), (unsigned)job.n_cols);
+    cz.z_src = n;
     if (job.cols && job.scatter.log_per >= 0) {
         NLC_CHECK(!inv, "scatter output is for forward transforms");
         launch_lo_f<OUT_SCATTER, false>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst, job.dst_stride,
@@ -578,7 +599,7 @@ void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
                                         job.row_base, job.col0, job.scatter);
         else
             launch_lo_f<OUT_COLS, false>(ctx, S, grid, cur, cur_stride, log_n, nullptr, scale, roots, job.dst,
-                                         job.dst_stride, job.row_base, job.col0, job.scatter);
+                                         job.dst_stride, job.row_base, job.col0, job.scatter, batched ? cz : NttCosets());
     } else {
         NLC_CHECK((const void*)cur != (const void*)job.dst || job.scatter.n_bcast, "ntt_run: NATURAL output must be out of place");
         if (inv)
@@ -589,12 +610,36 @@ void ntt_run_fast(nlc_ctx* ctx, const NttJob& job) {
                                             job.dst_stride, 0, 0, job.scatter);
     }
 }
+
+// power tables of the cosets [k0, k0 + count) of an LDE in LEAF order: table z = powers of 7 * w_N^bitrev_r(k0 + z)
+// (coset k of the domain 7<w_N> is the leaf range [bitrev_r(k) n, +n): SURVEY.md 8e.2), back to back; cached
+enum { KIND_PWC = 4 };
+} // namespace
+
+const u64* ntt_coset_tables(nlc_ctx* ctx, int log_n, int rate_bits, size_t kr0, size_t count) {
+    const size_t n = (size_t)1 << log_n;
+    TableKey key{KIND_PWC, log_n, rate_bits, (int)kr0, (u64)count, 0};
+    if (u64* p = get_table(ctx, key, count * n)) return p;
+    u64* p = ctx->tables[key];
+    const u64 w_N = gl::h_root_of_unity(log_n + rate_bits);
+    for (size_t z = 0; z < count; z++) {
+        size_t k = 0;
+        for (int t = 0; t < rate_bits; t++) k |= (((kr0 + z) >> t) & 1) << (rate_bits - 1 - t);
+        NLC_LAUNCH(ctx, k_pow_table, (unsigned)((n + 255) / 256), 256, 0, p + z * n, n,
+                   gl::h_mul(gl::GENERATOR, gl::h_pow(w_N, k)), (u64)1);
+    }
+    return p;
+}
+bool ntt_can_batch_cosets(int log_n) { return log_n >= 12; }
+
+namespace {
 } // namespace
 
 void ntt_run(nlc_ctx* ctx, const NttJob& job) {
     NLC_CHECK(job.log_n >= 0 && job.log_n <= 32, "log_n out of range (two-adicity is 32)");
     NLC_CHECK(job.n_cols > 0 && job.n_cols <= 65535u, "column count out of range");
     if (job.log_n >= 12 && !job.rows) return ntt_run_fast(ctx, job);
+    NLC_CHECK(job.log_cosets == 0 && !job.pre_tables, "coset batches need the fast path (log_n >= 12)");
     ensure_attrs(ctx);
     const int log_n = job.log_n;
     const size_t n = (size_t)1 << log_n;
