@@ -331,6 +331,109 @@ def run_stark_proof(args):
         raise SystemExit(f"bench.py: stark proof differs from the oracle's: {same}")
 
 
+def run_plonk_proof(args):
+    """--workload plonk_proof_demo: ONE WHOLE plonk proof from the witness on (plonk/prover.rs `prove`) under
+    standard_recursion_config at degree 2^16 -- wires commit (135), partial products + Z (parallel prefix product on the
+    device) and their commit (20), the vanishing polynomial over the 2^19-point quotient domain with the gate constraints
+    run from bytecode, quotient commit (16), openings, prove_openings over the four oracles -- against the same sequence
+    through the CPU oracle (oracle/plonk.py).  Circuit: plonk.build_demo_circuit (arithmetic, extension-arithmetic,
+    base-sum, constant, public-input gates; random copy constraints; a satisfying witness)."""
+    import torch
+    from oracle import plonk as OP
+    pkg = graft.load_package()
+    P2, K = pkg.plonky2, pkg.plonk
+    O = graft.load_oracle()
+    O.set_threads(len(os.sched_getaffinity(0)))
+    degree_bits = args.plonk_degree_bits
+    cfg = K.CircuitConfig.standard_recursion_config()
+    fc = cfg.fri_config
+    r, cap = fc.rate_bits, fc.cap_height
+    t0 = time.perf_counter()
+    common, consts, sig, wires, pih = K.build_demo_circuit(cfg, degree_bits, 0xC0FFEE + 30)
+    t_build = time.perf_counter() - t0
+    cs_vals = np.concatenate([consts, sig])
+    pd = K.ProverOnlyCircuitData(P2.PolynomialBatch.from_values(list(cs_vals), r, False, cap), sig)
+    wire_cols = list(wires)
+
+    def gpu_once():
+        t0 = time.perf_counter()
+        proof = K.PlonkProver.prove(common, pd, wire_cols, pih)
+        return time.perf_counter() - t0, proof
+    gpu_once()
+    runs = [gpu_once() for _ in range(max(args.steps, 1))]
+    t_gpu = float(np.median([x[0] for x in runs]))
+    proof = runs[-1][1]
+    # the two new legs alone
+    gw = P2.PolynomialBatch.from_values(wire_cols, r, False, cap)
+    betas, gammas, alphas = [3, 5], [7, 11], [13, 17]
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            out = fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps, out
+    t_pp_gpu, gz = timed(lambda: K.PlonkProver.zs_partial_products_commitment(common, pd, gw, betas, gammas))
+    t_q_gpu, _ = timed(lambda: K.PlonkProver.quotient_commitment(common, pd, pih, gw, gz, betas, gammas, alphas))
+    # -- the oracle-driven proof
+    t0 = time.perf_counter()
+    rcs = O.commit_from_values(cs_vals, r, cap)  # preprocessing, not part of `prove`
+    t_pre = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    ch = O.Challenger()
+    ch.observe_elements(pd.circuit_digest)
+    ch.observe_elements(pih)
+    rw = O.commit_from_values(wires, r, cap)
+    ch.observe_cap(rw.cap)
+    b2, g2 = ch.get_n_challenges(2), ch.get_n_challenges(2)
+    t1 = time.perf_counter()
+    vals = OP.partial_products_and_zs(common, wires, sig, b2, g2)
+    t_pp_cpu = time.perf_counter() - t1
+    rz = O.commit_from_values(vals, r, cap)
+    ch.observe_cap(rz.cap)
+    a2 = ch.get_n_challenges(2)
+    t1 = time.perf_counter()
+    qv = OP.vanishing_values(common, rcs, rw, rz, pih, b2, g2, a2, r)
+    t_van_cpu = time.perf_counter() - t1
+    rq = O.quotient_commit(qv, degree_bits, 3, 8, False, r, cap)
+    ch.observe_cap(rq.cap)
+    zeta = ch.get_extension_challenge()
+    g = pow(1753635133440165772, 1 << (32 - degree_bits), P)
+    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
+    ev = lambda b, z: [O.eval_poly_ext(c, np.array(z, np.uint64)) for c in b.coeffs]
+    cs_z, w_z, zp_z, q_z, zp_n = ev(rcs, zeta), ev(rw, zeta), ev(rz, zeta), ev(rq, zeta), ev(rz, zeta_next)
+    for batch in (cs_z + w_z + zp_z + q_z, zp_n[:2]):
+        ch.observe_elements([c for e in batch for c in e])
+    params = O.fri_params(degree_bits, r, cap, fc.proof_of_work_bits, fc.num_query_rounds, 4, 5)
+    widths = [rcs.coeffs.shape[0], rw.coeffs.shape[0], rz.coeffs.shape[0], rq.coeffs.shape[0]]
+    inst = O.FriInstance([(zeta, [(oi, i) for oi, wd in enumerate(widths) for i in range(wd)]), (zeta_next, [(2, 0), (2, 1)])])
+    oproof = O.prove_openings(inst, [rcs, rw, rz, rq], ch, params)
+    t_cpu = time.perf_counter() - t0
+    same = {"wires_cap": bool(np.array_equal(proof.wires_cap, rw.cap)),
+            "zs_partial_products_cap": bool(np.array_equal(proof.plonk_zs_partial_products_cap, rz.cap)),
+            "quotient_cap": bool(np.array_equal(proof.quotient_polys_cap, rq.cap)),
+            "opening_proof": bool(np.array_equal(np.asarray(proof.opening_proof.flat), np.asarray(oproof)))}
+    prog = common.compile_gate_constraints()
+    out = {"metric": "plonk proof time (witness columns in, proof out)", "value": t_gpu, "unit": "s", "n_gpus": 1,
+           "steps": args.steps, "warmup": 1, "ms_per_step": t_gpu * 1e3, "higher_is_better": False, "scaling": "weak",
+           "vs_baseline": None, "dtype": "u64", "data": "synthetic (demo circuit with a satisfying witness)",
+           "config": {"workload": args.workload, "degree_bits": degree_bits, "num_wires": cfg.num_wires,
+                      "num_routed_wires": cfg.num_routed_wires, "rate_bits": r, "cap_height": cap, "queries": fc.num_query_rounds,
+                      "gates": [gt.id() for gt in common.gates], "gate_constraints": common.num_gate_constraints,
+                      "bytecode_ops": prog.n_ops, "bytecode_registers": prog.n_regs},
+           "zs_partial_products_commit": {"gpu_s": t_pp_gpu, "cpu_oracle_partial_products_s": t_pp_cpu},
+           "quotient_commit": {"gpu_s": t_q_gpu, "cpu_oracle_vanishing_s": t_van_cpu, "points": 1 << (degree_bits + 3)},
+           "cpu_baseline": {"value": t_cpu, "unit": "s", "cores": O.get_threads(), "kind": "port",
+                            "sample": f"the same proof once through the oracle ({t_cpu:.2f} s; numpy-vector restatement of the "
+                                      f"quotient side, C/OpenMP commits); circuit build {t_build:.1f} s and the constants/sigmas "
+                                      f"commit ({t_pre:.2f} s) are preprocessing on both sides", "bit_exact": same}}
+    print(json.dumps(out), flush=True)
+    if not all(same.values()):
+        raise SystemExit(f"bench.py: plonk proof differs from the oracle's: {same}")
+
+
 def oracle_quality(O):
     """Single-thread rates of the CPU port, so that the quality of the baseline is on record beside every GPU/CPU
     factor: Poseidon permutations/s/core (fast partial rounds, as upstream runs them) and FFT butterflies/s/core."""
@@ -839,6 +942,25 @@ def run_ours(args, rank, local_rank, world):
                     "achieved": ab["ntt"] / (ntt_ms * 1e-3) / 1e9 if ntt_ms > 0 else 0.0, "peak": peak, "unit": "GB/s",
                     "ms": ntt_ms}
     roofline_ntt["frac"] = roofline_ntt["achieved"] / peak
+    # the roof that actually binds the transforms: the ALU pipe (64-bit modular add/sub and shift twiddles are carry
+    # chains); its utilisation in the committed capture of the two pass kernels, weighted by their durations
+    ntt_caps = [(ncu_pipes(args.workload, kk), ncu_capture_meta(args.workload, kk)) for kk in ("k_ntt_hi_f", "k_ntt_lo_f")]
+    if all(c[0] for c in ntt_caps) and ntt_ms > 0:
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tj = json.load(f)[args.workload]
+            wts = [tj[kk]["duration_us"] for kk in ("k_ntt_hi_f", "k_ntt_lo_f")]
+            alu = sum(c[0]["alu"] * w for c, w in zip(ntt_caps, wts)) / sum(wts)
+            fmah = sum(c[0]["fmaheavy (IMAD)"] * w for c, w in zip(ntt_caps, wts)) / sum(wts)
+            bfly = W * (n * log_n // 2) * (1 + (1 << r))
+            files, sha, cap_name = ntt_caps[0][1]
+            roofline_ntt["ncu_pipes_pct_of_peak"] = {kk: c[0] for kk, c in zip(("k_ntt_hi_f", "k_ntt_lo_f"), ntt_caps)}
+            roofline_ntt["traffic"] = {kk: tj[kk]["dram_bytes_per_launch"] for kk in ("k_ntt_hi_f", "k_ntt_lo_f")}
+            roofline_ntt["int_pipe"] = {"bound": "alu", "achieved": bfly / (ntt_ms * 1e-3), "peak": bfly / (ntt_ms * 1e-3) * 100.0 / alu,
+                                        "unit": "butterflies/s", "frac": alu / 100.0, "fmaheavy_frac": fmah / 100.0,
+                                        "capture": cap_name, "stale_capture": (sha is None) or (kernel_source_hash(files) != sha)}
+        except Exception:
+            pass
     commit_gbs = ab["commit"] / (ms_per_step * 1e-3) / 1e9
 
     # ---- e2e through the host-buffer C-ABI call (pinned host columns in, cap out) ----
@@ -999,7 +1121,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark", "stark_proof_fpmul"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark", "stark_proof_fpmul", "plonk_proof_demo"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
@@ -1007,6 +1129,7 @@ def main():
     ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the single-commit strong-scaling block")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl", "nccl-pack"],
                     help="--shard-commit with more ranks than cosets (SURVEY 8e.3): how leaf rows reach their shard")
+    ap.add_argument("--plonk-degree-bits", type=int, default=16, help="--workload plonk_proof_demo: log2 rows of the circuit")
     ap.add_argument("--ref-sample-log-rows", type=int, default=None,
                     help="reference arm: opt in to a bounded row sample (log2 rows); default = the workload's own size")
     args = ap.parse_args()
@@ -1019,6 +1142,9 @@ def main():
     elif args.workload == "stark_proof_fpmul":
         if rank == 0:
             run_stark_proof(args)
+    elif args.workload == "plonk_proof_demo":
+        if rank == 0:
+            run_plonk_proof(args)
     elif args.impl == "reference":
         run_reference(args, rank, world)
     else:

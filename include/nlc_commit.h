@@ -285,6 +285,44 @@ int nlc_stark_quotient_commit(nlc_ctx* ctx, const nlc_air_program* air, nlc_batc
                               const uint64_t* alphas, size_t n_alphas, size_t quotient_degree_factor, int cap_height,
                               nlc_batch** out);
 
+/* ---- the plonk-side quotient path (plonky2::plonk::{prover, vanishing_poly}) ----------------------
+ * What `plonk::prover::prove` does between the wires commitment and the openings, with every LDE row read where it
+ * already lives (call site in tree: /root/reference/nearx/src/test_utils.rs:62 `circuit.prove`, and every circuit the
+ * operator builds, /root/reference/scripts/build-circuit.sh:10-18).  The circuit-dependent part -- the gates' constraint
+ * polynomials -- arrives as an nlc_air_program: the caller evaluates every gate's FILTERED constraints ONCE against a
+ * recording parser (the way `eval_unfiltered_circuit` records them for recursion), sums them per constraint index and
+ * emits NLC_AIR_CONSTRAINT for the HIGHEST index first (near-light-client_b200/plonk.py: compile_gate_constraints).  In
+ * that program LOCAL column j is constants_sigmas polynomial j for j < constants_sigmas width, then wire j - width;
+ * PUBLIC i is public_inputs_hash[i]; NEXT and the row-filtered constraint ops are rejected. */
+typedef struct {
+    size_t num_constants;        /* polynomials of constants_sigmas before the sigmas: selectors, then gate constants */
+    size_t num_routed_wires;     /* config.num_routed_wires; the sigmas are constants_sigmas[num_constants ..][..routed] */
+    size_t num_challenges;       /* config.num_challenges: betas, gammas and alphas each hold this many (<= 8) */
+    size_t num_partial_products; /* common_data.num_partial_products = ceil(routed / quotient_degree_factor) - 1 */
+    int quotient_degree_factor;  /* common_data.quotient_degree_factor (the permutation argument's chunk size) */
+    const uint64_t* k_is;        /* common_data.k_is: num_routed_wires coset shifts */
+} nlc_plonk_circuit;
+/* all_wires_permutation_partial_products + the prover's column order [Z per challenge | partial products per challenge]
+ * + PolynomialBatch::from_values(zs_partial_products, rate_bits, false, cap_height): the wire and sigma values on the
+ * subgroup are recovered from the two resident commitments (one forward NTT of their coefficients), the running
+ * product Z(g x) = Z(x) * row product is a parallel prefix product over the rows. */
+int nlc_plonk_zs_partial_products_commit(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, nlc_batch* constants_sigmas,
+                                         nlc_batch* wires, const uint64_t* betas, const uint64_t* gammas, int cap_height,
+                                         nlc_batch** out);
+/* eval_vanishing_poly_base_batch for every point of the quotient domain (size = n << log2_ceil(quotient_degree_factor)):
+ * evals_out = size x num_challenges row-major, natural order, NOT yet multiplied by 1/Z_H (as nlc_air_eval). */
+int nlc_plonk_vanishing_eval(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, const nlc_air_program* gate_constraints,
+                             nlc_batch* constants_sigmas, nlc_batch* wires, nlc_batch* zs_partial_products,
+                             const uint64_t public_inputs_hash[4], const uint64_t* betas, const uint64_t* gammas,
+                             const uint64_t* alphas, uint64_t* evals_out);
+/* compute_quotient_polys + the quotient commitment of `prove`: the evaluation above, the 1/Z_H scaling, per-challenge
+ * coset_ifft(F::coset_shift()), trim_to_len(quotient_degree) / chunks(degree), from_coeffs(chunks, rate_bits, false,
+ * cap_height) -- num_challenges * quotient_degree_factor polynomials. */
+int nlc_plonk_quotient_commit(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, const nlc_air_program* gate_constraints,
+                              nlc_batch* constants_sigmas, nlc_batch* wires, nlc_batch* zs_partial_products,
+                              const uint64_t public_inputs_hash[4], const uint64_t* betas, const uint64_t* gammas,
+                              const uint64_t* alphas, int cap_height, nlc_batch** out);
+
 /* ---- a4: Poseidon (plonky2::hash::{poseidon,hashing}) -------------------------------------- */
 /* PoseidonPermutation::permute on `count` independent 12-lane states (in place). */
 int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count);

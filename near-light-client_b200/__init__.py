@@ -9,3 +9,4 @@ from ._ffi import NlcError  # noqa: F401
 from . import plonky2  # noqa: F401
 from . import sharding  # noqa: F401
 from . import starky  # noqa: F401
+from . import plonk  # noqa: F401

@@ -40,6 +40,11 @@ class CAirProgram(C.Structure):
                 ("n_public", C.c_uint32), ("n_global", C.c_uint32), ("n_challenge", C.c_uint32)]
 
 
+class CPlonkCircuit(C.Structure):
+    _fields_ = [("num_constants", C.c_size_t), ("num_routed_wires", C.c_size_t), ("num_challenges", C.c_size_t),
+                ("num_partial_products", C.c_size_t), ("quotient_degree_factor", C.c_int), ("k_is", u64p)]
+
+
 class CFriInstance(C.Structure):
     _fields_ = [("n_batches", C.c_int), ("points", u64p), ("batch_offsets", u32p), ("poly_oracle", u32p),
                 ("poly_index", u32p)]
@@ -93,6 +98,11 @@ SIGNATURES = {
                                C.c_int, u64p]),
     "nlc_stark_quotient_commit": (C.c_int, [vp, C.POINTER(CAirProgram), C.POINTER(vp), C.c_int, u64p, u64p, u64p, u64p,
                                             C.c_size_t, C.c_size_t, C.c_int, C.POINTER(vp)]),
+    "nlc_plonk_zs_partial_products_commit": (C.c_int, [vp, C.POINTER(CPlonkCircuit), vp, vp, u64p, u64p, C.c_int, C.POINTER(vp)]),
+    "nlc_plonk_vanishing_eval": (C.c_int, [vp, C.POINTER(CPlonkCircuit), C.POINTER(CAirProgram), vp, vp, vp, u64p, u64p, u64p,
+                                           u64p, u64p]),
+    "nlc_plonk_quotient_commit": (C.c_int, [vp, C.POINTER(CPlonkCircuit), C.POINTER(CAirProgram), vp, vp, vp, u64p, u64p, u64p,
+                                            u64p, C.c_int, C.POINTER(vp)]),
     "nlc_batch_free": (None, [vp]),
     "nlc_batch_info": (C.c_int, [vp, C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nlc_batch_cap": (C.c_int, [vp, u64p]),

@@ -14,38 +14,13 @@
 // and the quotient domain g<w_size> is exactly the leaf prefix [0, size) of that order (point i = leaf
 // bitrev_{log size}(i)), so one thread per LEAF reads its local row with fully coalesced column loads; the next row
 // (i + next_step) differs from it in a few middle bits, the same for a whole warp, so those loads coalesce too.
-#include "batch.cuh"
+#include "air.cuh"
 
 namespace {
 
 enum { KIND_QX = 10, KIND_QLF = 11, KIND_QLL = 12 };
 
-struct AirArgs {
-    const u32* code;          // n_ops x 4 words {op, dst, a, b}
-    u32 n_ops;
-    const u64* pool;          // 64-bit constants
-    const u64* const* cols;   // device pointers to the columns of the concatenated trace (lde + j*N of every batch)
-    const u64* publics;
-    const u64* globals;
-    const u64* challenges;
-    const u64* alphas;
-    u32 n_alphas;
-    u32 n_regs;
-    int log_size;             // log2(quotient domain) = log_n + quotient_degree_bits
-    int qdb;
-    const u64* coset_x;       // g * w_size^i, natural order
-    const u64* lagrange_first;
-    const u64* lagrange_last;
-    u64 last;                 // w_n^-1: the last point of the subgroup (z_last = x - last)
-    u64* regs;                // n_regs x n_threads scratch (register r of thread t at regs[r * n_threads + t])
-    u64* out;                 // size x n_alphas row-major, natural order of i (the `quotient_values` before transpose)
-};
-
-constexpr int AIR_THREADS = 128;
-constexpr int MAX_ALPHAS = 8;
-
-// One thread per leaf k of the quotient-domain prefix; the virtual registers of the program live in a
-// thread-interleaved scratch matrix (coalesced), the program counter is uniform across the grid.
+// One thread per leaf k of the quotient-domain prefix.
 __global__ void __launch_bounds__(AIR_THREADS) k_air_eval(const AirArgs A) {
     const size_t size = (size_t)1 << A.log_size;
     const size_t stride = (size_t)gridDim.x * AIR_THREADS;
@@ -59,37 +34,7 @@ __global__ void __launch_bounds__(AIR_THREADS) k_air_eval(const AirArgs A) {
         u64 acc[MAX_ALPHAS];
 #pragma unroll
         for (int j = 0; j < MAX_ALPHAS; j++) acc[j] = 0;
-        for (u32 pc = 0; pc < A.n_ops; pc++) {
-            const uint4 ins = __ldg(reinterpret_cast<const uint4*>(A.code) + pc);
-            const u32 op = ins.x;
-            u64 r;
-            switch (op) {
-            case NLC_AIR_LOCAL: r = gl::dcanon(A.cols[ins.z][k]); break;
-            case NLC_AIR_NEXT: r = gl::dcanon(A.cols[ins.z][k_next]); break;
-            case NLC_AIR_PUBLIC: r = A.publics[ins.z]; break;
-            case NLC_AIR_GLOBAL: r = A.globals[ins.z]; break;
-            case NLC_AIR_CHALLENGE: r = A.challenges[ins.z]; break;
-            case NLC_AIR_CONST: r = A.pool[ins.z]; break;
-            case NLC_AIR_ADD: r = gl::dadd(regs[ins.z * stride], regs[ins.w * stride]); break;
-            case NLC_AIR_SUB: r = gl::dsub(regs[ins.z * stride], regs[ins.w * stride]); break;
-            case NLC_AIR_MUL: r = gl::mul(regs[ins.z * stride], regs[ins.w * stride]); break;
-            case NLC_AIR_NEG: r = gl::neg(regs[ins.z * stride]); break;
-            case NLC_AIR_MUL_CONST: r = gl::mul(regs[ins.z * stride], A.pool[ins.w]); break;
-            case NLC_AIR_ADD_CONST: r = gl::dadd(regs[ins.z * stride], A.pool[ins.w]); break;
-            case NLC_AIR_SUB_CONST: r = gl::dsub(regs[ins.z * stride], A.pool[ins.w]); break;
-            default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
-                u64 c = regs[ins.z * stride];
-                if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
-                else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
-                else if (op == NLC_AIR_CONSTRAINT_LAST_ROW) c = gl::mul(c, l_last);
-#pragma unroll
-                for (int j = 0; j < MAX_ALPHAS; j++)
-                    if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
-                continue;
-            }
-            }
-            regs[ins.y * stride] = r;
-        }
+        air_run(A, regs, stride, k, k_next, z_last, l_first, l_last, acc);
 #pragma unroll
         for (int j = 0; j < MAX_ALPHAS; j++)
             if ((u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];
@@ -183,88 +128,18 @@ void air_eval_dev(nlc_ctx* ctx, const nlc_air_program* prog, nlc_batch* const* b
         const size_t N = batches[b]->n_local();
         for (size_t j = 0; j < batches[b]->W; j++) cols.push_back(batches[b]->lde + j * N);
     }
-    // validate the program on the host: every operand in range, every source register written before it is read
-    {
-        std::vector<char> written(prog->n_regs, 0);
-        for (u32 pc = 0; pc < prog->n_ops; pc++) {
-            const u32 op = prog->code[4 * pc], dst = prog->code[4 * pc + 1], a = prog->code[4 * pc + 2], b = prog->code[4 * pc + 3];
-            auto reg = [&](u32 r) { NLC_CHECK(r < prog->n_regs && written[r], "AIR program reads a register before writing it"); };
-            switch (op) {
-            case NLC_AIR_LOCAL: case NLC_AIR_NEXT: NLC_CHECK(a < cols.size(), "AIR program: trace column out of range"); break;
-            case NLC_AIR_PUBLIC: NLC_CHECK(a < prog->n_public, "AIR program: public input out of range"); break;
-            case NLC_AIR_GLOBAL: NLC_CHECK(a < prog->n_global, "AIR program: global value out of range"); break;
-            case NLC_AIR_CHALLENGE: NLC_CHECK(a < prog->n_challenge, "AIR program: challenge out of range"); break;
-            case NLC_AIR_CONST: NLC_CHECK(a < prog->n_pool, "AIR program: constant out of range"); break;
-            case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a); reg(b); break;
-            case NLC_AIR_NEG: reg(a); break;
-            case NLC_AIR_MUL_CONST: case NLC_AIR_ADD_CONST: case NLC_AIR_SUB_CONST:
-                reg(a); NLC_CHECK(b < prog->n_pool, "AIR program: constant out of range"); break;
-            case NLC_AIR_CONSTRAINT: case NLC_AIR_CONSTRAINT_TRANSITION: case NLC_AIR_CONSTRAINT_FIRST_ROW:
-            case NLC_AIR_CONSTRAINT_LAST_ROW: reg(a); continue;
-            default: NLC_CHECK(false, "AIR program: unknown opcode");
-            }
-            NLC_CHECK(dst < prog->n_regs, "AIR program: destination register out of range");
-            written[dst] = 1;
-        }
-    }
+    validate_program(prog, cols.size(), false);
     const size_t size = (size_t)1 << (log_n + qdb);
     const u64 *x, *lf, *ll;
     quotient_tables_dev(ctx, log_n, qdb, &x, &lf, &ll);
-    size_t blocks = (size + AIR_THREADS - 1) / AIR_THREADS;
-    const size_t full = (size_t)ctx->sm_count * 8;
-    if (blocks > full) blocks = full;
-    const size_t n_threads = blocks * AIR_THREADS;
-    const size_t n_small = prog->n_pool + prog->n_public + prog->n_global + prog->n_challenge + n_alphas;
-    u64* code_dev = ctx->dmalloc(((size_t)prog->n_ops * 4 + 1) / 2 + 2);
-    u64* small = ctx->dmalloc(n_small + 1);
-    u64* cols_dev = ctx->dmalloc(cols.size());
-    u64* regs = ctx->dmalloc(std::max<size_t>((size_t)prog->n_regs * n_threads, 1));
-    try {
-        // pageable sources: the runtime stages them before returning
-        NLC_CUDA(cudaMemcpyAsync(code_dev, prog->code, (size_t)prog->n_ops * 16, cudaMemcpyHostToDevice, ctx->stream));
-        std::vector<u64> host(n_small + 1, 0);
-        size_t o = 0;
-        auto put = [&](const u64* p, size_t cnt) {
-            NLC_CHECK(p || !cnt, "null input array");
-            for (size_t q = 0; q < cnt; q++) host[o + q] = gl::canon(p[q]);
-            o += cnt;
-            return o - cnt;
-        };
-        const size_t o_pool = put(prog->pool, prog->n_pool), o_pub = put(publics, prog->n_public),
-                     o_glob = put(globals, prog->n_global), o_chal = put(challenges, prog->n_challenge),
-                     o_alpha = put(alphas, n_alphas);
-        NLC_CUDA(cudaMemcpyAsync(small, host.data(), host.size() * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-        NLC_CUDA(cudaMemcpyAsync(cols_dev, cols.data(), cols.size() * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
-        NLC_CUDA(cudaStreamSynchronize(ctx->stream)); // `host` / `cols` are stack-lifetime staging sources
-        AirArgs A;
-        A.code = reinterpret_cast<const u32*>(code_dev);
-        A.n_ops = prog->n_ops;
-        A.pool = small + o_pool;
-        A.cols = reinterpret_cast<const u64* const*>(cols_dev);
-        A.publics = small + o_pub;
-        A.globals = small + o_glob;
-        A.challenges = small + o_chal;
-        A.alphas = small + o_alpha;
-        A.n_alphas = (u32)n_alphas;
-        A.n_regs = prog->n_regs;
-        A.log_size = log_n + qdb;
-        A.qdb = qdb;
-        A.coset_x = x;
-        A.lagrange_first = lf;
-        A.lagrange_last = ll;
-        A.last = gl::h_inv(gl::h_root_of_unity(log_n));
-        A.regs = regs;
-        A.out = out_dev;
-        NLC_LAUNCH(ctx, k_air_eval, (unsigned)blocks, AIR_THREADS, 0, A);
-    } catch (...) {
-        ctx->dfree(regs);
-        ctx->dfree(cols_dev);
-        ctx->dfree(small);
-        ctx->dfree(code_dev);
-        throw;
-    }
-    ctx->dfree(regs);
-    ctx->dfree(cols_dev);
-    ctx->dfree(small);
-    ctx->dfree(code_dev);
+    AirDevice dev(ctx, prog, cols, publics, globals, challenges, alphas, n_alphas, size);
+    AirArgs& A = dev.A;
+    A.log_size = log_n + qdb;
+    A.qdb = qdb;
+    A.coset_x = x;
+    A.lagrange_first = lf;
+    A.lagrange_last = ll;
+    A.last = gl::h_inv(gl::h_root_of_unity(log_n));
+    A.out = out_dev;
+    NLC_LAUNCH(ctx, k_air_eval, (unsigned)dev.blocks, AIR_THREADS, 0, A);
 }

@@ -1,0 +1,169 @@
+// air.cuh -- the constraint-program interpreter shared by the STARK (air.cu) and plonk (plonk.cu) quotient kernels:
+// program operands on the device (AirArgs / AirDevice), host-side validation, and the per-point interpreter air_run.
+// The bytecode is the recording of an AIR's / a gate set's `eval` against a recording parser (include/nlc_commit.h,
+// nlc_air_program; starkyx air/parser.rs:6-75).
+#pragma once
+#include "batch.cuh"
+
+namespace {
+
+struct AirArgs {
+    const u32* code;          // n_ops x 4 words {op, dst, a, b}
+    u32 n_ops;
+    const u64* pool;          // 64-bit constants
+    const u64* const* cols;   // device pointers to the columns of the concatenated trace (lde + j*N of every batch)
+    const u64* publics;
+    const u64* globals;
+    const u64* challenges;
+    const u64* alphas;
+    u32 n_alphas;
+    u32 n_regs;
+    int log_size;             // log2(quotient domain) = log_n + quotient_degree_bits
+    int qdb;
+    const u64* coset_x;       // g * w_size^i, natural order
+    const u64* lagrange_first;
+    const u64* lagrange_last;
+    u64 last;                 // w_n^-1: the last point of the subgroup (z_last = x - last)
+    u64* regs;                // n_regs x n_threads scratch (register r of thread t at regs[r * n_threads + t])
+    u64* out;                 // size x n_alphas row-major, natural order of i (the `quotient_values` before transpose)
+};
+
+constexpr int AIR_THREADS = 128;
+constexpr int MAX_ALPHAS = 8;
+
+// The interpreter: runs the straight-line program for ONE point (leaf k, next row at leaf k_next); the virtual
+// registers of the program live in a thread-interleaved scratch matrix (coalesced), the program counter is uniform
+// across the grid.  CONSTRAINT ops fold into acc_j = acc_j * alpha_j + c (ConstraintConsumer, consumer.rs:54-78).
+__device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_t stride, const size_t k, const size_t k_next,
+                                        const u64 z_last, const u64 l_first, const u64 l_last, u64 (&acc)[MAX_ALPHAS]) {
+    for (u32 pc = 0; pc < A.n_ops; pc++) {
+        const uint4 ins = __ldg(reinterpret_cast<const uint4*>(A.code) + pc);
+        const u32 op = ins.x;
+        u64 r;
+        switch (op) {
+        case NLC_AIR_LOCAL: r = gl::dcanon(A.cols[ins.z][k]); break;
+        case NLC_AIR_NEXT: r = gl::dcanon(A.cols[ins.z][k_next]); break;
+        case NLC_AIR_PUBLIC: r = A.publics[ins.z]; break;
+        case NLC_AIR_GLOBAL: r = A.globals[ins.z]; break;
+        case NLC_AIR_CHALLENGE: r = A.challenges[ins.z]; break;
+        case NLC_AIR_CONST: r = A.pool[ins.z]; break;
+        case NLC_AIR_ADD: r = gl::dadd(regs[ins.z * stride], regs[ins.w * stride]); break;
+        case NLC_AIR_SUB: r = gl::dsub(regs[ins.z * stride], regs[ins.w * stride]); break;
+        case NLC_AIR_MUL: r = gl::mul(regs[ins.z * stride], regs[ins.w * stride]); break;
+        case NLC_AIR_NEG: r = gl::neg(regs[ins.z * stride]); break;
+        case NLC_AIR_MUL_CONST: r = gl::mul(regs[ins.z * stride], A.pool[ins.w]); break;
+        case NLC_AIR_ADD_CONST: r = gl::dadd(regs[ins.z * stride], A.pool[ins.w]); break;
+        case NLC_AIR_SUB_CONST: r = gl::dsub(regs[ins.z * stride], A.pool[ins.w]); break;
+        default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
+            u64 c = regs[ins.z * stride];
+            if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
+            else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
+            else if (op == NLC_AIR_CONSTRAINT_LAST_ROW) c = gl::mul(c, l_last);
+#pragma unroll
+            for (int j = 0; j < MAX_ALPHAS; j++)
+                if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
+            continue;
+        }
+        }
+        regs[ins.y * stride] = r;
+    }
+}
+
+// validate a program on the host: every operand in range, every source register written before it is read
+void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_constraints_only) {
+    NLC_CHECK(prog && (prog->code || prog->n_ops == 0), "null AIR program");
+    std::vector<char> written(prog->n_regs, 0);
+    for (u32 pc = 0; pc < prog->n_ops; pc++) {
+        const u32 op = prog->code[4 * pc], dst = prog->code[4 * pc + 1], a = prog->code[4 * pc + 2], b = prog->code[4 * pc + 3];
+        auto reg = [&](u32 r) { NLC_CHECK(r < prog->n_regs && written[r], "AIR program reads a register before writing it"); };
+        switch (op) {
+        case NLC_AIR_NEXT: NLC_CHECK(!plain_constraints_only, "gate constraints read the local row only");
+        // fall through
+        case NLC_AIR_LOCAL: NLC_CHECK(a < n_cols, "AIR program: trace column out of range"); break;
+        case NLC_AIR_PUBLIC: NLC_CHECK(a < prog->n_public, "AIR program: public input out of range"); break;
+        case NLC_AIR_GLOBAL: NLC_CHECK(a < prog->n_global, "AIR program: global value out of range"); break;
+        case NLC_AIR_CHALLENGE: NLC_CHECK(a < prog->n_challenge, "AIR program: challenge out of range"); break;
+        case NLC_AIR_CONST: NLC_CHECK(a < prog->n_pool, "AIR program: constant out of range"); break;
+        case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a); reg(b); break;
+        case NLC_AIR_NEG: reg(a); break;
+        case NLC_AIR_MUL_CONST: case NLC_AIR_ADD_CONST: case NLC_AIR_SUB_CONST:
+            reg(a); NLC_CHECK(b < prog->n_pool, "AIR program: constant out of range"); break;
+        case NLC_AIR_CONSTRAINT_TRANSITION: case NLC_AIR_CONSTRAINT_FIRST_ROW: case NLC_AIR_CONSTRAINT_LAST_ROW:
+            NLC_CHECK(!plain_constraints_only, "gate constraints carry no row filters");
+        // fall through
+        case NLC_AIR_CONSTRAINT: reg(a); continue;
+        default: NLC_CHECK(false, "AIR program: unknown opcode");
+        }
+        NLC_CHECK(dst < prog->n_regs, "AIR program: destination register out of range");
+        written[dst] = 1;
+    }
+}
+
+// A program and its small operands resident on the device for one launch; frees in stream order on destruction.
+struct AirDevice {
+    nlc_ctx* ctx;
+    u64 *code_dev = nullptr, *small = nullptr, *cols_dev = nullptr, *regs = nullptr;
+    AirArgs A{};
+    size_t blocks = 0;
+    AirDevice(nlc_ctx* c, const nlc_air_program* prog, const std::vector<const u64*>& cols, const u64* publics, const u64* globals,
+              const u64* challenges, const u64* alphas, size_t n_alphas, size_t n_points, const u64* extra = nullptr, size_t n_extra = 0,
+              const u64** extra_dev = nullptr)
+        : ctx(c) {
+        blocks = (n_points + AIR_THREADS - 1) / AIR_THREADS;
+        const size_t full = (size_t)ctx->sm_count * 8;
+        if (blocks > full) blocks = full;
+        const size_t n_threads = blocks * AIR_THREADS;
+        const size_t n_small = prog->n_pool + prog->n_public + prog->n_global + prog->n_challenge + n_alphas + n_extra;
+        try {
+            code_dev = ctx->dmalloc(((size_t)prog->n_ops * 4 + 1) / 2 + 2);
+            small = ctx->dmalloc(n_small + 1);
+            cols_dev = ctx->dmalloc(cols.size() + 1);
+            regs = ctx->dmalloc(std::max<size_t>((size_t)prog->n_regs * n_threads, 1));
+            // pageable sources: the runtime stages them before returning
+            if (prog->n_ops)
+                NLC_CUDA(cudaMemcpyAsync(code_dev, prog->code, (size_t)prog->n_ops * 16, cudaMemcpyHostToDevice, ctx->stream));
+            std::vector<u64> host(n_small + 1, 0);
+            size_t o = 0;
+            auto put = [&](const u64* p, size_t cnt) {
+                NLC_CHECK(p || !cnt, "null input array");
+                for (size_t q = 0; q < cnt; q++) host[o + q] = gl::canon(p[q]);
+                o += cnt;
+                return o - cnt;
+            };
+            const size_t o_pool = put(prog->pool, prog->n_pool), o_pub = put(publics, prog->n_public),
+                         o_glob = put(globals, prog->n_global), o_chal = put(challenges, prog->n_challenge),
+                         o_alpha = put(alphas, n_alphas), o_extra = put(extra, n_extra);
+            NLC_CUDA(cudaMemcpyAsync(small, host.data(), host.size() * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+            if (!cols.empty())
+                NLC_CUDA(cudaMemcpyAsync(cols_dev, cols.data(), cols.size() * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+            NLC_CUDA(cudaStreamSynchronize(ctx->stream)); // `host` / `cols` are stack-lifetime staging sources
+            A.code = reinterpret_cast<const u32*>(code_dev);
+            A.n_ops = prog->n_ops;
+            A.pool = small + o_pool;
+            A.cols = reinterpret_cast<const u64* const*>(cols_dev);
+            A.publics = small + o_pub;
+            A.globals = small + o_glob;
+            A.challenges = small + o_chal;
+            A.alphas = small + o_alpha;
+            A.n_alphas = (u32)n_alphas;
+            A.n_regs = prog->n_regs;
+            A.regs = regs;
+            if (extra_dev) *extra_dev = small + o_extra;
+        } catch (...) {
+            release();
+            throw;
+        }
+    }
+    void release() {
+        ctx->dfree(regs);
+        ctx->dfree(cols_dev);
+        ctx->dfree(small);
+        ctx->dfree(code_dev);
+        regs = cols_dev = small = code_dev = nullptr;
+    }
+    ~AirDevice() { release(); }
+    AirDevice(const AirDevice&) = delete;
+    AirDevice& operator=(const AirDevice&) = delete;
+};
+
+} // namespace

@@ -995,6 +995,65 @@ int nlc_stark_quotient_commit(nlc_ctx* ctx, const nlc_air_program* air, nlc_batc
     });
 }
 
+// ---- plonk-side quotient path (plonk.cu) ----
+static void same_ctx(nlc_ctx* ctx, std::initializer_list<nlc_batch*> bs) {
+    for (nlc_batch* b : bs) NLC_CHECK(b && b->ctx == ctx, "commitment missing or from another context");
+}
+int nlc_plonk_zs_partial_products_commit(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, nlc_batch* constants_sigmas,
+                                         nlc_batch* wires, const uint64_t* betas, const uint64_t* gammas, int cap_height,
+                                         nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(out != nullptr, "null output handle");
+        *out = nullptr;
+        same_ctx(ctx, {constants_sigmas, wires});
+        *out = plonk_zs_partial_products_commit_dev(ctx, circuit, constants_sigmas, wires, betas, gammas, cap_height);
+        sync(ctx);
+    });
+}
+int nlc_plonk_vanishing_eval(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, const nlc_air_program* gate_constraints,
+                             nlc_batch* constants_sigmas, nlc_batch* wires, nlc_batch* zs_partial_products,
+                             const uint64_t public_inputs_hash[4], const uint64_t* betas, const uint64_t* gammas,
+                             const uint64_t* alphas, uint64_t* evals_out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(circuit && evals_out, "null argument");
+        same_ctx(ctx, {constants_sigmas, wires, zs_partial_products});
+        int qdb = 0;
+        while ((1 << qdb) < circuit->quotient_degree_factor) qdb++;
+        const size_t words = circuit->num_challenges << (wires->log_n + qdb);
+        DevBuf ev(ctx, words);
+        plonk_vanishing_dev(ctx, circuit, gate_constraints, constants_sigmas, wires, zs_partial_products, public_inputs_hash,
+                            betas, gammas, alphas, ev.p);
+        d2h(ctx, evals_out, ev.p, words * sizeof(u64));
+        sync(ctx);
+    });
+}
+int nlc_plonk_quotient_commit(nlc_ctx* ctx, const nlc_plonk_circuit* circuit, const nlc_air_program* gate_constraints,
+                              nlc_batch* constants_sigmas, nlc_batch* wires, nlc_batch* zs_partial_products,
+                              const uint64_t public_inputs_hash[4], const uint64_t* betas, const uint64_t* gammas,
+                              const uint64_t* alphas, int cap_height, nlc_batch** out) {
+    if (!ctx) return 1;
+    return nlc_guarded(ctx, [&] {
+        CtxGuard g(ctx);
+        NLC_CHECK(circuit && out, "null argument");
+        *out = nullptr;
+        same_ctx(ctx, {constants_sigmas, wires, zs_partial_products});
+        int qdb = 0;
+        while ((1 << qdb) < circuit->quotient_degree_factor) qdb++;
+        const int log_n = wires->log_n, rate_bits = wires->rate_bits;
+        quotient_check(circuit->num_challenges, log_n, qdb, (size_t)circuit->quotient_degree_factor, rate_bits);
+        DevBuf ev(ctx, circuit->num_challenges << (log_n + qdb));
+        plonk_vanishing_dev(ctx, circuit, gate_constraints, constants_sigmas, wires, zs_partial_products, public_inputs_hash,
+                            betas, gammas, alphas, ev.p);
+        *out = quotient_commit_dev(ctx, ev.p, circuit->num_challenges, log_n, qdb, (size_t)circuit->quotient_degree_factor, true,
+                                   rate_bits, cap_height);
+        sync(ctx);
+    });
+}
+
 // ---- a4 ----
 int nlc_poseidon_permute(nlc_ctx* ctx, uint64_t* states, size_t count) {
     if (!ctx) return 1;

@@ -76,6 +76,13 @@ void quotient_tables_dev(nlc_ctx* ctx, int log_n, int qdb, const u64** x, const 
 void air_eval_dev(nlc_ctx* ctx, const nlc_air_program* prog, nlc_batch* const* batches, int n_batches, const u64* publics,
                   const u64* globals, const u64* challenges, const u64* alphas, size_t n_alphas, int qdb, u64* out_dev);
 
+// ---- plonk.cu ----
+nlc_batch* plonk_zs_partial_products_commit_dev(nlc_ctx* ctx, const nlc_plonk_circuit* c, nlc_batch* cs, nlc_batch* wires,
+                                                const u64* betas, const u64* gammas, int cap_height);
+void plonk_vanishing_dev(nlc_ctx* ctx, const nlc_plonk_circuit* c, const nlc_air_program* gates, nlc_batch* cs, nlc_batch* wires,
+                         nlc_batch* zs_pp, const u64* public_inputs_hash, const u64* betas, const u64* gammas,
+                         const u64* alphas, u64* out_dev);
+
 // ---- fri.cu ----
 void challenger_observe_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, const u64* elems_dev, size_t n);
 void challenger_get_dev(nlc_ctx* ctx, nlc_challenger* ch_dev, size_t n, u64* out_dev);

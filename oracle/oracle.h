@@ -143,6 +143,7 @@ void orc_vec_sub(const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
 void orc_vec_mul(const uint64_t* a, const uint64_t* b, uint64_t* out, size_t n);
 void orc_vec_neg(const uint64_t* a, uint64_t* out, size_t n);
 void orc_vec_mul_scalar_add(const uint64_t* a, uint64_t s, const uint64_t* c, uint64_t* out, size_t n);
+void orc_vec_inv(const uint64_t* a, uint64_t* out, size_t n);
 
 #ifdef __cplusplus
 }

@@ -30,3 +30,8 @@ void orc_vec_mul_scalar_add(const uint64_t* a, uint64_t s, const uint64_t* c, ui
 #pragma omp parallel for num_threads(orc_get_threads()) schedule(static)
     for (size_t i = 0; i < n; i++) out[i] = gl_add(gl_mul(gl_canon(a[i]), s), gl_canon(c[i]));
 }
+/* element-wise inverse (Fermat); 0 has none: plonky2's batch_multiplicative_inverse panics on it, here out = 0 */
+void orc_vec_inv(const uint64_t* a, uint64_t* out, size_t n) {
+#pragma omp parallel for num_threads(orc_get_threads()) schedule(static)
+    for (size_t i = 0; i < n; i++) out[i] = gl_inv(gl_canon(a[i]));
+}
