@@ -23,7 +23,7 @@ namespace {
 enum { KIND_ROOTS = 1, KIND_TW = 2, KIND_PW = 3 };
 constexpr int NTT_THREADS = 256;
 #ifndef NTT_MINB
-#define NTT_MINB 4
+#define NTT_MINB 3
 #endif
 
 __device__ __forceinline__ u32 brev(u32 x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
