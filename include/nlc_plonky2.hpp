@@ -429,6 +429,61 @@ class PolynomialBatch {
         c.check(nlc_batch_cap(h, b.merkle_tree.cap.hashes[0].elements));
         return b;
     }
+    // from_values that also fills the PUBLIC struct fields a patched plonky2 keeps on the host -- `polynomials`,
+    // merkle_tree.leaves (flat N x W), merkle_tree.digests -- while the commit runs.
+    struct HostFields {
+        std::vector<F> leaves;       // N x W row-major, row k = leaf k (index-bit-reversed LDE point)
+        std::vector<HashOut> digests;
+    };
+    static PolynomialBatch from_values_materialised(const std::vector<PolynomialValues>& values, size_t rate_bits, bool blinding,
+                                                    size_t cap_height, HostFields* fields = nullptr) {
+        if (blinding) throw Panic("blinding = true is not used on this path (prover.rs:91-93,171-178 pass false)");
+        if (values.empty()) throw Panic("PolynomialBatch: at least one polynomial required");
+        if (!lens_equal(values)) throw Panic("All polynomials in a batch must have the same length");
+        Context& c = Context::current();
+        const size_t n = values[0].len(), W = values.size();
+        const int log_n = (int)log2_strict(n);
+        const size_t N = n << rate_bits;
+        if (cap_height > (size_t)log_n + rate_bits) throw Panic("cap_height should be at most log2(leaves.len())");
+        PolynomialBatch b;
+        b.polys_.assign(W, PolynomialCoeffs(std::vector<F>(n)));
+        std::vector<const uint64_t*> cols;
+        std::vector<uint64_t*> cout;
+        for (const auto& v : values) cols.push_back(v.values.data());
+        for (auto& p : b.polys_) cout.push_back(p.coeffs.data());
+        b.merkle_tree.cap.hashes.resize((size_t)1 << cap_height);
+        if (fields) {
+            fields->leaves.assign(N * W, 0);
+            fields->digests.assign(2 * (N - ((size_t)1 << cap_height)), HashOut());
+        }
+        nlc_batch* h = nullptr;
+        c.check(nlc_commit_from_values_materialised(c.raw(), cols.data(), W, log_n, (int)rate_bits, (int)cap_height, cout.data(),
+                                                    fields ? fields->leaves.data() : nullptr,
+                                                    fields && !fields->digests.empty() ? fields->digests[0].elements : nullptr,
+                                                    b.merkle_tree.cap.hashes[0].elements, &h));
+        b.h_.reset(h, nlc_batch_free);
+        b.n_polys_ = W;
+        b.degree_log = (size_t)log_n;
+        b.rate_bits = rate_bits;
+        b.cap_height_ = cap_height;
+        return b;
+    }
+    // wrap a handle produced by one of the quotient-side entry points (stark:: / plonk:: below)
+    static PolynomialBatch adopt(nlc_batch* h) {
+        Context& c = Context::current();
+        PolynomialBatch b;
+        b.h_.reset(h, nlc_batch_free);
+        size_t W = 0;
+        int log_n = 0, r = 0, cap = 0;
+        c.check(nlc_batch_info(h, &W, &log_n, &r, &cap));
+        b.n_polys_ = W;
+        b.degree_log = (size_t)log_n;
+        b.rate_bits = (size_t)r;
+        b.cap_height_ = (size_t)cap;
+        b.merkle_tree.cap.hashes.resize((size_t)1 << cap);
+        c.check(nlc_batch_cap(h, b.merkle_tree.cap.hashes[0].elements));
+        return b;
+    }
     size_t num_polys() const { return n_polys_; }
     // `polynomials` field (proof.rs:307-310 evaluates them at zeta): fetched from HBM on first use
     const std::vector<PolynomialCoeffs>& polynomials() {
@@ -569,5 +624,105 @@ class PolynomialBatch {
         if (w != f.size()) throw Panic("FriProof: flat layout mismatch");
     }
 };
+
+// ---- starkyx's quotient with the AIR evaluated on the device --------------------------------------
+// An AIR recorded once against a recording AirParser (vendor/starkyx/starkyx/src/air/parser.rs:6-75): the straight-line
+// program of include/nlc_commit.h (nlc_air_program).  `emit` appends one instruction {op, dst, a, b}.
+struct AirProgram {
+    std::vector<uint32_t> code;
+    std::vector<F> pool;
+    uint32_t n_regs = 0, n_public = 0, n_global = 0, n_challenge = 0;
+    void emit(uint32_t op, uint32_t dst, uint32_t a, uint32_t b = 0) {
+        code.insert(code.end(), {op, dst, a, b});
+        if (op < NLC_AIR_CONSTRAINT && dst + 1 > n_regs) n_regs = dst + 1;
+    }
+    nlc_air_program c() const {
+        nlc_air_program p{};
+        p.code = code.data();
+        p.n_ops = (uint32_t)(code.size() / 4);
+        p.n_regs = n_regs;
+        p.pool = pool.data();
+        p.n_pool = (uint32_t)pool.size();
+        p.n_public = n_public;
+        p.n_global = n_global;
+        p.n_challenge = n_challenge;
+        return p;
+    }
+};
+namespace stark {
+inline std::vector<nlc_batch*> handles(const std::vector<const PolynomialBatch*>& bs) {
+    std::vector<nlc_batch*> hs;
+    for (const PolynomialBatch* b : bs) hs.push_back(b->raw());
+    return hs;
+}
+// the constraint accumulators of prover.rs:306-335 for every point of the quotient domain, before 1/Z_H
+inline std::vector<F> air_eval(const AirProgram& air, const std::vector<const PolynomialBatch*>& trace_data,
+                               const std::vector<F>& public_inputs, const std::vector<F>& global_values,
+                               const std::vector<F>& challenges, const std::vector<F>& alphas, size_t quotient_degree_bits) {
+    Context& c = Context::current();
+    const nlc_air_program p = air.c();
+    auto hs = handles(trace_data);
+    std::vector<F> out(alphas.size() << (trace_data.at(0)->degree_log + quotient_degree_bits));
+    c.check(nlc_air_eval(c.raw(), &p, hs.data(), (int)hs.size(), public_inputs.data(), global_values.data(), challenges.data(),
+                         alphas.data(), alphas.size(), (int)quotient_degree_bits, out.data()));
+    return out;
+}
+// quotient_polys + trim / chunks / from_coeffs (prover.rs:144-178), all on the device
+inline PolynomialBatch quotient_commitment(const AirProgram& air, const std::vector<const PolynomialBatch*>& trace_data,
+                                           const std::vector<F>& public_inputs, const std::vector<F>& global_values,
+                                           const std::vector<F>& challenges, const std::vector<F>& alphas,
+                                           size_t quotient_degree_factor, size_t cap_height) {
+    Context& c = Context::current();
+    const nlc_air_program p = air.c();
+    auto hs = handles(trace_data);
+    nlc_batch* h = nullptr;
+    c.check(nlc_stark_quotient_commit(c.raw(), &p, hs.data(), (int)hs.size(), public_inputs.data(), global_values.data(),
+                                      challenges.data(), alphas.data(), alphas.size(), quotient_degree_factor, (int)cap_height, &h));
+    return PolynomialBatch::adopt(h);
+}
+} // namespace stark
+
+// ---- plonk::prover::prove between the wires commitment and the openings ---------------------------
+namespace plonk {
+struct CircuitShape { // the fields of CommonCircuitData the quotient path reads
+    size_t num_constants = 0, num_routed_wires = 0, num_challenges = 0, num_partial_products = 0, quotient_degree_factor = 0;
+    std::vector<F> k_is;
+    nlc_plonk_circuit c() const {
+        nlc_plonk_circuit p{};
+        p.num_constants = num_constants;
+        p.num_routed_wires = num_routed_wires;
+        p.num_challenges = num_challenges;
+        p.num_partial_products = num_partial_products;
+        p.quotient_degree_factor = (int)quotient_degree_factor;
+        p.k_is = k_is.data();
+        return p;
+    }
+};
+// all_wires_permutation_partial_products + the zs_partial_products commitment (plonk/prover.rs)
+inline PolynomialBatch zs_partial_products_commitment(const CircuitShape& circuit, const PolynomialBatch& constants_sigmas,
+                                                      const PolynomialBatch& wires, const std::vector<F>& betas,
+                                                      const std::vector<F>& gammas, size_t cap_height) {
+    Context& c = Context::current();
+    const nlc_plonk_circuit p = circuit.c();
+    nlc_batch* h = nullptr;
+    c.check(nlc_plonk_zs_partial_products_commit(c.raw(), &p, constants_sigmas.raw(), wires.raw(), betas.data(), gammas.data(),
+                                                 (int)cap_height, &h));
+    return PolynomialBatch::adopt(h);
+}
+// compute_quotient_polys + the quotient commitment
+inline PolynomialBatch quotient_commitment(const CircuitShape& circuit, const AirProgram& gate_constraints,
+                                           const PolynomialBatch& constants_sigmas, const PolynomialBatch& wires,
+                                           const PolynomialBatch& zs_partial_products, const HashOut& public_inputs_hash,
+                                           const std::vector<F>& betas, const std::vector<F>& gammas,
+                                           const std::vector<F>& alphas, size_t cap_height) {
+    Context& c = Context::current();
+    const nlc_plonk_circuit p = circuit.c();
+    const nlc_air_program g = gate_constraints.c();
+    nlc_batch* h = nullptr;
+    c.check(nlc_plonk_quotient_commit(c.raw(), &p, &g, constants_sigmas.raw(), wires.raw(), zs_partial_products.raw(),
+                                      public_inputs_hash.elements, betas.data(), gammas.data(), alphas.data(), (int)cap_height, &h));
+    return PolynomialBatch::adopt(h);
+}
+} // namespace plonk
 
 } // namespace plonky2

@@ -150,6 +150,70 @@ int main() {
     challenger.observe_cap(quotient_commitment.merkle_tree.cap);
     orc_challenger_observe(&och, oquot.capv.data(), oquot.capv.size());
 
+    // ---- an AIR evaluated on the device (prover.rs:306-352), driven from C++ ----
+    {   // trace columns (a, b, c = a * b, d): constraints  a * b - c  (all rows)  and  (d_next - d - 1) (transition);
+        // quotient_degree_factor 1 (degree-2 constraints), 2 alphas: acc = (a b - c) alpha + (d' - d - 1) z_last
+        const size_t n = degree;
+        std::vector<std::vector<F>> cols(4, std::vector<F>(n));
+        for (size_t i = 0; i < n; i++) {
+            cols[0][i] = rand_field();
+            cols[1][i] = rand_field();
+            cols[2][i] = mulmod(cols[0][i], cols[1][i]);
+            cols[3][i] = (F)(1000 + i);
+        }
+        std::vector<PolynomialValues> tv(cols.begin(), cols.end());
+        PolynomialBatch::HostFields fields;
+        PolynomialBatch t = PolynomialBatch::from_values_materialised(tv, rate_bits, false, cap_height, &fields);
+        OracleBatch ot = oracle_commit(cols, (int)rate_bits, (int)cap_height, true);
+        CHECK(t.merkle_tree.cap.flatten() == ot.capv);       // fields written back while the commit ran
+        CHECK(fields.leaves == ot.leaves);
+        CHECK(std::memcmp(fields.digests[0].elements, ot.digests.data(), ot.digests.size() * 8) == 0);
+        for (size_t j = 0; j < 4; j++) CHECK(std::memcmp(t.polynomials()[j].coeffs.data(), ot.coeffs.data() + j * n, n * 8) == 0);
+        AirProgram air;  // what a recording AirParser produces for this AIR
+        air.pool = {1};
+        air.emit(NLC_AIR_LOCAL, 0, 0);
+        air.emit(NLC_AIR_LOCAL, 1, 1);
+        air.emit(NLC_AIR_MUL, 0, 0, 1);
+        air.emit(NLC_AIR_LOCAL, 1, 2);
+        air.emit(NLC_AIR_SUB, 0, 0, 1);
+        air.emit(NLC_AIR_CONSTRAINT, 0, 0);
+        air.emit(NLC_AIR_NEXT, 0, 3);
+        air.emit(NLC_AIR_LOCAL, 1, 3);
+        air.emit(NLC_AIR_SUB, 0, 0, 1);
+        air.emit(NLC_AIR_SUB_CONST, 0, 0, 0);
+        air.emit(NLC_AIR_CONSTRAINT_TRANSITION, 0, 0);
+        const std::vector<F> al = {rand_field(), rand_field()};
+        std::vector<F> acc = stark::air_eval(air, {&t}, {}, {}, {}, al, 0);
+        // the same accumulators from the oracle's LDE rows: point i of the quotient domain = LDE point i * 2^rate_bits
+        const size_t lN = degree_bits + rate_bits;
+        auto brev = [&](size_t x) { size_t r = 0; for (size_t b = 0; b < lN; b++) r |= ((x >> b) & 1) << (lN - 1 - b); return r; };
+        const F w = powmod(1753635133440165772ULL, (uint64_t)1 << (32 - degree_bits));
+        const F last = powmod(w, ORDER - 2);
+        F x = COSET_SHIFT;
+        auto sub = [](F a, F b) { return a >= b ? a - b : a + (ORDER - b); };
+        std::vector<F> want(acc.size());
+        for (size_t i = 0; i < n; i++, x = mulmod(x, w)) {
+            const F* row = &ot.leaves[brev(i << rate_bits) * 4];
+            const F* nxt = &ot.leaves[brev(((i + 1) % n) << rate_bits) * 4];
+            const F c0 = sub(mulmod(row[0], row[1]), row[2]);
+            const F c1 = mulmod(sub(sub(nxt[3], row[3]), 1), sub(x, last));
+            for (size_t a = 0; a < 2; a++) want[i * 2 + a] = (F)(((unsigned __int128)mulmod(c0, al[a]) + c1) % ORDER);
+        }
+        CHECK(acc == want);
+        // ... and the quotient commitment in one call: evaluate, 1/Z_H, coset_ifft, chunks, from_coeffs
+        PolynomialBatch q = stark::quotient_commitment(air, {&t}, {}, {}, {}, al, 1, cap_height);
+        OracleBatch oq;
+        oq.W = 2;
+        oq.log_n = (int)degree_bits;
+        oq.coeffs.resize(2 * n);
+        oq.leaves.resize((n << rate_bits) * 2);
+        oq.digests.resize(8 * ((n << rate_bits) - ((size_t)1 << cap_height)));
+        oq.capv.resize((size_t)4 << cap_height);
+        CHECK(orc_quotient_commit(want.data(), 2, (int)degree_bits, 0, 1, 1, (int)rate_bits, (int)cap_height, oq.coeffs.data(),
+                                  oq.leaves.data(), oq.digests.data(), oq.capv.data()) == 0);
+        CHECK(q.num_polys() == 2 && q.merkle_tree.cap.flatten() == oq.capv);
+    }
+
     // ---- zeta, openings (prover.rs:183-193; proof.rs:300-328) ----
     FE zeta = challenger.get_extension_challenge();
     uint64_t ozeta[2];
