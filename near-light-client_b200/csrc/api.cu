@@ -315,6 +315,7 @@ int nlc_init(int device, nlc_ctx** out) {
         NLC_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         unsigned long long thresh = ~0ull; // keep freed blocks in the pool: commits reuse the same sizes
         NLC_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        if (const char* e = getenv("NLC_CACHE_MB")) ctx->cache_budget = (size_t)strtoull(e, nullptr, 10) << 20;
         cudaSetDevice(prev);
         *out = ctx;
         return 0;
@@ -331,6 +332,7 @@ void nlc_destroy(nlc_ctx* ctx) {
     {
         CtxGuard g(ctx);
         cudaStreamSynchronize(ctx->stream);
+        ctx->cache_release_all();
         for (auto& kv : ctx->tables) cudaFree(kv.second);
         if (ctx->pinned) cudaFreeHost(ctx->pinned);
         ctx->downloader.shutdown();

@@ -99,14 +99,71 @@ struct nlc_ctx {
         cudaEventRecord(timing_events.back().second.second, stream);
     }
 
+    // Device buffers come from the stream-ordered pool (cudaMallocAsync) THROUGH a size-keyed cache of this context:
+    // a proof commits a handful of shapes over and over (wires 135, Z 20, quotient 16 columns, FRI rounds), and when
+    // their buffers are released in one order and requested in another the driver pool has to remap physical pages
+    // into new contiguous ranges -- measured: a 2^16 x 124 trace commit 4.5 ms when its blocks come back as they were,
+    // 35-140 ms when the pool has to grow or remap.  A freed block therefore waits here, keyed by its (rounded) size,
+    // and the next request of that size takes it back without a driver call.  Safe because every reuse is ordered on
+    // this context's stream: the other streams of a call (copy, download) are joined before the call returns, and
+    // nlc_set_stream synchronises the old stream before switching.  Budget NLC_CACHE_MB (default 16384): blocks beyond
+    // it go back to the driver; everything goes back when an allocation fails, and at nlc_destroy.
+    std::multimap<size_t, void*> cache_free; // rounded bytes -> block
+    std::map<void*, size_t> cache_live;      // block -> rounded bytes
+    size_t cache_bytes = 0, cache_budget = (size_t)16384 << 20;
+    static size_t cache_round(size_t bytes) {
+        const size_t g = bytes < ((size_t)1 << 20) ? 512 : ((size_t)2 << 20);
+        return (bytes + g - 1) / g * g;
+    }
+    void cache_release_all() {
+        for (auto& kv : cache_free) cudaFreeAsync(kv.second, stream);
+        cache_free.clear();
+        cache_bytes = 0;
+    }
     u64* dmalloc(size_t words) {
-        void* p = nullptr;
         if (words == 0) words = 1;
-        NLC_CUDA(cudaMallocAsync(&p, words * sizeof(u64), stream));
+        size_t bytes = cache_round(words * sizeof(u64));
+        void* p = nullptr;
+        auto it = cache_free.lower_bound(bytes);
+        if (it != cache_free.end() && it->first <= bytes + bytes / 8) { // same shape (or within 1/8 of it) as a freed block
+            p = it->second;
+            bytes = it->first;
+            cache_bytes -= bytes;
+            cache_free.erase(it);
+        } else {
+            cudaError_t e = cudaMallocAsync(&p, bytes, stream);
+            if (e == cudaErrorMemoryAllocation) { // give the cached blocks back and try once more
+                cudaGetLastError();
+                cache_release_all();
+                cudaStreamSynchronize(stream);
+                e = cudaMallocAsync(&p, bytes, stream);
+            }
+            NLC_CUDA(e);
+        }
+        cache_live[p] = bytes;
         return (u64*)p;
     }
     void dfree(void* p) {
-        if (p) cudaFreeAsync(p, stream);
+        if (!p) return;
+        auto it = cache_live.find(p);
+        if (it == cache_live.end()) {
+            cudaFreeAsync(p, stream);
+            return;
+        }
+        const size_t bytes = it->second;
+        cache_live.erase(it);
+        if (bytes > cache_budget) {
+            cudaFreeAsync(p, stream);
+            return;
+        }
+        cache_free.emplace(bytes, p);
+        cache_bytes += bytes;
+        while (cache_bytes > cache_budget && !cache_free.empty()) { // over budget: the largest blocks go first
+            auto last = std::prev(cache_free.end());
+            cudaFreeAsync(last->second, stream);
+            cache_bytes -= last->first;
+            cache_free.erase(last);
+        }
     }
     u64* pin(size_t words) {
         if (words > pinned_words) {
