@@ -239,6 +239,13 @@ int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_ch
  * RecursiveStarkParser, plonky2/parser/mod.rs:30-38, records a circuit): any AIR written against the AirParser trait --
  * Chip<L> constraint lists (chip/mod.rs:58-66), ArithmeticConstraint (chip/arithmetic/mod.rs:13-50), the field
  * instructions (chip/field/add.rs, mul.rs, ...) -- compiles unchanged.  One instruction = 4 x uint32 {op, dst, a, b}: */
+/* Instruction word 0 = opcode (bits 0-7) | flags (bits 8-10).  The interpreter keeps the previous instruction's result
+ * in an accumulator: A_LAST / B_LAST take operand a / b from it instead of from a register, NO_STORE says every use of
+ * this result comes before the next result is produced, so it is never written to its register (dst is ignored).
+ * Flags are an optimisation the recording compiler may or may not use; a program without them is equally valid. */
+#define NLC_AIR_FLAG_A_LAST 1u
+#define NLC_AIR_FLAG_B_LAST 2u
+#define NLC_AIR_FLAG_NO_STORE 4u
 #define NLC_AIR_LOCAL 0                  /* dst = local_slice()[a]      (a indexes the columns of all trace commitments, concatenated) */
 #define NLC_AIR_NEXT 1                   /* dst = next_slice()[a] */
 #define NLC_AIR_PUBLIC 2                 /* dst = public_slice()[a] */

