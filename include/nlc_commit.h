@@ -54,6 +54,10 @@ int nlc_synchronize(nlc_ctx* ctx);
  * (b) keep input and output device buffers alive and unmodified until nlc_synchronize(ctx) or a later synchronising
  * accessor (nlc_batch_cap, ...) has returned. */
 int nlc_wait_stream(nlc_ctx* ctx, void* producer_stream);
+/* Device buffers are cached per context by size (budget NLC_CACHE_MB, default 16384): out[0] = requests
+ * served from the cache, out[1] = requests that went to the driver (cudaMallocAsync), out[2] = microseconds spent in
+ * those driver calls, out[3] = bytes waiting in the cache now. */
+int nlc_cache_stats(nlc_ctx* ctx, uint64_t out[4]);
 /* Number of kernels this library has launched on ctx since creation (bench.py's gpu_launches). */
 uint64_t nlc_launch_count(nlc_ctx* ctx);
 
@@ -263,6 +267,7 @@ int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_ch
 #define NLC_AIR_CONSTRAINT_TRANSITION 14 /* constraint_transition(reg a): * z_last = x - g^(n-1) */
 #define NLC_AIR_CONSTRAINT_FIRST_ROW 15  /* constraint_first_row(reg a): * lagrange_basis_first */
 #define NLC_AIR_CONSTRAINT_LAST_ROW 16   /* constraint_last_row(reg a):  * lagrange_basis_last */
+#define NLC_AIR_MULADD_CONST 17          /* dst = reg a * pool[b] + accumulator (the previous result): sums of constant multiples */
 typedef struct {
     const uint32_t* code; /* n_ops x 4 */
     uint32_t n_ops;

@@ -634,7 +634,7 @@ struct AirProgram {
     uint32_t n_regs = 0, n_public = 0, n_global = 0, n_challenge = 0;
     void emit(uint32_t op, uint32_t dst, uint32_t a, uint32_t b = 0) {
         code.insert(code.end(), {op, dst, a, b});
-        if (op < NLC_AIR_CONSTRAINT && dst + 1 > n_regs) n_regs = dst + 1;
+        if ((op < NLC_AIR_CONSTRAINT || op == NLC_AIR_MULADD_CONST) && dst + 1 > n_regs) n_regs = dst + 1;
     }
     nlc_air_program c() const {
         nlc_air_program p{};

@@ -59,6 +59,7 @@ SIGNATURES = {
     "nlc_set_stream": (C.c_int, [vp, vp]),
     "nlc_synchronize": (C.c_int, [vp]),
     "nlc_wait_stream": (C.c_int, [vp, vp]),
+    "nlc_cache_stats": (C.c_int, [vp, u64p]),
     "nlc_launch_count": (C.c_uint64, [vp]),
     "nlc_timing_enable": (C.c_int, [vp, C.c_int]),
     "nlc_timing_read": (C.c_int, [vp, C.POINTER(CTiming)]),

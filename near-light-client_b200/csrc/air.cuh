@@ -51,6 +51,7 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_
             case NLC_AIR_MUL_CONST: r = gl::mul(ra, A.pool[ins.w]); break;
             case NLC_AIR_ADD_CONST: r = gl::dadd(ra, A.pool[ins.w]); break;
             case NLC_AIR_SUB_CONST: r = gl::dsub(ra, A.pool[ins.w]); break;
+            case NLC_AIR_MULADD_CONST: r = gl::dadd(gl::mul(ra, A.pool[ins.w]), last); break;
             default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
                 u64 c = ra;
                 if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
@@ -103,6 +104,8 @@ void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_con
         case NLC_AIR_CONST: NLC_CHECK(a < prog->n_pool, "AIR program: constant out of range"); break;
         case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a, NLC_AIR_FLAG_A_LAST); reg(b, NLC_AIR_FLAG_B_LAST); break;
         case NLC_AIR_NEG: reg(a, NLC_AIR_FLAG_A_LAST); break;
+        case NLC_AIR_MULADD_CONST: NLC_CHECK(have_last, "AIR program reads the accumulator before any result exists");
+        // fall through
         case NLC_AIR_MUL_CONST: case NLC_AIR_ADD_CONST: case NLC_AIR_SUB_CONST:
             reg(a, NLC_AIR_FLAG_A_LAST); NLC_CHECK(b < prog->n_pool, "AIR program: constant out of range"); break;
         case NLC_AIR_CONSTRAINT_TRANSITION: case NLC_AIR_CONSTRAINT_FIRST_ROW: case NLC_AIR_CONSTRAINT_LAST_ROW:

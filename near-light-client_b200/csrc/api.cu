@@ -359,6 +359,15 @@ int nlc_set_stream(nlc_ctx* ctx, void* cuda_stream) {
         ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     });
 }
+int nlc_cache_stats(nlc_ctx* ctx, uint64_t out[4]) {
+    if (!ctx || !out) return 1;
+    CtxGuard g(ctx);
+    out[0] = ctx->cache_hits;
+    out[1] = ctx->cache_misses;
+    out[2] = ctx->cache_miss_us;
+    out[3] = ctx->cache_bytes;
+    return 0;
+}
 int nlc_wait_stream(nlc_ctx* ctx, void* producer_stream) {
     if (!ctx) return 1;
     return nlc_guarded(ctx, [&] {

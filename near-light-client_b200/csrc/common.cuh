@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <exception>
@@ -104,13 +105,14 @@ struct nlc_ctx {
     // their buffers are released in one order and requested in another the driver pool has to remap physical pages
     // into new contiguous ranges -- measured: a 2^16 x 124 trace commit 4.5 ms when its blocks come back as they were,
     // 35-140 ms when the pool has to grow or remap.  A freed block therefore waits here, keyed by its (rounded) size,
-    // and the next request of that size takes it back without a driver call.  Safe because every reuse is ordered on
+    // and the next request of exactly that size takes it back without a driver call.  Safe because every reuse is ordered on
     // this context's stream: the other streams of a call (copy, download) are joined before the call returns, and
     // nlc_set_stream synchronises the old stream before switching.  Budget NLC_CACHE_MB (default 16384): blocks beyond
     // it go back to the driver; everything goes back when an allocation fails, and at nlc_destroy.
     std::multimap<size_t, void*> cache_free; // rounded bytes -> block
     std::map<void*, size_t> cache_live;      // block -> rounded bytes
     size_t cache_bytes = 0, cache_budget = (size_t)16384 << 20;
+    u64 cache_hits = 0, cache_misses = 0, cache_miss_us = 0; // nlc_cache_stats
     static size_t cache_round(size_t bytes) {
         const size_t g = bytes < ((size_t)1 << 20) ? 512 : ((size_t)2 << 20);
         return (bytes + g - 1) / g * g;
@@ -124,13 +126,21 @@ struct nlc_ctx {
         if (words == 0) words = 1;
         size_t bytes = cache_round(words * sizeof(u64));
         void* p = nullptr;
-        auto it = cache_free.lower_bound(bytes);
-        if (it != cache_free.end() && it->first <= bytes + bytes / 8) { // same shape (or within 1/8 of it) as a freed block
+        auto it = cache_free.find(bytes); // exact (rounded) size only: a proof's multiset of shapes is then served from the
+        if (it != cache_free.end()) {     // second proof on, whatever the order of requests and releases
             p = it->second;
             bytes = it->first;
             cache_bytes -= bytes;
             cache_free.erase(it);
+            cache_hits++;
         } else {
+            cache_misses++;
+            const auto t0 = std::chrono::steady_clock::now();
+            struct Timer {
+                u64& acc;
+                std::chrono::steady_clock::time_point t0;
+                ~Timer() { acc += (u64)std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count(); }
+            } timer{cache_miss_us, t0};
             cudaError_t e = cudaMallocAsync(&p, bytes, stream);
             if (e == cudaErrorMemoryAllocation) { // give the cached blocks back and try once more
                 cudaGetLastError();

@@ -7,7 +7,7 @@ DESIGN.md section 2; in-tree call sites: /root/reference/nearx/src/test_utils.rs
 /root/reference/nearx/src/main.rs and the circuit builds of /root/reference/scripts/build-circuit.sh:10-18):
   plonk/circuit_data.rs   CircuitConfig::standard_recursion_config, CommonCircuitData::{constants_range, sigmas_range,
                           zs_range, partial_products_range, get_fri_instance}
-  gates/{arithmetic_base, arithmetic_extension, constant, public_input, noop, base_sum}.rs
+  gates/{arithmetic_base, arithmetic_extension, constant, public_input, noop, base_sum, poseidon}.rs
                           the gates' eval_unfiltered, written against the AirParser-style interface of starky.py
   gates/selectors.rs      selector_polynomials, SelectorsInfo, UNUSED_SELECTOR;  gates/gate.rs compute_filter
   plonk/permutation_argument.rs  WirePartition::get_sigma_polys (the cyclic neighbour map)
@@ -217,6 +217,148 @@ class BaseSumGate(Gate):
 
 
 
+def _poseidon_round_constants():
+    """ALL_ROUND_CONSTANTS, read from the generated header the kernels compile in (csrc/poseidon_constants.h)."""
+    import os
+    import re
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "poseidon_constants.h")
+    rc = [int(h, 16) for h in re.findall(r"0x([0-9a-fA-F]{16})ULL", open(path).read())]
+    assert len(rc) == 360
+    return rc
+
+
+class PoseidonGate(Gate):
+    """gates/poseidon.rs: one width-12 permutation per row -- the gate the 135-wire configuration is sized for.  Wires:
+    input 0..12, output 12..24, swap 24, delta 25..29, then the S-box INPUTS of every round but the first as witness
+    wires (full rounds 1..3: 29..65, partial rounds: 65..87, second full rounds: 87..135), so that every constraint has
+    degree <= 7: swap (swap - 1); delta_i - swap (rhs_i - lhs_i); state - sbox_in at each S-box; output - state.
+    123 constraints.  Upstream evaluates the partial rounds in their fast (sparse-matrix) form; the S-box inputs and the
+    final state are the same field elements in the naive form used here (constant layer, S-box on lane 0, MDS), and so
+    are the constraint polynomials, affine in the wires between two S-box layers."""
+    WIDTH, HALF_FULL, N_PARTIAL = 12, 4, 22
+    MDS_CIRC = [17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20]
+    MDS_DIAG = [8] + [0] * 11
+    WIRE_SWAP, START_DELTA, START_FULL_0, START_PARTIAL, START_FULL_1 = 24, 25, 29, 65, 87
+    _RC = None
+
+    @classmethod
+    def rc(cls):
+        if cls._RC is None:
+            cls._RC = _poseidon_round_constants()
+        return cls._RC
+
+    def degree(self):
+        return 7
+
+    def num_constraints(self):
+        return 1 + 4 + 12 * 3 + 22 + 12 * 4 + 12
+
+    @staticmethod
+    def wire_full_sbox_0(r, i):
+        return PoseidonGate.START_FULL_0 + 12 * (r - 1) + i
+
+    @staticmethod
+    def wire_partial_sbox(r):
+        return PoseidonGate.START_PARTIAL + r
+
+    @staticmethod
+    def wire_full_sbox_1(r, i):
+        return PoseidonGate.START_FULL_1 + 12 * r + i
+
+    def _mds(self, parser, state):
+        out = []
+        for r in range(12):
+            acc = parser.mul_const(state[r], self.MDS_CIRC[0] + self.MDS_DIAG[r])
+            for i in range(1, 12):
+                acc = parser.add(acc, parser.mul_const(state[(i + r) % 12], self.MDS_CIRC[i]))
+            out.append(acc)
+        return out
+
+    @staticmethod
+    def _sbox(parser, x):
+        x2 = parser.mul(x, x)
+        x4 = parser.mul(x2, x2)
+        return parser.mul(parser.mul(x, x2), x4)
+
+    def eval_unfiltered(self, parser, local_constants, local_wires, public_inputs_hash):
+        rc = self.rc()
+        w = local_wires
+        cons = []
+        swap = w[self.WIRE_SWAP]
+        cons.append(parser.mul(swap, parser.sub_const(swap, 1)))
+        state = [None] * 12
+        for i in range(4):
+            lhs, rhs, delta = w[i], w[i + 4], w[self.START_DELTA + i]
+            cons.append(parser.sub(parser.mul(swap, parser.sub(rhs, lhs)), delta))
+            state[i] = parser.add(lhs, delta)
+            state[i + 4] = parser.sub(rhs, delta)
+        for i in range(8, 12):
+            state[i] = w[i]
+        rnd = 0
+        for r in range(self.HALF_FULL):
+            state = [parser.add_const(state[i], rc[12 * rnd + i]) for i in range(12)]
+            if r != 0:
+                for i in range(12):
+                    sbox_in = w[self.wire_full_sbox_0(r, i)]
+                    cons.append(parser.sub(state[i], sbox_in))
+                    state[i] = sbox_in
+            state = self._mds(parser, [self._sbox(parser, x) for x in state])
+            rnd += 1
+        for r in range(self.N_PARTIAL):
+            state = [parser.add_const(state[i], rc[12 * rnd + i]) for i in range(12)]
+            sbox_in = w[self.wire_partial_sbox(r)]
+            cons.append(parser.sub(state[0], sbox_in))
+            state[0] = self._sbox(parser, sbox_in)
+            state = self._mds(parser, state)
+            rnd += 1
+        for r in range(self.HALF_FULL):
+            state = [parser.add_const(state[i], rc[12 * rnd + i]) for i in range(12)]
+            for i in range(12):
+                sbox_in = w[self.wire_full_sbox_1(r, i)]
+                cons.append(parser.sub(state[i], sbox_in))
+                state[i] = sbox_in
+            state = self._mds(parser, [self._sbox(parser, x) for x in state])
+            rnd += 1
+        for i in range(12):
+            cons.append(parser.sub(w[12 + i], state[i]))
+        return cons
+
+    def generate(self, inputs, swap: int):
+        """PoseidonGenerator: the 135 wire values of one row (Python ints)."""
+        rc = self.rc()
+        row = [0] * 135
+        row[:12] = [int(x) % P for x in inputs]
+        row[self.WIRE_SWAP] = swap
+        state = list(row[:12])
+        for i in range(4):
+            delta = swap * (state[i + 4] - state[i]) % P
+            row[self.START_DELTA + i] = delta
+            state[i], state[i + 4] = (state[i] + delta) % P, (state[i + 4] - delta) % P
+        mds = lambda st: [(sum(st[(i + r) % 12] * self.MDS_CIRC[i] for i in range(12)) + st[r] * self.MDS_DIAG[r]) % P for r in range(12)]
+        rnd = 0
+        for r in range(self.HALF_FULL):
+            state = [(state[i] + rc[12 * rnd + i]) % P for i in range(12)]
+            if r != 0:
+                for i in range(12):
+                    row[self.wire_full_sbox_0(r, i)] = state[i]
+            state = mds([pow(x, 7, P) for x in state])
+            rnd += 1
+        for r in range(self.N_PARTIAL):
+            state = [(state[i] + rc[12 * rnd + i]) % P for i in range(12)]
+            row[self.wire_partial_sbox(r)] = state[0]
+            state[0] = pow(state[0], 7, P)
+            state = mds(state)
+            rnd += 1
+        for r in range(self.HALF_FULL):
+            state = [(state[i] + rc[12 * rnd + i]) % P for i in range(12)]
+            for i in range(12):
+                row[self.wire_full_sbox_1(r, i)] = state[i]
+            state = mds([pow(x, 7, P) for x in state])
+            rnd += 1
+        row[12:24] = state
+        return row
+
+
 # ---------------------------------------------------------------------------------------------
 # gates/selectors.rs, gates/gate.rs
 # ---------------------------------------------------------------------------------------------
@@ -376,7 +518,7 @@ class ProverOnlyCircuitData:
     circuit_digest: np.ndarray = field(default_factory=lambda: np.zeros(4, np.uint64))
 
 
-def build_demo_circuit(config: CircuitConfig, degree_bits: int, seed: int, gate_mix=None):
+def build_demo_circuit(config: CircuitConfig, degree_bits: int, seed: int, gate_mix=None, max_poseidon_rows: int = 256):
     """A circuit for tests and the bench: every row holds one gate drawn from `gate_mix` with random constants; a random
     wire partition ties some operands to slots of earlier rows; returns (common, constants (num_constants x n values),
     sigma values, witness wires (num_wires x n), public_inputs_hash).  The witness satisfies every gate AND every copy
@@ -385,10 +527,16 @@ def build_demo_circuit(config: CircuitConfig, degree_bits: int, seed: int, gate_
     n, R, Wn = 1 << degree_bits, config.num_routed_wires, config.num_wires
     gates = gate_mix or [NoopGate(), PublicInputGate(), ConstantGate(config.num_constants),
                          BaseSumGate(min(63, R - 1)), ArithmeticGate.new_from_config(config),
-                         ArithmeticExtensionGate.new_from_config(config)]
+                         ArithmeticExtensionGate.new_from_config(config)] + ([PoseidonGate()] if Wn >= 135 else [])
     gates = sorted(gates, key=lambda g: (g.degree(), g.id()))
     weights = np.array([1 if isinstance(g, (NoopGate, PublicInputGate)) else 6 for g in gates], float)
     instances = [int(i) for i in rng.choice(len(gates), n, p=weights / weights.sum())]
+    pos = [i for i, g in enumerate(gates) if isinstance(g, PoseidonGate)]
+    if pos:  # the witness of a Poseidon row is a whole permutation in Python ints: keep their number bounded
+        rows_p = [r for r, i in enumerate(instances) if i == pos[0]]
+        other = [i for i in range(len(gates)) if i != pos[0]]
+        for r in rows_p[max_poseidon_rows:]:
+            instances[r] = other[r % len(other)]
     sel_polys, info = selector_polynomials(gates, instances, config.max_quotient_degree_factor + 1)
     common = CommonCircuitData(config, degree_bits, gates, info)
     ns = info.num_selectors()
@@ -406,6 +554,8 @@ def build_demo_circuit(config: CircuitConfig, degree_bits: int, seed: int, gate_
         if isinstance(g, ConstantGate):
             constants[ns:ns + g.num_consts, row] = gate_consts[:g.num_consts, row]
             wires[:g.num_consts, row] = gate_consts[:g.num_consts, row]
+        elif isinstance(g, PoseidonGate):
+            wires[:, row] = np.array(g.generate(wires[:12, row], int(rng.integers(0, 2))), dtype=object).astype(np.uint64)
         elif isinstance(g, PublicInputGate):
             wires[:4, row] = pih
         elif isinstance(g, BaseSumGate):

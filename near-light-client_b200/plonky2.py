@@ -78,6 +78,12 @@ class Context:
         if torch is not None and torch.cuda.is_available() and torch.cuda.is_initialized():
             self.wait_stream(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def cache_stats(self) -> dict:
+        """The context's device-buffer cache: hits, driver allocations, time in them, bytes cached."""
+        out = np.zeros(4, np.uint64)
+        self._check(_ffi.lib().nlc_cache_stats(self._h, _p(out)))
+        return {"hits": int(out[0]), "misses": int(out[1]), "miss_us": int(out[2]), "cached_bytes": int(out[3])}
+
     def launch_count(self) -> int:
         return int(_ffi.lib().nlc_launch_count(self._h))
 
@@ -313,7 +319,10 @@ class _BatchTree:
     """The `merkle_tree` field of a PolynomialBatch (same accessors as MerkleTree, lazily materialised)."""
 
     def __init__(self, batch: "PolynomialBatch"):
-        self._b = batch
+        import weakref
+        # a proxy, not a reference: batch <-> tree would be a cycle, and the batch's device buffers would then wait for
+        # the cyclic garbage collector instead of being released when the last reference to the batch goes
+        self._b = weakref.proxy(batch)
         self._cap = self._local_cap = self._leaves = self._digests = None
 
     @property

@@ -29,7 +29,7 @@ P = 0xFFFFFFFF00000001
 
 OP = {name: i for i, name in enumerate(
     ["LOCAL", "NEXT", "PUBLIC", "GLOBAL", "CHALLENGE", "CONST", "ADD", "SUB", "MUL", "NEG", "MUL_CONST", "ADD_CONST",
-     "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW"])}
+     "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW", "MULADD_CONST"])}
 
 
 A_LAST, B_LAST, NO_STORE = 1, 2, 4  # flag bits of the instruction word, above the 8-bit opcode (NLC_AIR_FLAG_*)
@@ -172,17 +172,39 @@ class BytecodeParser:
         30-40 % of the register traffic, which is what bounds the interpreter."""
         reads_reg = {OP[k] for k in ("ADD", "SUB", "MUL")}
         reads_a = {OP[k] for k in ("NEG", "MUL_CONST", "ADD_CONST", "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION",
-                                   "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW")}
+                                   "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW", "MULADD_CONST")}
         srcs = lambda op, a, b: (a, b) if op in reads_reg else (a,) if op in reads_a else ()
+        # peephole: t = mul_const(x, c); y = add(prev, t) with prev the result just before t and t used nowhere else
+        # becomes y = x * c + accumulator (MULADD_CONST): sums of constant multiples -- an MDS row, a Horner step --
+        # then run in the accumulator, one register read per term instead of two reads and a write
+        n_uses: dict[int, int] = {}
+        for op, dst, a, b in self.ops:
+            for v in srcs(op, a, b):
+                n_uses[v] = n_uses.get(v, 0) + 1
+        fused, acc_of, i = [], {}, 0
+        while i < len(self.ops):
+            op, dst, a, b = self.ops[i]
+            if op == OP["MUL_CONST"] and i + 1 < len(self.ops) and fused and fused[-1][1] is not None and n_uses.get(dst, 0) == 1:
+                op2, dst2, a2, b2 = self.ops[i + 1]
+                prev = fused[-1][1]
+                if op2 == OP["ADD"] and {a2, b2} == {dst, prev} and dst != prev:
+                    fused.append((OP["MULADD_CONST"], dst2, a, b))
+                    acc_of[dst2] = prev
+                    i += 2
+                    continue
+            fused.append(self.ops[i])
+            i += 1
         needed, kept = set(), []
-        for o in reversed(self.ops):  # one backward pass: a value nobody (alive) reads gets no instruction
+        for o in reversed(fused):  # one backward pass: a value nobody (alive) reads gets no instruction
             if o[1] is None or o[1] in needed:
                 kept.append(o)
                 needed.update(srcs(o[0], o[2], o[3]))
+                if o[1] in acc_of:
+                    needed.add(acc_of[o[1]])
         kept.reverse()
         last_use: dict[int, int] = {}
         for pc, (op, dst, a, b) in enumerate(kept):
-            for v in srcs(op, a, b):
+            for v in srcs(op, a, b) + ((acc_of[dst],) if dst in acc_of else ()):
                 last_use[v] = pc
         next_def = [len(kept)] * len(kept)  # index of the next value-producing instruction after pc
         nd = len(kept)
@@ -198,6 +220,8 @@ class BytecodeParser:
         for pc, (op, dst, a, b) in enumerate(kept):
             ra, rb, flags = a, b, 0
             operands = srcs(op, a, b)
+            if dst in acc_of:
+                assert acc_of[dst] == last_value, "fused multiply-add lost its accumulator"
             regs_out = []
             for k, v in enumerate(operands):
                 if v == last_value:

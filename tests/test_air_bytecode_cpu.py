@@ -32,6 +32,7 @@ def run_bytecode(O, OA, prog, local_vars, next_vars, publics, globals_, challeng
         elif op == 10: r = vec("orc_vec_mul", ra(), full(prog.pool[b]))
         elif op == 11: r = vec("orc_vec_add", ra(), full(prog.pool[b]))
         elif op == 12: r = vec("orc_vec_sub", ra(), full(prog.pool[b]))
+        elif op == 17: r = vec("orc_vec_add", vec("orc_vec_mul", ra(), full(prog.pool[b])), last)
         elif op in (13, 14, 15, 16):
             getattr(consumer, ["constraint", "constraint_transition", "constraint_first_row", "constraint_last_row"][op - 13])(ra())
             continue

@@ -128,6 +128,8 @@ def test_gate_constraint_recording_matches_direct_evaluation(O, K):
                 r = (ra + int(prog.pool[b])) % P
             elif name == "SUB_CONST":
                 r = (ra - int(prog.pool[b])) % P
+            elif name == "MULADD_CONST":
+                r = (ra * int(prog.pool[b]) + last) % P
             elif name == "CONSTRAINT":
                 emitted.append(ra)
                 continue

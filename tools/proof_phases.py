@@ -30,6 +30,7 @@ def main():
     wc = zs = q = None
     for rep in range(4):
         t = {}
+        c0 = ctx.cache_stats()
         def lap(name, t0):
             ctx.synchronize()
             t[name] = t.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
@@ -57,7 +58,9 @@ def main():
         lap("prove_openings", t0)
         total = (time.perf_counter() - T0) * 1e3
         if rep >= 1:
-            print(f"plonk proof, degree 2^{degree_bits}: {total:.2f} ms")
+            c1 = ctx.cache_stats()
+            print(f"plonk proof, degree 2^{degree_bits}: {total:.2f} ms   buffer cache: {c1['hits'] - c0['hits']} hits, "
+                  f"{c1['misses'] - c0['misses']} driver allocations ({(c1['miss_us'] - c0['miss_us']) / 1e3:.2f} ms), {c1['cached_bytes'] >> 20} MiB cached")
             for k, v in t.items():
                 print(f"  {k:50s} {v:7.2f} ms")
     n = 1 << degree_bits
