@@ -268,6 +268,11 @@ int nlc_quotient_commit_dev(nlc_ctx* ctx, const uint64_t* evals_dev, size_t n_ch
 #define NLC_AIR_CONSTRAINT_FIRST_ROW 15  /* constraint_first_row(reg a): * lagrange_basis_first */
 #define NLC_AIR_CONSTRAINT_LAST_ROW 16   /* constraint_last_row(reg a):  * lagrange_basis_last */
 #define NLC_AIR_MULADD_CONST 17          /* dst = reg a * pool[b] + accumulator (the previous result): sums of constant multiples */
+/* dst = sum of `a` terms reg * constant: the terms follow in ceil(a / 2) words {reg, constant VALUE (< 2^16), reg,
+ * constant}; a reg field with NLC_AIR_DOT_TERM_LAST set is the accumulator.  The 96-bit products are summed unreduced
+ * (at most 2^12 terms), one reduction at the end: an MDS row, a limb recombination. */
+#define NLC_AIR_DOT_CONST 18
+#define NLC_AIR_DOT_TERM_LAST 0x80000000u
 typedef struct {
     const uint32_t* code; /* n_ops x 4 */
     uint32_t n_ops;

@@ -42,16 +42,38 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_
         const u32 op = ins.x & 0xffu, flags = ins.x >> 8;
         u64 r;
         if (op >= NLC_AIR_ADD) { // register operands
-            const u64 ra = (flags & NLC_AIR_FLAG_A_LAST) ? last : regs[ins.z * stride];
+            const u64 ra = (flags & NLC_AIR_FLAG_A_LAST) || op == NLC_AIR_DOT_CONST ? last : regs[ins.z * stride];
             switch (op) {
             case NLC_AIR_ADD: r = gl::dadd(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
             case NLC_AIR_SUB: r = gl::dsub(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
             case NLC_AIR_MUL: r = gl::mul(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
             case NLC_AIR_NEG: r = gl::neg(ra); break;
-            case NLC_AIR_MUL_CONST: r = gl::mul(ra, A.pool[ins.w]); break;
+            case NLC_AIR_MUL_CONST: { const u64 c = A.pool[ins.w]; r = (c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c); break; }
             case NLC_AIR_ADD_CONST: r = gl::dadd(ra, A.pool[ins.w]); break;
             case NLC_AIR_SUB_CONST: r = gl::dsub(ra, A.pool[ins.w]); break;
-            case NLC_AIR_MULADD_CONST: r = gl::dadd(gl::mul(ra, A.pool[ins.w]), last); break;
+            case NLC_AIR_DOT_CONST: { // ins.z terms in the following words; 96-bit products summed in two 64-bit lanes
+                u64 s0 = 0, s1 = 0;
+                for (u32 t = 0; t < ins.z; t += 2) {
+                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(A.code) + ++pc);
+                    const u64 v0 = (w.x & NLC_AIR_DOT_TERM_LAST) ? last : regs[(size_t)w.x * stride];
+                    s0 += (u64)(u32)v0 * w.y;
+                    s1 += (v0 >> 32) * w.y;
+                    if (t + 1 < ins.z) {
+                        const u64 v1 = (w.z & NLC_AIR_DOT_TERM_LAST) ? last : regs[(size_t)w.z * stride];
+                        s0 += (u64)(u32)v1 * w.w;
+                        s1 += (v1 >> 32) * w.w;
+                    }
+                }
+                // s0 + 2^32 s1 with s0, s1 < 2^60 (<= 2^12 terms, constants < 2^16):  2^32 s1 = (s1_lo << 32) + s1_hi 2^64
+                const unsigned __int128 T = (unsigned __int128)s0 + ((u64)(u32)s1 << 32) + (s1 >> 32) * gl::EPS;
+                r = gl::dcanon(gl::reduce128_dev_nc((u64)T, (u64)(T >> 64)));
+                break;
+            }
+            case NLC_AIR_MULADD_CONST: { // the constant is the same for the whole grid: the branch is uniform
+                const u64 c = A.pool[ins.w];
+                r = gl::dadd((c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c), last);
+                break;
+            }
             default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
                 u64 c = ra;
                 if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
@@ -104,6 +126,18 @@ void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_con
         case NLC_AIR_CONST: NLC_CHECK(a < prog->n_pool, "AIR program: constant out of range"); break;
         case NLC_AIR_ADD: case NLC_AIR_SUB: case NLC_AIR_MUL: reg(a, NLC_AIR_FLAG_A_LAST); reg(b, NLC_AIR_FLAG_B_LAST); break;
         case NLC_AIR_NEG: reg(a, NLC_AIR_FLAG_A_LAST); break;
+        case NLC_AIR_DOT_CONST: {
+            const u32 words = (a + 1) / 2;
+            NLC_CHECK(a >= 1 && a <= (1u << 12) && pc + words < prog->n_ops + 0u && pc + words >= pc, "AIR program: dot product runs past the end");
+            for (u32 t = 0; t < a; t++) {
+                const u32 r = prog->code[4 * (pc + 1 + t / 2) + 2 * (t & 1)], cst = prog->code[4 * (pc + 1 + t / 2) + 2 * (t & 1) + 1];
+                NLC_CHECK(cst < (1u << 16), "AIR program: dot-product constant too large");
+                if (r & NLC_AIR_DOT_TERM_LAST) NLC_CHECK(have_last, "AIR program reads the accumulator before any result exists");
+                else NLC_CHECK(r < prog->n_regs && written[r], "AIR program reads a register before writing it");
+            }
+            pc += words;
+            break;
+        }
         case NLC_AIR_MULADD_CONST: NLC_CHECK(have_last, "AIR program reads the accumulator before any result exists");
         // fall through
         case NLC_AIR_MUL_CONST: case NLC_AIR_ADD_CONST: case NLC_AIR_SUB_CONST:

@@ -117,6 +117,17 @@ __device__ __forceinline__ uint64_t mul_nc(uint64_t a, uint64_t b) {
     return reduce128_dev_nc((uint64_t)p, (uint64_t)(p >> 64));
 }
 __device__ __forceinline__ uint64_t mul(uint64_t a, uint64_t b) { return dcanon(mul_nc(a, b)); }
+// a * c for a 32-bit c (small constants: MDS entries, limb weights): two IMAD.WIDE; the 96-bit product lo + 2^64 h has
+// h < 2^32, and 2^64 == eps, so it is lo + h * eps with one conditional repair -- half the work of a full product
+__device__ __forceinline__ uint64_t mul_u32(uint64_t a, uint32_t c) {
+    const uint64_t p0 = (uint64_t)(uint32_t)a * c, p1 = (a >> 32) * c;
+    const uint64_t mid = p1 + (p0 >> 32);                       // < 2^64: (2^32-1)^2 + 2^32 - 1
+    const uint64_t lo = (mid << 32) | (uint32_t)p0, h = mid >> 32; // a * c = lo + 2^64 h
+    const uint64_t t = (h << 32) - h;                            // h * eps < 2^64
+    uint64_t r = lo + t;
+    if (r < t) r += EPS;                                         // wrapped once: + 2^64 == + eps, cannot wrap again
+    return dcanon(r);
+}
 
 // x * 2^s (mod p) for a compile-time s in [0, 96), canonical in, canonical out, no multiplier: 2 generates the
 // 192-element subgroup of F_p^* (2^96 == -1), so every root of unity of order <= 64 is a power of two and the

@@ -29,10 +29,11 @@ P = 0xFFFFFFFF00000001
 
 OP = {name: i for i, name in enumerate(
     ["LOCAL", "NEXT", "PUBLIC", "GLOBAL", "CHALLENGE", "CONST", "ADD", "SUB", "MUL", "NEG", "MUL_CONST", "ADD_CONST",
-     "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW", "MULADD_CONST"])}
+     "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION", "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW", "MULADD_CONST", "DOT_CONST"])}
 
 
 A_LAST, B_LAST, NO_STORE = 1, 2, 4  # flag bits of the instruction word, above the 8-bit opcode (NLC_AIR_FLAG_*)
+DOT_TERM_LAST = 1 << 31             # a DOT_CONST term whose operand is the accumulator (NLC_AIR_DOT_TERM_LAST)
 
 # ---------------------------------------------------------------------------------------------
 # air/parser.rs: the recording parser
@@ -194,17 +195,39 @@ class BytecodeParser:
                     continue
             fused.append(self.ops[i])
             i += 1
+        # second peephole: mul_const followed by a run of multiply-adds whose partial sums nobody else reads, all with
+        # small constants, is ONE dot product with constants (DOT_CONST): its terms follow the instruction two to a
+        # word with the constant VALUE inline, and the interpreter sums the 96-bit products without reducing in between
+        pool_value = {idx: value for value, idx in self._pool.items()}
+        dots, j = [], 0
+        while j < len(fused):
+            op, dst, a, b = fused[j]
+            if op == OP["MUL_CONST"] and pool_value[b] < (1 << 16):
+                terms, k, cur = [(a, pool_value[b])], j + 1, dst
+                while (k < len(fused) and fused[k][0] == OP["MULADD_CONST"] and acc_of.get(fused[k][1]) == cur
+                       and n_uses.get(cur, 0) == 1 and pool_value[fused[k][3]] < (1 << 16) and len(terms) < (1 << 12)):
+                    terms.append((fused[k][2], pool_value[fused[k][3]]))
+                    cur = fused[k][1]
+                    k += 1
+                if len(terms) >= 3:
+                    dots.append((OP["DOT_CONST"], cur, tuple(terms), None))
+                    j = k
+                    continue
+            dots.append(fused[j])
+            j += 1
+        fused = dots
+        srcs_of = lambda o: tuple(t[0] for t in o[2]) if o[0] == OP["DOT_CONST"] else srcs(o[0], o[2], o[3])
         needed, kept = set(), []
         for o in reversed(fused):  # one backward pass: a value nobody (alive) reads gets no instruction
             if o[1] is None or o[1] in needed:
                 kept.append(o)
-                needed.update(srcs(o[0], o[2], o[3]))
-                if o[1] in acc_of:
+                needed.update(srcs_of(o))
+                if o[1] in acc_of and o[0] == OP["MULADD_CONST"]:
                     needed.add(acc_of[o[1]])
         kept.reverse()
         last_use: dict[int, int] = {}
-        for pc, (op, dst, a, b) in enumerate(kept):
-            for v in srcs(op, a, b) + ((acc_of[dst],) if dst in acc_of else ()):
+        for pc, o in enumerate(kept):
+            for v in srcs_of(o) + ((acc_of[o[1]],) if o[0] == OP["MULADD_CONST"] else ()):
                 last_use[v] = pc
         next_def = [len(kept)] * len(kept)  # index of the next value-producing instruction after pc
         nd = len(kept)
@@ -215,24 +238,22 @@ class BytecodeParser:
         reg_of: dict[int, int] = {}
         free: list[int] = []
         n_regs = 0
-        code = np.zeros((len(kept), 4), np.uint32)
+        code: list = []
         last_value = None
-        for pc, (op, dst, a, b) in enumerate(kept):
+        for pc, o in enumerate(kept):
+            op, dst, a, b = o
             ra, rb, flags = a, b, 0
-            operands = srcs(op, a, b)
-            if dst in acc_of:
+            operands = srcs_of(o)
+            if op == OP["MULADD_CONST"]:
                 assert acc_of[dst] == last_value, "fused multiply-add lost its accumulator"
             regs_out = []
             for k, v in enumerate(operands):
                 if v == last_value:
-                    flags |= A_LAST if k == 0 else B_LAST
-                    regs_out.append(0)
+                    if op != OP["DOT_CONST"]:
+                        flags |= A_LAST if k == 0 else B_LAST
+                    regs_out.append(DOT_TERM_LAST)
                 else:
                     regs_out.append(reg_of[v])
-            if operands:
-                ra = regs_out[0]
-                if len(operands) == 2:
-                    rb = regs_out[1]
             for v in set(operands):  # operands are read before the destination is written: the register can be reused now
                 if last_use[v] == pc and v in reg_of:
                     free.append(reg_of.pop(v))
@@ -248,12 +269,23 @@ class BytecodeParser:
                         n_regs += 1
                     reg_of[dst] = rd
                 last_value = dst
-            code[pc] = (op | (flags << 8), rd, ra, rb)
+            if op == OP["DOT_CONST"]:
+                consts = [t[1] for t in a]
+                code.append((op | (flags << 8), rd, len(consts), 0))
+                for t in range(0, len(consts), 2):
+                    second = (regs_out[t + 1], consts[t + 1]) if t + 1 < len(consts) else (0, 0)
+                    code.append((regs_out[t], consts[t]) + second)
+                continue
+            if operands:
+                ra = 0 if regs_out[0] == DOT_TERM_LAST else regs_out[0]
+                if len(operands) == 2:
+                    rb = 0 if regs_out[1] == DOT_TERM_LAST else regs_out[1]
+            code.append((op | (flags << 8), rd, ra, rb))
         pool = np.zeros(len(self._pool), np.uint64)
         for value, idx in self._pool.items():
             pool[idx] = value
-        return AirProgram(code, pool, max(n_regs, 1), self.n_public, self.n_global, self.n_challenge,
-                          self.n_columns, self.n_constraints)
+        return AirProgram(np.array(code, np.uint32).reshape(-1, 4), pool, max(n_regs, 1), self.n_public, self.n_global,
+                          self.n_challenge, self.n_columns, self.n_constraints)
 
 
 class _LazySlice:

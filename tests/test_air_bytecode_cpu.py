@@ -15,8 +15,23 @@ def run_bytecode(O, OA, prog, local_vars, next_vars, publics, globals_, challeng
     full = lambda v: np.full(n, int(v) % P, np.uint64)
     vec = lambda fn, *a: OA._vec(fn, *a, n=n)
     last = None  # the accumulator of the instruction word's flags (NLC_AIR_FLAG_A_LAST / B_LAST / NO_STORE)
-    for word, d, a, b in prog.code.tolist():
+    words = prog.code.tolist()
+    pc = -1
+    while pc + 1 < len(words):
+        pc += 1
+        word, d, a, b = words[pc]
         op, flags = word & 0xFF, word >> 8
+        if op == 18:  # DOT_CONST: a terms {reg | LAST bit, constant} in the following words, two per word
+            r = full(0)
+            for t in range(a):
+                w = words[pc + 1 + t // 2]
+                reg_t, c_t = w[2 * (t & 1)], w[2 * (t & 1) + 1]
+                r = vec("orc_vec_add", r, vec("orc_vec_mul", last if reg_t >> 31 else regs[reg_t], full(c_t)))
+            pc += (a + 1) // 2
+            if not flags & 4:
+                regs[d] = r
+            last = r
+            continue
         ra = (lambda: last if flags & 1 else regs[a])
         rb = (lambda: last if flags & 2 else regs[b])
         if op == 0: r = local_vars[a]

@@ -103,9 +103,23 @@ def test_gate_constraint_recording_matches_direct_evaluation(O, K):
     for row in range(4):
         local = [int(x) for x in consts[:, row]] + [int(x) for x in sig[:, row]] + [int(x) for x in rng.integers(0, P, cfg.num_wires, dtype=np.uint64)]
         regs, emitted, last = {}, [], None
-        for word, rd, a, b in prog.code.tolist():
+        words, pc = prog.code.tolist(), -1
+        while pc + 1 < len(words):
+            pc += 1
+            word, rd, a, b = words[pc]
             op, flags = word & 0xFF, word >> 8
             name = next(k for k, v in S.OP.items() if v == op)
+            if name == "DOT_CONST":
+                r = 0
+                for t in range(a):
+                    w = words[pc + 1 + t // 2]
+                    reg_t, c_t = w[2 * (t & 1)], w[2 * (t & 1) + 1]
+                    r = (r + (last if reg_t >> 31 else regs[reg_t]) * c_t) % P
+                pc += (a + 1) // 2
+                if not flags & S.NO_STORE:
+                    regs[rd] = r
+                last = r
+                continue
             ra = last if flags & S.A_LAST else regs.get(a)
             rb = last if flags & S.B_LAST else regs.get(b)
             if name == "LOCAL":
