@@ -434,6 +434,56 @@ class FibonacciAir(RAirData):
         pass
 
 
+class PermutationAir(RAirData):
+    """A two-round AIR in the shape of starkyx's lookup / bus arguments (chip/table/*, machine/bytes): round 0 commits
+    columns (a, b) with b a permutation of a; the verifier's challenge gamma follows; round 1 commits the running product
+    z, z_0 = 1, z' (b + gamma) = z (a + gamma), and publishes the product after the last row as a global value, which must
+    be 1.  It exercises what the Fibonacci AIR does not: several trace commitments concatenated into local / next
+    (prover.rs:289-294), challenge and global slices, all four constraint kinds."""
+
+    def constraint_degree(self):
+        return 2
+
+    def width(self):
+        return 3
+
+    def round_data(self):
+        return [RoundDatum(2, (0, 0), 1), RoundDatum(1, (0, 1), 0)]
+
+    def eval(self, parser):
+        a, b, z = (parser.local_slice()[i] for i in range(3))
+        z_next = parser.next_slice()[2]
+        gamma = parser.challenge_slice()[0]
+        num, den = parser.add(a, gamma), parser.add(b, gamma)
+        parser.constraint_first_row(parser.sub_const(z, 1))
+        parser.constraint_transition(parser.sub(parser.mul(z_next, den), parser.mul(z, num)))
+        total = parser.global_slice()[0]
+        parser.constraint_last_row(parser.sub(parser.mul(total, den), parser.mul(z, num)))
+        parser.constraint(parser.mul(parser.sub_const(total, 1), parser.sub_const(total, 1)))  # total = 1 (squared: degree 2)
+
+    def eval_global(self, parser):
+        pass
+
+    @staticmethod
+    def trace_generator(a_col: np.ndarray, perm: np.ndarray):
+        """TraceGenerator::generate_round for this AIR: round 0 -> (a, a[perm]); round 1 -> z from the challenge."""
+        b_col = a_col[perm]
+
+        def generate_round(air, r, challenges, global_values, public_inputs):
+            n = a_col.size
+            if r == 0:
+                return np.ascontiguousarray(np.stack([a_col, b_col], axis=1))
+            gamma = int(challenges[0])
+            z = np.zeros((n, 1), np.uint64)
+            acc = 1
+            for i in range(n):
+                z[i, 0] = acc
+                acc = acc * ((int(a_col[i]) + gamma) % P) % P * pow((int(b_col[i]) + gamma) % P, P - 2, P) % P
+            global_values[0] = acc
+            return z
+        return generate_round
+
+
 # ---------------------------------------------------------------------------------------------
 # chip/register/memory.rs, chip/arithmetic/{expression_slice,expression,mod}.rs
 # ---------------------------------------------------------------------------------------------
@@ -707,7 +757,7 @@ class Starky:
 
     def program(self, n_challenge: int = 0) -> AirProgram:
         if self._program is None:
-            self._program = compile_air(self.air, n_challenge)
+            self._program = compile_air(self.air, max(n_challenge, sum(rd.num_challenges for rd in self.air.round_data())))
         return self._program
 
     def fri_instance(self, zeta, g: int, config: StarkyConfig) -> P2.FriInstanceInfo:
@@ -766,24 +816,31 @@ class StarkyProver:
                                   config.fri_config.cap_height)
 
     @staticmethod
-    def prove(config: StarkyConfig, stark: Starky, trace_rows: np.ndarray, public_inputs, ctx=None) -> StarkProof:
-        """generate_trace + prove_with_trace for a single-round AIR (prover.rs:50-225): row-major AirTrace in,
-        StarkProof out; every commitment, the AIR evaluation and the FRI proof run on the GPU."""
+    def generate_trace(config: StarkyConfig, stark: Starky, trace_generator, public_inputs, challenger, ctx=None):
+        """StarkyProver::generate_trace (prover.rs:50-111): round by round -- generate_round(air, r, challenges,
+        global_values, public_inputs) -> the round's row-major AirTrace; commit it; observe the round's global values and
+        the cap; draw the round's challenges.  Returns (trace_commitments, global_values, challenges)."""
         fc = config.fri_config
-        challenger = P2.Challenger(ctx)
+        challenges: list = []
         global_values = [0] * stark.air.num_global_values()
         challenger.observe_elements(public_inputs)
-        rounds = stark.air.round_data()
-        if len(rounds) != 1:
-            raise NlcError("StarkyProver.prove mirrors single-round AIRs; multi-round AIRs drive the steps themselves")
-        rd = rounds[0]
-        commitment = P2.PolynomialBatch.from_trace_rows(trace_rows, 0, rd.num_columns, fc.rate_bits, fc.cap_height, ctx=ctx)
-        id0, id1 = rd.global_values_range
-        challenger.observe_elements(global_values[id0:id1])
-        challenger.observe_cap(commitment.merkle_tree.cap)
-        challenges = challenger.get_n_challenges(rd.num_challenges)
-        trace_commitments = [commitment]
-        fri_params = config.fri_params()
+        trace_commitments = []
+        for r, rd in enumerate(stark.air.round_data()):
+            id0, id1 = rd.global_values_range
+            round_trace = trace_generator(stark.air, r, challenges, global_values, public_inputs)
+            if round_trace.shape[1] != rd.num_columns:
+                raise NlcError("generate_round returned a trace of the wrong width")
+            commitment = P2.PolynomialBatch.from_trace_rows(round_trace, 0, rd.num_columns, fc.rate_bits, fc.cap_height, ctx=ctx)
+            challenger.observe_elements(global_values[id0:id1])
+            challenger.observe_cap(commitment.merkle_tree.cap)
+            trace_commitments.append(commitment)
+            challenges.extend(int(c) for c in challenger.get_n_challenges(rd.num_challenges))
+        return trace_commitments, global_values, challenges
+
+    @staticmethod
+    def prove_with_trace(config: StarkyConfig, stark: Starky, trace_commitments, public_inputs, global_values, challenges,
+                         challenger) -> StarkProof:
+        """prover.rs:113-225: quotient, openings, opening proof over all round commitments + the quotient's."""
         quotient_commitment = StarkyProver.quotient_commitment(stark, config, trace_commitments, challenges, global_values,
                                                                public_inputs, challenger)
         quotient_polys_cap = quotient_commitment.merkle_tree.cap
@@ -794,5 +851,23 @@ class StarkyProver:
         for batch in openings.to_fri_openings():
             challenger.observe_extension_elements(batch)
         opening_proof = P2.PolynomialBatch.prove_openings(stark.fri_instance(zeta, g, config),
-                                                          trace_commitments + [quotient_commitment], challenger, fri_params)
-        return StarkProof([commitment.merkle_tree.cap], quotient_polys_cap, openings, opening_proof, global_values)
+                                                          list(trace_commitments) + [quotient_commitment], challenger,
+                                                          config.fri_params())
+        return StarkProof([c.merkle_tree.cap for c in trace_commitments], quotient_polys_cap, openings, opening_proof,
+                          global_values)
+
+    @staticmethod
+    def prove(config: StarkyConfig, stark: Starky, trace, public_inputs, ctx=None) -> StarkProof:
+        """StarkyProver::prove (prover.rs:227-251): `trace` is the row-major AirTrace of a single-round AIR, or a
+        trace generator  f(air, round, challenges, global_values, public_inputs) -> row-major round trace  for AIRs with
+        several rounds (it may fill global_values[..id_1] of its round in place, as TraceGenerator::generate_round does).
+        Every commitment, the AIR evaluation and the FRI proof run on the GPU."""
+        challenger = P2.Challenger(ctx)
+        if callable(trace):
+            generator = trace
+        else:
+            if len(stark.air.round_data()) != 1:
+                raise NlcError("an AIR with several rounds needs a trace generator, not one trace")
+            generator = lambda air, r, challenges, global_values, public_inputs: trace
+        tc, gv, ch = StarkyProver.generate_trace(config, stark, generator, public_inputs, challenger, ctx=ctx)
+        return StarkyProver.prove_with_trace(config, stark, tc, public_inputs, gv, ch, challenger)

@@ -171,3 +171,52 @@ def test_fibonacci_stark_proof_end_to_end(P2, O, pkg):
     oproof = O.prove_openings(inst, [tref, qref], ch, params)
     assert np.array_equal(proof.opening_proof.flat, oproof)
     assert O.fri_verify(inst, local + quot + nxt, [tref, qref], ch_for_verifier, params, oproof) == 0
+
+
+@pytest.mark.parametrize("log_n", [6, 12])
+def test_two_round_air_proof_end_to_end(P2, O, pkg, rng, log_n):
+    """An AIR with two rounds (prover.rs:50-111: commit, observe, draw challenges, generate the next round from them):
+    two trace commitments concatenated into local / next vars, a challenge, a global value, all four constraint kinds.
+    StarkyProver::prove on the GPU equals the oracle-driven sequence and the restated FRI verifier accepts it."""
+    from oracle import air as OA
+    S = pkg.starky
+    n = 1 << log_n
+    air = S.PermutationAir()
+    stark = S.Starky(air)
+    a_col = O.random_field(rng, (n,))
+    perm = rng.permutation(n)
+    gen = air.trace_generator(a_col, perm)
+    cfg = S.StarkyConfig.standard_fast_config(n)
+    fc = cfg.fri_config
+    proof = S.StarkyProver.prove(cfg, stark, gen, [])
+    assert proof.global_values == [1]
+    # -- oracle-driven, in the order of prover.rs:50-225
+    ch = O.Challenger()
+    ch.observe_elements([])
+    gv = [0]
+    t0 = O.commit_from_values(np.ascontiguousarray(gen(air, 0, [], gv, []).T), fc.rate_bits, fc.cap_height)
+    ch.observe_cap(t0.cap)
+    challenges = [int(c) for c in ch.get_n_challenges(1)]
+    t1 = O.commit_from_values(np.ascontiguousarray(gen(air, 1, challenges, gv, []).T), fc.rate_bits, fc.cap_height)
+    ch.observe_elements(gv)
+    ch.observe_cap(t1.cap)
+    assert np.array_equal(proof.trace_caps[0], t0.cap) and np.array_equal(proof.trace_caps[1], t1.cap)
+    alphas = ch.get_n_challenges(cfg.num_challenges)
+    qv = OA.quotient_values(air, [t0, t1], challenges, gv, [], alphas, log_n, fc.rate_bits)
+    qref = O.quotient_commit(qv, log_n, 0, 1, False, fc.rate_bits, fc.cap_height)
+    assert np.array_equal(proof.quotient_polys_cap, qref.cap)
+    ch.observe_cap(qref.cap)
+    zeta = ch.get_extension_challenge()
+    g = pow(G32, 1 << (32 - log_n), P)
+    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
+    ev = lambda b, z: [O.eval_poly_ext(c, np.array(z, np.uint64)) for c in b.coeffs]
+    local, nxt, quot = ev(t0, zeta) + ev(t1, zeta), ev(t0, zeta_next) + ev(t1, zeta_next), ev(qref, zeta)
+    for batch in (local + quot, nxt):
+        ch.observe_elements([c for e in batch for c in e])
+    ch_v = ch.clone()
+    params = O.fri_params(log_n, fc.rate_bits, fc.cap_height, fc.proof_of_work_bits, fc.num_query_rounds, 4, 5)
+    trace_polys = [(0, 0), (0, 1), (1, 0)]
+    inst = O.FriInstance([(zeta, trace_polys + [(2, i) for i in range(qref.coeffs.shape[0])]), (zeta_next, trace_polys)])
+    oproof = O.prove_openings(inst, [t0, t1, qref], ch, params)
+    assert np.array_equal(proof.opening_proof.flat, oproof)
+    assert O.fri_verify(inst, local + quot + nxt, [t0, t1, qref], ch_v, params, oproof) == 0
