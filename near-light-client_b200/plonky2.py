@@ -318,11 +318,11 @@ class MerkleTree:
 class _BatchTree:
     """The `merkle_tree` field of a PolynomialBatch (same accessors as MerkleTree, lazily materialised)."""
 
-    def __init__(self, batch: "PolynomialBatch"):
-        import weakref
-        # a proxy, not a reference: batch <-> tree would be a cycle, and the batch's device buffers would then wait for
-        # the cyclic garbage collector instead of being released when the last reference to the batch goes
-        self._b = weakref.proxy(batch)
+    def __init__(self, state: "_BatchState"):
+        # the tree shares the batch's STATE (device handle + shape), not the batch: batch <-> tree would be a reference
+        # cycle and the device buffers would wait for the cyclic garbage collector; the handle is freed when the last
+        # of {batch, tree} goes, so `PolynomialBatch.from_values(..).merkle_tree.cap` works on a temporary as in Rust
+        self._b = state
         self._cap = self._local_cap = self._leaves = self._digests = None
 
     @property
@@ -610,16 +610,45 @@ def quotient_domain(degree_log: int, quotient_degree_bits: int, ctx=None):
     return x, lf, ll, zh
 
 
+class _BatchState:
+    """What a PolynomialBatch and its `merkle_tree` view share: the device handle and the shape."""
+
+    def __init__(self, ctx, handle, n_polys, degree_log, rate_bits, cap_height):
+        self._ctx, self._h = ctx, handle
+        self.n_polys, self.degree_log, self.rate_bits, self.cap_height = n_polys, degree_log, rate_bits, cap_height
+        self.shard_idx, self.n_shards = 0, 1
+
+    @property
+    def lde_size(self) -> int:
+        return 1 << (self.degree_log + self.rate_bits)
+
+    def free(self):
+        if self._h and self._ctx._h:  # a handle must not be touched once its context is gone
+            _ffi.lib().nlc_batch_free(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def _shared(name):
+    return property(lambda self: getattr(self._s, name), lambda self, v: setattr(self._s, name, v))
+
+
 class PolynomialBatch:
     """plonky2::fri::oracle::PolynomialBatch resident in HBM.  Struct fields (`polynomials`,
     `merkle_tree.{cap,leaves,digests}`) are materialised on first access."""
+    _ctx, _h = _shared("_ctx"), _shared("_h")
+    n_polys, degree_log, rate_bits, cap_height = (_shared(k) for k in ("n_polys", "degree_log", "rate_bits", "cap_height"))
+    shard_idx, n_shards = _shared("shard_idx"), _shared("n_shards")
 
     def __init__(self, ctx: Context, handle, n_polys: int, degree_log: int, rate_bits: int, cap_height: int):
-        self._ctx, self._h = ctx, handle
-        self.n_polys, self.degree_log, self.rate_bits, self.cap_height = n_polys, degree_log, rate_bits, cap_height
+        self._s = _BatchState(ctx, handle, n_polys, degree_log, rate_bits, cap_height)
         self.blinding = False
-        self.shard_idx, self.n_shards = 0, 1
-        self.merkle_tree = _BatchTree(self)
+        self.merkle_tree = _BatchTree(self._s)
         self._polys = None
 
     # -- constructors ---------------------------------------------------------------------------
@@ -1016,15 +1045,7 @@ class PolynomialBatch:
         return FriProof.parse(out, fri_params, [o.n_polys for o in oracles])
 
     def free(self):
-        if self._h and self._ctx._h:  # a handle must not be touched once its context is gone
-            _ffi.lib().nlc_batch_free(self._h)
-        self._h = None
-
-    def __del__(self):
-        try:
-            self.free()
-        except Exception:
-            pass
+        self._s.free()
 
 
 class FriCommitPhase:
