@@ -1,6 +1,7 @@
 // common.cuh -- context, error handling and launch bookkeeping shared by the nlc_commit translation units.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h> // header-only; ranges are no-ops unless a profiler (nsys) is attached
 
 #include <atomic>
 #include <chrono>
@@ -87,7 +88,14 @@ struct nlc_ctx {
     // measured with CUDA events on the launching stream when enabled
     bool timing = false;
     std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> timing_events;
+    // plonky2's TimingTree scopes ("IFFT", "FFT + blinding", "build Merkle tree") as NVTX ranges (SURVEY.md section 5:
+    // tracing), and -- when nlc_timing_enable is on -- as CUDA-event pairs on the launching stream
+    bool nvtx_open = false;
     void phase_begin(int phase) {
+        static const char* const names[] = {"nlc: IFFT", "nlc: FFT + blinding (coset LDE)", "nlc: leaf hashing",
+                                            "nlc: Merkle digest levels", "nlc: leaf hashing (column chunk)"};
+        nvtxRangePushA(phase >= 0 && phase < 5 ? names[phase] : "nlc: phase");
+        nvtx_open = true;
         if (!timing) return;
         cudaEvent_t a, b;
         cudaEventCreate(&a);
@@ -96,6 +104,10 @@ struct nlc_ctx {
         timing_events.push_back({phase, {a, b}});
     }
     void phase_end() {
+        if (nvtx_open) {
+            nvtxRangePop();
+            nvtx_open = false;
+        }
         if (!timing || timing_events.empty()) return;
         cudaEventRecord(timing_events.back().second.second, stream);
     }
