@@ -145,6 +145,121 @@ __device__ __forceinline__ void split3(uint64_t v, uint32_t& l0, uint32_t& l1, u
     l2 = (uint32_t)(v >> 43);
 }
 
+// ---- the MDS layer of the FULL rounds on the FP64 pipe: built, bit-exact, measured, NOT faster -> off by default -------
+// B200's FP64 pipe issues DFMA / DADD at the rate of the integer pipes (tools/ubench/ubench_fp64.cu: 63 per clock per
+// SM, and it co-issues with IMAD: 119 per clock for the two streams together) and the hash leaves it idle.  Integers
+// below 2^53 are exact in a double, so a lane is cut into its two 32-bit halves, the 12-point circular correlation runs
+// on each half in doubles (inputs < 2^32, every intermediate < 2^41), and the next round's constants ride along with a
+// bias that makes the result's mantissa the integer itself: 2 planes instead of 3, no masks, a cheaper glue.  SASS of a
+// full round: 1325 -> 1264 instructions (204 of them DADD / DFMA), busiest integer pipe 1546 -> 1244 clocks -- and the
+// permutation rate does not move (1.330 -> 1.332 G/s; 6.61 -> 6.80 ms inside the commit): the kernel is bound by
+// issue-slot utilisation (~0.73 instructions per clock per sub-partition), not by any one pipe, so only fewer
+// instructions would help, and 61 of 20 100 is noise.  Kept as a compile-time variant (-DNLC_MDS_FP64=1).
+#ifndef NLC_MDS_FP64
+#define NLC_MDS_FP64 0
+#endif
+
+// J0 = O0 + 2^51 + 2^19, J1 = O1 + 2^51 - 2^20 are what the biased planes hold in their mantissas; the biases cancel:
+// 2^51 + 2^19 + 2^32 (2^51 - 2^20) = 2^83 + 2^51 - 2^52 + 2^19 == (2^51 - 2^19) + 2^51 - 2^52 + 2^19 = 0  (2^64 == 2^32 - 1).
+constexpr double FP64_BIAS0 = 6755399441055744.0 + 524288.0;  // 1.5 * 2^52 + 2^19
+constexpr double FP64_BIAS1 = 6755399441055744.0 - 1048576.0; // 1.5 * 2^52 - 2^20
+struct RcDoubles {
+    double v[(N_ROUNDS + 1) * 2 * WIDTH]; // v[(r*2 + plane)*12 + lane], biased; round N_ROUNDS = the closing zero round
+};
+constexpr RcDoubles make_rc_doubles() {
+    RcDoubles t{};
+    constexpr uint64_t rc[NLC_POSEIDON_N_RC] = NLC_POSEIDON_RC_INIT;
+    for (int r = 0; r <= N_ROUNDS; r++)
+        for (int i = 0; i < WIDTH; i++) {
+            const uint64_t c = r < N_ROUNDS ? rc[r * WIDTH + i] : 0;
+            t.v[(r * 2 + 0) * WIDTH + i] = (double)(uint32_t)c + FP64_BIAS0;
+            t.v[(r * 2 + 1) * WIDTH + i] = (double)(uint32_t)(c >> 32) + FP64_BIAS1;
+        }
+    return t;
+}
+static __constant__ RcDoubles c_rc_doubles = make_rc_doubles();
+
+__device__ __forceinline__ double u32_to_double(uint32_t v) { // exact: 2^52 + v has v in its low mantissa word
+    return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;
+}
+
+// the same two-level even/odd split as circ12, in doubles (fma for the power-of-two weights)
+__device__ __forceinline__ void circ12d(const double (&x)[WIDTH], double (&o)[WIDTH], const double* __restrict__ rc) {
+    double p[6], m[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        p[j] = x[j] + x[j + 6];
+        m[j] = x[j] - x[j + 6];
+    }
+    double t[3], w[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        t[j] = p[j] + p[j + 3];
+        w[j] = p[j] - p[j + 3];
+    }
+    const double S = t[0] + t[1] + t[2];
+    const double ap[3] = {S + t[2], S + t[0], S + t[1]};
+    const double am[3] = {fma(8.0, w[2], fma(-2.0, w[1], -w[0])), fma(-8.0, w[0], fma(-2.0, w[2], -w[1])),
+                          fma(2.0, w[0], fma(-8.0, w[1], -w[2]))};
+    double A[6];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        A[j] = fma(16.0, ap[j], am[j]);
+        A[j + 3] = fma(16.0, ap[j], -am[j]);
+    }
+    double B[6];
+    B[0] = fma(-16.0, m[4], fma(4.0, m[5], fma(2.0, m[0], (m[2] + m[1]) - m[3])));
+    B[1] = fma(-16.0, m[5], fma(-4.0, m[0], fma(2.0, m[1], (m[3] + m[2]) - m[4])));
+    B[2] = fma(16.0, m[0], fma(-4.0, m[1], fma(2.0, m[2], (m[4] + m[3]) - m[5])));
+    B[3] = fma(16.0, m[1], fma(-4.0, m[2], fma(2.0, m[3], (m[0] + m[5]) + m[4])));
+    B[4] = fma(16.0, m[2], fma(-4.0, m[3], fma(2.0, m[4], (m[1] - m[0]) + m[5])));
+    B[5] = fma(16.0, m[3], fma(-4.0, m[4], fma(2.0, m[5], (m[2] - m[1]) - m[0])));
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        o[j] = (A[j] + rc[j]) + B[j];
+        o[j + 6] = (A[j] + rc[j + 6]) - B[j];
+    }
+    o[0] = fma(8.0, x[0], o[0]); // MDS_MATRIX_DIAG = [8, 0, ...]
+}
+
+// (J0, J1) -> J0 + 2^32 J1 mod p, any representative.  J = hi 2^32 + lo with hi < 2^20 (the mantissa's top 20 bits):
+// 2^32 J1 = 2^32 lo1 + 2^64 hi1 == 2^32 (lo1 + hi1) - hi1; J0 >= 2^50 so J0 - hi1 cannot borrow, and adding
+// lo1 + hi1 < 2^33 to a high word < 2^20 carries out at most once, repaid with + eps (which cannot wrap again).
+__device__ __forceinline__ uint64_t glue2(double J0, double J1) {
+    const uint32_t lo0 = (uint32_t)__double2loint(J0), hi0 = (uint32_t)__double2hiint(J0) & 0xFFFFFu;
+    const uint32_t lo1 = (uint32_t)__double2loint(J1), hi1 = (uint32_t)__double2hiint(J1) & 0xFFFFFu;
+    uint32_t r0, r1;
+    asm("{\n\t"
+        ".reg .u32 t0,t1,k,m;\n\t"
+        "sub.cc.u32 t0,%2,%5;\n\t"
+        "subc.u32 t1,%3,0;\n\t"
+        "add.u32 t1,t1,%5;\n\t"
+        "add.cc.u32 t1,t1,%4;\n\t"
+        "addc.u32 k,0,0;\n\t"
+        "sub.u32 m,0,k;\n\t"
+        "add.cc.u32 %0,t0,m;\n\t"
+        "addc.u32 %1,t1,0;\n\t"
+        "}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(lo0), "r"(hi0), "r"(lo1), "r"(hi1));
+    return ((uint64_t)r1 << 32) | r0;
+}
+
+// s <- MDS s + rc of round `next_round`, on the FP64 pipe (full rounds)
+__device__ __forceinline__ void mds_layer_fp64(uint64_t (&s)[WIDTH], const int next_round) {
+    double L0[WIDTH], L1[WIDTH], O0[WIDTH], O1[WIDTH];
+#pragma unroll
+    for (int i = 0; i < WIDTH; i++) {
+        L0[i] = u32_to_double((uint32_t)s[i]);
+        L1[i] = u32_to_double((uint32_t)(s[i] >> 32));
+    }
+    const double* rc = c_rc_doubles.v + next_round * 2 * WIDTH;
+    circ12d(L0, O0, rc);
+    circ12d(L1, O1, rc + WIDTH);
+#pragma unroll
+    for (int i = 0; i < WIDTH; i++) s[i] = glue2(O0[i], O1[i]);
+}
+
 // s <- MDS s + rc, rc = 36 limb words of the NEXT round's constants (full rounds: 64-bit lanes in and out).
 __device__ __forceinline__ void mds_layer(uint64_t (&s)[WIDTH], const uint32_t* __restrict__ rc, const uint32_t z) {
     uint32_t L0[WIDTH], L1[WIDTH], L2[WIDTH], O0[WIDTH], O1[WIDTH], O2[WIDTH];
@@ -173,6 +288,7 @@ __device__ __forceinline__ void permute_nc(uint64_t (&s)[WIDTH]) {
     for (int i = 0; i < WIDTH; i++) s[i] = gl::add_nc(s[i], c_rc[i]);
     const uint32_t* rc = c_rc_limbs.v;
     const uint32_t z = c_zero;
+    int rnd = 0; // rounds done: the layer of round r adds the constants of round r + 1
 #pragma unroll 1
     for (int phase = 0; phase < 2; phase++) {
 #pragma unroll 1
@@ -180,9 +296,15 @@ __device__ __forceinline__ void permute_nc(uint64_t (&s)[WIDTH]) {
 #pragma unroll
             for (int i = 0; i < WIDTH; i++) s[i] = sbox7(s[i]);
             rc += 3 * WIDTH;
+            rnd++;
+#if NLC_MDS_FP64
+            mds_layer_fp64(s, rnd);
+#else
             mds_layer(s, rc, z);
+#endif
         }
         if (phase) break;
+        rnd += N_PARTIAL;
         uint32_t L0[WIDTH], L1[WIDTH], L2[WIDTH];
 #pragma unroll
         for (int i = 1; i < WIDTH; i++) split3(s[i], L0[i], L1[i], L2[i]);
