@@ -259,3 +259,30 @@ def test_nlc_device_env(P2, pkg, monkeypatch):
     monkeypatch.setenv("NLC_DEVICE", "gpu0")
     with pytest.raises(pkg.NlcError, match="NLC_DEVICE"):
         P2.Context(-1)
+
+
+def _random_shapes():
+    rng = np.random.default_rng(20261105)
+    out = []
+    for _ in range(36):  # small transforms (generic NTT path), any width / rate / cap
+        log_n, r = int(rng.integers(0, 12)), int(rng.integers(0, 5))
+        out.append((int(rng.integers(1, 70)), log_n, r, int(rng.integers(0, min(log_n + r, 6) + 1))))
+    for _ in range(14):  # fast NTT path (>= 2^12): all 2^r cosets in one launch per pass, in place
+        log_n, r = int(rng.integers(12, 15)), int(rng.integers(0, 5))
+        out.append((int(rng.integers(1, 41)), log_n, r, int(rng.integers(0, 7))))
+    return out
+
+
+@pytest.mark.parametrize("W,log_n,rate_bits,cap_height", _random_shapes())
+def test_random_shapes_resident_and_host_fed(P2, O, W, log_n, rate_bits, cap_height):
+    """Randomly drawn (W, degree, rate_bits, cap_height), incl. rate_bits 0 and 4 (16 cosets in one launch) and caps
+    from 0 to the tree height: from_values through host vectors, from_coeffs, and the device-resident entry point all
+    give the oracle's cap, coefficients, leaves and digests."""
+    import torch
+    rng = np.random.default_rng(W * 1000 + log_n * 10 + rate_bits)
+    values = O.random_field(rng, (W, 1 << log_n))
+    ref = O.commit_from_values(values, rate_bits, cap_height)
+    check_batch(P2.PolynomialBatch.from_values(list(values), rate_bits, False, cap_height), ref)
+    check_batch(P2.PolynomialBatch.from_coeffs(list(ref.coeffs), rate_bits, False, cap_height), ref)
+    dev = torch.from_numpy(values.view(np.int64)).cuda()
+    check_batch(P2.PolynomialBatch.from_device(dev.data_ptr(), W, log_n, rate_bits, cap_height), ref)

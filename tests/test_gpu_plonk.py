@@ -11,9 +11,9 @@ P = 0xFFFFFFFF00000001
 G32 = 1753635133440165772
 
 
-def setup(P2, O, K, degree_bits, seed, gate_mix=None, cap=4):
+def setup(P2, O, K, degree_bits, seed, gate_mix=None, cap=4, cfg=None):
     from oracle import plonk as OP
-    cfg = K.CircuitConfig.standard_recursion_config()
+    cfg = cfg or K.CircuitConfig.standard_recursion_config()
     cfg.fri_config = P2.FriConfig(3, cap, 16, P2.FriReductionStrategy.ConstantArityBits(4, 5), 28)
     common, consts, sig, wires, pih = K.build_demo_circuit(cfg, degree_bits, seed, gate_mix)
     r = cfg.fri_config.rate_bits
@@ -54,6 +54,31 @@ def test_partial_products_vanishing_and_quotient(P2, O, pkg, degree_bits, seed):
     class B:  # coefficient views of the GPU batches
         def __init__(self, b):
             self.coeffs = b.coeff_matrix
+    assert OP.vanishing_identity_holds(common, B(pd.constants_sigmas_commitment), B(gw), B(gz), B(gq), pih, betas, gammas, alphas, zeta)
+
+
+def test_ragged_last_chunk_and_three_challenges(P2, O, pkg):
+    """A configuration whose routed wires do not fill the last partial-product chunk (37 = 4 x 8 + 5), three challenges,
+    100 wires (no Poseidon gate): the chunk bounds of k_pp_rows / check_partial_products and num_challenges != 2."""
+    K = pkg.plonk
+    cfg = K.CircuitConfig(num_wires=100, num_routed_wires=37, num_constants=2, num_challenges=3, max_quotient_degree_factor=8)
+    OP, cfg, common, consts, sig, wires, pih, pd, gw, rcs, rw = setup(P2, O, K, 8, 21, cfg=cfg)
+    assert common.num_partial_products == 4
+    r, cap = 3, 4
+    rng = np.random.default_rng(33)
+    betas, gammas, alphas = ([int(x) for x in rng.integers(1, P, 3, dtype=np.uint64)] for _ in range(3))
+    gz = K.PlonkProver.zs_partial_products_commitment(common, pd, gw, betas, gammas)
+    rz = O.commit_from_values(OP.partial_products_and_zs(common, wires, sig, betas, gammas), r, cap)
+    assert gz.n_polys == 15 and np.array_equal(gz.coeff_matrix, rz.coeffs) and np.array_equal(gz.merkle_tree.cap, rz.cap)
+    got = K.PlonkProver.vanishing_values(common, pd, pih, gw, gz, betas, gammas, alphas)
+    assert np.array_equal(got, OP.vanishing_values(common, rcs, rw, rz, pih, betas, gammas, alphas, r, divide_by_zh=False))
+    gq = K.PlonkProver.quotient_commitment(common, pd, pih, gw, gz, betas, gammas, alphas)
+    rq = O.quotient_commit(OP.vanishing_values(common, rcs, rw, rz, pih, betas, gammas, alphas, r), 8, 3, 8, False, r, cap)
+    assert gq.n_polys == 24 and np.array_equal(gq.coeff_matrix, rq.coeffs)
+    class B:
+        def __init__(self, b):
+            self.coeffs = b.coeff_matrix
+    zeta = int(rng.integers(2, P, dtype=np.uint64))
     assert OP.vanishing_identity_holds(common, B(pd.constants_sigmas_commitment), B(gw), B(gz), B(gq), pih, betas, gammas, alphas, zeta)
 
 
