@@ -21,6 +21,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -1077,13 +1078,7 @@ def run_ours(args, rank, local_rank, world):
                         "sample": f"1 full commit of {args.workload} ({dt:.2f} s); cap equals the GPU's: {ok}",
                         "port_quality": oracle_quality(O)}
 
-    strong = parity = None
-    if world > 1 and not sharded and not args.no_strong:
-        strong = strong_scaling_block(pkg, ctx, stream, rank, world, flush, args.steps)
-        ctx.set_stream(None)  # the mirror's sharded commits bring their own stream
-        parity = sharded_parity_block(pkg, ctx, rank, world)
-        ctx.set_stream(stream.cuda_stream)
-
+    line = None
     if rank == 0:
         line = {"metric": "LDE+Merkle commit throughput (input trace elements/s)", "value": value,
                 "unit": "elements/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -1103,10 +1098,63 @@ def run_ours(args, rank, local_rank, world):
                 "commit_algorithmic_gbs": commit_gbs, "commit_frac_of_hbm": commit_gbs / peak,
                 "phases_ms": {kk: (v / k if kk != "commits" else v) for kk, v in phases.items()},
                 "cpu_baseline": cpu_baseline}
-        if strong is not None:
+
+    # The single-commit blocks come after every number of the contract line is final.  They use CUDA IPC, peer stores and
+    # extra collectives; if one of them fails or stalls on a box (no peer access, a rank out of memory), the contract
+    # line is still printed -- with the failure in it -- instead of being lost, and the process ends non-zero.
+    strong = parity = None
+    extra_error = None
+    if world > 1 and not sharded and not args.no_strong:
+        # a rank that fails says so through a marker file the other ranks' watchers poll: they may be inside a collective
+        # the failed rank never joins, and torchrun would otherwise end them before rank 0 has printed anything
+        marker = os.path.join(tempfile.gettempdir(), f"nlc_bench_failed_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}")
+        if rank == 0 and os.path.exists(marker):
+            os.remove(marker)
+        dist.barrier()
+        done = threading.Event()
+
+        def watch():
+            t0 = time.time()
+            while not done.wait(0.5):
+                why = None
+                if os.path.exists(marker):
+                    why = "another rank failed: " + open(marker).read()[:400]
+                elif time.time() - t0 > args.strong_timeout:
+                    why = f"single-commit blocks did not finish within {args.strong_timeout} s"
+                if why is not None:
+                    if rank == 0:
+                        line["strong"] = {"error": why}
+                        line["sharded_parity"] = None
+                        print(json.dumps(line), flush=True)
+                    os._exit(3)
+        threading.Thread(target=watch, daemon=True).start()
+        try:
+            if args.inject_strong_failure == rank:
+                raise RuntimeError("injected failure (--inject-strong-failure)")
+            strong = strong_scaling_block(pkg, ctx, stream, rank, world, flush, args.steps)
+            ctx.set_stream(None)  # the mirror's sharded commits bring their own stream
+            parity = sharded_parity_block(pkg, ctx, rank, world)
+            ctx.set_stream(stream.cuda_stream)
+        except Exception as e:
+            extra_error = repr(e)
+            print(f"[rank {rank}] single-commit blocks: {extra_error}", file=sys.stderr, flush=True)
+            with open(marker, "w") as f:
+                f.write(f"rank {rank}: {extra_error}")
+            if rank != 0:
+                time.sleep(3.0)  # rank 0's watcher prints the line first
+                os._exit(3)
+        done.set()
+
+    if rank == 0:
+        if extra_error is not None:
+            line["strong"] = {"error": extra_error}
+            line["sharded_parity"] = parity
+        elif strong is not None:
             line["strong"] = strong
             line["sharded_parity"] = parity
         print(json.dumps(line), flush=True)
+    if extra_error is not None:
+        os._exit(3)  # the other ranks may be inside a collective this rank will never join
     if world > 1:
         dist.destroy_process_group()
     if parity is not None and any(v is False for v in parity.values()):
@@ -1127,6 +1175,10 @@ def main():
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
                          "of one independent commit per rank")
     ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the single-commit strong-scaling block")
+    ap.add_argument("--inject-strong-failure", type=int, default=-1,
+                    help="debug: make this rank fail at the start of the single-commit blocks (checks that the contract line survives)")
+    ap.add_argument("--strong-timeout", type=float, default=600.0,
+                    help="N > 1: seconds the single-commit blocks may take before the contract line is printed without them")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl", "nccl-pack"],
                     help="--shard-commit with more ranks than cosets (SURVEY 8e.3): how leaf rows reach their shard")
     ap.add_argument("--plonk-degree-bits", type=int, default=16, help="--workload plonk_proof_demo: log2 rows of the circuit")
