@@ -358,6 +358,22 @@ int nlc_tree_digests(nlc_tree* t, uint64_t* out);
 int nlc_tree_open(nlc_tree* t, size_t leaf_index, uint64_t* leaf_out, uint64_t* siblings_out);
 void nlc_tree_free(nlc_tree* t);
 
+/* ---- no allocation: Merkle cap with static device scratch ----------------------------------- */
+/* No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * nlc_merkle_new + nlc_tree_cap (MerkleTree::new(leaves, cap_height).cap), but:
+ *   - leaves_dev (n_leaves x leaf_len row-major) and cap_out_dev (2^cap_height x 4) are DEVICE pointers of the caller;
+ *   - the digest layers and the leaf-unit counter live in a file-scope __device__ array of the library
+ *     (csrc/static_scratch.cu: 4 MiB + 256 bytes, held by every GPU that loads the library until the process exits),
+ *     so n_leaves <= NLC_STATIC_MAX_LEAVES; larger trees are rejected (non-zero, message in nlc_last_error);
+ *   - the call makes no cudaMalloc / cudaFree / allocating library call and does not synchronise: the kernels are
+ *     enqueued on the context's stream (nlc_set_stream), cap_out_dev is valid once that stream reaches the call's end;
+ *   - all calls share the one array per GPU: calls that overlap on the same GPU (two streams, two contexts on one
+ *     device) race; the array keeps the previous call's contents, the library clears what must start at zero. */
+#define NLC_STATIC_MAX_LEAVES 65536
+int nlc_merkle_cap_static_dev(nlc_ctx* ctx, const uint64_t* leaves_dev, size_t n_leaves, size_t leaf_len,
+                              int cap_height, uint64_t* cap_out_dev);
+
 /* ---- a9: Challenger (plonky2::iop::challenger) -------------------------------------------- */
 /* The transcript state crosses the boundary as plain data, exactly the fields of
  * Challenger { sponge_state, input_buffer, output_buffer }.  The Rust Challenger keeps running on

@@ -127,6 +127,7 @@ SIGNATURES = {
     "nlc_hash_no_pad": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, u64p]),
     "nlc_hash_or_noop": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, u64p]),
     "nlc_two_to_one": (C.c_int, [vp, u64p, u64p, C.c_size_t, u64p]),
+    "nlc_merkle_cap_static_dev": (C.c_int, [vp, vp, C.c_size_t, C.c_size_t, C.c_int, vp]),
     "nlc_merkle_new": (C.c_int, [vp, u64p, C.c_size_t, C.c_size_t, C.c_int, C.POINTER(vp)]),
     "nlc_tree_cap": (C.c_int, [vp, u64p]),
     "nlc_tree_digests": (C.c_int, [vp, u64p]),
