@@ -605,10 +605,20 @@ class Strong:
             b.record(self.stream)
         torch.cuda.synchronize()
         dist.barrier()
-        clocks = sampler.stop()
         t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / steps], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+        # a timed region shorter than nvidia-smi's start-up + sampling period would carry no clock sample: keep the same
+        # commits running (untimed; the count follows from the all-reduced time, so every rank runs as many) while it samples
+        extra = 0 if steps * ms >= 400.0 else min(2000, int(400.0 / max(ms, 0.05)))
+        for _ in range(extra):
+            self.flush.zero_()
+            self.step_resident()
+        torch.cuda.synchronize()
+        dist.barrier()
+        clocks = sampler.stop()
+        if extra:
+            clocks["window"] = f"the {steps} timed commits + {extra} more of the same, untimed"
         # phases (this rank's CUDA events; max over ranks per phase)
         self.ctx.timing_enable(True)
         self.ctx.timing_read()

@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(AIR_THREADS) k_air_eval(const AirArgs A) {
         u64 acc[MAX_ALPHAS];
 #pragma unroll
         for (int j = 0; j < MAX_ALPHAS; j++) acc[j] = 0;
-        air_run(A, regs, stride, k, k_next, z_last, l_first, l_last, acc);
+        air_run(A, regs, k, k_next, z_last, l_first, l_last, acc);
 #pragma unroll
         for (int j = 0; j < MAX_ALPHAS; j++)
             if ((u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];

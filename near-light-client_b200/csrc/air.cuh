@@ -24,7 +24,7 @@ struct AirArgs {
     const u64* lagrange_first;
     const u64* lagrange_last;
     u64 last;                 // w_n^-1: the last point of the subgroup (z_last = x - last)
-    u64* regs;                // n_regs x n_threads scratch (register r of thread t at regs[r * n_threads + t])
+    u64* regs;                // (n_regs + 1) x n_threads scratch (register r of thread t at regs[r * n_threads + t])
     u64* out;                 // size x n_alphas row-major, natural order of i (the `quotient_values` before transpose)
 };
 
@@ -34,47 +34,51 @@ constexpr int MAX_ALPHAS = 8;
 // The interpreter: runs the straight-line program for ONE point (leaf k, next row at leaf k_next); the virtual
 // registers of the program live in a thread-interleaved scratch matrix (coalesced), the program counter is uniform
 // across the grid.  CONSTRAINT ops fold into acc_j = acc_j * alpha_j + c (ConstraintConsumer, consumer.rs:54-78).
-__device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_t stride, const size_t k, const size_t k_next,
+//
+// The code it runs is the LOWERED form AirDevice makes of a validated program (lower_program): every register operand
+// is already the element offset of that register's row in the scratch matrix (register r -> r * n_threads), so an
+// operand fetch is one IMAD.WIDE + one LDG instead of a 64-bit multiply; a DOT_CONST whose terms name the accumulator
+// first parks it in a slot of its own (device flag AIR_DEV_PARK_LAST), so that its term loop is plain loads, and odd
+// term counts are padded with a zero coefficient.  Measured on the demo gate set (4698 words, 4320 of them dot-product
+// terms): 80.7 -> see DESIGN.md 7 instructions per code word.
+constexpr u32 AIR_DEV_PARK_LAST = 8; // device-only instruction flag (bit 3 of the flag byte), set by lower_program
+__device__ __forceinline__ void air_run(const AirArgs& A, u64* __restrict__ g, const size_t k, const size_t k_next,
                                         const u64 z_last, const u64 l_first, const u64 l_last, u64 (&acc)[MAX_ALPHAS]) {
     u64 last = 0; // the accumulator: the previous instruction's result (NLC_AIR_FLAG_*)
-    for (u32 pc = 0; pc < A.n_ops; pc++) {
-        const uint4 ins = __ldg(reinterpret_cast<const uint4*>(A.code) + pc);
+    const uint4* __restrict__ code = reinterpret_cast<const uint4*>(A.code);
+    uint4 nxt = __ldg(code);
+    for (u32 pc = 0; pc < A.n_ops;) {
+        const uint4 ins = nxt;
         const u32 op = ins.x & 0xffu, flags = ins.x >> 8;
+        // the next instruction word is on its way while this one executes (a DOT_CONST skips its term words)
+        const u32 pc_next = pc + 1 + (op == NLC_AIR_DOT_CONST ? (ins.z + 1) >> 1 : 0);
+        nxt = __ldg(code + (pc_next < A.n_ops ? pc_next : pc));
         u64 r;
         if (op >= NLC_AIR_ADD) { // register operands
-            const u64 ra = (flags & NLC_AIR_FLAG_A_LAST) || op == NLC_AIR_DOT_CONST ? last : regs[ins.z * stride];
-            switch (op) {
-            case NLC_AIR_ADD: r = gl::dadd(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
-            case NLC_AIR_SUB: r = gl::dsub(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
-            case NLC_AIR_MUL: r = gl::mul(ra, (flags & NLC_AIR_FLAG_B_LAST) ? last : regs[ins.w * stride]); break;
-            case NLC_AIR_NEG: r = gl::neg(ra); break;
-            case NLC_AIR_MUL_CONST: { const u64 c = A.pool[ins.w]; r = (c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c); break; }
-            case NLC_AIR_ADD_CONST: r = gl::dadd(ra, A.pool[ins.w]); break;
-            case NLC_AIR_SUB_CONST: r = gl::dsub(ra, A.pool[ins.w]); break;
-            case NLC_AIR_DOT_CONST: { // ins.z terms in the following words; 96-bit products summed in two 64-bit lanes
+            u64 ra = last, rb = last;
+            if (!(flags & NLC_AIR_FLAG_A_LAST) && op != NLC_AIR_DOT_CONST) ra = g[ins.z];
+            if (op <= NLC_AIR_MUL) {
+                if (!(flags & NLC_AIR_FLAG_B_LAST)) rb = g[ins.w];
+                r = op == NLC_AIR_MUL ? gl::mul(ra, rb) : op == NLC_AIR_ADD ? gl::dadd(ra, rb) : gl::dsub(ra, rb);
+            } else if (op == NLC_AIR_DOT_CONST) { // ins.z terms in the following words; 96-bit products summed in two 64-bit lanes
+                if (flags & AIR_DEV_PARK_LAST) g[ins.w] = last;
                 u64 s0 = 0, s1 = 0;
-                for (u32 t = 0; t < ins.z; t += 2) {
-                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(A.code) + ++pc);
-                    const u64 v0 = (w.x & NLC_AIR_DOT_TERM_LAST) ? last : regs[(size_t)w.x * stride];
+                const uint4* __restrict__ tw = code + pc + 1;
+                const u32 words = (ins.z + 1) >> 1;
+#pragma unroll 2
+                for (u32 t = 0; t < words; t++) {
+                    const uint4 w = __ldg(tw + t);
+                    const u64 v0 = g[w.x], v1 = g[w.z];
                     s0 += (u64)(u32)v0 * w.y;
                     s1 += (v0 >> 32) * w.y;
-                    if (t + 1 < ins.z) {
-                        const u64 v1 = (w.z & NLC_AIR_DOT_TERM_LAST) ? last : regs[(size_t)w.z * stride];
-                        s0 += (u64)(u32)v1 * w.w;
-                        s1 += (v1 >> 32) * w.w;
-                    }
+                    s0 += (u64)(u32)v1 * w.w;
+                    s1 += (v1 >> 32) * w.w;
                 }
                 // s0 + 2^32 s1 with s0, s1 < 2^60 (<= 2^12 terms, constants < 2^16):  2^32 s1 = (s1_lo << 32) + s1_hi 2^64
                 const unsigned __int128 T = (unsigned __int128)s0 + ((u64)(u32)s1 << 32) + (s1 >> 32) * gl::EPS;
                 r = gl::dcanon(gl::reduce128_dev_nc((u64)T, (u64)(T >> 64)));
-                break;
-            }
-            case NLC_AIR_MULADD_CONST: { // the constant is the same for the whole grid: the branch is uniform
-                const u64 c = A.pool[ins.w];
-                r = gl::dadd((c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c), last);
-                break;
-            }
-            default: { // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
+            } else if (op >= NLC_AIR_CONSTRAINT && op <= NLC_AIR_CONSTRAINT_LAST_ROW) {
+                // ConstraintConsumer (consumer.rs:54-78): filter, then acc_j = acc_j * alpha_j + c
                 u64 c = ra;
                 if (op == NLC_AIR_CONSTRAINT_TRANSITION) c = gl::mul(c, z_last);
                 else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
@@ -82,8 +86,18 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_
 #pragma unroll
                 for (int j = 0; j < MAX_ALPHAS; j++)
                     if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
+                pc = pc_next;
                 continue;
-            }
+            } else if (op == NLC_AIR_NEG) {
+                r = gl::neg(ra);
+            } else { // one register and one pooled constant (the same for the whole grid: the branches are uniform)
+                const u64 c = A.pool[ins.w];
+                switch (op) {
+                case NLC_AIR_MUL_CONST: r = (c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c); break;
+                case NLC_AIR_ADD_CONST: r = gl::dadd(ra, c); break;
+                case NLC_AIR_SUB_CONST: r = gl::dsub(ra, c); break;
+                default: r = gl::dadd((c >> 32) ? gl::mul(ra, c) : gl::mul_u32(ra, (u32)c), last); break; // MULADD_CONST
+                }
             }
         } else {
             switch (op) {
@@ -95,8 +109,9 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* regs, const size_
             default: r = A.pool[ins.z]; break; // NLC_AIR_CONST
             }
         }
-        if (!(flags & NLC_AIR_FLAG_NO_STORE)) regs[ins.y * stride] = r;
+        if (!(flags & NLC_AIR_FLAG_NO_STORE)) g[ins.y] = r;
         last = r;
+        pc = pc_next;
     }
 }
 
@@ -156,6 +171,49 @@ void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_con
     }
 }
 
+// The device form of a VALIDATED program for a grid of n_threads (see air_run): register operands become row offsets
+// into the scratch matrix, accumulator terms of a DOT_CONST go through the parking slot (row n_regs), odd term counts
+// are padded.  A renaming of operands: results are unchanged.
+inline std::vector<u32> lower_program(const nlc_air_program* prog, size_t n_threads) {
+    NLC_CHECK(((size_t)prog->n_regs + 1) * n_threads < ((size_t)1 << 32), "AIR program: register file too large for 32-bit offsets");
+    std::vector<u32> code(prog->code, prog->code + (size_t)prog->n_ops * 4);
+    const u32 nt = (u32)n_threads, park = prog->n_regs * nt;
+    for (u32 pc = 0; pc < prog->n_ops; pc++) {
+        u32* w = code.data() + 4 * (size_t)pc;
+        const u32 op = w[0] & 0xffu, flags = w[0] >> 8;
+        if (op < NLC_AIR_ADD) { // loads: a = column / table index
+            w[1] *= nt;
+            continue;
+        }
+        if (op == NLC_AIR_DOT_CONST) {
+            const u32 terms = w[2], words = (terms + 1) / 2;
+            bool parks = false;
+            u32 first = 0;
+            for (u32 t = 0; t < 2 * words; t++) {
+                u32* term = code.data() + 4 * (size_t)(pc + 1 + t / 2) + 2 * (t & 1);
+                if (t >= terms) { // padding: any readable slot, coefficient 0
+                    term[0] = first;
+                    term[1] = 0;
+                } else if (term[0] & NLC_AIR_DOT_TERM_LAST) {
+                    term[0] = park;
+                    parks = true;
+                } else
+                    term[0] *= nt;
+                if (t == 0) first = term[0];
+            }
+            if (parks) w[0] |= AIR_DEV_PARK_LAST << 8;
+            w[1] *= nt;
+            w[3] = park;
+            pc += words;
+            continue;
+        }
+        if (!(flags & NLC_AIR_FLAG_A_LAST)) w[2] *= nt;
+        if (op <= NLC_AIR_MUL && !(flags & NLC_AIR_FLAG_B_LAST)) w[3] *= nt;
+        if (!(op >= NLC_AIR_CONSTRAINT && op <= NLC_AIR_CONSTRAINT_LAST_ROW)) w[1] *= nt;
+    }
+    return code;
+}
+
 // A program and its small operands resident on the device for one launch; frees in stream order on destruction.
 struct AirDevice {
     nlc_ctx* ctx;
@@ -175,10 +233,11 @@ struct AirDevice {
             code_dev = ctx->dmalloc(((size_t)prog->n_ops * 4 + 1) / 2 + 2);
             small = ctx->dmalloc(n_small + 1);
             cols_dev = ctx->dmalloc(cols.size() + 1);
-            regs = ctx->dmalloc(std::max<size_t>((size_t)prog->n_regs * n_threads, 1));
+            regs = ctx->dmalloc(((size_t)prog->n_regs + 1) * n_threads); // + the parking slot of lower_program
             // pageable sources: the runtime stages them before returning
+            const std::vector<u32> code = lower_program(prog, n_threads);
             if (prog->n_ops)
-                NLC_CUDA(cudaMemcpyAsync(code_dev, prog->code, (size_t)prog->n_ops * 16, cudaMemcpyHostToDevice, ctx->stream));
+                NLC_CUDA(cudaMemcpyAsync(code_dev, code.data(), (size_t)prog->n_ops * 16, cudaMemcpyHostToDevice, ctx->stream));
             std::vector<u64> host(n_small + 1, 0);
             size_t o = 0;
             auto put = [&](const u64* p, size_t cnt) {

@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(AIR_THREADS) k_plonk_vanishing(const AirArgs A
                 if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), term);
         };
         // gate constraint terms, highest index first (the host emits them in that order)
-        air_run(A, regs, stride, k, k_next, 0, 0, 0, acc);
+        air_run(A, regs, k, k_next, 0, 0, 0, acc);
         // check_partial_products, last challenge and last chunk first
         const u64 x = A.coset_x[i]; // shifted_x = g * w^i
         for (u32 ch = V.num_ch; ch-- > 0;) {
