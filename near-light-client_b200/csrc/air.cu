@@ -21,7 +21,8 @@ namespace {
 enum { KIND_QX = 10, KIND_QLF = 11, KIND_QLL = 12 };
 
 // One thread per leaf k of the quotient-domain prefix.
-__global__ void __launch_bounds__(AIR_THREADS) k_air_eval(const AirArgs A) {
+template <int NA>
+__global__ void __launch_bounds__(AIR_THREADS, air_min_blocks(NA)) k_air_eval(const AirArgs A) {
     const size_t size = (size_t)1 << A.log_size;
     const size_t stride = (size_t)gridDim.x * AIR_THREADS;
     u64* regs = A.regs + (size_t)blockIdx.x * AIR_THREADS + threadIdx.x;
@@ -31,13 +32,13 @@ __global__ void __launch_bounds__(AIR_THREADS) k_air_eval(const AirArgs A) {
         const size_t k_next = A.log_size ? (__brevll(i_next) >> (64 - A.log_size)) : 0;
         const u64 z_last = gl::sub(A.coset_x[i], A.last);
         const u64 l_first = A.lagrange_first[i], l_last = A.lagrange_last[i];
-        u64 acc[MAX_ALPHAS];
+        u64 acc[NA];
 #pragma unroll
-        for (int j = 0; j < MAX_ALPHAS; j++) acc[j] = 0;
-        air_run(A, regs, k, k_next, z_last, l_first, l_last, acc);
+        for (int j = 0; j < NA; j++) acc[j] = 0;
+        air_run<NA>(A, regs, k, k_next, z_last, l_first, l_last, acc);
 #pragma unroll
-        for (int j = 0; j < MAX_ALPHAS; j++)
-            if ((u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];
+        for (int j = 0; j < NA; j++)
+            if (NA < MAX_ALPHAS || (u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];
     }
 }
 
@@ -132,7 +133,8 @@ void air_eval_dev(nlc_ctx* ctx, const nlc_air_program* prog, nlc_batch* const* b
     const size_t size = (size_t)1 << (log_n + qdb);
     const u64 *x, *lf, *ll;
     quotient_tables_dev(ctx, log_n, qdb, &x, &lf, &ll);
-    AirDevice dev(ctx, prog, cols, publics, globals, challenges, alphas, n_alphas, size);
+    AirDevice dev(ctx, prog, cols, publics, globals, challenges, alphas, n_alphas, size, nullptr, 0, nullptr,
+                  air_min_blocks(air_na(n_alphas)));
     AirArgs& A = dev.A;
     A.log_size = log_n + qdb;
     A.qdb = qdb;
@@ -141,5 +143,11 @@ void air_eval_dev(nlc_ctx* ctx, const nlc_air_program* prog, nlc_batch* const* b
     A.lagrange_last = ll;
     A.last = gl::h_inv(gl::h_root_of_unity(log_n));
     A.out = out_dev;
-    NLC_LAUNCH(ctx, k_air_eval, (unsigned)dev.blocks, AIR_THREADS, 0, A);
+    switch (air_na(n_alphas)) {
+    case 1: NLC_LAUNCH(ctx, k_air_eval<1>, (unsigned)dev.blocks, AIR_THREADS, 0, A); break;
+    case 2: NLC_LAUNCH(ctx, k_air_eval<2>, (unsigned)dev.blocks, AIR_THREADS, 0, A); break;
+    case 3: NLC_LAUNCH(ctx, k_air_eval<3>, (unsigned)dev.blocks, AIR_THREADS, 0, A); break;
+    case 4: NLC_LAUNCH(ctx, k_air_eval<4>, (unsigned)dev.blocks, AIR_THREADS, 0, A); break;
+    default: NLC_LAUNCH(ctx, k_air_eval<MAX_ALPHAS>, (unsigned)dev.blocks, AIR_THREADS, 0, A); break;
+    }
 }

@@ -30,6 +30,11 @@ struct AirArgs {
 
 constexpr int AIR_THREADS = 128;
 constexpr int MAX_ALPHAS = 8;
+// The interpreter kernels are compiled per accumulator count NA: NA = 1..4 hold exactly n_alphas accumulators (a starky
+// or plonk proof has 2 or 3: 12 fewer live registers than the generic form),
+// NA = MAX_ALPHAS serves 5..8 with a bound check per accumulator.
+constexpr int air_na(size_t n_alphas) { return n_alphas <= 4 ? (int)n_alphas : MAX_ALPHAS; }
+constexpr int air_min_blocks(int) { return 8; } // 64 registers per thread (measured: 10 CTAs of 48 registers are 8-15 % slower)
 
 // The interpreter: runs the straight-line program for ONE point (leaf k, next row at leaf k_next); the virtual
 // registers of the program live in a thread-interleaved scratch matrix (coalesced), the program counter is uniform
@@ -40,11 +45,32 @@ constexpr int MAX_ALPHAS = 8;
 // operand fetch is one IMAD.WIDE + one LDG instead of a 64-bit multiply; a DOT_CONST whose terms name the accumulator
 // first parks it in a slot of its own (device flag AIR_DEV_PARK_LAST), so that its term loop is plain loads, and odd
 // term counts are padded with a zero coefficient.  Measured on the demo gate set (4698 words, 4320 of them dot-product
-// terms): 80.7 -> see DESIGN.md 7 instructions per code word.
+// terms): 379 k -> 230 k executed instructions per warp.
 constexpr u32 AIR_DEV_PARK_LAST = 8; // device-only instruction flag (bit 3 of the flag byte), set by lower_program
-__device__ __forceinline__ void air_run(const AirArgs& A, u64* __restrict__ g, const size_t k, const size_t k_next,
-                                        const u64 z_last, const u64 l_first, const u64 l_last, u64 (&acc)[MAX_ALPHAS]) {
+// d = a * b + c with a, b 32-bit: ONE IMAD.WIDE.U32 (the compiler's own rendering of `c += (u64)a * b` drags zero
+// carry words along)
+__device__ __forceinline__ u64 mad_wide(u32 a, u32 b, u64 c) {
+    u64 d;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+    return d;
+}
+// scratch-matrix accesses as explicit global-space instructions: `g` below is deliberately opaque to the compiler, which
+// would otherwise fall back to generic loads
+__device__ __forceinline__ u64 reg_ld(const u64* g, u32 off) {
+    u64 v;
+    asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(g + off) : "memory");
+    return v;
+}
+__device__ __forceinline__ void reg_st(u64* g, u32 off, u64 v) {
+    asm volatile("st.global.u64 [%0], %1;" ::"l"(g + off), "l"(v) : "memory");
+}
+template <int NA>
+__device__ __forceinline__ void air_run(const AirArgs& A, u64* g, const size_t k, const size_t k_next,
+                                        const u64 z_last, const u64 l_first, const u64 l_last, u64 (&acc)[NA]) {
     u64 last = 0; // the accumulator: the previous instruction's result (NLC_AIR_FLAG_*)
+    // the thread's column of the scratch matrix as ONE opaque 64-bit value: an operand address is then a single
+    // IMAD.WIDE (offset * 8 + g) instead of the re-associated (base + (offset + thread) * 8) in four instructions
+    asm volatile("" : "+l"(g));
     const uint4* __restrict__ code = reinterpret_cast<const uint4*>(A.code);
     uint4 nxt = __ldg(code);
     for (u32 pc = 0; pc < A.n_ops;) {
@@ -56,23 +82,23 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* __restrict__ g, c
         u64 r;
         if (op >= NLC_AIR_ADD) { // register operands
             u64 ra = last, rb = last;
-            if (!(flags & NLC_AIR_FLAG_A_LAST) && op != NLC_AIR_DOT_CONST) ra = g[ins.z];
+            if (!(flags & NLC_AIR_FLAG_A_LAST) && op != NLC_AIR_DOT_CONST) ra = reg_ld(g, ins.z);
             if (op <= NLC_AIR_MUL) {
-                if (!(flags & NLC_AIR_FLAG_B_LAST)) rb = g[ins.w];
+                if (!(flags & NLC_AIR_FLAG_B_LAST)) rb = reg_ld(g, ins.w);
                 r = op == NLC_AIR_MUL ? gl::mul(ra, rb) : op == NLC_AIR_ADD ? gl::dadd(ra, rb) : gl::dsub(ra, rb);
             } else if (op == NLC_AIR_DOT_CONST) { // ins.z terms in the following words; 96-bit products summed in two 64-bit lanes
-                if (flags & AIR_DEV_PARK_LAST) g[ins.w] = last;
+                if (flags & AIR_DEV_PARK_LAST) reg_st(g, ins.w, last);
                 u64 s0 = 0, s1 = 0;
                 const uint4* __restrict__ tw = code + pc + 1;
                 const u32 words = (ins.z + 1) >> 1;
 #pragma unroll 2
                 for (u32 t = 0; t < words; t++) {
                     const uint4 w = __ldg(tw + t);
-                    const u64 v0 = g[w.x], v1 = g[w.z];
-                    s0 += (u64)(u32)v0 * w.y;
-                    s1 += (v0 >> 32) * w.y;
-                    s0 += (u64)(u32)v1 * w.w;
-                    s1 += (v1 >> 32) * w.w;
+                    const u64 v0 = reg_ld(g, w.x), v1 = reg_ld(g, w.z);
+                    s0 = mad_wide((u32)v0, w.y, s0);
+                    s1 = mad_wide((u32)(v0 >> 32), w.y, s1);
+                    s0 = mad_wide((u32)v1, w.w, s0);
+                    s1 = mad_wide((u32)(v1 >> 32), w.w, s1);
                 }
                 // s0 + 2^32 s1 with s0, s1 < 2^60 (<= 2^12 terms, constants < 2^16):  2^32 s1 = (s1_lo << 32) + s1_hi 2^64
                 const unsigned __int128 T = (unsigned __int128)s0 + ((u64)(u32)s1 << 32) + (s1 >> 32) * gl::EPS;
@@ -84,8 +110,8 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* __restrict__ g, c
                 else if (op == NLC_AIR_CONSTRAINT_FIRST_ROW) c = gl::mul(c, l_first);
                 else if (op == NLC_AIR_CONSTRAINT_LAST_ROW) c = gl::mul(c, l_last);
 #pragma unroll
-                for (int j = 0; j < MAX_ALPHAS; j++)
-                    if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
+                for (int j = 0; j < NA; j++)
+                    if (NA < MAX_ALPHAS || (u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
                 pc = pc_next;
                 continue;
             } else if (op == NLC_AIR_NEG) {
@@ -109,7 +135,7 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* __restrict__ g, c
             default: r = A.pool[ins.z]; break; // NLC_AIR_CONST
             }
         }
-        if (!(flags & NLC_AIR_FLAG_NO_STORE)) g[ins.y] = r;
+        if (!(flags & NLC_AIR_FLAG_NO_STORE)) reg_st(g, ins.y, r);
         last = r;
         pc = pc_next;
     }
@@ -222,10 +248,10 @@ struct AirDevice {
     size_t blocks = 0;
     AirDevice(nlc_ctx* c, const nlc_air_program* prog, const std::vector<const u64*>& cols, const u64* publics, const u64* globals,
               const u64* challenges, const u64* alphas, size_t n_alphas, size_t n_points, const u64* extra = nullptr, size_t n_extra = 0,
-              const u64** extra_dev = nullptr)
+              const u64** extra_dev = nullptr, int ctas_per_sm = 8)
         : ctx(c) {
         blocks = (n_points + AIR_THREADS - 1) / AIR_THREADS;
-        const size_t full = (size_t)ctx->sm_count * 8;
+        const size_t full = (size_t)ctx->sm_count * ctas_per_sm;
         if (blocks > full) blocks = full;
         const size_t n_threads = blocks * AIR_THREADS;
         const size_t n_small = prog->n_pool + prog->n_public + prog->n_global + prog->n_challenge + n_alphas + n_extra;

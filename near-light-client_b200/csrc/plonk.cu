@@ -151,7 +151,8 @@ struct VanishArgs {
 
 // eval_vanishing_poly_base_batch for every point of the quotient domain; one thread per leaf k of the domain prefix.
 // out[i * num_ch + j] = sum_k term_k alpha_j^k, BEFORE the multiplication by 1/Z_H (quotient_commit_dev applies it).
-__global__ void __launch_bounds__(AIR_THREADS) k_plonk_vanishing(const AirArgs A, const VanishArgs V) {
+template <int NA>
+__global__ void __launch_bounds__(AIR_THREADS, air_min_blocks(NA)) k_plonk_vanishing(const AirArgs A, const VanishArgs V) {
     const size_t size = (size_t)1 << A.log_size;
     const size_t stride = (size_t)gridDim.x * AIR_THREADS;
     u64* regs = A.regs + (size_t)blockIdx.x * AIR_THREADS + threadIdx.x;
@@ -160,16 +161,16 @@ __global__ void __launch_bounds__(AIR_THREADS) k_plonk_vanishing(const AirArgs A
         const size_t i = A.log_size ? (__brevll(k) >> (64 - A.log_size)) : 0;
         const size_t i_next = (i + ((size_t)1 << A.qdb)) & (size - 1);
         const size_t k_next = A.log_size ? (__brevll(i_next) >> (64 - A.log_size)) : 0;
-        u64 acc[MAX_ALPHAS];
+        u64 acc[NA];
 #pragma unroll
-        for (int j = 0; j < MAX_ALPHAS; j++) acc[j] = 0;
+        for (int j = 0; j < NA; j++) acc[j] = 0;
         auto fold = [&](const u64 term) {
 #pragma unroll
-            for (int j = 0; j < MAX_ALPHAS; j++)
-                if ((u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), term);
+            for (int j = 0; j < NA; j++)
+                if (NA < MAX_ALPHAS || (u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), term);
         };
         // gate constraint terms, highest index first (the host emits them in that order)
-        air_run(A, regs, k, k_next, 0, 0, 0, acc);
+        air_run<NA>(A, regs, k, k_next, 0, 0, 0, acc);
         // check_partial_products, last challenge and last chunk first
         const u64 x = A.coset_x[i]; // shifted_x = g * w^i
         for (u32 ch = V.num_ch; ch-- > 0;) {
@@ -193,8 +194,8 @@ __global__ void __launch_bounds__(AIR_THREADS) k_plonk_vanishing(const AirArgs A
         const u64 l0 = A.lagrange_first[i];
         for (u32 ch = V.num_ch; ch-- > 0;) fold(gl::mul(l0, gl::dsub(gl::dcanon(V.zs_pp[ch][k]), 1)));
 #pragma unroll
-        for (int j = 0; j < MAX_ALPHAS; j++)
-            if ((u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];
+        for (int j = 0; j < NA; j++)
+            if (NA < MAX_ALPHAS || (u32)j < A.n_alphas) A.out[i * A.n_alphas + j] = acc[j];
     }
 }
 
@@ -329,7 +330,8 @@ void plonk_vanishing_dev(nlc_ctx* ctx, const nlc_plonk_circuit* c, const nlc_air
     quotient_tables_dev(ctx, log_n, qdb, &x, &lf, &ll);
     const u64* extra_dev = nullptr;
     NLC_CHECK(gates->n_public <= 4, "the gate program's public inputs are the 4 elements of public_inputs_hash");
-    AirDevice dev(ctx, gates, cols, public_inputs_hash, nullptr, nullptr, alphas, nch, size, extra.data(), extra.size(), &extra_dev);
+    AirDevice dev(ctx, gates, cols, public_inputs_hash, nullptr, nullptr, alphas, nch, size, extra.data(), extra.size(), &extra_dev,
+                  air_min_blocks(air_na(nch)));
     AirArgs& A = dev.A;
     A.log_size = log_n + qdb;
     A.qdb = qdb;
@@ -349,5 +351,11 @@ void plonk_vanishing_dev(nlc_ctx* ctx, const nlc_plonk_circuit* c, const nlc_air
     V.chunk = (u32)c->quotient_degree_factor;
     V.n_chunks = (u32)n_chunks;
     V.num_ch = (u32)nch;
-    NLC_LAUNCH(ctx, k_plonk_vanishing, (unsigned)dev.blocks, AIR_THREADS, 0, A, V);
+    switch (air_na(nch)) {
+    case 1: NLC_LAUNCH(ctx, k_plonk_vanishing<1>, (unsigned)dev.blocks, AIR_THREADS, 0, A, V); break;
+    case 2: NLC_LAUNCH(ctx, k_plonk_vanishing<2>, (unsigned)dev.blocks, AIR_THREADS, 0, A, V); break;
+    case 3: NLC_LAUNCH(ctx, k_plonk_vanishing<3>, (unsigned)dev.blocks, AIR_THREADS, 0, A, V); break;
+    case 4: NLC_LAUNCH(ctx, k_plonk_vanishing<4>, (unsigned)dev.blocks, AIR_THREADS, 0, A, V); break;
+    default: NLC_LAUNCH(ctx, k_plonk_vanishing<MAX_ALPHAS>, (unsigned)dev.blocks, AIR_THREADS, 0, A, V); break;
+    }
 }
