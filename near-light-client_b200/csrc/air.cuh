@@ -47,6 +47,7 @@ constexpr int air_min_blocks(int) { return 8; } // 64 registers per thread (meas
 // term counts are padded with a zero coefficient.  Measured on the demo gate set (4698 words, 4320 of them dot-product
 // terms): 379 k -> 230 k executed instructions per warp.
 constexpr u32 AIR_DEV_PARK_LAST = 8; // device-only instruction flag (bit 3 of the flag byte), set by lower_program
+constexpr u32 AIR_DEV_END = 0xff;     // device-only opcode: end of the lowered program
 // d = a * b + c with a, b 32-bit: ONE IMAD.WIDE.U32 (the compiler's own rendering of `c += (u64)a * b` drags zero
 // carry words along)
 __device__ __forceinline__ u64 mad_wide(u32 a, u32 b, u64 c) {
@@ -71,14 +72,12 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* g, const size_t k
     // the thread's column of the scratch matrix as ONE opaque 64-bit value: an operand address is then a single
     // IMAD.WIDE (offset * 8 + g) instead of the re-associated (base + (offset + thread) * 8) in four instructions
     asm volatile("" : "+l"(g));
-    const uint4* __restrict__ code = reinterpret_cast<const uint4*>(A.code);
-    uint4 nxt = __ldg(code);
-    for (u32 pc = 0; pc < A.n_ops;) {
-        const uint4 ins = nxt;
+    // the lowered code carries, in the upper half of its first word, the distance to the next instruction (a DOT_CONST
+    // skips its term words) and ends with an AIR_DEV_END word: no program counter, no bound check, no clamp -- the next
+    // instruction word is on its way while this one executes
+    // one instruction; `cur` points at its word (a DOT_CONST reads its terms from cur + 1)
+    auto exec = [&](const uint4 ins, const uint4* const cur) {
         const u32 op = ins.x & 0xffu, flags = ins.x >> 8;
-        // the next instruction word is on its way while this one executes (a DOT_CONST skips its term words)
-        const u32 pc_next = pc + 1 + (op == NLC_AIR_DOT_CONST ? (ins.z + 1) >> 1 : 0);
-        nxt = __ldg(code + (pc_next < A.n_ops ? pc_next : pc));
         u64 r;
         if (op >= NLC_AIR_ADD) { // register operands
             u64 ra = last, rb = last;
@@ -89,7 +88,7 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* g, const size_t k
             } else if (op == NLC_AIR_DOT_CONST) { // ins.z terms in the following words; 96-bit products summed in two 64-bit lanes
                 if (flags & AIR_DEV_PARK_LAST) reg_st(g, ins.w, last);
                 u64 s0 = 0, s1 = 0;
-                const uint4* __restrict__ tw = code + pc + 1;
+                const uint4* __restrict__ tw = cur + 1;
                 const u32 words = (ins.z + 1) >> 1;
 #pragma unroll 2
                 for (u32 t = 0; t < words; t++) {
@@ -112,8 +111,7 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* g, const size_t k
 #pragma unroll
                 for (int j = 0; j < NA; j++)
                     if (NA < MAX_ALPHAS || (u32)j < A.n_alphas) acc[j] = gl::dadd(gl::mul(acc[j], A.alphas[j]), c);
-                pc = pc_next;
-                continue;
+                return;
             } else if (op == NLC_AIR_NEG) {
                 r = gl::neg(ra);
             } else { // one register and one pooled constant (the same for the whole grid: the branches are uniform)
@@ -137,7 +135,22 @@ __device__ __forceinline__ void air_run(const AirArgs& A, u64* g, const size_t k
         }
         if (!(flags & NLC_AIR_FLAG_NO_STORE)) reg_st(g, ins.y, r);
         last = r;
-        pc = pc_next;
+    };
+    // the dispatch loop, two instructions per trip so that the instruction words alternate between two register sets
+    // instead of being copied (nxt -> ins) every time
+    const uint4* cp = reinterpret_cast<const uint4*>(A.code);
+    uint4 wa = __ldg(cp), wb;
+    for (;;) {
+        if ((wa.x & 0xffu) == AIR_DEV_END) break;
+        const uint4* cur = cp;
+        cp += wa.x >> 16;
+        wb = __ldg(cp);
+        exec(wa, cur);
+        if ((wb.x & 0xffu) == AIR_DEV_END) break;
+        cur = cp;
+        cp += wb.x >> 16;
+        wa = __ldg(cp);
+        exec(wb, cur);
     }
 }
 
@@ -203,10 +216,12 @@ void validate_program(const nlc_air_program* prog, size_t n_cols, bool plain_con
 inline std::vector<u32> lower_program(const nlc_air_program* prog, size_t n_threads) {
     NLC_CHECK(((size_t)prog->n_regs + 1) * n_threads < ((size_t)1 << 32), "AIR program: register file too large for 32-bit offsets");
     std::vector<u32> code(prog->code, prog->code + (size_t)prog->n_ops * 4);
+    code.insert(code.end(), {AIR_DEV_END | (1u << 16), 0u, 0u, 0u});
     const u32 nt = (u32)n_threads, park = prog->n_regs * nt;
     for (u32 pc = 0; pc < prog->n_ops; pc++) {
         u32* w = code.data() + 4 * (size_t)pc;
         const u32 op = w[0] & 0xffu, flags = w[0] >> 8;
+        w[0] |= (op == NLC_AIR_DOT_CONST ? 1u + (w[2] + 1) / 2 : 1u) << 16; // distance to the next instruction (<= 2049 words)
         if (op < NLC_AIR_ADD) { // loads: a = column / table index
             w[1] *= nt;
             continue;
@@ -262,8 +277,7 @@ struct AirDevice {
             regs = ctx->dmalloc(((size_t)prog->n_regs + 1) * n_threads); // + the parking slot of lower_program
             // pageable sources: the runtime stages them before returning
             const std::vector<u32> code = lower_program(prog, n_threads);
-            if (prog->n_ops)
-                NLC_CUDA(cudaMemcpyAsync(code_dev, code.data(), (size_t)prog->n_ops * 16, cudaMemcpyHostToDevice, ctx->stream));
+            NLC_CUDA(cudaMemcpyAsync(code_dev, code.data(), code.size() * sizeof(u32), cudaMemcpyHostToDevice, ctx->stream));
             std::vector<u64> host(n_small + 1, 0);
             size_t o = 0;
             auto put = [&](const u64* p, size_t cnt) {
