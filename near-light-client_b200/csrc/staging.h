@@ -8,6 +8,10 @@
 // slot k.  Pinned / registered sources skip it.
 #pragma once
 #include <cuda_runtime.h>
+#if defined(__x86_64__) && defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+#include <cstdint>
 
 #include <condition_variable>
 #include <deque>
@@ -96,6 +100,36 @@ struct HostStager {
     static void run_granule(const Granule& g) {
         const size_t sp = g.src_pitch ? g.src_pitch : g.len, dp = g.dst_pitch ? g.dst_pitch : g.len;
         for (size_t r = 0; r < g.rows; r++) memcpy(g.dst + r * dp, g.src + r * sp, g.len);
+    }
+    // The same for device -> pageable reads, whose destination is a large buffer of the caller that nobody reads back
+    // soon: non-temporal stores write whole lines without first reading them (no read-for-ownership: two thirds of a
+    // cached copy's memory traffic) and leave the caches to the ring.  Granules are 512 KiB, below the size at which
+    // the C library's memcpy switches to such stores by itself.  NLC_NT_STORES=0 turns it off.
+    static void stream_copy(char* d, const char* s, size_t n) {
+#if defined(__x86_64__) && defined(__SSE2__)
+        static const bool on = [] { const char* e = getenv("NLC_NT_STORES"); return !(e && atoi(e) == 0); }();
+        if (on && n >= 4096) {
+            const size_t head = (16 - ((uintptr_t)d & 15)) & 15;
+            memcpy(d, s, head);
+            d += head, s += head, n -= head;
+            const size_t lines = n / 64;
+            for (size_t i = 0; i < lines; i++, d += 64, s += 64) {
+                const __m128i a = _mm_loadu_si128((const __m128i*)s), b = _mm_loadu_si128((const __m128i*)(s + 16)),
+                              c = _mm_loadu_si128((const __m128i*)(s + 32)), e = _mm_loadu_si128((const __m128i*)(s + 48));
+                _mm_stream_si128((__m128i*)d, a);
+                _mm_stream_si128((__m128i*)(d + 16), b);
+                _mm_stream_si128((__m128i*)(d + 32), c);
+                _mm_stream_si128((__m128i*)(d + 48), e);
+            }
+            n -= lines * 64;
+            _mm_sfence();
+        }
+#endif
+        memcpy(d, s, n);
+    }
+    static void run_granule_out(const Granule& g) {
+        const size_t sp = g.src_pitch ? g.src_pitch : g.len, dp = g.dst_pitch ? g.dst_pitch : g.len;
+        for (size_t r = 0; r < g.rows; r++) stream_copy(g.dst + r * dp, g.src + r * sp, g.len);
     }
     std::vector<Granule> pending;
     CopyPool* pool = nullptr;
@@ -245,7 +279,7 @@ struct HostStager {
                 pending.push_back({(char*)dst + (first_of[tail] + o) * dst_pitch, (const char*)slot[tail] + o * row_bytes,
                                    row_bytes, k, 0, dst_pitch});
             }
-            pool->parallel_for(pending.size(), [&](size_t i) { run_granule(pending[i]); });
+            pool->parallel_for(pending.size(), [&](size_t i) { run_granule_out(pending[i]); });
             pending.clear();
             drained += rows_of[tail];
             tail = (tail + 1) % N_SLOTS;
@@ -298,7 +332,7 @@ struct HostStager {
                 seg_off += take;
                 if (seg_off == g.len) seg_i++, seg_off = 0;
             }
-            pool->parallel_for(pending.size(), [&](size_t i) { run_granule(pending[i]); });
+            pool->parallel_for(pending.size(), [&](size_t i) { run_granule_out(pending[i]); });
             pending.clear();
             drained += len_of[tail];
             tail = (tail + 1) % N_SLOTS;
