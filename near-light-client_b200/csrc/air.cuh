@@ -268,6 +268,14 @@ struct AirDevice {
         blocks = (n_points + AIR_THREADS - 1) / AIR_THREADS;
         const size_t full = (size_t)ctx->sm_count * ctas_per_sm;
         if (blocks > full) blocks = full;
+        // the scratch matrix is (n_regs + 1) x threads words: a program with very many live values runs on fewer CTAs
+        // (the kernels stride over the points) rather than on more memory -- at most NLC_AIR_SCRATCH_MB (default 8192),
+        // which also keeps every row offset of the lowered program inside 32 bits
+        const char* e = getenv("NLC_AIR_SCRATCH_MB");
+        const size_t budget_words = ((size_t)std::min<long>(std::max<long>(e ? atol(e) : 8192, 1), 16384) << 20) / sizeof(u64);
+        const size_t fit = budget_words / ((size_t)prog->n_regs + 1) / AIR_THREADS;
+        NLC_CHECK(fit >= 1, "AIR program: too many registers for the scratch budget (NLC_AIR_SCRATCH_MB)");
+        if (blocks > fit) blocks = fit;
         const size_t n_threads = blocks * AIR_THREADS;
         const size_t n_small = prog->n_pool + prog->n_public + prog->n_global + prog->n_challenge + n_alphas + n_extra;
         try {

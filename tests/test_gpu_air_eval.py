@@ -128,6 +128,34 @@ def test_bad_programs_are_rejected(P2, O, pkg, rng):
         S.StarkyProver.air_eval(st, [b], [], [0, 0, 0], [0, 1, 2], [5], 2)
 
 
+def test_wide_register_file_runs_on_fewer_ctas(P2, O, pkg, rng, monkeypatch):
+    """A program with thousands of live registers under a small scratch budget (NLC_AIR_SCRATCH_MB): the interpreter runs
+    fewer CTAs that stride over the points; same accumulators as the three-register program computing the same sums."""
+    S = pkg.starky
+    log_n, R = 14, 2000
+    b, _ = commit_both(P2, O, O.random_field(rng, (1 << log_n, 3)), 1, 2)
+    L, ADD, MULC, CON = S.OP["LOCAL"], S.OP["ADD"], S.OP["MUL_CONST"], S.OP["CONSTRAINT"]
+
+    def run(code, n_regs, pool=()):
+        prog = S.AirProgram(np.array(code, np.uint32).reshape(-1, 4), np.array(pool, np.uint64), n_regs, 0, 0, 0, 3, 1)
+        st = S.Starky(S.FibonacciAir())
+        st._program = prog
+        return S.StarkyProver.air_eval(st, [b], [], [], [], [5, 7], 0)
+    wide = [[L, i, i % 3, 0] for i in range(R)]                      # R live values ...
+    wide += [[ADD, R, 0, 1]] + [[ADD, R, R, i] for i in range(2, R)]  # ... summed into register R
+    wide += [[CON, 0, R, 0]]
+    counts = [len(range(c, R, 3)) for c in range(3)]
+    narrow = [[L, c, c, 0] for c in range(3)] + [[MULC, c, c, c] for c in range(3)]
+    narrow += [[ADD, 3, 0, 1], [ADD, 3, 3, 2], [CON, 0, 3, 0]]
+    want = run(narrow, 4, counts)
+    monkeypatch.setenv("NLC_AIR_SCRATCH_MB", "64")  # 2001 registers: 32 CTAs of 128 threads for 2^14 points
+    got = run(wide, R + 1)
+    assert got.shape == (1 << log_n, 2) and np.array_equal(got, want)
+    monkeypatch.setenv("NLC_AIR_SCRATCH_MB", "1")
+    with pytest.raises(pkg.NlcError, match="too many registers"):
+        run(wide, R + 1)
+
+
 def test_fibonacci_stark_proof_end_to_end(P2, O, pkg):
     """test_plonky2_fibonacci_stark (plonky2/stark/mod.rs:243-265) as the prover sees it: StarkyProver::prove on the
     GPU equals the same sequence driven through the oracle (commit, direct AIR evaluation, quotient commit, openings,
