@@ -706,6 +706,245 @@ class FpMulChip(RAirData):
 
 
 # ---------------------------------------------------------------------------------------------
+# chip/field/{inner_product,mul_const,den}.rs and chip/ec/edwards/add.rs: the ed25519 point addition gadget
+# ---------------------------------------------------------------------------------------------
+def _limbs(v: int, n: int = Fp25519.NB_LIMBS) -> list:
+    return [(v >> (16 * i)) & 0xFFFF for i in range(n)]
+
+
+def _field_witness(pr, van: list) -> dict:
+    """util.rs:48-84 compute_root_quotient_and_shift + split_u32_limbs_to_u16_limbs: vanishing(x) / (x - 2^16) shifted by
+    WITNESS_OFFSET, as low / high 16-bit limbs (the vanishing polynomial has integer coefficients, degree NB_WITNESS_LIMBS)."""
+    assert len(van) == 2 * pr.NB_LIMBS - 1
+    q = [0] * (len(van) - 1)
+    acc = 0
+    for i in range(len(van) - 1, 0, -1):
+        acc = van[i] + (acc << 16)
+        q[i - 1] = acc
+    assert van[0] + (q[0] << 16) == 0, "vanishing polynomial does not vanish at 2^16"
+    w = [x + pr.WITNESS_OFFSET for x in q]
+    assert all(0 <= x < 1 << 32 for x in w)
+    return {"witness_low": [x & 0xFFFF for x in w], "witness_high": [x >> 16 for x in w]}
+
+
+def _poly_int_mul(a: list, b: list) -> list:
+    out = [0] * (len(a) + len(b) - 1)
+    for i, x in enumerate(a):
+        for j, y in enumerate(b):
+            out[i + j] += x * y
+    return out
+
+
+def _finish_field_instruction(self, parser, p_lhs_minus_rhs):
+    """Common tail of the field instructions: - carry(x) p(x), then util.rs eval_field_operation."""
+    pr = self.params
+    p_limbs = constant_poly(parser, pr.MODULUS[:pr.NB_LIMBS])
+    p_carry = list(self.carry.eval_slice(parser))
+    p_vanishing = poly_sub(parser, p_lhs_minus_rhs, poly_mul(parser, p_carry, p_limbs))
+    eval_field_operation(parser, pr, p_vanishing, list(self.witness_low.eval_slice(parser)),
+                         list(self.witness_high.eval_slice(parser)))
+
+
+@dataclass
+class FpInnerProductInstruction:
+    """sum_i a_i b_i = result (mod p) (inner_product.rs:78-109)."""
+    a: list
+    b: list
+    result: MemorySlice
+    carry: MemorySlice
+    witness_low: MemorySlice
+    witness_high: MemorySlice
+    params: type = Fp25519
+
+    def eval(self, parser):
+        acc = [parser.zero()]  # parser.zero_poly()
+        for ra, rb in zip(self.a, self.b):
+            acc = poly_add(parser, acc, poly_mul(parser, list(ra.eval_slice(parser)), list(rb.eval_slice(parser))))
+        _finish_field_instruction(self, parser, poly_sub(parser, acc, list(self.result.eval_slice(parser))))
+
+    def write(self, a_ints: list, b_ints: list) -> dict:
+        pr = self.params
+        modulus = pr.modulus()
+        inner = sum(x * y for x, y in zip(a_ints, b_ints))
+        result = inner % modulus
+        carry = (inner - result) // modulus
+        assert carry < 2 * modulus
+        van = [0] * (2 * pr.NB_LIMBS - 1)
+        for x, y in zip(a_ints, b_ints):
+            for i, c in enumerate(_poly_int_mul(_limbs(x), _limbs(y))):
+                van[i] += c
+        for i, c in enumerate(_poly_int_mul(_limbs(carry), _limbs(modulus))):
+            van[i] -= c
+        for i, c in enumerate(_limbs(result)):
+            van[i] -= c
+        return {"value": result, "result": _limbs(result), "carry": _limbs(carry), **_field_witness(pr, van)}
+
+
+@dataclass
+class FpMulConstInstruction:
+    """a * c = result (mod p) with c a constant in 16-bit limbs (mul_const.rs:75-103)."""
+    a: MemorySlice
+    c: list
+    result: MemorySlice
+    carry: MemorySlice
+    witness_low: MemorySlice
+    witness_high: MemorySlice
+    params: type = Fp25519
+
+    def eval(self, parser):
+        p_a_mul_c = poly_mul_poly_const(parser, list(self.a.eval_slice(parser)), self.c[:self.params.NB_LIMBS])
+        _finish_field_instruction(self, parser, poly_sub(parser, p_a_mul_c, list(self.result.eval_slice(parser))))
+
+    def write(self, a_int: int) -> dict:
+        pr = self.params
+        modulus = pr.modulus()
+        c_int = sum(limb << (16 * i) for i, limb in enumerate(self.c))
+        result = a_int * c_int % modulus
+        carry = (a_int * c_int - result) // modulus
+        van = _poly_int_mul(_limbs(a_int), _limbs(c_int))
+        for i, c in enumerate(_poly_int_mul(_limbs(carry), _limbs(modulus))):
+            van[i] -= c
+        for i, c in enumerate(_limbs(result)):
+            van[i] -= c
+        return {"value": result, "result": _limbs(result), "carry": _limbs(carry), **_field_witness(pr, van)}
+
+
+@dataclass
+class FpDenInstruction:
+    """result = a / (1 + b) (sign) or a / (1 - b): only result * denominator = a (mod p) is constrained (den.rs:84-117)."""
+    a: MemorySlice
+    b: MemorySlice
+    sign: bool
+    result: MemorySlice
+    carry: MemorySlice
+    witness_low: MemorySlice
+    witness_high: MemorySlice
+    params: type = Fp25519
+
+    def eval(self, parser):
+        p_a, p_b = list(self.a.eval_slice(parser)), list(self.b.eval_slice(parser))
+        p_result = list(self.result.eval_slice(parser))
+        p_b_times_res = poly_mul(parser, p_b, p_result)
+        lhs = poly_add(parser, p_b_times_res, p_result if self.sign else p_a)
+        rhs = p_a if self.sign else p_result
+        _finish_field_instruction(self, parser, poly_sub(parser, lhs, rhs))
+
+    def write(self, a_int: int, b_int: int) -> dict:
+        pr = self.params
+        p = pr.modulus()
+        denominator = ((b_int if self.sign else p - b_int) + 1) % p
+        result = a_int * pow(denominator, p - 2, p) % p
+        lhs = b_int * result + (result if self.sign else a_int)
+        rhs = a_int if self.sign else result
+        carry = (lhs - rhs) // p
+        assert carry * p == lhs - rhs and 0 <= carry < p
+        van = _poly_int_mul(_limbs(b_int), _limbs(result))
+        plus, minus = (_limbs(result), _limbs(a_int)) if self.sign else (_limbs(a_int), _limbs(result))
+        for i in range(pr.NB_LIMBS):
+            van[i] += plus[i] - minus[i]
+        for i, c in enumerate(_poly_int_mul(_limbs(carry), _limbs(p))):
+            van[i] -= c
+        return {"value": result, "result": _limbs(result), "carry": _limbs(carry), **_field_witness(pr, van)}
+
+
+class Ed25519:
+    """chip/ec/edwards/ed25519/params.rs:44-75."""
+    D = [30883, 4953, 19914, 30187, 55467, 16705, 2637, 112, 59544, 30585, 16505, 36039, 65139, 11119, 27886, 20995]
+    GENERATOR = (15112221349535400772501151409588531511454012693041857206046113283949847762202,
+                 46316835694926478169428394003475163141307993866256225615783033603165251855960)
+
+    @classmethod
+    def d(cls) -> int:
+        return sum(limb << (16 * i) for i, limb in enumerate(cls.D))
+
+    @classmethod
+    def add(cls, pt, qt):
+        """Affine twisted-Edwards addition (a = -1) over the integers mod 2^255 - 19."""
+        p = Fp25519.modulus()
+        (x1, y1), (x2, y2) = pt, qt
+        f = cls.d() * x1 * x2 % p * y1 * y2 % p
+        x3 = (x1 * y2 + x2 * y1) * pow(1 + f, p - 2, p) % p
+        y3 = (y1 * y2 + x1 * x2) * pow(1 - f, p - 2, p) % p
+        return x3, y3
+
+
+class EdAddChip(RAirData):
+    """AirBuilder::ed_add (chip/ec/edwards/add.rs:8-54) as a Chip of its eight field instructions on one row: the point
+    addition every step of the ed25519 scalar multiplication and signature check is made of.
+        x3_numerator = <(x1, x2), (y2, y1)>, y3_numerator = <(y1, x1), (y2, x2)>      (fp_inner_product)
+        f = (x1 y1)(x2 y2), d f                                                         (3 fp_mul, fp_mul_const)
+        x3 = x3_numerator / (1 + d f), y3 = y3_numerator / (1 - d f)                    (2 fp_den)
+    Columns: x1 | y1 | x2 | y2 (4 x 16) and per instruction result | carry | witness_low | witness_high (16 + 16 + 30 + 30):
+    800 = NUM_ARITHMETIC_COLUMNS of add.rs `Ed25519AddTest`; 8 x 31 = 248 constraints of degree 2.  (The 16-bit range
+    checks of those columns are starkyx's lookup argument, outside this chip, as for FpMulChip.)"""
+
+    def __init__(self):
+        L, Wn = Fp25519.NB_LIMBS, Fp25519.NB_WITNESS_LIMBS
+        self._o = 0
+
+        def alloc(n):
+            m = MemorySlice("Local", self._o, n)
+            self._o += n
+            return m
+        self.x1, self.y1, self.x2, self.y2 = alloc(L), alloc(L), alloc(L), alloc(L)
+        out = lambda: (alloc(L), alloc(L), alloc(Wn), alloc(Wn))
+        x1, y1, x2, y2 = self.x1, self.y1, self.x2, self.y2
+        self.x3_num = FpInnerProductInstruction([x1, x2], [y2, y1], *out())
+        self.y3_num = FpInnerProductInstruction([y1, x1], [y2, x2], *out())
+        self.x1y1 = FpMulInstruction(x1, y1, *out())
+        self.x2y2 = FpMulInstruction(x2, y2, *out())
+        self.f = FpMulInstruction(self.x1y1.result, self.x2y2.result, *out())
+        self.df = FpMulConstInstruction(self.f.result, list(Ed25519.D), *out())
+        self.x3 = FpDenInstruction(self.x3_num.result, self.df.result, True, *out())
+        self.y3 = FpDenInstruction(self.y3_num.result, self.df.result, False, *out())
+        self.instructions = [self.x3_num, self.y3_num, self.x1y1, self.x2y2, self.f, self.df, self.x3, self.y3]
+        self._width = self._o
+
+    def constraint_degree(self):
+        return 2
+
+    def width(self):
+        return self._width
+
+    def eval(self, parser):
+        for ins in self.instructions:
+            ins.eval(parser)
+
+    def eval_global(self, parser):
+        pass
+
+    def write_row(self, pt, qt) -> list:
+        (x1, y1), (x2, y2) = pt, qt
+        w = [self.x3_num.write([x1, x2], [y2, y1]), self.y3_num.write([y1, x1], [y2, x2]), self.x1y1.write(x1, y1),
+             self.x2y2.write(x2, y2)]
+        a, b = x1 * y1 % Fp25519.modulus(), x2 * y2 % Fp25519.modulus()
+        w.append(self.f.write(a, b))
+        f = a * b % Fp25519.modulus()
+        w.append(self.df.write(f))
+        w.append(self.x3.write(w[0]["value"], w[5]["value"]))
+        w.append(self.y3.write(w[1]["value"], w[5]["value"]))
+        assert (w[6]["value"], w[7]["value"]) == Ed25519.add(pt, qt), "the gadget's witness is not the curve's sum"
+        row = _limbs(x1) + _limbs(y1) + _limbs(x2) + _limbs(y2)
+        for d in w:
+            row += d["result"] + d["carry"] + d["witness_low"] + d["witness_high"]
+        return row
+
+    def generate_trace(self, rng, num_rows: int) -> np.ndarray:
+        """Row-major AirTrace (num_rows x 800): row r adds two multiples of the base point (add.rs test_ed25519_add
+        writes a G + b G on every row; here the multiples walk along, so that the rows differ)."""
+        rows = np.zeros((num_rows, self._width), np.uint64)
+        g = Ed25519.GENERATOR
+        pt = g
+        for _ in range(int(rng.integers(1, 64))):
+            pt = Ed25519.add(pt, g)
+        qt = Ed25519.add(pt, pt)
+        for r in range(num_rows):
+            rows[r] = self.write_row(pt, qt)
+            pt, qt = Ed25519.add(pt, g), Ed25519.add(qt, pt)
+        return rows
+
+
+# ---------------------------------------------------------------------------------------------
 # plonky2/stark: config, opening set, prover
 # ---------------------------------------------------------------------------------------------
 @dataclass

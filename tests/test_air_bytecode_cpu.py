@@ -164,6 +164,45 @@ def test_fpmul_chip_bytecode_matches_direct(O, pkg, rng):
     assert q.shape == (16, 1)
 
 
+class _EveryConstraint:
+    """A consumer that keeps each constraint's values instead of folding them."""
+
+    def __init__(self, n):
+        self.n, self.values = n, []
+
+    def constraint(self, c):
+        self.values.append(np.array(c, copy=True))
+
+    constraint_transition = constraint_first_row = constraint_last_row = constraint
+
+
+def test_ed_add_chip_bytecode_matches_direct(O, pkg, rng):
+    """The ed25519 point-addition gadget (chip/ec/edwards/add.rs): 800 columns, 8 field instructions, 248 constraints."""
+    from oracle import air as OA
+    S = pkg.starky
+    chip = S.EdAddChip()
+    trace = chip.generate_trace(rng, 1 << 4)
+    assert chip.width() == 800 and trace.max() < 1 << 16
+    # the witness is right: every constraint vanishes on every trace row (and stops vanishing when a limb is changed)
+    def constraint_values(rows):
+        cons = _EveryConstraint(rows.shape[0])
+        chip.eval(OA.StarkParser([np.ascontiguousarray(rows[:, j]) for j in range(rows.shape[1])], None, [], [], [], cons))
+        return cons.values
+    vals = constraint_values(trace)
+    assert len(vals) == 248 and not any(v.any() for v in vals)
+    bad = trace.copy()
+    bad[3, chip.x3.result.index + 5] ^= 1
+    assert any(v[3] != 0 for v in constraint_values(bad)) and not any(v[2] != 0 for v in constraint_values(bad))
+    # x3 | y3 of every row is the curve's sum of the row's two points
+    val = lambda row, m: sum(int(row[m.index + i]) << (16 * i) for i in range(m.length))
+    for row in trace[:4]:
+        want = S.Ed25519.add((val(row, chip.x1), val(row, chip.y1)), (val(row, chip.x2), val(row, chip.y2)))
+        assert (val(row, chip.x3.result), val(row, chip.y3.result)) == want
+    want, got, prog = direct_and_bytecode(O, OA, S, chip, 4, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
+    assert np.array_equal(want, got)
+    assert prog.n_constraints == 248 and prog.n_regs < 256
+
+
 @pytest.mark.parametrize("seed", range(6))
 def test_random_expression_trees(O, pkg, seed):
     from oracle import air as OA

@@ -78,6 +78,23 @@ def test_fpmul_chip(P2, O, pkg, rng, log_n):
     assert np.array_equal(q.coeff_matrix, qref.coeffs)
 
 
+@pytest.mark.parametrize("log_n", [5, 14])
+def test_ed_add_chip(P2, O, pkg, rng, log_n):
+    """The ed25519 point-addition gadget (chip/ec/edwards/add.rs ed_add: two inner products, three products, a product
+    with the curve constant d, two divisions): 800 columns, 248 degree-2 constraints, valid traces."""
+    S = pkg.starky
+    chip = S.EdAddChip()
+    n = 1 << log_n
+    base = chip.generate_trace(rng, min(n, 1 << 6))
+    trace = np.ascontiguousarray(np.tile(base, (n // base.shape[0], 1)))  # rows are independent: repetition stays valid
+    alphas = O.random_field(rng, (2,)).tolist()
+    stark, gb, rb, qref = check_air(P2, O, S, chip, log_n, 1, 4, [trace], [], [], [], alphas)
+    cfg = S.StarkyConfig.standard_fast_config(n)
+    q = S.StarkyProver.quotient_commitment(stark, cfg, gb, [], [], [], FixedChallenger(alphas))
+    assert np.array_equal(q.merkle_tree.cap, qref.cap)
+    assert np.array_equal(q.coeff_matrix, qref.coeffs)
+
+
 @pytest.mark.parametrize("seed,degree,rate_bits", [(0, 3, 2), (1, 3, 1), (2, 4, 2), (3, 2, 1), (4, 5, 3)])
 def test_random_constraint_lists(P2, O, pkg, seed, degree, rate_bits):
     """Every opcode, every MemorySlice kind, two trace commitments concatenated (prover.rs:289-294), 1..3 alphas,
