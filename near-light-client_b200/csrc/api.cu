@@ -128,8 +128,17 @@ void dl_segments(nlc_ctx* ctx, const u64* src, const std::vector<HostStager::Seg
         NLC_CUDA(cudaStreamSynchronize(ctx->dl_stream));
     }
 }
+// A row-major host matrix as the source of a commit (starkyx's AirTrace, trace/mod.rs:19-24): columns
+// [col0, col0 + W) of `rows` (n x width).  Chunk c of the pipeline below is then the [c0, c0 + nc) strip of EVERY row:
+// it crosses PCIe as n pieces of nc words (gathered into the pinned ring by the host copy threads when the matrix is
+// pageable, a 2-D DMA otherwise) and one transpose pass on the compute stream turns it into nc columns.
+struct RowSource {
+    const u64* rows;
+    size_t width, col0;
+};
 int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int rate_bits, int cap_height,
-                bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0, const Materialise* mat = nullptr) {
+                bool is_values, nlc_batch** out, int shard_log = 0, size_t shard_idx = 0, const Materialise* mat = nullptr,
+                const RowSource* rs = nullptr) {
     if (!ctx) return 1;
     return nlc_guarded(ctx, [&] {
         CtxGuard g(ctx);
@@ -167,6 +176,19 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             const size_t N = b->n_local();
             DevBuf vals(ctx, is_values ? W * n : 1);
             DevBuf sponge(ctx, stream_hash ? 12 * N : 1);
+            // the chunk sequence (also used below): 16 columns first, then growing
+            auto next_chunk = [&](size_t c0, size_t prev) {
+                size_t want = chunk;
+                if (stream_hash) want = c0 == 0 ? 16 : std::min(chunk_cap, rate_bits >= 2 ? 3 * prev : (prev * 3 / 2 + 7) / 8 * 8);
+                size_t nc = W - c0 < want ? W - c0 : want;
+                if (stream_hash && W - c0 - nc < 16) nc = W - c0; // no tiny last chunk
+                return nc;
+            };
+            size_t max_nc = 0;
+            for (size_t c0 = 0, nc = 0; rs && c0 < W; c0 += nc) max_nc = std::max(max_nc, nc = next_chunk(c0, nc));
+            DevBuf strip0(ctx, rs ? n * max_nc : 1), strip1(ctx, rs ? n * max_nc : 1); // row-major strips, alternating
+            const bool rows_pageable = rs && HostStager::pageable(rs->rows);
+            std::vector<cudaEvent_t> transposed;
             if (want_leaves) slab = ctx->dmalloc(N * W); // row-major image of the LDE, freed once it is on the host
             // jobs for the downloader thread (it owns dl_stream): after `ev`, drain one piece
             auto after_compute = [&]() {
@@ -215,23 +237,35 @@ int commit_host(nlc_ctx* ctx, const u64* const* cols, size_t W, int log_n, int r
             u64* stage = is_values ? vals.p : b->coeffs;
             NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream)); // buffers allocated on the compute stream
             NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
-            NLC_CHECK(cols != nullptr, "null column table");
-            for (size_t j = 0; j < W; j++) NLC_CHECK(cols[j] != nullptr, "null column pointer"); // before any upload is issued
-            std::vector<cudaEvent_t> evs;
-            for (size_t c0 = 0, nc = 0; c0 < W; c0 += nc) {
-                size_t want = chunk;
-                if (stream_hash) want = c0 == 0 ? 16 : std::min(chunk_cap, rate_bits >= 2 ? 3 * nc : (nc * 3 / 2 + 7) / 8 * 8);
-                nc = W - c0 < want ? W - c0 : want;
-                if (stream_hash && W - c0 - nc < 16) nc = W - c0; // no tiny last chunk
-                for (size_t j = c0; j < c0 + nc; j++) {
-                    NLC_CHECK(cols[j] != nullptr, "null column pointer");
-                    h2d_on(ctx, ctx->copy_stream, stage + j * n, cols[j], n * sizeof(u64), false);
-                }
+            NLC_CHECK(rs || cols != nullptr, "null column table");
+            for (size_t j = 0; !rs && j < W; j++) NLC_CHECK(cols[j] != nullptr, "null column pointer"); // before any upload is issued
+            size_t n_ev = 0;
+            for (size_t c0 = 0, nc = 0, k = 0; c0 < W; c0 += nc, k++) {
+                nc = next_chunk(c0, nc);
+                u64* strip = k & 1 ? strip1.p : strip0.p;
+                if (rs) {
+                    // the transpose that last read this strip buffer must be done before it is overwritten
+                    if (k >= 2) NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, transposed[k - 2], 0));
+                    const u64* src = rs->rows + rs->col0 + c0;
+                    if (rows_pageable)
+                        ctx->stager.upload_rows(ctx->copy_stream, strip, src, rs->width * sizeof(u64), nc * sizeof(u64), n);
+                    else
+                        NLC_CUDA(cudaMemcpy2DAsync(strip, nc * sizeof(u64), src, rs->width * sizeof(u64), nc * sizeof(u64), n,
+                                                   cudaMemcpyHostToDevice, ctx->copy_stream));
+                } else
+                    for (size_t j = c0; j < c0 + nc; j++) {
+                        NLC_CHECK(cols[j] != nullptr, "null column pointer");
+                        h2d_on(ctx, ctx->copy_stream, stage + j * n, cols[j], n * sizeof(u64), false);
+                    }
                 ctx->stager.flush(ctx->copy_stream);
-                cudaEvent_t e = ctx->chunk_event(evs.size());
-                evs.push_back(e);
+                cudaEvent_t e = ctx->chunk_event(n_ev++);
                 NLC_CUDA(cudaEventRecord(e, ctx->copy_stream));
                 NLC_CUDA(cudaStreamWaitEvent(ctx->stream, e, 0));
+                if (rs) {
+                    transpose_trace_cols(ctx, strip, nc, 0, nc, n, stage + c0 * n, n);
+                    transposed.push_back(ctx->chunk_event(n_ev++));
+                    NLC_CUDA(cudaEventRecord(transposed.back(), ctx->stream));
+                }
                 if (is_values) batch_ifft_cols(b, vals.p + c0 * n, c0, nc);
                 dl_coeffs(c0, nc); // the coefficients of this chunk cross PCIe while later chunks compute
                 batch_lde_cols(b, c0, nc);
@@ -608,52 +642,19 @@ int nlc_batch_shard(const nlc_batch* b, size_t* shard_idx, size_t* n_shards) {
 int nlc_commit_from_trace_rows(nlc_ctx* ctx, const uint64_t* rows, size_t width, size_t col0, size_t n_cols, int log_n,
                                int rate_bits, int cap_height, nlc_batch** out) {
     if (!ctx) return 1;
-    return nlc_guarded(ctx, [&] {
-        CtxGuard g(ctx);
+    const int rc = nlc_guarded(ctx, [&] {
         NLC_CHECK(out && rows, "null argument");
         *out = nullptr;
         NLC_CHECK(n_cols > 0 && col0 + n_cols <= width, "column range outside the trace");
         NLC_CHECK(log_n >= 0 && log_n <= 32, "bad shape");
-        const size_t n = (size_t)1 << log_n;
-        // Only the [col0, col0 + n_cols) strip of each row crosses PCIe (ed25519: 1 651 of 4 153 columns), in row
-        // chunks on the copy stream; the compute stream transposes chunk k into the column-major value matrix while
-        // chunk k+1 uploads.  Two strip buffers alternate.
-        size_t chunk_rows = ((size_t)32 << 20) / (n_cols * sizeof(u64)); // ~32 MiB per chunk
-        chunk_rows = std::max<size_t>(chunk_rows / 32 * 32, 32);
-        if (chunk_rows > n) chunk_rows = n;
-        DevBuf strip0(ctx, chunk_rows * n_cols), strip1(ctx, chunk_rows * n_cols), vals(ctx, n * n_cols);
-        u64* strip[2] = {strip0.p, strip1.p};
-        const bool pageable = HostStager::pageable(rows);
-        try {
-            NLC_CUDA(cudaEventRecord(ctx->ev_ready, ctx->stream));
-            NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_ready, 0));
-            size_t k = 0;
-            for (size_t r0 = 0; r0 < n; r0 += chunk_rows, k++) {
-                const size_t nr = n - r0 < chunk_rows ? n - r0 : chunk_rows;
-                if (k >= 2) // the transpose that last read this strip buffer must be done before it is overwritten
-                    NLC_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->chunk_event(2 * (k - 2) + 1), 0));
-                const u64* src = rows + r0 * width + col0;
-                if (pageable) {
-                    ctx->stager.upload_rows(ctx->copy_stream, strip[k & 1], src, width * sizeof(u64), n_cols * sizeof(u64), nr);
-                    ctx->stager.flush(ctx->copy_stream);
-                } else {
-                    NLC_CUDA(cudaMemcpy2DAsync(strip[k & 1], n_cols * sizeof(u64), src, width * sizeof(u64),
-                                               n_cols * sizeof(u64), nr, cudaMemcpyHostToDevice, ctx->copy_stream));
-                }
-                NLC_CUDA(cudaEventRecord(ctx->chunk_event(2 * k), ctx->copy_stream));
-                NLC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_event(2 * k), 0));
-                transpose_trace_cols(ctx, strip[k & 1], n_cols, 0, n_cols, nr, vals.p + r0, n);
-                NLC_CUDA(cudaEventRecord(ctx->chunk_event(2 * k + 1), ctx->stream));
-            }
-            *out = commit_dev(ctx, vals.p, true, n_cols, log_n, rate_bits, cap_height);
-            sync(ctx);
-        } catch (...) {
-            ctx->stager.abandon();
-            cudaStreamSynchronize(ctx->copy_stream);
-            cudaStreamSynchronize(ctx->stream);
-            throw;
-        }
     });
+    if (rc) return rc;
+    // Only the [col0, col0 + n_cols) strip of each row crosses PCIe (ed25519: 1 651 of 4 153 columns), and it does so in
+    // COLUMN chunks through the pipeline of commit_host: while chunk c+1 uploads, chunk c is transposed, inverse-
+    // transformed, extended and absorbed by the leaf sponge -- the commit of a wide trace ends one chunk after its upload
+    // instead of a whole commit after it (2^16 x 800 from pageable rows: ~32 -> ~20 ms).
+    const RowSource rs{rows, width, col0};
+    return commit_host(ctx, nullptr, n_cols, log_n, rate_bits, cap_height, true, out, 0, 0, nullptr, &rs);
 }
 
 // SURVEY.md section 5 "checkpoint / resume": a PolynomialBatch that was built earlier and serialised (circuit data:
