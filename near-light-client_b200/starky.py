@@ -945,6 +945,97 @@ class EdAddChip(RAirData):
 
 
 # ---------------------------------------------------------------------------------------------
+# chip/instruction/{cycle,bit}.rs and chip/ec/scalar.rs: the control columns of the ed25519 scalar multiplication
+# ---------------------------------------------------------------------------------------------
+def _bit_constraint(parser, m: MemorySlice):
+    """instruction/bit.rs:14-28: b (b - 1) = 0 for every cell of the slice (what alloc::<BitRegister>() registers)."""
+    for bit in m.eval_slice(parser):
+        parser.constraint(parser.mul(bit, parser.sub_const(bit, 1)))
+
+
+class ScalarBitsChip(RAirData):
+    """The row-to-row machinery of `scalar_mul_batch` (machine/ec/builder.rs:61-190) around the curve arithmetic: a
+    cycle of 32 rows (`AirBuilder::cycle(5)`, instruction/cycle.rs:48-170: a walk through the 32nd roots of unity with
+    start / end bits pinned by inverse witnesses), the process id counting finished cycles (cycle.rs:239-250) and the
+    little-endian bit decomposition of one 32-bit scalar limb per cycle (`bit_decomposition`, ec/scalar.rs:43-107).
+    In the reference the limb arrives over the memory bus; here it is a column.  Every kind of constraint (plain, first
+    row, transition) and real `next` reads: 9 columns, 14 constraints of degree 2."""
+    LOG = 5
+
+    def __init__(self):
+        cell = lambda i: MemorySlice("Local", i, 1)
+        (self.start_bit, self.end_bit, self.element, self.start_bit_witness, self.end_bit_witness, self.process_id, self.limb,
+         self.bit_accumulator, self.bit) = [cell(i) for i in range(9)]
+        g = pow(1753635133440165772, 1 << (32 - self.LOG), P)
+        self.group = [pow(g, i, P) for i in range(1 << self.LOG)]
+
+    def constraint_degree(self):
+        return 2
+
+    def width(self):
+        return 9
+
+    def eval(self, parser):
+        v = lambda m: m.eval_slice(parser)[0]
+        _bit_constraint(parser, self.start_bit)
+        _bit_constraint(parser, self.end_bit)
+        # Cycle::eval (cycle.rs:117-170)
+        element = v(self.element)
+        parser.constraint_first_row(parser.sub_const(element, 1))
+        generator, generator_inv = self.group[1], self.group[-1]
+        parser.constraint_transition(parser.sub(v(self.element.next()), parser.mul_const(element, generator)))
+        start_bit = v(self.start_bit)
+        elem_minus_one = parser.sub_const(element, 1)
+        parser.constraint(parser.mul(start_bit, elem_minus_one))
+        w = parser.mul(parser.add(elem_minus_one, start_bit), v(self.start_bit_witness))
+        parser.constraint(parser.sub_const(w, 1))
+        end_bit = v(self.end_bit)
+        elem_minus_gen_inv = parser.sub_const(element, generator_inv)
+        parser.constraint(parser.mul(end_bit, elem_minus_gen_inv))
+        w = parser.mul(parser.add(elem_minus_gen_inv, parser.mul_const(end_bit, generator_inv)), v(self.end_bit_witness))
+        parser.constraint(parser.sub_const(w, 1))
+        # ProcessIdInstruction::eval (cycle.rs:239-250)
+        process_id = v(self.process_id)
+        parser.constraint_first_row(process_id)
+        parser.constraint_transition(parser.sub(parser.sub(v(self.process_id.next()), process_id), end_bit))
+        # LimbBitInstruction::eval (ec/scalar.rs:69-107)
+        _bit_constraint(parser, self.bit)
+        bit_accumulator, bit = v(self.bit_accumulator), v(self.bit)
+        parser.constraint(parser.mul(start_bit, parser.sub(bit_accumulator, v(self.limb))))
+        not_end_bit = parser.sub(parser.one(), end_bit)
+        t = parser.mul_const(v(self.bit_accumulator.next()), 2)
+        t = parser.add(parser.sub(t, bit_accumulator), bit)
+        parser.constraint_transition(parser.mul(not_end_bit, t))
+        parser.constraint(parser.mul(end_bit, parser.sub(bit_accumulator, bit)))
+
+    def eval_global(self, parser):
+        pass
+
+    def generate_trace(self, rng, num_rows: int) -> np.ndarray:
+        """Cycle::write, ProcessIdInstruction::write, LimbBitInstruction::write for random 32-bit limbs."""
+        size = 1 << self.LOG
+        assert num_rows % size == 0
+        rows = np.zeros((num_rows, 9), np.uint64)
+        inv = lambda x: pow(x % P, P - 2, P)
+        gen_inverse = self.group[-1]
+        acc = limb = 0
+        for r in range(num_rows):
+            c = r % size
+            element = self.group[c]
+            if c == 0:
+                limb = acc = int(rng.integers(0, 1 << 32))
+                sb, eb, sbw, ebw = 1, 0, inv(element), inv(element - gen_inverse)
+            elif c == size - 1:
+                sb, eb, sbw, ebw = 0, 1, inv(element - 1), inv(element)
+            else:
+                sb, eb, sbw, ebw = 0, 0, inv(element - 1), inv(element - gen_inverse)
+            bit = (limb >> c) & 1
+            rows[r] = [sb, eb, element, sbw, ebw, r // size, limb, acc, bit]
+            acc = (acc - bit) // 2
+        return rows
+
+
+# ---------------------------------------------------------------------------------------------
 # plonky2/stark: config, opening set, prover
 # ---------------------------------------------------------------------------------------------
 @dataclass

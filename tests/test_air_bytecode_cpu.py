@@ -165,15 +165,26 @@ def test_fpmul_chip_bytecode_matches_direct(O, pkg, rng):
 
 
 class _EveryConstraint:
-    """A consumer that keeps each constraint's values instead of folding them."""
+    """A consumer that keeps each constraint's values (and its kind) instead of folding them."""
 
     def __init__(self, n):
-        self.n, self.values = n, []
+        self.n, self.values, self.kinds = n, [], []
+
+    def _keep(self, kind, c):
+        self.values.append(np.array(c, copy=True))
+        self.kinds.append(kind)
 
     def constraint(self, c):
-        self.values.append(np.array(c, copy=True))
+        self._keep("all", c)
 
-    constraint_transition = constraint_first_row = constraint_last_row = constraint
+    def constraint_transition(self, c):
+        self._keep("transition", c)
+
+    def constraint_first_row(self, c):
+        self._keep("first", c)
+
+    def constraint_last_row(self, c):
+        self._keep("last", c)
 
 
 def test_ed_add_chip_bytecode_matches_direct(O, pkg, rng):
@@ -201,6 +212,38 @@ def test_ed_add_chip_bytecode_matches_direct(O, pkg, rng):
     want, got, prog = direct_and_bytecode(O, OA, S, chip, 4, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
     assert np.array_equal(want, got)
     assert prog.n_constraints == 248 and prog.n_regs < 256
+
+
+def test_scalar_bits_chip(O, pkg, rng):
+    """The control columns of scalar_mul_batch (cycle of 32, process id, bit decomposition of a limb): the generated
+    trace satisfies every constraint where it applies -- plain ones on every row, transitions on all rows but the last
+    (the window (row, row + 1)), first-row ones on row 0 -- a flipped bit breaks them, and the bytecode equals the AIR."""
+    from oracle import air as OA
+    S = pkg.starky
+    chip = S.ScalarBitsChip()
+    trace = chip.generate_trace(rng, 1 << 7)
+
+    def violations(rows):
+        n = rows.shape[0]
+        cons = _EveryConstraint(n)
+        loc = [np.ascontiguousarray(rows[:, j]) for j in range(rows.shape[1])]
+        nxt = [np.roll(c, -1) for c in loc]
+        chip.eval(OA.StarkParser(loc, nxt, [], [], [], cons))
+        bad = 0
+        for kind, v in zip(cons.kinds, cons.values):
+            bad += int(v[:-1].any()) if kind == "transition" else int(v[0] != 0) if kind == "first" else int(v.any())
+        return bad, cons.kinds
+    bad, kinds = violations(trace)
+    assert bad == 0 and len(kinds) == 14 and kinds.count("transition") == 3 and kinds.count("first") == 2
+    # the bits of every cycle are the limb's
+    for c in range(4):
+        limb = int(trace[32 * c, chip.limb.index])
+        assert sum(int(trace[32 * c + i, chip.bit.index]) << i for i in range(32)) == limb
+    flipped = trace.copy()
+    flipped[40, chip.bit.index] ^= 1
+    assert violations(flipped)[0] > 0
+    want, got, prog = direct_and_bytecode(O, OA, S, chip, 7, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
+    assert np.array_equal(want, got) and prog.n_constraints == 14
 
 
 @pytest.mark.parametrize("seed", range(6))

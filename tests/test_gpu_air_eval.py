@@ -95,6 +95,47 @@ def test_ed_add_chip(P2, O, pkg, rng, log_n):
     assert np.array_equal(q.coeff_matrix, qref.coeffs)
 
 
+@pytest.mark.parametrize("log_n", [5, 13])
+def test_scalar_bits_chip_proof(P2, O, pkg, rng, log_n):
+    """The control columns of the ed25519 scalar multiplication (instruction/cycle.rs, ec/scalar.rs: cycle of 32 rows,
+    process id, bit decomposition): first-row, transition and plain constraints with real `next` reads.  Accumulators
+    and quotient commitment against the oracle, then the whole proof: the quotient exists (the trace is valid), the
+    proof equals the oracle-driven one and the restated FRI verifier accepts it."""
+    from oracle import air as OA
+    S = pkg.starky
+    chip = S.ScalarBitsChip()
+    n = 1 << log_n
+    trace = chip.generate_trace(rng, n)
+    alphas = O.random_field(rng, (2,)).tolist()
+    stark, gb, rb, qref = check_air(P2, O, S, chip, log_n, 1, 4, [trace], [], [], [], alphas)
+    cfg = S.StarkyConfig.standard_fast_config(n)
+    fc = cfg.fri_config
+    proof = S.StarkyProver.prove(cfg, stark, trace, [])
+    ch = O.Challenger()
+    ch.observe_elements([])
+    tref = O.commit_from_values(np.ascontiguousarray(trace.T), fc.rate_bits, fc.cap_height)
+    ch.observe_cap(tref.cap)
+    al = ch.get_n_challenges(cfg.num_challenges)
+    qv = OA.quotient_values(chip, [tref], [], [], [], al, log_n, fc.rate_bits)
+    q2 = O.quotient_commit(qv, log_n, 0, 1, False, fc.rate_bits, fc.cap_height)  # raises when Z_H does not divide
+    assert np.array_equal(proof.trace_caps[0], tref.cap) and np.array_equal(proof.quotient_polys_cap, q2.cap)
+    ch.observe_cap(q2.cap)
+    zeta = ch.get_extension_challenge()
+    g = pow(G32, 1 << (32 - log_n), P)
+    zeta_next = (zeta[0] * g % P, zeta[1] * g % P)
+    ev = lambda b, z: [O.eval_poly_ext(c, np.array(z, np.uint64)) for c in b.coeffs]
+    local, nxt, quot = ev(tref, zeta), ev(tref, zeta_next), ev(q2, zeta)
+    for batch in (local + quot, nxt):
+        ch.observe_elements([c for e in batch for c in e])
+    ch_for_verifier = ch.clone()
+    params = O.fri_params(log_n, fc.rate_bits, fc.cap_height, fc.proof_of_work_bits, fc.num_query_rounds, 4, 5)
+    W, Q = chip.width(), q2.coeffs.shape[0]
+    inst = O.FriInstance([(zeta, [(0, i) for i in range(W)] + [(1, i) for i in range(Q)]), (zeta_next, [(0, i) for i in range(W)])])
+    oproof = O.prove_openings(inst, [tref, q2], ch, params)
+    assert np.array_equal(proof.opening_proof.flat, oproof)
+    assert O.fri_verify(inst, local + quot + nxt, [tref, q2], ch_for_verifier, params, oproof) == 0
+
+
 @pytest.mark.parametrize("seed,degree,rate_bits", [(0, 3, 2), (1, 3, 1), (2, 4, 2), (3, 2, 1), (4, 5, 3)])
 def test_random_constraint_lists(P2, O, pkg, seed, degree, rate_bits):
     """Every opcode, every MemorySlice kind, two trace commitments concatenated (prover.rs:289-294), 1..3 alphas,
