@@ -245,9 +245,10 @@ def run_replay_workload(args):
 
 
 def run_stark_proof(args):
-    """--workload stark_proof_fpmul | stark_proof_ed_add: ONE WHOLE starky proof (prover.rs:50-225) of a field-arithmetic
+    """--workload stark_proof_fpmul | stark_proof_ed_add | stark_proof_ed_scalar_mul: ONE WHOLE starky proof (prover.rs:50-225) of a field-arithmetic
     chip (chip/field/mul.rs FpMulInstruction<Fp25519>: 124 columns, 31 degree-2 constraints) or of the ed25519
-    point-addition gadget (chip/ec/edwards/add.rs: 800 columns, 248 constraints) at 2^16 rows under
+    point-addition gadget (chip/ec/edwards/add.rs: 800 columns, 248 constraints) or of the ed25519 scalar multiplication
+    (machine/ec/builder.rs scalar_mul_batch: 1651 columns, 720 constraints incl. transitions) at 2^16 rows under
     standard_fast_config -- trace commit from the row-major AirTrace, AIR evaluation over the quotient domain ON THE
     DEVICE (csrc/air.cu), quotient commit, openings, prove_openings -- against the same sequence driven through the CPU
     oracle (direct AIR evaluation, oracle/air.py).  The `air_eval` leg is timed alone on both sides."""
@@ -260,12 +261,16 @@ def run_stark_proof(args):
     log_n = 16
     n = 1 << log_n
     rng = np.random.default_rng(0xC0FFEE + 20)
-    if args.workload == "stark_proof_ed_add":  # chip/ec/edwards/add.rs ed_add: 800 columns, 248 constraints
-        chip, base_rows, what = S.EdAddChip(), 1 << 6, "valid ed25519 point-addition trace: 2^6 additions of multiples of the base point, tiled"
+    if args.workload == "stark_proof_ed_scalar_mul":  # machine/ec/builder.rs scalar_mul_batch: 2^16 x 1651, 720 constraints
+        chip, what = S.EdScalarMulChip(), "valid ed25519 scalar-multiplication trace: 256 multiplications of 256 rows, two distinct ones repeated"
+        trace = chip.generate_trace(rng, n, distinct=2)
     else:
-        chip, base_rows, what = S.FpMulChip(), 1 << 10, "valid FpMul trace: 2^10 random multiplications mod 2^255-19, tiled"
-    base = chip.generate_trace(rng, base_rows)
-    trace = np.ascontiguousarray(np.tile(base, (n // base.shape[0], 1)))  # rows are independent: repetition stays valid
+        if args.workload == "stark_proof_ed_add":  # chip/ec/edwards/add.rs ed_add: 800 columns, 248 constraints
+            chip, base_rows, what = S.EdAddChip(), 1 << 6, "valid ed25519 point-addition trace: 2^6 additions of multiples of the base point, tiled"
+        else:
+            chip, base_rows, what = S.FpMulChip(), 1 << 10, "valid FpMul trace: 2^10 random multiplications mod 2^255-19, tiled"
+        base = chip.generate_trace(rng, base_rows)
+        trace = np.ascontiguousarray(np.tile(base, (n // base.shape[0], 1)))  # rows are independent: repetition stays valid
     stark = S.Starky(chip)
     cfg = S.StarkyConfig.standard_fast_config(n)
     fc = cfg.fri_config
@@ -1183,7 +1188,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark", "stark_proof_fpmul", "stark_proof_ed_add", "plonk_proof_demo"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["replay_plonk", "replay_stark", "stark_proof_fpmul", "stark_proof_ed_add", "stark_proof_ed_scalar_mul", "plonk_proof_demo"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard-commit", action="store_true",
                     help="N > 1: split ONE commit by LDE coset over the ranks (strong scaling, N <= 2^rate_bits) instead "
@@ -1205,7 +1210,7 @@ def main():
     if args.workload.startswith("replay_"):
         if rank == 0:
             run_replay_workload(args)
-    elif args.workload in ("stark_proof_fpmul", "stark_proof_ed_add"):
+    elif args.workload in ("stark_proof_fpmul", "stark_proof_ed_add", "stark_proof_ed_scalar_mul"):
         if rank == 0:
             run_stark_proof(args)
     elif args.workload == "plonk_proof_demo":

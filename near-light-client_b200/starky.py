@@ -953,6 +953,73 @@ def _bit_constraint(parser, m: MemorySlice):
         parser.constraint(parser.mul(bit, parser.sub_const(bit, 1)))
 
 
+def _v(parser, m: MemorySlice):
+    return m.eval_slice(parser)[0]
+
+
+@dataclass
+class Cycle:
+    """AirBuilder::cycle(length_log) (instruction/cycle.rs:17-25,48-68): a walk through the 2^length_log-th roots of
+    unity with the start / end bits pinned by inverse witnesses."""
+    start_bit: MemorySlice
+    end_bit: MemorySlice
+    element: MemorySlice
+    start_bit_witness: MemorySlice
+    end_bit_witness: MemorySlice
+    length_log: int
+
+    def __post_init__(self):
+        g = pow(1753635133440165772, 1 << (32 - self.length_log), P)
+        self.group = [pow(g, i, P) for i in range(1 << self.length_log)]
+
+    def eval(self, parser):  # cycle.rs:117-170
+        element = _v(parser, self.element)
+        parser.constraint_first_row(parser.sub_const(element, 1))
+        generator, generator_inv = self.group[1], self.group[-1]
+        parser.constraint_transition(parser.sub(_v(parser, self.element.next()), parser.mul_const(element, generator)))
+        start_bit = _v(parser, self.start_bit)
+        elem_minus_one = parser.sub_const(element, 1)
+        parser.constraint(parser.mul(start_bit, elem_minus_one))
+        w = parser.mul(parser.add(elem_minus_one, start_bit), _v(parser, self.start_bit_witness))
+        parser.constraint(parser.sub_const(w, 1))
+        end_bit = _v(parser, self.end_bit)
+        elem_minus_gen_inv = parser.sub_const(element, generator_inv)
+        parser.constraint(parser.mul(end_bit, elem_minus_gen_inv))
+        w = parser.mul(parser.add(elem_minus_gen_inv, parser.mul_const(end_bit, generator_inv)), _v(parser, self.end_bit_witness))
+        parser.constraint(parser.sub_const(w, 1))
+
+    def write(self, row_index: int) -> dict:  # cycle.rs:173-205
+        inv = lambda x: pow(x % P, P - 2, P)
+        c = row_index % len(self.group)
+        element, gen_inverse = self.group[c], self.group[-1]
+        if c == 0:
+            sb, eb, sbw, ebw = 1, 0, inv(element), inv(element - gen_inverse)
+        elif c == len(self.group) - 1:
+            sb, eb, sbw, ebw = 0, 1, inv(element - 1), inv(element)
+        else:
+            sb, eb, sbw, ebw = 0, 0, inv(element - 1), inv(element - gen_inverse)
+        return {self.start_bit.index: sb, self.end_bit.index: eb, self.element.index: element,
+                self.start_bit_witness.index: sbw, self.end_bit_witness.index: ebw}
+
+
+def _process_id_eval(parser, process_id: MemorySlice, end_bit: MemorySlice):
+    """ProcessIdInstruction::eval (cycle.rs:239-250): the cumulative sum of end bits."""
+    pid = _v(parser, process_id)
+    parser.constraint_first_row(pid)
+    parser.constraint_transition(parser.sub(parser.sub(_v(parser, process_id.next()), pid), _v(parser, end_bit)))
+
+
+def _limb_bit_eval(parser, bit, bit_accumulator, limb, start_bit, end_bit):
+    """LimbBitInstruction::eval (ec/scalar.rs:69-107)."""
+    acc, b, sb, eb = _v(parser, bit_accumulator), _v(parser, bit), _v(parser, start_bit), _v(parser, end_bit)
+    parser.constraint(parser.mul(sb, parser.sub(acc, _v(parser, limb))))
+    not_end_bit = parser.sub(parser.one(), eb)
+    t = parser.mul_const(_v(parser, bit_accumulator.next()), 2)
+    t = parser.add(parser.sub(t, acc), b)
+    parser.constraint_transition(parser.mul(not_end_bit, t))
+    parser.constraint(parser.mul(eb, parser.sub(acc, b)))
+
+
 class ScalarBitsChip(RAirData):
     """The row-to-row machinery of `scalar_mul_batch` (machine/ec/builder.rs:61-190) around the curve arithmetic: a
     cycle of 32 rows (`AirBuilder::cycle(5)`, instruction/cycle.rs:48-170: a walk through the 32nd roots of unity with
@@ -964,10 +1031,9 @@ class ScalarBitsChip(RAirData):
 
     def __init__(self):
         cell = lambda i: MemorySlice("Local", i, 1)
-        (self.start_bit, self.end_bit, self.element, self.start_bit_witness, self.end_bit_witness, self.process_id, self.limb,
-         self.bit_accumulator, self.bit) = [cell(i) for i in range(9)]
-        g = pow(1753635133440165772, 1 << (32 - self.LOG), P)
-        self.group = [pow(g, i, P) for i in range(1 << self.LOG)]
+        self.cycle = Cycle(cell(0), cell(1), cell(2), cell(3), cell(4), self.LOG)
+        self.start_bit, self.end_bit = self.cycle.start_bit, self.cycle.end_bit
+        self.process_id, self.limb, self.bit_accumulator, self.bit = cell(5), cell(6), cell(7), cell(8)
 
     def constraint_degree(self):
         return 2
@@ -976,37 +1042,12 @@ class ScalarBitsChip(RAirData):
         return 9
 
     def eval(self, parser):
-        v = lambda m: m.eval_slice(parser)[0]
         _bit_constraint(parser, self.start_bit)
         _bit_constraint(parser, self.end_bit)
-        # Cycle::eval (cycle.rs:117-170)
-        element = v(self.element)
-        parser.constraint_first_row(parser.sub_const(element, 1))
-        generator, generator_inv = self.group[1], self.group[-1]
-        parser.constraint_transition(parser.sub(v(self.element.next()), parser.mul_const(element, generator)))
-        start_bit = v(self.start_bit)
-        elem_minus_one = parser.sub_const(element, 1)
-        parser.constraint(parser.mul(start_bit, elem_minus_one))
-        w = parser.mul(parser.add(elem_minus_one, start_bit), v(self.start_bit_witness))
-        parser.constraint(parser.sub_const(w, 1))
-        end_bit = v(self.end_bit)
-        elem_minus_gen_inv = parser.sub_const(element, generator_inv)
-        parser.constraint(parser.mul(end_bit, elem_minus_gen_inv))
-        w = parser.mul(parser.add(elem_minus_gen_inv, parser.mul_const(end_bit, generator_inv)), v(self.end_bit_witness))
-        parser.constraint(parser.sub_const(w, 1))
-        # ProcessIdInstruction::eval (cycle.rs:239-250)
-        process_id = v(self.process_id)
-        parser.constraint_first_row(process_id)
-        parser.constraint_transition(parser.sub(parser.sub(v(self.process_id.next()), process_id), end_bit))
-        # LimbBitInstruction::eval (ec/scalar.rs:69-107)
+        self.cycle.eval(parser)
+        _process_id_eval(parser, self.process_id, self.end_bit)
         _bit_constraint(parser, self.bit)
-        bit_accumulator, bit = v(self.bit_accumulator), v(self.bit)
-        parser.constraint(parser.mul(start_bit, parser.sub(bit_accumulator, v(self.limb))))
-        not_end_bit = parser.sub(parser.one(), end_bit)
-        t = parser.mul_const(v(self.bit_accumulator.next()), 2)
-        t = parser.add(parser.sub(t, bit_accumulator), bit)
-        parser.constraint_transition(parser.mul(not_end_bit, t))
-        parser.constraint(parser.mul(end_bit, parser.sub(bit_accumulator, bit)))
+        _limb_bit_eval(parser, self.bit, self.bit_accumulator, self.limb, self.start_bit, self.end_bit)
 
     def eval_global(self, parser):
         pass
@@ -1016,22 +1057,222 @@ class ScalarBitsChip(RAirData):
         size = 1 << self.LOG
         assert num_rows % size == 0
         rows = np.zeros((num_rows, 9), np.uint64)
-        inv = lambda x: pow(x % P, P - 2, P)
-        gen_inverse = self.group[-1]
         acc = limb = 0
         for r in range(num_rows):
             c = r % size
-            element = self.group[c]
             if c == 0:
                 limb = acc = int(rng.integers(0, 1 << 32))
-                sb, eb, sbw, ebw = 1, 0, inv(element), inv(element - gen_inverse)
-            elif c == size - 1:
-                sb, eb, sbw, ebw = 0, 1, inv(element - 1), inv(element)
-            else:
-                sb, eb, sbw, ebw = 0, 0, inv(element - 1), inv(element - gen_inverse)
             bit = (limb >> c) & 1
-            rows[r] = [sb, eb, element, sbw, ebw, r // size, limb, acc, bit]
+            for col, val in self.cycle.write(r).items():
+                rows[r, col] = val
+            rows[r, 5:] = [r // size, limb, acc, bit]
             acc = (acc - bit) // 2
+        return rows
+
+
+@dataclass
+class SelectInstruction:
+    """AirBuilder::select (chip/bool.rs:28-92): result = bit ? true_value : false_value, limb by limb."""
+    bit: MemorySlice
+    true_value: MemorySlice
+    false_value: MemorySlice
+    result: MemorySlice
+
+    def eval(self, parser):
+        bit = _v(parser, self.bit)
+        one_minus_bit = parser.sub(parser.one(), bit)
+        for x_true, x_false, x in zip(self.true_value.eval_slice(parser), self.false_value.eval_slice(parser),
+                                      self.result.eval_slice(parser)):
+            expected = parser.add(parser.mul(x_true, bit), parser.mul(x_false, one_minus_bit))
+            parser.constraint(parser.sub(expected, x))
+
+
+class _EdAddGadget:
+    """ed_add (chip/ec/edwards/add.rs:8-54) over given input registers: the eight field instructions and their columns."""
+
+    def __init__(self, alloc, x1, y1, x2, y2):
+        L, Wn = Fp25519.NB_LIMBS, Fp25519.NB_WITNESS_LIMBS
+        out = lambda: (alloc(L), alloc(L), alloc(Wn), alloc(Wn))
+        self.x3_num = FpInnerProductInstruction([x1, x2], [y2, y1], *out())
+        self.y3_num = FpInnerProductInstruction([y1, x1], [y2, x2], *out())
+        self.x1y1 = FpMulInstruction(x1, y1, *out())
+        self.x2y2 = FpMulInstruction(x2, y2, *out())
+        self.f = FpMulInstruction(self.x1y1.result, self.x2y2.result, *out())
+        self.df = FpMulConstInstruction(self.f.result, list(Ed25519.D), *out())
+        self.x3 = FpDenInstruction(self.x3_num.result, self.df.result, True, *out())
+        self.y3 = FpDenInstruction(self.y3_num.result, self.df.result, False, *out())
+        self.instructions = [self.x3_num, self.y3_num, self.x1y1, self.x2y2, self.f, self.df, self.x3, self.y3]
+
+    def eval(self, parser):
+        for ins in self.instructions:
+            ins.eval(parser)
+
+    def write(self, row, pt, qt):
+        """Fill the gadget's columns of `row` (a list) for pt + qt; returns the sum."""
+        (x1, y1), (x2, y2) = pt, qt
+        m = Fp25519.modulus()
+        w = [self.x3_num.write([x1, x2], [y2, y1]), self.y3_num.write([y1, x1], [y2, x2]), self.x1y1.write(x1, y1),
+             self.x2y2.write(x2, y2)]
+        a, b = x1 * y1 % m, x2 * y2 % m
+        w.append(self.f.write(a, b))
+        w.append(self.df.write(a * b % m))
+        w.append(self.x3.write(w[0]["value"], w[5]["value"]))
+        w.append(self.y3.write(w[1]["value"], w[5]["value"]))
+        for ins, d in zip(self.instructions, w):
+            for key, reg in (("result", ins.result), ("carry", ins.carry), ("witness_low", ins.witness_low),
+                             ("witness_high", ins.witness_high)):
+                row[reg.index:reg.index + reg.length] = d[key]
+        return w[6]["value"], w[7]["value"]
+
+
+class EdScalarMulChip(RAirData):
+    """The ed25519 scalar multiplication AIR of `scalar_mul_batch` / `double_and_add` (machine/ec/builder.rs:61-264;
+    `Ed25519ScalarMulTest`, builder.rs:291-303: NUM_ARITHMETIC_COLUMNS 1632 + NUM_FREE_COLUMNS 19 = the 2^16 x 1651 trace of
+    SURVEY.md 8d): one scalar bit per row, 256 rows per multiplication.
+      arithmetic columns (1632): temp | temp_next = 2 temp (ed_add gadget, 736) | result | addend = is_res_valid ? result :
+        temp_next | sum = temp + addend (736) | res_plus_temp = is_res_valid ? sum : temp | result_next = bit ? res_plus_temp
+        : result
+      free columns (19): cycle(8) and cycle(5) (5 + 5), the two process ids, the scalar limb, bit accumulator and bit,
+        is_res_valid, next_res_valid, not_end_bit, clk
+    Constraints as in the reference for everything on the row and for result / is_res_valid / the counters across rows.
+    ONE difference: the reference moves `temp`, the scalar limbs and the finished results through its memory bus (a
+    multiset argument in the cubic extension: the 2502 - 1651 extended columns, challenges, a second round); here
+    `temp` is carried by a transition constraint (not_end_bit * (temp' - temp_next) = 0) and the limb is a column."""
+
+    def __init__(self):
+        L = Fp25519.NB_LIMBS
+        self._o = 0
+
+        def alloc(n):
+            m = MemorySlice("Local", self._o, n)
+            self._o += n
+            return m
+        point = lambda: (alloc(L), alloc(L))
+        self.temp = point()
+        self.double = _EdAddGadget(alloc, *self.temp, *self.temp)
+        self.temp_next = (self.double.x3.result, self.double.y3.result)
+        self.result = point()
+        self.addend = point()
+        self.add = _EdAddGadget(alloc, *self.temp, *self.addend)
+        self.sum = (self.add.x3.result, self.add.y3.result)
+        self.res_plus_temp = point()
+        self.result_next = point()
+        assert self._o == 1632
+        cell = lambda: alloc(1)
+        self.cycle = Cycle(cell(), cell(), cell(), cell(), cell(), 8)
+        self.cycle_32 = Cycle(cell(), cell(), cell(), cell(), cell(), 5)
+        self.process_id, self.process_id_u32, self.limb = cell(), cell(), cell()
+        self.bit_accumulator, self.bit = cell(), cell()
+        self.is_res_valid, self.next_res_valid, self.not_end_bit, self.clk = cell(), cell(), cell(), cell()
+        assert self._o == 1651
+        self.selects = [SelectInstruction(self.is_res_valid, self.result[k], self.temp_next[k], self.addend[k]) for k in (0, 1)]
+        self.selects += [SelectInstruction(self.is_res_valid, self.sum[k], self.temp[k], self.res_plus_temp[k]) for k in (0, 1)]
+        self.selects += [SelectInstruction(self.bit, self.res_plus_temp[k], self.result[k], self.result_next[k]) for k in (0, 1)]
+
+    def constraint_degree(self):
+        return 2
+
+    def width(self):
+        return self._o
+
+    def eval(self, parser):
+        v = lambda m: _v(parser, m)
+        end_bit, start_bit = self.cycle.end_bit, self.cycle.start_bit
+        # control: the two cycles, process ids, clock, the bit of this row
+        for c in (self.cycle, self.cycle_32):
+            _bit_constraint(parser, c.start_bit)
+            _bit_constraint(parser, c.end_bit)
+            c.eval(parser)
+        _process_id_eval(parser, self.process_id, end_bit)
+        _process_id_eval(parser, self.process_id_u32, self.cycle_32.end_bit)
+        clk = v(self.clk)                                                  # instruction/clock.rs:16-27
+        parser.constraint_first_row(clk)
+        parser.constraint_transition(parser.sub_const(parser.sub(v(self.clk.next()), clk), 1))
+        _bit_constraint(parser, self.bit)
+        _limb_bit_eval(parser, self.bit, self.bit_accumulator, self.limb, self.cycle_32.start_bit, self.cycle_32.end_bit)
+        # double_and_add (builder.rs:194-264)
+        _bit_constraint(parser, self.is_res_valid)
+        parser.constraint_first_row(v(self.is_res_valid))
+        _bit_constraint(parser, self.next_res_valid)
+        one = parser.one()
+        valid, bit, eb = v(self.is_res_valid), v(self.bit), v(end_bit)
+        expr = parser.add(valid, parser.mul(bit, parser.sub(one, valid)))
+        parser.constraint(parser.sub(v(self.next_res_valid), expr))
+        not_eb = parser.sub(one, eb)
+        expr = parser.add(parser.mul(eb, v(start_bit)), parser.mul(not_eb, v(self.next_res_valid)))  # select_next
+        parser.constraint_transition(parser.sub(v(self.is_res_valid.next()), expr))
+        parser.constraint(parser.sub(v(self.not_end_bit), not_eb))
+        self.double.eval(parser)
+        for k in (0, 1):  # in place of the memory bus: temp' = temp_next inside a cycle
+            for nx, cur in zip(self.temp[k].next().eval_slice(parser), self.temp_next[k].eval_slice(parser)):
+                parser.constraint_transition(parser.mul(v(self.not_end_bit), parser.sub(nx, cur)))
+        for k in (0, 1):
+            for x in self.result[k].eval_slice(parser):
+                parser.constraint_first_row(x)
+        self.selects[0].eval(parser)
+        self.selects[1].eval(parser)
+        self.add.eval(parser)
+        for sel in self.selects[2:]:
+            sel.eval(parser)
+        for k in (0, 1):  # select_next_ec_point(end_bit, (0, 0), result_next, result)
+            for nx, rn in zip(self.result[k].next().eval_slice(parser), self.result_next[k].eval_slice(parser)):
+                parser.constraint_transition(parser.sub(nx, parser.mul(not_eb, rn)))
+
+    def eval_global(self, parser):
+        pass
+
+    def generate_block(self, point, scalar: int) -> np.ndarray:
+        """The 256 rows of ONE multiplication scalar * point (process id 0, clk from 0; see generate_trace)."""
+        rows = np.zeros((256, self._o), np.uint64)
+        temp, result, valid = point, (0, 0), 0
+        acc = 0
+        for r in range(256):
+            row = [0] * self._o
+            put = lambda reg, val: row.__setitem__(slice(reg.index, reg.index + reg.length), _limbs(val, reg.length) if reg.length > 1 else [val])
+            for c in (self.cycle, self.cycle_32):
+                for col, val in c.write(r).items():
+                    row[col] = val
+            if r % 32 == 0:
+                limb = acc = (scalar >> r) & 0xFFFFFFFF
+            bit = (limb >> (r % 32)) & 1
+            end = int(r == 255)
+            put(self.process_id, 0), put(self.process_id_u32, r // 32), put(self.limb, limb)
+            put(self.bit_accumulator, acc), put(self.bit, bit), put(self.clk, r)
+            put(self.is_res_valid, valid), put(self.not_end_bit, 1 - end)
+            next_valid = valid + bit * (1 - valid)
+            put(self.next_res_valid, next_valid)
+            for k in (0, 1):
+                put(self.temp[k], temp[k]), put(self.result[k], result[k])
+            temp_next = self.double.write(row, temp, temp)
+            addend = result if valid else temp_next
+            total = self.add.write(row, temp, addend)
+            res_plus_temp = total if valid else temp
+            result_next = res_plus_temp if bit else result
+            for k in (0, 1):
+                put(self.addend[k], addend[k]), put(self.res_plus_temp[k], res_plus_temp[k]), put(self.result_next[k], result_next[k])
+            rows[r] = row
+            acc = (acc - bit) // 2
+            temp, result, valid = temp_next, result_next, next_valid
+        self.last_result = result
+        return rows
+
+    def generate_trace(self, rng, num_rows: int, distinct: int = 1) -> np.ndarray:
+        """num_rows / 256 multiplications: `distinct` different ones, repeated (the blocks of a trace are independent but
+        for the counters, which are set per block)."""
+        assert num_rows % 256 == 0
+        blocks = []
+        for _ in range(distinct):
+            k = int.from_bytes(rng.bytes(32), "little")
+            pt = Ed25519.GENERATOR
+            for _ in range(int(rng.integers(1, 32))):
+                pt = Ed25519.add(pt, Ed25519.GENERATOR)
+            blocks.append(self.generate_block(pt, k))
+        n_blocks = num_rows // 256
+        rows = np.concatenate([blocks[i % distinct] for i in range(n_blocks)])
+        idx = np.arange(num_rows, dtype=np.uint64)
+        rows[:, self.process_id.index] = idx // 256
+        rows[:, self.process_id_u32.index] = idx // 32
+        rows[:, self.clk.index] = idx
         return rows
 
 

@@ -214,6 +214,20 @@ def test_ed_add_chip_bytecode_matches_direct(O, pkg, rng):
     assert prog.n_constraints == 248 and prog.n_regs < 256
 
 
+def _violations(OA, chip, rows):
+    """How many constraints of `chip` fail on the trace `rows` where they apply: plain ones on every row, transitions on
+    every window (row, row + 1) but the last row's, first-row ones on row 0.  Also returns the kinds, in order."""
+    n = rows.shape[0]
+    cons = _EveryConstraint(n)
+    loc = [np.ascontiguousarray(rows[:, j]) for j in range(rows.shape[1])]
+    nxt = [np.roll(c, -1) for c in loc]
+    chip.eval(OA.StarkParser(loc, nxt, [], [], [], cons))
+    bad = 0
+    for kind, v in zip(cons.kinds, cons.values):
+        bad += int(v[:-1].any()) if kind == "transition" else int(v[0] != 0) if kind == "first" else int(v.any())
+    return bad, cons.kinds
+
+
 def test_scalar_bits_chip(O, pkg, rng):
     """The control columns of scalar_mul_batch (cycle of 32, process id, bit decomposition of a limb): the generated
     trace satisfies every constraint where it applies -- plain ones on every row, transitions on all rows but the last
@@ -223,16 +237,7 @@ def test_scalar_bits_chip(O, pkg, rng):
     chip = S.ScalarBitsChip()
     trace = chip.generate_trace(rng, 1 << 7)
 
-    def violations(rows):
-        n = rows.shape[0]
-        cons = _EveryConstraint(n)
-        loc = [np.ascontiguousarray(rows[:, j]) for j in range(rows.shape[1])]
-        nxt = [np.roll(c, -1) for c in loc]
-        chip.eval(OA.StarkParser(loc, nxt, [], [], [], cons))
-        bad = 0
-        for kind, v in zip(cons.kinds, cons.values):
-            bad += int(v[:-1].any()) if kind == "transition" else int(v[0] != 0) if kind == "first" else int(v.any())
-        return bad, cons.kinds
+    violations = lambda rows: _violations(OA, chip, rows)
     bad, kinds = violations(trace)
     assert bad == 0 and len(kinds) == 14 and kinds.count("transition") == 3 and kinds.count("first") == 2
     # the bits of every cycle are the limb's
@@ -244,6 +249,43 @@ def test_scalar_bits_chip(O, pkg, rng):
     assert violations(flipped)[0] > 0
     want, got, prog = direct_and_bytecode(O, OA, S, chip, 7, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
     assert np.array_equal(want, got) and prog.n_constraints == 14
+
+
+def test_ed_scalar_mul_chip(O, pkg, rng):
+    """The ed25519 scalar multiplication AIR (machine/ec/builder.rs scalar_mul_batch / double_and_add): 1651 columns as
+    `Ed25519ScalarMulTest`, one scalar bit per row.  Two multiplications: every constraint holds where it applies, the
+    last row of each block carries scalar * point, a wrong limb or a wrong bit breaks it, bytecode = direct evaluation."""
+    from oracle import air as OA
+    S = pkg.starky
+    chip = S.EdScalarMulChip()
+    assert chip.width() == 1651
+    pt = S.Ed25519.add(S.Ed25519.GENERATOR, S.Ed25519.GENERATOR)
+    scalars = [int.from_bytes(rng.bytes(32), "little"), 5]
+    blocks, results = [], []
+    for k in scalars:
+        blocks.append(chip.generate_block(pt, k))
+        results.append(chip.last_result)
+    trace = np.concatenate(blocks)
+    idx = np.arange(512, dtype=np.uint64)
+    trace[:, chip.process_id.index], trace[:, chip.process_id_u32.index], trace[:, chip.clk.index] = idx // 256, idx // 32, idx
+    bad, kinds = _violations(OA, chip, trace)
+    assert bad == 0 and len(kinds) == 720 and "transition" in kinds and "first" in kinds
+    # the result is the curve's scalar multiple (AffinePoint::scalar_mul, chip/ec/scalar_mul/mod.rs:10-25)
+    val = lambda row, m: sum(int(row[m.index + i]) << (16 * i) for i in range(m.length))
+    for b, k in enumerate(scalars):
+        want, temp = None, pt
+        for i in range(256):
+            if (k >> i) & 1:
+                want = temp if want is None else S.Ed25519.add(want, temp)
+            temp = S.Ed25519.add(temp, temp)
+        last = trace[256 * b + 255]
+        assert (val(last, chip.result_next[0]), val(last, chip.result_next[1])) == want == results[b]
+    for col, r in ((chip.add.x3.result.index + 3, 300), (chip.bit.index, 77), (chip.temp[1].index, 200)):
+        broken = trace.copy()
+        broken[r, col] ^= 1
+        assert _violations(OA, chip, broken)[0] > 0
+    want, got, prog = direct_and_bytecode(O, OA, S, chip, 9, 1, trace, [], [], [], [3, 0xFFFFFFFF00000000])
+    assert np.array_equal(want, got) and prog.n_constraints == 720
 
 
 @pytest.mark.parametrize("seed", range(6))

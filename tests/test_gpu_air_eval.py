@@ -95,17 +95,18 @@ def test_ed_add_chip(P2, O, pkg, rng, log_n):
     assert np.array_equal(q.coeff_matrix, qref.coeffs)
 
 
-@pytest.mark.parametrize("log_n", [5, 13])
-def test_scalar_bits_chip_proof(P2, O, pkg, rng, log_n):
+@pytest.mark.parametrize("which,log_n", [("bits", 5), ("bits", 13), ("scalar_mul", 9)])
+def test_scalar_mul_chips_proof(P2, O, pkg, rng, which, log_n):
     """The control columns of the ed25519 scalar multiplication (instruction/cycle.rs, ec/scalar.rs: cycle of 32 rows,
     process id, bit decomposition): first-row, transition and plain constraints with real `next` reads.  Accumulators
     and quotient commitment against the oracle, then the whole proof: the quotient exists (the trace is valid), the
     proof equals the oracle-driven one and the restated FRI verifier accepts it."""
     from oracle import air as OA
     S = pkg.starky
-    chip = S.ScalarBitsChip()
+    # "scalar_mul": the whole AIR of scalar_mul_batch / double_and_add, 1651 columns, 720 constraints, two multiplications
+    chip = S.ScalarBitsChip() if which == "bits" else S.EdScalarMulChip()
     n = 1 << log_n
-    trace = chip.generate_trace(rng, n)
+    trace = chip.generate_trace(rng, n) if which == "bits" else chip.generate_trace(rng, n, distinct=2)
     alphas = O.random_field(rng, (2,)).tolist()
     stark, gb, rb, qref = check_air(P2, O, S, chip, log_n, 1, 4, [trace], [], [], [], alphas)
     cfg = S.StarkyConfig.standard_fast_config(n)

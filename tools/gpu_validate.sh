@@ -13,5 +13,6 @@ $B > gpurun_out/${TAG}_plain2.log 2>&1 && ncu --set full --clock-control none --
 $B > gpurun_out/${TAG}_plain3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_leaf_hash -c 1 -o gpurun_out/${TAG}_leaf $B > gpurun_out/${TAG}_ncu3.log 2>&1
 python bench.py --workload stark_proof_fpmul --steps 5 > gpurun_out/${TAG}_stark.log 2>&1
 python bench.py --workload stark_proof_ed_add --steps 3 > gpurun_out/${TAG}_stark_ed_add.log 2>&1
+python bench.py --workload stark_proof_ed_scalar_mul --steps 3 > gpurun_out/${TAG}_stark_ed_scalar_mul.log 2>&1
 python bench.py --workload plonk_proof_demo --steps 5 > gpurun_out/${TAG}_plonk.log 2>&1
 python bench.py --workload commit_2^20x400_r1_cap4 --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_config4.log 2>&1
