@@ -83,3 +83,23 @@ def test_challenger(P2, O, rng):
         m = int(rng.integers(0, 11))
         assert ch.get_n_challenges(m) == och.get_n_challenges(m)
         assert ch.state() == och.state()
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_challenger_long_observations(P2, O, seed):
+    """observe_elements takes whole blocks of 8 on a path of its own once the input buffer is empty (an opening set is
+    thousands of elements): runs that start and end inside, at and across block boundaries, non-canonical inputs,
+    interleaved with challenges -- the state after every step equals the oracle's."""
+    r = np.random.default_rng(seed)
+    el = r.integers(0, 0xFFFFFFFFFFFFFFFF, 4096, dtype=np.uint64, endpoint=True)
+    ch, och, pos = P2.Challenger(), O.Challenger(), 0
+    for step in range(14):
+        k = int(r.choice([0, 1, 3, 7, 8, 9, 15, 16, 17, 40, 64, 129, 1000]))
+        ch.observe_elements(el[pos:pos + k])
+        och.observe_elements(el[pos:pos + k])
+        pos = (pos + k) % 2048
+        assert ch.state() == och.state()
+        if r.integers(0, 2):
+            m = int(r.integers(1, 12))
+            assert ch.get_n_challenges(m) == och.get_n_challenges(m)
+    assert ch.get_n_challenges(3) == och.get_n_challenges(3)
