@@ -99,6 +99,7 @@ def test_row_shards_through_peer_buffers(P2, pkg, O, rng, W, log_n, r, cap, G):
             src = torch.from_numpy(values[c0:c0 + nc].view(np.int64)).cuda()
             cf, none = P2.PolynomialBatch.lde_columns_scatter(src, r, G, peer_ptrs=bufs, col0=c0)
             assert none is None
+            torch.cuda.synchronize()  # the *_dev call only enqueues on the context's stream: order torch's read after it
             assert np.array_equal(cf.cpu().numpy().view(np.uint64), ref.coeffs[c0:c0 + nc])
         torch.cuda.synchronize()
         shards = [P2.PolynomialBatch.from_lde_rows((bufs[g], W, None), log_n, r, cap, g, G) for g in range(G)]
