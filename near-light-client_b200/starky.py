@@ -170,7 +170,7 @@ class BytecodeParser:
         (include/nlc_commit.h): an operand that IS the previous instruction's result is taken from the interpreter's
         accumulator instead of its register (A_LAST / B_LAST), and a result whose every use comes before the next
         result is produced is never stored (NO_STORE; it gets no register at all).  For the programs here that removes
-        30-40 % of the register traffic, which is what bounds the interpreter."""
+        30-40 % of the register accesses (each one a load or store plus address arithmetic in an issue-bound kernel)."""
         reads_reg = {OP[k] for k in ("ADD", "SUB", "MUL")}
         reads_a = {OP[k] for k in ("NEG", "MUL_CONST", "ADD_CONST", "SUB_CONST", "CONSTRAINT", "CONSTRAINT_TRANSITION",
                                    "CONSTRAINT_FIRST_ROW", "CONSTRAINT_LAST_ROW", "MULADD_CONST")}
