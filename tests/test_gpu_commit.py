@@ -149,10 +149,11 @@ def test_from_trace_rows(P2, O, rng):
 
 @pytest.mark.parametrize("pinned", [False, True])
 def test_from_trace_rows_strip_chunks(P2, O, rng, pinned):
-    """Only the column strip crosses PCIe, in row chunks (32 MiB) overlapped with the transpose: several chunks, a
-    ragged last one is impossible (powers of two) but strip != width and col0 != 0 are; pageable and pinned hosts."""
+    """Only the column strip crosses PCIe, in COLUMN chunks through the host-fed pipeline (16, 24, 40, ... columns of every
+    row: gathered into the pinned ring from a pageable matrix, a 2-D DMA from a pinned one), strip != width and
+    col0 != 0; pageable and pinned hosts."""
     import torch
-    n, width, col0, nc = 1 << 16, 150, 7, 130  # 130 cols * 8 B -> 32 256 rows per chunk -> 3 chunks
+    n, width, col0, nc = 1 << 16, 150, 7, 130
     trace = O.random_field(rng, (n, width))
     host = trace
     if pinned:
@@ -164,6 +165,18 @@ def test_from_trace_rows_strip_chunks(P2, O, rng, pinned):
     assert np.array_equal(b.merkle_tree.cap, ref.cap)
     assert np.array_equal(b.coeff_matrix, ref.coeffs)
     assert np.array_equal(b.merkle_tree.digests, ref.digests)
+
+
+@pytest.mark.parametrize("nc,rate_bits", [(1, 1), (8, 3), (31, 1), (32, 1), (47, 2), (200, 1), (135, 3)])
+def test_from_trace_rows_widths(P2, O, rng, nc, rate_bits):
+    """Strip widths on both sides of the pipeline's thresholds (one launch below 32 columns, the chunked sponge above;
+    first chunk 16, a merged last chunk), two strips of the same matrix."""
+    n, width = 1 << 8, nc + 9
+    trace = O.random_field(rng, (n, width))
+    for col0 in (0, 9):
+        b = P2.PolynomialBatch.from_trace_rows(trace, col0, nc, rate_bits, 2)
+        check_batch(b, O.commit_from_values(np.ascontiguousarray(trace[:, col0:col0 + nc].T), rate_bits, 2))
+        b.free()
 
 
 def test_import_serialized(P2, pkg, O, rng):
